@@ -1,0 +1,314 @@
+// libptgs: error state, layout helpers (AoS->SoA), Manhattan transform (A13),
+// XY bounds (A2) and keep-mask compaction.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace ptgs {
+
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+
+// ---------------------------------------------------------------------------
+// AoS (N,3) f32 -> planar.  Each thread moves 4 points = 3 float4 loads.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) aos_to_soa_kernel(
+    const float* __restrict__ xyz, int64_t n, float* __restrict__ x,
+    float* __restrict__ y, float* __restrict__ z) {
+  const int64_t n4 = n / 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const float4* in = reinterpret_cast<const float4*>(xyz);
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4;
+       g += stride) {
+    float4 a = __ldg(in + 3 * g), b = __ldg(in + 3 * g + 1),
+           c = __ldg(in + 3 * g + 2);
+    reinterpret_cast<float4*>(x)[g] = make_float4(a.x, a.w, b.z, c.y);
+    reinterpret_cast<float4*>(y)[g] = make_float4(a.y, b.x, b.w, c.z);
+    reinterpret_cast<float4*>(z)[g] = make_float4(a.z, b.y, c.x, c.w);
+  }
+  // tail
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    int64_t i = n4 * 4 + threadIdx.x;
+    x[i] = xyz[3 * i];
+    y[i] = xyz[3 * i + 1];
+    z[i] = xyz[3 * i + 2];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Manhattan transform, f32 -> f64 (k-ordered fma accumulation, then + T).
+// ---------------------------------------------------------------------------
+struct Man {
+  double r[9];
+  double t[3];
+};
+__global__ void __launch_bounds__(256) manhattan_kernel(
+    const float* __restrict__ x, const float* __restrict__ y,
+    const float* __restrict__ z, int64_t n, Man m, double* __restrict__ ox,
+    double* __restrict__ oy, double* __restrict__ oz) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += stride) {
+    double px = x[i], py = y[i], pz = z[i];
+    double a = __dmul_rn(m.r[0], px);
+    a = fma(m.r[1], py, a);
+    a = fma(m.r[2], pz, a);
+    double b = __dmul_rn(m.r[3], px);
+    b = fma(m.r[4], py, b);
+    b = fma(m.r[5], pz, b);
+    double c = __dmul_rn(m.r[6], px);
+    c = fma(m.r[7], py, c);
+    c = fma(m.r[8], pz, c);
+    ox[i] = __dadd_rn(a, m.t[0]);
+    oy[i] = __dadd_rn(b, m.t[1]);
+    oz[i] = __dadd_rn(c, m.t[2]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// XY bounds: block reduce in registers/shuffles, one atomic per block on
+// order-preserving keys.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void bounds_init_kernel(typename KeyOf<T>::type* keys) {
+  using K = typename KeyOf<T>::type;
+  keys[0] = ~K(0);
+  keys[1] = ~K(0);
+  keys[2] = K(0);
+  keys[3] = K(0);
+}
+
+__device__ __forceinline__ void atomic_min_key(uint32_t* a, uint32_t v) { atomicMin(a, v); }
+__device__ __forceinline__ void atomic_max_key(uint32_t* a, uint32_t v) { atomicMax(a, v); }
+__device__ __forceinline__ void atomic_min_key(uint64_t* a, uint64_t v) {
+  atomicMin(reinterpret_cast<unsigned long long*>(a), (unsigned long long)v);
+}
+__device__ __forceinline__ void atomic_max_key(uint64_t* a, uint64_t v) {
+  atomicMax(reinterpret_cast<unsigned long long*>(a), (unsigned long long)v);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bounds_kernel(
+    const T* __restrict__ x, const T* __restrict__ y,
+    const int64_t* __restrict__ n_dev, typename KeyOf<T>::type* keys) {
+  using K = typename KeyOf<T>::type;
+  const int64_t n = *n_dev;
+  K xmin = ~K(0), ymin = ~K(0), xmax = 0, ymax = 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += stride) {
+    K kx = KeyOf<T>::encode(x[i]), ky = KeyOf<T>::encode(y[i]);
+    xmin = min(xmin, kx);
+    xmax = max(xmax, kx);
+    ymin = min(ymin, ky);
+    ymax = max(ymax, ky);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    xmin = min(xmin, __shfl_xor_sync(kFullMask, xmin, d));
+    ymin = min(ymin, __shfl_xor_sync(kFullMask, ymin, d));
+    xmax = max(xmax, __shfl_xor_sync(kFullMask, xmax, d));
+    ymax = max(ymax, __shfl_xor_sync(kFullMask, ymax, d));
+  }
+  if (lane_id() == 0 && xmin <= xmax) {
+    atomic_min_key(keys + 0, xmin);
+    atomic_min_key(keys + 1, ymin);
+    atomic_max_key(keys + 2, xmax);
+    atomic_max_key(keys + 3, ymax);
+  }
+}
+
+template <typename T>
+__global__ void bounds_finish_kernel(const typename KeyOf<T>::type* keys,
+                                     double* bounds) {
+  for (int i = 0; i < 4; ++i) bounds[i] = (double)KeyOf<T>::decode(keys[i]);
+}
+
+// ---------------------------------------------------------------------------
+// keep-mask compaction of (x, y): per-tile counts -> scan -> scatter.
+// ---------------------------------------------------------------------------
+constexpr int kCompactTile = 2048;  // 256 threads x 8
+
+__global__ void __launch_bounds__(256) compact_count_kernel(
+    const uint8_t* __restrict__ keep, int64_t n, int32_t* __restrict__ tile_count) {
+  __shared__ int s[33];
+  const int64_t base = (int64_t)blockIdx.x * kCompactTile;
+  int c = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    int64_t i = base + k * 256 + threadIdx.x;
+    c += (i < n && keep[i]) ? 1 : 0;
+  }
+  int tot;
+  block_exclusive_sum<int, 256>(c, s, &tot);
+  if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
+}
+
+// single-block exclusive scan of tile counts (n_tiles up to a few 100k).
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(
+    const int32_t* __restrict__ tile_count, int64_t n_tiles,
+    int64_t* __restrict__ tile_base, int64_t* __restrict__ total) {
+  __shared__ long long s[33];
+  long long carry = 0;
+  for (int64_t start = 0; start < n_tiles; start += 1024) {
+    int64_t i = start + threadIdx.x;
+    long long v = (i < n_tiles) ? tile_count[i] : 0;
+    long long tot;
+    long long ex = block_exclusive_sum<long long, 1024>(v, s, &tot);
+    if (i < n_tiles) tile_base[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) compact_scatter_kernel(
+    const T* __restrict__ x, const T* __restrict__ y,
+    const uint8_t* __restrict__ keep, int64_t n,
+    const int64_t* __restrict__ tile_base, T* __restrict__ ox,
+    T* __restrict__ oy) {
+  __shared__ int s[33];
+  const int64_t base = (int64_t)blockIdx.x * kCompactTile;
+  int64_t out = tile_base[blockIdx.x];
+  // index order: element (k, tid) -> base + k*256 + tid ; scan per k keeps it.
+#pragma unroll 1
+  for (int k = 0; k < 8; ++k) {
+    int64_t i = base + k * 256 + threadIdx.x;
+    int f = (i < n && keep[i]) ? 1 : 0;
+    int tot;
+    int ex = block_exclusive_sum<int, 256>(f, s, &tot);
+    if (f) {
+      ox[out + ex] = x[i];
+      oy[out + ex] = y[i];
+    }
+    out += tot;
+  }
+}
+
+static inline int grid_for(int64_t n, int per_block, int max_blocks) {
+  int64_t b = (n + per_block - 1) / per_block;
+  if (b < 1) b = 1;
+  if (b > max_blocks) b = max_blocks;
+  return (int)b;
+}
+
+}  // namespace ptgs
+
+using namespace ptgs;
+
+extern "C" {
+
+int ptgs_version(void) { return 100; }
+const char* ptgs_last_error(void) { return g_err; }
+int64_t ptgs_launch_count(void) { return g_launches; }
+void ptgs_reset_launch_count(void) { g_launches = 0; }
+
+int ptgs_aos_to_soa_f32(const float* xyz, int64_t n, float* x, float* y,
+                        float* z, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0, "n");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(((uintptr_t)xyz % 16 == 0) && ((uintptr_t)x % 16 == 0) &&
+                   ((uintptr_t)y % 16 == 0) && ((uintptr_t)z % 16 == 0),
+               "pointers must be 16-byte aligned");
+  int grid = grid_for(n / 4 + 1, 256, kNumSMs * 8);
+  aos_to_soa_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz, n, x, y, z);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_manhattan_apply(const float* x, const float* y, const float* z,
+                         int64_t n, const double* man_trans_host, double* ox,
+                         double* oy, double* oz, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && man_trans_host, "n / man_trans");
+  if (n == 0) return PTGS_OK;
+  Man m;
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) m.r[r * 3 + c] = man_trans_host[r * 4 + c];
+    m.t[r] = man_trans_host[r * 4 + 3];
+  }
+  int grid = grid_for(n, 256, kNumSMs * 8);
+  manhattan_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, y, z, n, m, ox, oy, oz);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+template <typename T>
+static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
+                       int64_t n_capacity, double* bounds, cudaStream_t st) {
+  using K = typename KeyOf<T>::type;
+  // the 4 keys live in the output buffer itself? no: bounds is 4 doubles = 32 B,
+  // keys need 4*sizeof(K) <= 32 B -> reuse a small static-free scratch: the
+  // caller's bounds buffer is only 32 B, so run keys in a cudaMallocAsync'd
+  // block to stay re-entrant.
+  K* keys = nullptr;
+  PTGS_CUDA_TRY(cudaMallocAsync(&keys, 4 * sizeof(K), st));
+  bounds_init_kernel<T><<<1, 1, 0, st>>>(keys);
+  PTGS_LAUNCH_CHECK();
+  int grid = grid_for(n_capacity, 256 * 8, kNumSMs * 8);
+  bounds_kernel<T><<<grid, 256, 0, st>>>((const T*)x, (const T*)y, n_dev, keys);
+  PTGS_LAUNCH_CHECK();
+  bounds_finish_kernel<T><<<1, 1, 0, st>>>(keys, bounds);
+  PTGS_LAUNCH_CHECK();
+  PTGS_CUDA_TRY(cudaFreeAsync(keys, st));
+  return PTGS_OK;
+}
+
+int ptgs_bounds_xy(int dtype, const void* x, const void* y,
+                   const int64_t* n_dev, int64_t n_capacity, double* bounds,
+                   ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_capacity >= 0 && n_dev && bounds, "arguments");
+  if (dtype == PTGS_F32)
+    return bounds_impl<float>(x, y, n_dev, n_capacity, bounds, (cudaStream_t)stream);
+  if (dtype == PTGS_F64)
+    return bounds_impl<double>(x, y, n_dev, n_capacity, bounds, (cudaStream_t)stream);
+  PTGS_REQUIRE(false, "dtype");
+}
+
+size_t ptgs_compact_xy_workspace_bytes(int64_t n) {
+  int64_t tiles = (n + kCompactTile - 1) / kCompactTile + 1;
+  return align_up(tiles * 4, 256) + align_up(tiles * 8, 256) + 256;
+}
+
+int ptgs_compact_xy(int dtype, const void* x, const void* y,
+                    const uint8_t* keep, int64_t n, void* out_x, void* out_y,
+                    int64_t* n_out, void* workspace, size_t workspace_bytes,
+                    ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && n_out, "arguments");
+  PTGS_REQUIRE(dtype == PTGS_F32 || dtype == PTGS_F64, "dtype");
+  if (workspace_bytes < ptgs_compact_xy_workspace_bytes(n)) {
+    set_error("compact_xy: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t tiles = (n + kCompactTile - 1) / kCompactTile;
+  if (tiles == 0) {
+    PTGS_CUDA_TRY(cudaMemsetAsync(n_out, 0, 8, st));
+    return PTGS_OK;
+  }
+  Carver cv(workspace);
+  int32_t* tile_count = cv.take<int32_t>(tiles);
+  int64_t* tile_base = cv.take<int64_t>(tiles);
+  compact_count_kernel<<<(int)tiles, 256, 0, st>>>(keep, n, tile_count);
+  PTGS_LAUNCH_CHECK();
+  scan_tiles_kernel<<<1, 1024, 0, st>>>(tile_count, tiles, tile_base, n_out);
+  PTGS_LAUNCH_CHECK();
+  if (dtype == PTGS_F32)
+    compact_scatter_kernel<float><<<(int)tiles, 256, 0, st>>>(
+        (const float*)x, (const float*)y, keep, n, tile_base, (float*)out_x, (float*)out_y);
+  else
+    compact_scatter_kernel<double><<<(int)tiles, 256, 0, st>>>(
+        (const double*)x, (const double*)y, keep, n, tile_base, (double*)out_x, (double*)out_y);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,289 @@
+/*
+ * libptgs -- B200 (sm_100a) point-count scene partitioner, C ABI.
+ *
+ * Drop-in boundary for the hot path of 92401/Based-on-point-cloud-partitions
+ * (the reference has no FFI: its boundary is the set of Python callables
+ * `run_DataPartition` invokes, scene/ptgs/shen_partition_utils.py:57-93).
+ * Each entry point below names the reference interface it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into memory owned by the caller unless
+ *     the parameter is documented as "host"; the library never frees or
+ *     retains caller memory.
+ *   - sizes are int64_t; the last argument is the CUDA stream (cudaStream_t)
+ *     on which all work is enqueued; calls are asynchronous unless documented
+ *     "synchronises".
+ *   - scratch memory is caller provided: ask ptgs_<op>_workspace_bytes() first.
+ *   - return value: PTGS_OK (0) or a negative ptgs_status; the message of the
+ *     last failure on the calling thread is ptgs_last_error().
+ *   - variable-length outputs: caller allocates capacity, the library writes a
+ *     device-side count; PTGS_E_CAPACITY is reported through the device-side
+ *     status word (see each call) because the overflow is detected on device.
+ *   - no global mutable state: re-entrant across streams, devices and threads.
+ *   - arithmetic: every kernel is compiled with -fmad=false and IEEE division;
+ *     fused multiply-adds appear only where this header says "fma".
+ */
+#ifndef PTGS_H_
+#define PTGS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* ptgs_stream_t; /* cudaStream_t */
+
+typedef enum ptgs_status {
+  PTGS_OK = 0,
+  PTGS_E_INVALID = -1,   /* bad argument */
+  PTGS_E_CUDA = -2,      /* CUDA runtime error (see ptgs_last_error) */
+  PTGS_E_CAPACITY = -3,  /* caller-provided capacity too small */
+  PTGS_E_RANGE = -4,     /* value does not fit the packed key layout */
+  PTGS_E_WORKSPACE = -5  /* workspace smaller than *_workspace_bytes() */
+} ptgs_status;
+
+/* Coordinate type selector: the reference runs the split / expansion /
+ * down-sampling on float32 point clouds, and on float64 ones when a Manhattan
+ * transform is applied (scene/ptgs/shen_data_read.py:126-130). */
+typedef enum ptgs_dtype { PTGS_F32 = 0, PTGS_F64 = 1 } ptgs_dtype;
+
+int ptgs_version(void);
+const char* ptgs_last_error(void);
+/* Number of kernel launches issued by this library on the calling thread
+ * since the last ptgs_reset_launch_count() (bench.py `gpu_launches`). */
+int64_t ptgs_launch_count(void);
+void ptgs_reset_launch_count(void);
+
+/* ------------------------------------------------------------------ *
+ * Layout helpers
+ * ------------------------------------------------------------------ */
+
+/* (N,3) row-major float32 -> three planar arrays (vectorised float4 loads).
+ * Replaces the implicit column slicing `points[:, 0]` etc. everywhere in the
+ * reference (e.g. density_partition.py:22-23). */
+int ptgs_aos_to_soa_f32(const float* xyz, int64_t n, float* x, float* y,
+                        float* z, ptgs_stream_t stream);
+
+/* A13 -- Manhattan transform of the point cloud,
+ * scene/ptgs/shen_data_read.py:126-130 (fetchPly):
+ *     new = R(3x3,f64) . p(f32->f64) + T        (f64 result)
+ * evaluated as t = r0*x; t = fma(r1,y,t); t = fma(r2,z,t); out = t + T
+ * (the k-ordered FMA accumulation of the BLAS dgemm micro-kernel NumPy calls).
+ * `man_trans` is a HOST pointer to the row-major 4x4 matrix. */
+int ptgs_manhattan_apply(const float* x, const float* y, const float* z,
+                         int64_t n, const double* man_trans_host, double* ox,
+                         double* oy, double* oz, ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A1 -- radius outlier removal
+ *   replaces o3d PointCloud.remove_radius_outlier(nb_points, radius) as
+ *   called at scene/ptgs/shen_partition_utils.py:50 (third-party open3d,
+ *   un-pinned): keep point i iff #{j : |pi-pj|^2 < radius^2, j incl. i}
+ *   > nb_points, distances in float64.
+ *   out keep[n] (uint8) and *n_keep (device int64).
+ * ------------------------------------------------------------------ */
+size_t ptgs_radius_outlier_workspace_bytes(int64_t n);
+int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
+                             const void* z, int64_t n, double radius,
+                             int nb_points, uint8_t* keep, int64_t* n_keep,
+                             void* workspace, size_t workspace_bytes,
+                             ptgs_stream_t stream);
+
+/* Stream compaction of the kept points (index order preserved), i.e.
+ * `pcd.select_by_index(ind)`; only x and y are needed by the split.
+ * out_x/out_y have capacity n; *n_out receives the count. */
+size_t ptgs_compact_xy_workspace_bytes(int64_t n);
+int ptgs_compact_xy(int dtype, const void* x, const void* y,
+                    const uint8_t* keep, int64_t n, void* out_x, void* out_y,
+                    int64_t* n_out, void* workspace, size_t workspace_bytes,
+                    ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A2 -- XY bounds, scene/ptgs/shen_partition_utils.py:66-70.
+ *   n is a DEVICE count (so it can be chained after ptgs_compact_xy).
+ *   bounds[4] = {xmin, ymin, xmax, ymax} as float64.
+ * ------------------------------------------------------------------ */
+int ptgs_bounds_xy(int dtype, const void* x, const void* y,
+                   const int64_t* n_dev, int64_t n_capacity, double* bounds,
+                   ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A3 -- balanced binary (exact median) split
+ *   replaces quad_tree_partition (shen_partation_densify.py:37-49) ->
+ *   density_partition (density_partition.py:148-166) ->
+ *   balanced_binary_partition (density_partition.py:9-99).
+ *   Leaf when n <= leaf_limit (= threshold*1.2 evaluated by the caller in
+ *   float64) or depth >= max_depth; axis = x when x_range >= y_range; split
+ *   value = the element of rank n/2 along the axis (exact radix select);
+ *   both children are closed rectangles that share the split line.
+ *   Outputs (DFS, left first): leaf_bounds[L][4] f64 {minx,miny,maxx,maxy},
+ *   leaf_path[L] (bit i of the path = branch taken at depth i, MSB first in
+ *   a `depth`-bit field), leaf_depth[L], leaf_count[L]; *n_leaves (device).
+ *   status_dev: device int32, PTGS_OK or PTGS_E_CAPACITY when the working
+ *   buffers (sized by capacity_factor) overflowed (duplicate split-line
+ *   points are copied into both children).
+ *   max_leaves must be >= 2^max_depth.
+ * ------------------------------------------------------------------ */
+size_t ptgs_balanced_split_workspace_bytes(int dtype, int64_t n_capacity,
+                                           double capacity_factor,
+                                           int max_depth);
+int ptgs_balanced_split(int dtype, const void* x, const void* y,
+                        const int64_t* n_dev, int64_t n_capacity,
+                        const double* root_bounds, double leaf_limit,
+                        int max_depth, double capacity_factor,
+                        double* leaf_bounds, uint32_t* leaf_path,
+                        int32_t* leaf_depth, int64_t* leaf_count,
+                        int32_t* n_leaves, int32_t max_leaves,
+                        int32_t* status_dev, void* workspace,
+                        size_t workspace_bytes, ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A4 -- expanded-block point selection
+ *   replaces expand_partitions/extract_point_cloud
+ *   (shen_partation_densify.py:182-252, mask at :201-202): closed
+ *   rectangle test of every (unfiltered) point against every block's
+ *   expanded box.  rects[L][4] = {minx, maxx, miny, maxy} in the point
+ *   dtype (the caller rounds the float64 bounds to float32 exactly as
+ *   NumPy does when comparing a float32 array with a Python float).
+ *   Two calls: _count fills counts[L] (int64) and the workspace, the caller
+ *   reads counts, allocates `indices` (int32, sum(counts)) and calls _fill,
+ *   which writes each block's indices in ascending order
+ *   (CSR offsets = exclusive scan of counts, written to offsets[L+1]).
+ * ------------------------------------------------------------------ */
+size_t ptgs_expand_workspace_bytes(int64_t n, int32_t n_blocks);
+int ptgs_expand_count(int dtype, const void* x, const void* y, int64_t n,
+                      const void* rects, int32_t n_blocks, int64_t* counts,
+                      void* workspace, size_t workspace_bytes,
+                      ptgs_stream_t stream);
+int ptgs_expand_fill(int dtype, const void* x, const void* y, int64_t n,
+                     const void* rects, int32_t n_blocks, int64_t* offsets,
+                     int32_t* indices, int64_t indices_capacity,
+                     void* workspace, size_t workspace_bytes,
+                     ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A5 -- camera -> block assignment
+ *   replaces assign_cameras_to_partitions (shen_partation_densify.py:362-408):
+ *   camera c belongs to block b iff its centre is STRICTLY inside the
+ *   expanded box in XY (shapely contains(Point), :388), float64 compares.
+ *   centers[C][3] float64 (the caller evaluates -R^T T in float32 exactly as
+ *   scene/cameras.py:56-58 and widens); boxes[L][4] = {minx,miny,maxx,maxy}.
+ *   cam_offsets[L+1] (int64) is always written; cam_index (int32, ascending
+ *   per block) only up to cam_capacity (a second call with a larger buffer
+ *   is needed when cam_offsets[L] > cam_capacity).
+ * ------------------------------------------------------------------ */
+int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
+                        const double* boxes, int32_t n_blocks,
+                        int64_t* cam_offsets, int32_t* cam_index,
+                        int64_t cam_capacity, ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A6 -- voxel down-sampling of every block
+ *   replaces downsample_point_cloud(pc, voxel) (shen_partation_densify.py:
+ *   541-614): per block  vid = floor((p - min_b)/voxel) (point dtype
+ *   arithmetic, :572), one output point per occupied voxel = the mean of its
+ *   points accumulated sequentially in index order then divided by the
+ *   count (:588-591), cast to float32 (:605).
+ *   Inputs: planar coordinates, block CSR (offsets[L+1], indices).
+ *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
+ *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
+ *   index list of the first point of the voxel.  Voxels of a block are
+ *   emitted in ascending (vx,vy,vz) order; the reference's first-occurrence
+ *   order is ds_first ascending (ptgs_voxel_reference_order).
+ *   status_dev: PTGS_E_RANGE when a voxel index exceeds the key layout.
+ * ------------------------------------------------------------------ */
+size_t ptgs_voxel_downsample_workspace_bytes(int64_t n_entries,
+                                             int32_t n_blocks);
+int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
+                          const void* z, const int64_t* offsets,
+                          const int32_t* indices, int64_t n_entries,
+                          int32_t n_blocks, double voxel_size, float* ds_x,
+                          float* ds_y, float* ds_z, int32_t* ds_first,
+                          int64_t* ds_offsets, int32_t* status_dev,
+                          void* workspace, size_t workspace_bytes,
+                          ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * A7-A9 -- camera visibility
+ *   replaces project_points_to_camera (shen_partation_densify.py:410-477),
+ *   run_graham_scan (:481-539), process_camera_visibility (:890-910) and the
+ *   selection loop of visibility_based_camera_selection (:911-954).
+ *
+ * Camera record: 20 floats
+ *   [0..8]  R row-major (world->camera rotation, float32 of camera.R)
+ *   [9..11] T
+ *   [12] fx  [13] fy  [14] cx  [15] cy     (float32 of the Python doubles)
+ *   [16] u_limit (image_width)  [17] v_limit (image_height)
+ *   [18] front_axis (1.0 = camera-space Y > 0 as the reference, :447;
+ *                    2.0 = Z > 0)          [19] reserved (0)
+ * One test (fp32):
+ *   Xc = ((r00*x (+fma) r01*y) (+fma) r02*z) + tx          (k-ordered GEMM)
+ *   uh = fma(cx, Zc, fx*Xc), vh = fma(cy, Zc, fy*Yc), u = uh/Zc, v = vh/Zc
+ *   hit = front > 0 && 0 <= u < u_limit && 0 <= v < v_limit
+ * ------------------------------------------------------------------ */
+#define PTGS_CAMERA_FLOATS 20
+
+/* Sweep: every point of block b against every camera listed for block b.
+ * pair p = cam_offsets[b] + (position of the camera in the block's list).
+ * Hits are appended to rec_{u,v,pair} (capacity rec_capacity); *n_records
+ * (device int64) receives the TOTAL number of hits even when it exceeds the
+ * capacity (the caller then re-runs with a larger buffer).
+ * coord_absmax: max |coordinate| over the points (for the conservative
+ * pre-filter slack).  */
+size_t ptgs_visibility_sweep_workspace_bytes(int32_t n_blocks);
+int ptgs_visibility_sweep(const float* px, const float* py, const float* pz,
+                          const int64_t* pt_offsets, int32_t n_blocks,
+                          const float* cameras, const int64_t* cam_offsets,
+                          const int32_t* cam_index, float coord_absmax,
+                          float* rec_u, float* rec_v, uint32_t* rec_pair,
+                          int64_t rec_capacity, int64_t* n_records,
+                          void* workspace, size_t workspace_bytes,
+                          ptgs_stream_t stream);
+
+/* Group the hit records by pair (counting sort): n_hit[n_pairs] (int32),
+ * hit_offsets[n_pairs+1] (int64), hits_uv[n_records] (float2). */
+size_t ptgs_group_hits_workspace_bytes(int64_t n_pairs);
+int ptgs_group_hits(const float* rec_u, const float* rec_v,
+                    const uint32_t* rec_pair, int64_t n_records,
+                    int64_t n_pairs, int32_t* n_hit, int64_t* hit_offsets,
+                    float* hits_uv, void* workspace, size_t workspace_bytes,
+                    ptgs_stream_t stream);
+
+/* Hull area + keep decision per pair.  hits_uv is used as scratch (permuted).
+ * pair_cam[n_pairs]: camera index of each pair (to fetch W,H).
+ * area[n_pairs] float64 (reference Graham-scan semantics incl. its tie
+ * handling), ratio = area / (W*H); keep = n_hit > min_hits && ratio >= thr;
+ * near = |ratio - thr| <= near_eps. */
+int ptgs_hull_select(float* hits_uv, const int64_t* hit_offsets,
+                     const int32_t* n_hit, int64_t n_pairs,
+                     const int32_t* pair_cam, const float* cameras,
+                     int32_t min_hits, double ratio_threshold,
+                     double near_eps, double* area, double* ratio,
+                     uint8_t* keep, uint8_t* near, ptgs_stream_t stream);
+
+/* A9 selection: per block compaction of the kept cameras (ascending order of
+ * the block's camera list).  kept_offsets[L+1] int64, kept_index capacity =
+ * cam_offsets[L]. */
+int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
+                        const int32_t* cam_index, int32_t n_blocks,
+                        int64_t* kept_offsets, int32_t* kept_index,
+                        ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
+ * Coverage sweep (config 5; the camera x all-points pass of the Vast path,
+ * scene/ptgs/data_partition.py:385-424, :505): every point against every
+ * camera cam_first..cam_first+cam_count-1; n_hit[cam_count] int32 (must be
+ * zeroed by the caller... it is zeroed by the call); optional seen[n] uint8
+ * (may be NULL): 1 when any camera of the range sees the point.
+ * ------------------------------------------------------------------ */
+int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
+                        int64_t n, const float* cameras, int32_t cam_first,
+                        int32_t cam_count, float coord_absmax, int32_t* n_hit,
+                        uint8_t* seen, ptgs_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTGS_H_ */
