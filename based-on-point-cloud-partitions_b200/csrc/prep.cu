@@ -201,6 +201,27 @@ static inline int grid_for(int64_t n, int per_block, int max_blocks) {
   return (int)b;
 }
 
+template <typename T>
+static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
+                       int64_t n_capacity, double* bounds, cudaStream_t st) {
+  using K = typename KeyOf<T>::type;
+  // the 4 keys live in the output buffer itself? no: bounds is 4 doubles = 32 B,
+  // keys need 4*sizeof(K) <= 32 B -> reuse a small static-free scratch: the
+  // caller's bounds buffer is only 32 B, so run keys in a cudaMallocAsync'd
+  // block to stay re-entrant.
+  K* keys = nullptr;
+  PTGS_CUDA_TRY(cudaMallocAsync(&keys, 4 * sizeof(K), st));
+  bounds_init_kernel<T><<<1, 1, 0, st>>>(keys);
+  PTGS_LAUNCH_CHECK();
+  int grid = grid_for(n_capacity, 256 * 8, kNumSMs * 8);
+  bounds_kernel<T><<<grid, 256, 0, st>>>((const T*)x, (const T*)y, n_dev, keys);
+  PTGS_LAUNCH_CHECK();
+  bounds_finish_kernel<T><<<1, 1, 0, st>>>(keys, bounds);
+  PTGS_LAUNCH_CHECK();
+  PTGS_CUDA_TRY(cudaFreeAsync(keys, st));
+  return PTGS_OK;
+}
+
 }  // namespace ptgs
 
 using namespace ptgs;
@@ -238,27 +259,6 @@ int ptgs_manhattan_apply(const float* x, const float* y, const float* z,
   int grid = grid_for(n, 256, kNumSMs * 8);
   manhattan_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, y, z, n, m, ox, oy, oz);
   PTGS_LAUNCH_CHECK();
-  return PTGS_OK;
-}
-
-template <typename T>
-static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
-                       int64_t n_capacity, double* bounds, cudaStream_t st) {
-  using K = typename KeyOf<T>::type;
-  // the 4 keys live in the output buffer itself? no: bounds is 4 doubles = 32 B,
-  // keys need 4*sizeof(K) <= 32 B -> reuse a small static-free scratch: the
-  // caller's bounds buffer is only 32 B, so run keys in a cudaMallocAsync'd
-  // block to stay re-entrant.
-  K* keys = nullptr;
-  PTGS_CUDA_TRY(cudaMallocAsync(&keys, 4 * sizeof(K), st));
-  bounds_init_kernel<T><<<1, 1, 0, st>>>(keys);
-  PTGS_LAUNCH_CHECK();
-  int grid = grid_for(n_capacity, 256 * 8, kNumSMs * 8);
-  bounds_kernel<T><<<grid, 256, 0, st>>>((const T*)x, (const T*)y, n_dev, keys);
-  PTGS_LAUNCH_CHECK();
-  bounds_finish_kernel<T><<<1, 1, 0, st>>>(keys, bounds);
-  PTGS_LAUNCH_CHECK();
-  PTGS_CUDA_TRY(cudaFreeAsync(keys, st));
   return PTGS_OK;
 }
 

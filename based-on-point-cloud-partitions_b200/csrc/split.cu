@@ -383,7 +383,8 @@ static int split_impl(const void* x, const void* y, const int64_t* n_dev, int64_
   PTGS_CUDA_TRY(cudaMemsetAsync(s.hist, 0, (size_t)level_nodes * kBins * 4, st));
   split_init_kernel<T><<<1, 1, 0, st>>>(s, n_dev, root_bounds);
   PTGS_LAUNCH_CHECK();
-  int gpack = (int)min<int64_t>((n_capacity + 2047) / 2048 + 1, kNumSMs * 8);
+  int64_t gpack64 = (n_capacity + 2047) / 2048 + 1;
+  int gpack = (int)(gpack64 < (int64_t)kNumSMs * 8 ? gpack64 : (int64_t)kNumSMs * 8);
   pack_xy_kernel<T><<<gpack, 256, 0, st>>>((const T*)x, (const T*)y, n_dev, bufs[0]);
   PTGS_LAUNCH_CHECK();
   const int tiles = (int)((cap + kSplitTile - 1) / kSplitTile);

@@ -1,0 +1,797 @@
+// libptgs A7-A9: camera visibility sweep.
+// Reference: project_points_to_camera (scene/ptgs/shen_partation_densify.py:
+// 410-477), run_graham_scan (:481-539), process_camera_visibility (:890-910).
+//
+// One persistent kernel sweeps (block, point tile) work items.  A tile of 2048
+// points is staged into shared memory with 1-D bulk copies (TMA, mbarrier
+// completion, double buffered so the next tile lands while the current one is
+// being swept), moved once into registers (8 points per thread) and then
+// tested against every camera of the block; camera records are broadcast
+// from shared memory.  Per test: 3 x (mul + 2 fma + add) camera transform in
+// the k-ordered accumulation of the reference's SGEMM, 2 x (mul + fma)
+// intrinsics, a division-free conservative reject, and IEEE divisions only
+// for the survivors.  Counts are reduced with redux.sync per warp and one
+// shared-memory atomic per (warp, camera); shared accumulators are flushed
+// with one global atomic per (work item, camera).
+//
+//   MODE 0  hit counts (+ optional per-point "seen" flag)      -- coverage sweep
+//   MODE 1  hit counts + Graham pivot + 8 directional extremes -- sweep 1
+//   MODE 2  hull candidates                                   -- sweep 2
+#include "common.cuh"
+
+namespace ptgs {
+
+constexpr int kSwThreads = 256;
+constexpr int kSwP = 8;                          // points per thread
+constexpr int kSwTile = kSwThreads * kSwP;       // 2048 points per tile
+constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
+constexpr int kSwCamChunk = 32;                  // cameras staged per round
+constexpr int kSwMaxBlocks = 1024;
+constexpr int kCamFloats = PTGS_CAMERA_FLOATS;   // 20
+constexpr int kPolyFloats = PTGS_POLY_FLOATS;    // 28
+
+// ---- mbarrier / bulk copy (TMA) -------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(phase)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes,
+                                         uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// ---- one visibility test ----------------------------------------------------
+struct Cam {
+  float r00, r01, r02, r10, r11, r12, r20, r21, r22, tx, ty, tz;
+  float fx, fy, cx, cy, w, h, front_axis, pad;
+};
+
+__device__ __forceinline__ Cam load_cam(const float* s) {
+  const float4* q = reinterpret_cast<const float4*>(s);
+  const float4 a = q[0], b = q[1], c = q[2], d = q[3], e = q[4];
+  Cam k;
+  k.r00 = a.x; k.r01 = a.y; k.r02 = a.z; k.r10 = a.w;
+  k.r11 = b.x; k.r12 = b.y; k.r20 = b.z; k.r21 = b.w;
+  k.r22 = c.x; k.tx = c.y; k.ty = c.z; k.tz = c.w;
+  k.fx = d.x; k.fy = d.y; k.cx = d.z; k.cy = d.w;
+  k.w = e.x; k.h = e.y; k.front_axis = e.z; k.pad = e.w;
+  return k;
+}
+
+// camera space, k-ordered accumulation (r0*x, fma r1*y, fma r2*z, + t): the
+// order of the 4x4 @ 4xN SGEMM at densify:444.
+__device__ __forceinline__ float cam_row(float r0, float r1, float r2, float t, float x, float y,
+                                         float z) {
+  float a = __fmul_rn(r0, x);
+  a = __fmaf_rn(r1, y, a);
+  a = __fmaf_rn(r2, z, a);
+  return __fadd_rn(a, t);
+}
+
+struct Proj {
+  float uh, vh, Z;
+  bool maybe;
+};
+
+// everything up to (not including) the divisions; `maybe` is a conservative
+// superset of the hits (see DESIGN.md "division-free reject").
+__device__ __forceinline__ Proj project_pre(const Cam& c, float w1, float h1, float x, float y,
+                                            float z) {
+  const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x, y, z);
+  const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x, y, z);
+  const float Z = cam_row(c.r20, c.r21, c.r22, c.tz, x, y, z);
+  const float front = (c.front_axis == 1.0f) ? Y : Z;              // densify:447
+  Proj p;
+  p.Z = Z;
+  p.uh = __fmaf_rn(c.cx, Z, __fmul_rn(c.fx, X));                   // densify:467
+  p.vh = __fmaf_rn(c.cy, Z, __fmul_rn(c.fy, Y));
+  const uint32_t sgn = __float_as_uint(Z) & 0x80000000u;
+  const float a = __uint_as_float(__float_as_uint(p.uh) ^ sgn);
+  const float b = __uint_as_float(__float_as_uint(p.vh) ^ sgn);
+  const float az = fabsf(Z);
+  p.maybe = (front > 0.0f) && (a >= -az) && (a <= __fmul_rn(w1, az)) && (b >= -az) &&
+            (b <= __fmul_rn(h1, az));
+  return p;
+}
+
+__device__ __forceinline__ bool project_exact(const Cam& c, const Proj& p, float& u, float& v) {
+  u = __fdiv_rn(p.uh, p.Z);                                        // densify:468
+  v = __fdiv_rn(p.vh, p.Z);
+  return (u >= 0.0f) && (u < c.w) && (v >= 0.0f) && (v < c.h);     // densify:470-471
+}
+
+__device__ __forceinline__ uint32_t order_key(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// ---- work item schedule -----------------------------------------------------
+// item_prefix[b] = number of work items of the blocks before b; a block has
+// tiles_b * split_b items, split_b = min(cam_split, C_b).
+__global__ void __launch_bounds__(1024) sweep_schedule_kernel(
+    const int64_t* __restrict__ pt_offsets, const int64_t* __restrict__ cam_offsets, int L,
+    int cam_split, int64_t* __restrict__ item_prefix) {
+  __shared__ long long sm[33];
+  long long carry = 0;
+  for (int s = 0; s < L; s += 1024) {
+    const int b = s + threadIdx.x;
+    long long v = 0;
+    if (b < L) {
+      const int64_t m = pt_offsets[b + 1] - pt_offsets[b];
+      const int64_t c = cam_offsets[b + 1] - cam_offsets[b];
+      const int64_t sp = c < cam_split ? c : cam_split;
+      v = ((m + kSwTile - 1) / kSwTile) * sp;
+    }
+    long long tot;
+    long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
+    if (b < L) item_prefix[b] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) item_prefix[L] = carry;
+}
+
+struct SweepArgs {
+  const float* px; const float* py; const float* pz;
+  const int64_t* pt_offsets;
+  int32_t n_blocks;
+  const float* cameras;
+  const int64_t* cam_offsets;
+  const int32_t* cam_index;       // nullptr: camera j of the list is camera cam_first + j
+  int32_t cam_first;
+  int32_t cam_split;
+  const int64_t* item_prefix;
+  // MODE 0/1
+  int32_t* n_hit;
+  uint8_t* seen;                  // MODE 0, optional
+  uint64_t* pivot;                // MODE 1
+  uint64_t* extreme;              // MODE 1
+  // MODE 2
+  const float* poly;
+  const int64_t* cand_offsets;
+  float2* cand_uv;
+  int32_t* cand_count;
+};
+
+struct Item {
+  int b;
+  int64_t tile;
+  int64_t start;     // first point (global position)
+  int cnt;           // points in the tile
+  int64_t cam_lo, cam_hi;  // positions inside the block's camera list
+};
+
+__device__ __forceinline__ Item decode_item(const SweepArgs& a, const int64_t* s_prefix,
+                                            int64_t item) {
+  int lo = 0, hi = a.n_blocks - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (s_prefix[mid] <= item) lo = mid; else hi = mid - 1;
+  }
+  // skip empty blocks that share the same prefix value: lo is the LAST block
+  // with prefix <= item, which is the one that owns it.
+  Item it;
+  it.b = lo;
+  const int64_t local = item - s_prefix[lo];
+  const int64_t p0 = a.pt_offsets[lo], p1 = a.pt_offsets[lo + 1];
+  const int64_t c = a.cam_offsets[lo + 1] - a.cam_offsets[lo];
+  const int64_t sp = c < a.cam_split ? c : a.cam_split;
+  it.tile = local / sp;
+  const int64_t s = local - it.tile * sp;
+  it.start = p0 + it.tile * kSwTile;
+  const int64_t rem = p1 - it.start;
+  it.cnt = (int)(rem < kSwTile ? rem : kSwTile);
+  it.cam_lo = c * s / sp;
+  it.cam_hi = c * (s + 1) / sp;
+  return it;
+}
+
+// ---- the sweep ---------------------------------------------------------------
+struct SweepSmem {
+  alignas(128) float tile[2][3][kSwStageFloats];
+  alignas(16) float cam[kSwCamChunk][kCamFloats];
+  alignas(16) float poly[kSwCamChunk][kPolyFloats];       // MODE 2
+  unsigned long long ext[kSwCamChunk][8];                 // MODE 1
+  unsigned long long pivot[kSwCamChunk];                  // MODE 1
+  long long cand_off[kSwCamChunk];                        // MODE 2
+  int cand_cap[kSwCamChunk];                              // MODE 2
+  int cnt[kSwCamChunk];
+  alignas(8) uint64_t bar[2];
+  int64_t prefix[kSwMaxBlocks + 1];
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+
+  for (int i = tid; i <= a.n_blocks; i += kSwThreads) S.prefix[i] = a.item_prefix[i];
+  if (tid == 0) {
+    mbar_init(&S.bar[0], 1);
+    mbar_init(&S.bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int64_t n_items = S.prefix[a.n_blocks];
+
+  auto issue = [&](const Item& it, int stage) {
+    // 16-byte granular window around [start, start + cnt)
+    const int64_t a0 = it.start & ~(int64_t)3;
+    const int shift = (int)(it.start - a0);
+    const uint32_t bytes = (uint32_t)(((shift + it.cnt + 3) & ~3) * 4);
+    mbar_expect_tx(&S.bar[stage], 3 * bytes);
+    bulk_g2s(S.tile[stage][0], a.px + a0, bytes, &S.bar[stage]);
+    bulk_g2s(S.tile[stage][1], a.py + a0, bytes, &S.bar[stage]);
+    bulk_g2s(S.tile[stage][2], a.pz + a0, bytes, &S.bar[stage]);
+  };
+
+  int64_t item = blockIdx.x;
+  Item cur;
+  if (item < n_items) {
+    cur = decode_item(a, S.prefix, item);
+    if (tid == 0) issue(cur, 0);
+  }
+  uint32_t phase[2] = {0, 0};
+  int stage = 0;
+  for (; item < n_items; item += gridDim.x, stage ^= 1) {
+    // ---- tile -> registers
+    mbar_wait(&S.bar[stage], phase[stage]);
+    phase[stage] ^= 1;
+    float x[kSwP], y[kSwP], z[kSwP];
+    {
+      const int shift = (int)(cur.start & 3);
+      const float qnan = __int_as_float(0x7fc00000);
+#pragma unroll
+      for (int k = 0; k < kSwP; ++k) {
+        const int i = k * kSwThreads + tid;
+        const bool ok = i < cur.cnt;
+        x[k] = ok ? S.tile[stage][0][shift + i] : qnan;   // NaN never hits
+        y[k] = ok ? S.tile[stage][1][shift + i] : qnan;
+        z[k] = ok ? S.tile[stage][2][shift + i] : qnan;
+      }
+    }
+    __syncthreads();   // every thread is done with stage^1 (previous item) and this stage
+    const int64_t next = item + gridDim.x;
+    Item nxt;
+    if (next < n_items) {
+      nxt = decode_item(a, S.prefix, next);
+      if (tid == 0) {
+        fence_proxy_async();
+        issue(nxt, stage ^ 1);
+      }
+    }
+
+    const int64_t cam_base = a.cam_offsets[cur.b];
+    unsigned seen_mask = 0;
+    for (int64_t c0 = cur.cam_lo; c0 < cur.cam_hi; c0 += kSwCamChunk) {
+      const int nc = (int)((cur.cam_hi - c0) < kSwCamChunk ? (cur.cam_hi - c0) : kSwCamChunk);
+      // ---- stage the camera chunk
+      for (int i = tid; i < nc * (kCamFloats / 4); i += kSwThreads) {
+        const int j = i / (kCamFloats / 4), q = i % (kCamFloats / 4);
+        const int64_t pos = cam_base + c0 + j;
+        const int64_t cam = a.cam_index ? (int64_t)a.cam_index[pos] : (int64_t)a.cam_first + (c0 + j);
+        reinterpret_cast<float4*>(S.cam[j])[q] =
+            __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
+      }
+      if (MODE == 2) {
+        for (int i = tid; i < nc * (kPolyFloats / 4); i += kSwThreads) {
+          const int j = i / (kPolyFloats / 4), q = i % (kPolyFloats / 4);
+          reinterpret_cast<float4*>(S.poly[j])[q] = __ldg(
+              reinterpret_cast<const float4*>(a.poly + (cam_base + c0 + j) * kPolyFloats) + q);
+        }
+      }
+      if (tid < nc) {
+        S.cnt[tid] = 0;
+        if (MODE == 1) {
+          S.pivot[tid] = ~0ull;
+#pragma unroll
+          for (int d = 0; d < 8; ++d) S.ext[tid][d] = 0ull;
+        }
+        if (MODE == 2) {
+          const int64_t pair = cam_base + c0 + tid;
+          const int64_t o0 = a.cand_offsets[pair], o1 = a.cand_offsets[pair + 1];
+          S.cand_off[tid] = o0;
+          S.cand_cap[tid] = (int)(o1 - o0);
+        }
+      }
+      __syncthreads();
+
+      // ---- sweep: 8 register points x nc cameras
+      for (int j = 0; j < nc; ++j) {
+        const Cam c = load_cam(S.cam[j]);
+        const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
+        int cnt = 0;
+#pragma unroll
+        for (int k = 0; k < kSwP; ++k) {
+          const Proj p = project_pre(c, w1, h1, x[k], y[k], z[k]);
+          if (p.maybe) {
+            float u, v;
+            if (project_exact(c, p, u, v)) {
+              if (MODE != 2) ++cnt;
+              if (MODE == 0) seen_mask |= 1u << k;
+              if (MODE == 1) {
+                u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                v = __fadd_rn(v, 0.0f);
+                const unsigned long long pk =
+                    ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
+                const unsigned long long idx =
+                    (unsigned long long)(cur.tile * kSwTile + k * kSwThreads + tid);
+                const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
+                const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
+#pragma unroll
+                for (int d = 0; d < 8; ++d) {
+                  const unsigned long long e = ((unsigned long long)order_key(dir[d]) << 32) | idx;
+                  if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
+                }
+              }
+              if (MODE == 2) {
+                u = __fadd_rn(u, 0.0f);
+                v = __fadd_rn(v, 0.0f);
+                const float* pl = S.poly[j];
+                // the pivot's row: only the pivot itself takes part (see ptgs.h)
+                const bool excluded = (v == pl[1]) && (u != pl[2]);
+                if (!excluded) {
+                  const int ne = (int)pl[0];
+                  const float margin = pl[3];
+                  bool inside = ne > 0;
+                  for (int e = 0; e < ne; ++e) {
+                    const float f = __fadd_rn(
+                        __fadd_rn(__fmul_rn(pl[4 + 3 * e], u), __fmul_rn(pl[5 + 3 * e], v)),
+                        pl[6 + 3 * e]);
+                    inside = inside && (f > margin);
+                  }
+                  if (!inside) {
+                    const int64_t pair = cam_base + c0 + j;
+                    const int slot = atomicAdd(a.cand_count + pair, 1);
+                    if (slot < S.cand_cap[j]) a.cand_uv[S.cand_off[j] + slot] = make_float2(u, v);
+                  }
+                }
+              }
+            }
+          }
+        }
+        if (MODE != 2) {
+          const int wsum = __reduce_add_sync(kFullMask, cnt);
+          if (lane == 0 && wsum) atomicAdd(&S.cnt[j], wsum);
+        }
+      }
+      __syncthreads();
+
+      // ---- flush the chunk's accumulators
+      if (MODE != 2 && tid < nc) {
+        const int cn = S.cnt[tid];
+        if (cn) {
+          const int64_t pair = (MODE == 0 && !a.cam_index) ? (c0 + tid) : (cam_base + c0 + tid);
+          atomicAdd(a.n_hit + pair, cn);
+          if (MODE == 1) {
+            atomicMin(reinterpret_cast<unsigned long long*>(a.pivot) + pair, S.pivot[tid]);
+#pragma unroll
+            for (int d = 0; d < 8; ++d)
+              if (S.ext[tid][d])
+                atomicMax(reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8 + d,
+                          S.ext[tid][d]);
+          }
+        }
+      }
+      __syncthreads();
+    }
+    if (MODE == 0 && a.seen) {
+#pragma unroll
+      for (int k = 0; k < kSwP; ++k)
+        if (seen_mask & (1u << k)) a.seen[cur.start + k * kSwThreads + tid] = 1;
+    }
+    cur = nxt;
+  }
+}
+
+// ---- inner polygon per pair --------------------------------------------------
+__global__ void __launch_bounds__(128) polygon_kernel(
+    const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz,
+    const int64_t* __restrict__ pt_offsets, int L, const float* __restrict__ cameras,
+    const int64_t* __restrict__ cam_offsets, const int32_t* __restrict__ cam_index,
+    const int32_t* __restrict__ n_hit, const uint64_t* __restrict__ pivot,
+    const uint64_t* __restrict__ extreme, float* __restrict__ poly) {
+  const int64_t n_pairs = cam_offsets[L];
+  const int64_t pair = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= n_pairs) return;
+  float* out = poly + pair * kPolyFloats;
+  for (int i = 0; i < kPolyFloats; ++i) out[i] = 0.0f;
+  out[1] = -1.0f; out[2] = -1.0f;     // no hit has a negative coordinate
+  if (n_hit[pair] <= 0) return;
+  int lo = 0, hi = L - 1;             // block of the pair
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (cam_offsets[mid] <= pair) lo = mid; else hi = mid - 1;
+  }
+  const int64_t p0 = pt_offsets[lo];
+  const Cam c = load_cam(cameras + (int64_t)cam_index[pair] * kCamFloats);
+  const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
+  const uint64_t pv = pivot[pair];
+  const float vp = __uint_as_float((uint32_t)(pv >> 32)), up = __uint_as_float((uint32_t)pv);
+  out[1] = vp; out[2] = up;
+  const float D = fmaxf(c.w, c.h);
+  out[3] = 4e-6f * D * D;             // > the float32 evaluation error of the half planes
+  double vx[8], vy[8];
+  int m = 0;
+  for (int d = 0; d < 8; ++d) {
+    const uint64_t e = extreme[pair * 8 + d];
+    if (!e) continue;
+    const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
+    const Proj p = project_pre(c, w1, h1, px[gi], py[gi], pz[gi]);
+    float u, v;
+    if (!project_exact(c, p, u, v)) continue;   // cannot happen: it was a hit in sweep 1
+    u = __fadd_rn(u, 0.0f); v = __fadd_rn(v, 0.0f);
+    if (v == vp && u != up) continue;           // pivot-row hit: not in the scanned set
+    if (m && vx[m - 1] == (double)u && vy[m - 1] == (double)v) continue;
+    vx[m] = u; vy[m] = v; ++m;
+  }
+  while (m > 1 && vx[m - 1] == vx[0] && vy[m - 1] == vy[0]) --m;
+  if (m < 3) return;
+  for (int i = 0; i < m; ++i) {
+    const int k = (i + 1 == m) ? 0 : i + 1;
+    const double ea = -(vy[k] - vy[i]), eb = vx[k] - vx[i];
+    out[4 + 3 * i] = (float)ea;
+    out[5 + 3 * i] = (float)eb;
+    out[6 + 3 * i] = (float)(-(ea * vx[i] + eb * vy[i]));
+  }
+  out[0] = (float)m;
+}
+
+// ---- exact hull + area per pair ----------------------------------------------
+constexpr int kHullThreads = 128;
+constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
+constexpr int kHullChain = 1024;    // max vertices per monotone chain
+
+__device__ __forceinline__ bool lex_less(float2 a, float2 b) {
+  return a.x < b.x || (a.x == b.x && a.y < b.y);
+}
+// cross product of (b-a) x (c-a) evaluated like the reference's Python floats
+// (densify:520-521): float64, no fma.
+__device__ __forceinline__ double cross3(float2 a, float2 b, float2 c) {
+  const double abx = __dsub_rn((double)b.x, (double)a.x), aby = __dsub_rn((double)b.y, (double)a.y);
+  const double acx = __dsub_rn((double)c.x, (double)a.x), acy = __dsub_rn((double)c.y, (double)a.y);
+  return __dsub_rn(__dmul_rn(abx, acy), __dmul_rn(aby, acx));
+}
+
+__global__ void __launch_bounds__(kHullThreads) hull_kernel(
+    const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
+    const int32_t* __restrict__ cand_count, const int32_t* __restrict__ n_hit, int64_t n_pairs,
+    const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
+    double thr, double near_eps, double* __restrict__ area_out, double* __restrict__ ratio_out,
+    uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out) {
+  __shared__ float2 buf[kHullBuf];
+  __shared__ float2 lower[kHullChain];
+  __shared__ float2 upper[kHullChain];
+  __shared__ int s_h, s_nl, s_nu, s_flags, s_col;
+  const int64_t pair = blockIdx.x;
+  if (pair >= n_pairs) return;
+  const int tid = threadIdx.x;
+  const int64_t off = cand_offsets[pair];
+  const int cap = (int)(cand_offsets[pair + 1] - off);
+  int K = cand_count[pair];
+  int flags = 0;
+  if (K > cap) { flags |= 4; K = cap; }
+  if (tid == 0) { s_h = 0; s_flags = 0; s_col = 0; }
+  __syncthreads();
+  const float inf = __int_as_float(0x7f800000);
+  int pos = 0;
+  bool single_round = true;
+  int rounds = 0;
+  while (pos < K || rounds == 0) {
+    const int h = s_h;
+    int m = K - pos;
+    if (m > kHullBuf - h) m = kHullBuf - h;
+    const int n = h + m;
+    int n2 = 1;
+    while (n2 < n) n2 <<= 1;
+    for (int i = tid; i < n2 - h; i += kHullThreads)
+      buf[h + i] = (i < m) ? cand_uv[off + pos + i] : make_float2(inf, inf);
+    __syncthreads();
+    // bitonic sort of buf[0..n2) by (u, v)
+    for (int k = 2; k <= n2; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int i = tid; i < n2; i += kHullThreads) {
+          const int l = i ^ j;
+          if (l > i) {
+            const float2 a = buf[i], b = buf[l];
+            const bool up = (i & k) == 0;
+            if (up ? lex_less(b, a) : lex_less(a, b)) { buf[i] = b; buf[l] = a; }
+          }
+        }
+        __syncthreads();
+      }
+    }
+    if (tid == 0) {
+      // Andrew's monotone chain; pop on cross <= 0 (densify:522)
+      int nl = 0, nu = 0;
+      bool overflow = false;
+      for (int i = 0; i < n; ++i) {
+        const float2 p = buf[i];
+        while (nl >= 2 && cross3(lower[nl - 2], lower[nl - 1], p) <= 0.0) --nl;
+        if (nl == 1 && lower[0].x == p.x && lower[0].y == p.y) --nl;
+        if (nl < kHullChain) lower[nl++] = p; else overflow = true;
+        while (nu >= 2 && cross3(upper[nu - 2], upper[nu - 1], p) >= 0.0) --nu;
+        if (nu == 1 && upper[0].x == p.x && upper[0].y == p.y) --nu;
+        if (nu < kHullChain) upper[nu++] = p; else overflow = true;
+      }
+      if (overflow) s_flags |= 8;
+      s_nl = nl; s_nu = nu;
+    }
+    __syncthreads();
+    pos += m;
+    ++rounds;
+    if (pos < K) {
+      // more candidates than one round holds: keep the hull, merge the rest
+      single_round = false;
+      const int nl = s_nl, nu = s_nu;
+      for (int i = tid; i < nl; i += kHullThreads) buf[i] = lower[i];
+      for (int i = tid; i < nu - 2; i += kHullThreads) buf[nl + i] = upper[nu - 2 - i];
+      __syncthreads();
+      if (tid == 0) s_h = nl + (nu > 2 ? nu - 2 : 0);
+      __syncthreads();
+      if (s_h > kHullBuf / 2) { if (tid == 0) s_flags |= 8; __syncthreads(); break; }
+    }
+  }
+  // hull, counter-clockwise in (u, v): lower left->right, then upper right->left
+  const int nl = s_nl, nu = s_nu;
+  const int nh = (nl >= 1 && nu >= 1) ? nl + (nu > 2 ? nu - 2 : 0) : 0;
+  auto vert = [&](int i) -> float2 { return i < nl ? lower[i] : upper[nu - 2 - (i - nl)]; };
+  // first-ray check (flag bit1): another candidate exactly on the edge that
+  // leaves the pivot counter-clockwise.  Only when one round saw every candidate.
+  if (nh >= 3 && single_round) {
+    // the pivot is the lowest-v, then lowest-u vertex
+    int ip = 0;
+    float2 pv = vert(0);
+    for (int i = 1; i < nh; ++i) {
+      const float2 q = vert(i);
+      if (q.y < pv.y || (q.y == pv.y && q.x < pv.x)) { pv = q; ip = i; }
+    }
+    const float2 nx = vert(ip + 1 == nh ? 0 : ip + 1);
+    const int n = K;
+    int found = 0;
+    for (int i = tid; i < n; i += kHullThreads) {
+      const float2 q = buf[i];
+      const bool same = (q.x == pv.x && q.y == pv.y) || (q.x == nx.x && q.y == nx.y);
+      if (!same && cross3(pv, nx, q) == 0.0) found = 1;
+    }
+    if (found) atomicOr(&s_col, 1);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double area = 0.0;
+    if (nh >= 3) {                                       // densify:529 (len(hull) < 3 -> 0)
+      const float2 o = vert(0);
+      double acc = 0.0;
+      for (int i = 1; i + 1 < nh; ++i) {
+        const float2 p = vert(i), q = vert(i + 1);
+        const double ax = (double)p.x - (double)o.x, ay = (double)p.y - (double)o.y;
+        const double bx = (double)q.x - (double)o.x, by = (double)q.y - (double)o.y;
+        acc += ax * by - ay * bx;
+      }
+      area = 0.5 * fabs(acc);                             // densify:535
+    }
+    const float* rec = cameras + (int64_t)pair_cam[pair] * kCamFloats;
+    const double ratio = area / ((double)rec[16] * (double)rec[17]);   // densify:537-538
+    const int nhit = n_hit[pair];
+    const bool enough = nhit > min_hits;                  // densify:898
+    flags |= s_flags;
+    if (s_col) flags |= 2;
+    if (enough && fabs(ratio - thr) <= near_eps) flags |= 1;
+    area_out[pair] = enough ? area : 0.0;
+    ratio_out[pair] = enough ? ratio : 0.0;
+    keep_out[pair] = (enough && ratio >= thr) ? 1 : 0;    // densify:904
+    flags_out[pair] = (uint8_t)flags;
+  }
+}
+
+__global__ void __launch_bounds__(256) vis_init_kernel(int64_t n_pairs, int32_t* n_hit,
+                                                       uint64_t* pivot, uint64_t* extreme,
+                                                       int32_t* cand_count) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs * 8; i += stride) {
+    if (extreme) extreme[i] = 0ull;
+    if (i < n_pairs) {
+      if (n_hit) n_hit[i] = 0;
+      if (pivot) pivot[i] = ~0ull;
+      if (cand_count) cand_count[i] = 0;
+    }
+  }
+}
+
+__global__ void coverage_setup_kernel(int64_t n, int32_t cam_count, int64_t* pt_off,
+                                      int64_t* cam_off) {
+  pt_off[0] = 0; pt_off[1] = n;
+  cam_off[0] = 0; cam_off[1] = cam_count;
+}
+
+// ---- host side -----------------------------------------------------------------
+template <int MODE>
+static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
+  static_assert(sizeof(SweepSmem) < 100 * 1024, "two CTAs per SM");
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(SweepSmem)));
+  sweep_kernel<MODE><<<kNumSMs * 2, kSwThreads, sizeof(SweepSmem), st>>>(a);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+static int schedule(const int64_t* pt_offsets, const int64_t* cam_offsets, int32_t L,
+                    int32_t cam_split, int64_t* item_prefix, cudaStream_t st) {
+  sweep_schedule_kernel<<<1, 1024, 0, st>>>(pt_offsets, cam_offsets, L, cam_split, item_prefix);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+static bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+}  // namespace ptgs
+
+using namespace ptgs;
+
+extern "C" {
+
+size_t ptgs_visibility_workspace_bytes(int32_t n_blocks) {
+  if (n_blocks < 1) n_blocks = 1;
+  return align_up((size_t)(n_blocks + 1) * 8, 256) + 256;
+}
+
+int ptgs_visibility_init(int64_t n_pairs, int32_t* n_hit, uint64_t* pivot, uint64_t* extreme,
+                         int32_t* cand_count, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_pairs >= 0, "n_pairs");
+  if (n_pairs == 0) return PTGS_OK;
+  int64_t g = (n_pairs * 8 + 255) / 256;
+  if (g > kNumSMs * 8) g = kNumSMs * 8;
+  vis_init_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(n_pairs, n_hit, pivot, extreme, cand_count);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_visibility_count(const float* px, const float* py, const float* pz,
+                          const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
+                          const int64_t* cam_offsets, const int32_t* cam_index, int32_t cam_split,
+                          int32_t* n_hit, uint64_t* pivot, uint64_t* extreme, void* workspace,
+                          size_t workspace_bytes, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && n_hit && pivot && extreme,
+               "arguments");
+  PTGS_REQUIRE(aligned16(px) && aligned16(py) && aligned16(pz) && aligned16(cameras),
+               "point / camera arrays must be 16-byte aligned");
+  PTGS_REQUIRE(cam_split >= 1, "cam_split");
+  if (workspace_bytes < ptgs_visibility_workspace_bytes(n_blocks)) {
+    set_error("visibility_count: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t* item_prefix = (int64_t*)workspace;
+  int rc = schedule(pt_offsets, cam_offsets, n_blocks, cam_split, item_prefix, st);
+  if (rc) return rc;
+  SweepArgs a = {};
+  a.px = px; a.py = py; a.pz = pz; a.pt_offsets = pt_offsets; a.n_blocks = n_blocks;
+  a.cameras = cameras; a.cam_offsets = cam_offsets; a.cam_index = cam_index;
+  a.cam_split = cam_split; a.item_prefix = item_prefix;
+  a.n_hit = n_hit; a.pivot = pivot; a.extreme = extreme;
+  return launch_sweep<1>(a, st);
+}
+
+int ptgs_visibility_polygon(const float* px, const float* py, const float* pz,
+                            const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
+                            const int64_t* cam_offsets, const int32_t* cam_index,
+                            const int32_t* n_hit, const uint64_t* pivot, const uint64_t* extreme,
+                            int64_t n_pairs, float* poly, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(n_pairs >= 0, "n_pairs");
+  if (n_pairs == 0) return PTGS_OK;
+  PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && n_hit && pivot && extreme && poly,
+               "arguments");
+  polygon_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      px, py, pz, pt_offsets, n_blocks, cameras, cam_offsets, cam_index, n_hit, pivot, extreme, poly);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_visibility_candidates(const float* px, const float* py, const float* pz,
+                               const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
+                               const int64_t* cam_offsets, const int32_t* cam_index,
+                               int32_t cam_split, const float* poly, const int64_t* cand_offsets,
+                               float* cand_uv, int32_t* cand_count, void* workspace,
+                               size_t workspace_bytes, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && poly && cand_offsets && cand_count,
+               "arguments");
+  PTGS_REQUIRE(aligned16(px) && aligned16(py) && aligned16(pz) && aligned16(cameras) && aligned16(poly),
+               "point / camera / polygon arrays must be 16-byte aligned");
+  PTGS_REQUIRE(((uintptr_t)cand_uv & 7) == 0, "cand_uv must be 8-byte aligned");
+  PTGS_REQUIRE(cam_split >= 1, "cam_split");
+  if (workspace_bytes < ptgs_visibility_workspace_bytes(n_blocks)) {
+    set_error("visibility_candidates: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t* item_prefix = (int64_t*)workspace;
+  int rc = schedule(pt_offsets, cam_offsets, n_blocks, cam_split, item_prefix, st);
+  if (rc) return rc;
+  SweepArgs a = {};
+  a.px = px; a.py = py; a.pz = pz; a.pt_offsets = pt_offsets; a.n_blocks = n_blocks;
+  a.cameras = cameras; a.cam_offsets = cam_offsets; a.cam_index = cam_index;
+  a.cam_split = cam_split; a.item_prefix = item_prefix;
+  a.poly = poly; a.cand_offsets = cand_offsets; a.cand_uv = (float2*)cand_uv; a.cand_count = cand_count;
+  return launch_sweep<2>(a, st);
+}
+
+int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
+                         const int32_t* cand_count, const int32_t* n_hit, int64_t n_pairs,
+                         const int32_t* pair_cam, const float* cameras, int32_t min_hits,
+                         double ratio_threshold, double near_eps, double* area, double* ratio,
+                         uint8_t* keep, uint8_t* flags, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_pairs >= 0 && n_pairs < (1ll << 31), "n_pairs");
+  if (n_pairs == 0) return PTGS_OK;
+  PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
+               "arguments");
+  hull_kernel<<<(unsigned)n_pairs, kHullThreads, 0, (cudaStream_t)stream>>>(
+      (const float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
+      ratio_threshold, near_eps, area, ratio, keep, flags);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64_t n,
+                        const float* cameras, int32_t cam_first, int32_t cam_count, int32_t* n_hit,
+                        uint8_t* seen, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && cam_first >= 0 && cam_count >= 0 && n_hit, "arguments");
+  PTGS_REQUIRE(aligned16(px) && aligned16(py) && aligned16(pz) && aligned16(cameras),
+               "point / camera arrays must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cam_count > 0) PTGS_CUDA_TRY(cudaMemsetAsync(n_hit, 0, sizeof(int32_t) * cam_count, st));
+  if (seen && n > 0) PTGS_CUDA_TRY(cudaMemsetAsync(seen, 0, (size_t)n, st));
+  if (n == 0 || cam_count == 0) return PTGS_OK;
+  int64_t* ws = nullptr;
+  PTGS_CUDA_TRY(cudaMallocAsync(&ws, 6 * sizeof(int64_t), st));
+  coverage_setup_kernel<<<1, 1, 0, st>>>(n, cam_count, ws, ws + 2);
+  PTGS_LAUNCH_CHECK();
+  // few tiles: split the camera list so that every SM has work
+  const int64_t tiles = (n + kSwTile - 1) / kSwTile;
+  int64_t split = 1;
+  if (tiles < 8 * kNumSMs) split = (8 * kNumSMs + tiles - 1) / tiles;
+  if (split > cam_count) split = cam_count;
+  int rc = schedule(ws, ws + 2, 1, (int32_t)split, ws + 4, st);
+  if (rc) return rc;
+  SweepArgs a = {};
+  a.px = px; a.py = py; a.pz = pz; a.pt_offsets = ws; a.n_blocks = 1;
+  a.cameras = cameras; a.cam_offsets = ws + 2; a.cam_index = nullptr; a.cam_first = cam_first;
+  a.cam_split = (int32_t)split; a.item_prefix = ws + 4;
+  a.n_hit = n_hit; a.seen = seen;
+  rc = launch_sweep<0>(a, st);
+  if (rc) return rc;
+  PTGS_CUDA_TRY(cudaFreeAsync(ws, st));
+  return PTGS_OK;
+}
+
+}  // extern "C"

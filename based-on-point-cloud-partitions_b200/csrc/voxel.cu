@@ -1,0 +1,404 @@
+// libptgs A6: voxel down-sampling of every block in one pass.
+// Reference: downsample_point_cloud, scene/ptgs/shen_partation_densify.py:541-614
+//   min_bound = min(points)                           (:567, per block)
+//   vid       = floor((p - min_bound) / voxel).int32  (:572, point dtype arithmetic)
+//   one output point per occupied voxel = mean of its points, accumulated
+//   sequentially in index order (np.mean(points[idx], axis=0), :588-591),
+//   cast to float32 (:605); voxels in first-occurrence order (:576-581).
+//
+// GPU form: per-block min/max by ordered-key atomics, a packed
+// (block | vx | vy | vz) 64-bit key per CSR entry, one stable LSD radix sort of
+// (key, entry position), segment heads by neighbour compare + scan, and one
+// thread per occupied voxel walking its (tiny) run in entry order so the sum
+// is the same left-to-right float addition the reference performs.  Voxels
+// come out in ascending key order; `ds_first` (position of the voxel's first
+// point inside its block) recovers the reference's first-occurrence order.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace ptgs {
+
+constexpr int kVoxMaxBlocks = 1024;
+
+struct VoxLayout {
+  int32_t bits_b, bits_x, bits_y, bits_z;   // field widths
+  int32_t total_bits;
+  int32_t max_vx, max_vy, max_vz;
+};
+
+template <typename T> struct VoxArith;
+template <> struct VoxArith<float> {
+  __device__ static __forceinline__ long long vid(float p, float mn, float voxel) {
+    // fp32: subtract, IEEE divide, floor, cast (NumPy: f32 array / weak Python float)
+    return (long long)floorf(__fdiv_rn(__fsub_rn(p, mn), voxel));
+  }
+};
+template <> struct VoxArith<double> {
+  __device__ static __forceinline__ long long vid(double p, double mn, double voxel) {
+    return (long long)floor(__ddiv_rn(__dsub_rn(p, mn), voxel));
+  }
+};
+
+__device__ __forceinline__ int find_block(const int64_t* s_off, int L, int64_t e) {
+  int lo = 0, hi = L - 1;  // last b with off[b] <= e
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (s_off[mid] <= e) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ void amin(uint32_t* a, uint32_t v) { atomicMin(a, v); }
+__device__ __forceinline__ void amax(uint32_t* a, uint32_t v) { atomicMax(a, v); }
+__device__ __forceinline__ void amin(uint64_t* a, uint64_t v) { atomicMin((unsigned long long*)a, (unsigned long long)v); }
+__device__ __forceinline__ void amax(uint64_t* a, uint64_t v) { atomicMax((unsigned long long*)a, (unsigned long long)v); }
+
+template <typename K>
+__global__ void vox_init_kernel(K* mm, int L) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < L * 6) mm[i] = ((i % 6) < 3) ? ~K(0) : K(0);
+}
+
+// per block min (slots 0..2) and max (3..5) as ordered keys.
+template <typename T>
+__global__ void __launch_bounds__(256) vox_minmax_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
+    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    int64_t n_entries, int L, typename KeyOf<T>::type* __restrict__ mm) {
+  using K = typename KeyOf<T>::type;
+  __shared__ int64_t s_off[kVoxMaxBlocks + 1];
+  for (int i = threadIdx.x; i <= L; i += blockDim.x) s_off[i] = offsets[i];
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t start = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t e0 = start - threadIdx.x % 32; e0 < n_entries; e0 += stride) {
+    const int64_t e = e0 + (threadIdx.x & 31);
+    const bool valid = e < n_entries;
+    int b = -1;
+    K k[3] = {~K(0), ~K(0), ~K(0)};
+    K kmax[3] = {0, 0, 0};
+    if (valid) {
+      b = find_block(s_off, L, e);
+      const int32_t i = indices[e];
+      k[0] = KeyOf<T>::encode(x[i]); k[1] = KeyOf<T>::encode(y[i]); k[2] = KeyOf<T>::encode(z[i]);
+      kmax[0] = k[0]; kmax[1] = k[1]; kmax[2] = k[2];
+    }
+    const int b0 = __shfl_sync(kFullMask, b, 0);
+    const bool uniform = __all_sync(kFullMask, b == b0 || !valid) && b0 >= 0;
+    if (uniform) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        K lo = k[a], hi = kmax[a];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          K o = __shfl_xor_sync(kFullMask, lo, d); lo = o < lo ? o : lo;
+          K p = __shfl_xor_sync(kFullMask, hi, d); hi = p > hi ? p : hi;
+        }
+        if (lane_id() == 0) { amin(mm + 6 * b0 + a, lo); amax(mm + 6 * b0 + 3 + a, hi); }
+      }
+    } else if (valid) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) { amin(mm + 6 * b + a, k[a]); amax(mm + 6 * b + 3 + a, kmax[a]); }
+    }
+  }
+}
+
+// single CTA: decode per block min, global max voxel index per axis, layout.
+template <typename T>
+__global__ void __launch_bounds__(1024) vox_layout_kernel(
+    const typename KeyOf<T>::type* __restrict__ mm, const int64_t* __restrict__ offsets, int L,
+    double voxel, T* __restrict__ bmin /* [L][3] */, VoxLayout* __restrict__ lay,
+    int32_t* __restrict__ status) {
+  __shared__ long long smax[3];
+  if (threadIdx.x < 3) smax[threadIdx.x] = 0;
+  __syncthreads();
+  for (int b = threadIdx.x; b < L; b += blockDim.x) {
+    const bool empty = offsets[b + 1] == offsets[b];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      T mn = empty ? T(0) : KeyOf<T>::decode(mm[6 * b + a]);
+      T mx = empty ? T(0) : KeyOf<T>::decode(mm[6 * b + 3 + a]);
+      bmin[3 * b + a] = mn;
+      long long v = VoxArith<T>::vid(mx, mn, (T)voxel);
+      if (v < 0) v = 0;
+      atomicMax((unsigned long long*)&smax[a], (unsigned long long)v);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    auto nbits = [](long long v) { int b = 1; while (b < 63 && (v >> b)) ++b; return b; };
+    VoxLayout l;
+    l.bits_b = nbits(L - 1);
+    l.bits_x = nbits(smax[0]); l.bits_y = nbits(smax[1]); l.bits_z = nbits(smax[2]);
+    l.total_bits = l.bits_b + l.bits_x + l.bits_y + l.bits_z;
+    const bool ok = smax[0] < 0x7fffffffll && smax[1] < 0x7fffffffll && smax[2] < 0x7fffffffll &&
+                    l.total_bits <= 64;
+    l.max_vx = (int32_t)min(smax[0], 0x7fffffffll);
+    l.max_vy = (int32_t)min(smax[1], 0x7fffffffll);
+    l.max_vz = (int32_t)min(smax[2], 0x7fffffffll);
+    *lay = l;
+    *status = ok ? PTGS_OK : PTGS_E_RANGE;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) vox_key_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
+    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    int64_t n_entries, int L, const T* __restrict__ bmin, double voxel,
+    const VoxLayout* __restrict__ lay, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  __shared__ int64_t s_off[kVoxMaxBlocks + 1];
+  for (int i = threadIdx.x; i <= L; i += blockDim.x) s_off[i] = offsets[i];
+  __syncthreads();
+  const VoxLayout l = *lay;
+  const T vs = (T)voxel;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
+    const int b = find_block(s_off, L, e);
+    const int32_t i = indices[e];
+    const uint64_t vx = (uint64_t)VoxArith<T>::vid(x[i], bmin[3 * b], vs);
+    const uint64_t vy = (uint64_t)VoxArith<T>::vid(y[i], bmin[3 * b + 1], vs);
+    const uint64_t vz = (uint64_t)VoxArith<T>::vid(z[i], bmin[3 * b + 2], vs);
+    uint64_t k = (uint64_t)b;
+    k = (k << l.bits_x) | vx;
+    k = (k << l.bits_y) | vy;
+    k = (k << l.bits_z) | vz;
+    keys[e] = k;
+    vals[e] = (uint32_t)e;
+  }
+}
+
+constexpr int kHeadTile = 2048;
+
+// head flag = key differs from the predecessor; per tile head counts.
+__global__ void __launch_bounds__(256) vox_head_count_kernel(
+    const uint64_t* __restrict__ keys, int64_t n, int32_t* __restrict__ tile_count) {
+  __shared__ int s[33];
+  const int64_t base = (int64_t)blockIdx.x * kHeadTile;
+  int c = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    if (i < n) c += (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
+  }
+  int tot;
+  block_exclusive_sum<int, 256>(c, s, &tot);
+  if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) vox_scan_tiles_kernel(
+    const int32_t* __restrict__ tile_count, int64_t n_tiles, int64_t* __restrict__ tile_base,
+    int64_t* __restrict__ total) {
+  __shared__ long long s[33];
+  long long carry = 0;
+  for (int64_t start = 0; start < n_tiles; start += 1024) {
+    const int64_t i = start + threadIdx.x;
+    long long v = (i < n_tiles) ? tile_count[i] : 0;
+    long long tot;
+    long long ex = block_exclusive_sum<long long, 1024>(v, s, &tot);
+    if (i < n_tiles) tile_base[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+// one thread per sorted entry; heads walk their run and emit the mean.
+template <typename T>
+__global__ void __launch_bounds__(256) vox_mean_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
+    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
+    int L, const VoxLayout* __restrict__ lay, const int64_t* __restrict__ tile_base,
+    float* __restrict__ ds_x, float* __restrict__ ds_y, float* __restrict__ ds_z,
+    int32_t* __restrict__ ds_first, int64_t* __restrict__ ds_offsets) {
+  __shared__ int s[33];
+  const VoxLayout l = *lay;
+  const int shift_b = l.bits_x + l.bits_y + l.bits_z;
+  const int64_t base = (int64_t)blockIdx.x * kHeadTile;
+  int64_t out = tile_base[blockIdx.x];
+#pragma unroll 1
+  for (int k = 0; k < 8; ++k) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    uint64_t key = 0;
+    int f = 0;
+    bool first_of_block = false;
+    if (i < n) {
+      key = keys[i];
+      if (i == 0) { f = 1; first_of_block = true; }
+      else {
+        const uint64_t prev = keys[i - 1];
+        f = key != prev;
+        first_of_block = (shift_b >= 64 ? 0 : (key >> shift_b)) != (shift_b >= 64 ? 0 : (prev >> shift_b));
+      }
+    }
+    int tot;
+    const int ex = block_exclusive_sum<int, 256>(f, s, &tot);
+    if (f) {
+      const int64_t rank = out + ex;
+      const int b = shift_b >= 64 ? 0 : (int)(key >> shift_b);
+      const uint32_t e0 = vals[i];
+      T sx, sy, sz;
+      {
+        const int32_t p = indices[e0];
+        sx = x[p]; sy = y[p]; sz = z[p];
+      }
+      int64_t j = i + 1;
+      long long cnt = 1;
+      for (; j < n && keys[j] == key; ++j) {
+        const int32_t p = indices[vals[j]];
+        sx = sx + x[p]; sy = sy + y[p]; sz = sz + z[p];   // sequential, entry order
+        ++cnt;
+      }
+      const T c = (T)cnt;
+      ds_x[rank] = (float)(sx / c);
+      ds_y[rank] = (float)(sy / c);
+      ds_z[rank] = (float)(sz / c);
+      ds_first[rank] = (int32_t)((int64_t)e0 - offsets[b]);
+      if (first_of_block) ds_offsets[b] = rank;   // provisional: non-empty blocks only
+    }
+    out += tot;
+  }
+}
+
+// single CTA: fill ds_offsets for empty blocks (monotone back-fill) and [L].
+__global__ void vox_fix_offsets_kernel(const int64_t* __restrict__ offsets, int L,
+                                       const int64_t* __restrict__ total,
+                                       int64_t* __restrict__ ds_offsets) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    int64_t next = *total;
+    ds_offsets[L] = next;
+    for (int b = L - 1; b >= 0; --b) {
+      if (offsets[b + 1] == offsets[b]) ds_offsets[b] = next;
+      else next = ds_offsets[b];
+    }
+  }
+}
+
+static size_t vox_sort_temp_bytes(int64_t n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0, 64);
+  return bytes;
+}
+
+struct VoxWs {
+  void* mm; void* bmin; VoxLayout* lay; uint64_t* keys_a; uint64_t* keys_b;
+  uint32_t* vals_a; uint32_t* vals_b; int32_t* tile_count; int64_t* tile_base; int64_t* total;
+  void* sort_tmp; size_t sort_bytes; int64_t n_tiles; size_t bytes;
+};
+static VoxWs carve_vox(void* ws, int64_t n, int32_t L) {
+  VoxWs v;
+  if (n < 1) n = 1;
+  Carver cv(ws);
+  v.mm = cv.take<uint64_t>((size_t)L * 6);
+  v.bmin = cv.take<double>((size_t)L * 3);
+  v.lay = cv.take<VoxLayout>(1);
+  v.keys_a = cv.take<uint64_t>(n);
+  v.keys_b = cv.take<uint64_t>(n);
+  v.vals_a = cv.take<uint32_t>(n);
+  v.vals_b = cv.take<uint32_t>(n);
+  v.n_tiles = (n + kHeadTile - 1) / kHeadTile;
+  v.tile_count = cv.take<int32_t>(v.n_tiles);
+  v.tile_base = cv.take<int64_t>(v.n_tiles);
+  v.total = cv.take<int64_t>(1);
+  v.sort_bytes = vox_sort_temp_bytes(n);
+  v.sort_tmp = cv.take<char>(v.sort_bytes);
+  v.bytes = cv.used() + 256;
+  return v;
+}
+
+template <typename T>
+static int voxel_impl(const void* vx, const void* vy, const void* vz, const int64_t* offsets,
+                      const int32_t* indices, int64_t n, int32_t L, double voxel,
+                      float* ds_x, float* ds_y, float* ds_z, int32_t* ds_first,
+                      int64_t* ds_offsets, int32_t* status_dev, void* ws, cudaStream_t st) {
+  using K = typename KeyOf<T>::type;
+  const T* x = (const T*)vx; const T* y = (const T*)vy; const T* z = (const T*)vz;
+  VoxWs w = carve_vox(ws, n, L);
+  K* mm = (K*)w.mm;
+  T* bmin = (T*)w.bmin;
+  vox_init_kernel<K><<<(L * 6 + 255) / 256, 256, 0, st>>>(mm, L);
+  PTGS_LAUNCH_CHECK();
+  int64_t g64 = (n + 2047) / 2048;
+  int grid = (int)(g64 < 1 ? 1 : (g64 > kNumSMs * 8 ? kNumSMs * 8 : g64));
+  vox_minmax_kernel<T><<<grid, 256, 0, st>>>(x, y, z, offsets, indices, n, L, mm);
+  PTGS_LAUNCH_CHECK();
+  vox_layout_kernel<T><<<1, 1024, 0, st>>>(mm, offsets, L, voxel, bmin, w.lay, status_dev);
+  PTGS_LAUNCH_CHECK();
+  VoxLayout lay;
+  int32_t status;
+  PTGS_CUDA_TRY(cudaMemcpyAsync(&lay, w.lay, sizeof(lay), cudaMemcpyDeviceToHost, st));
+  PTGS_CUDA_TRY(cudaMemcpyAsync(&status, status_dev, sizeof(status), cudaMemcpyDeviceToHost, st));
+  PTGS_CUDA_TRY(cudaStreamSynchronize(st));
+  if (status != PTGS_OK) {
+    set_error("voxel_downsample: voxel grid does not fit the 64-bit key (bits b/x/y/z = %d/%d/%d/%d)",
+              lay.bits_b, lay.bits_x, lay.bits_y, lay.bits_z);
+    return PTGS_E_RANGE;
+  }
+  vox_key_kernel<T><<<grid, 256, 0, st>>>(x, y, z, offsets, indices, n, L, bmin, voxel, w.lay,
+                                         w.keys_a, w.vals_a);
+  PTGS_LAUNCH_CHECK();
+  PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_bytes, w.keys_a, w.keys_b,
+                                                w.vals_a, w.vals_b, (int64_t)n, 0, lay.total_bits, st));
+  count_launch(2 + (lay.total_bits + 7) / 8);
+  vox_head_count_kernel<<<(unsigned)w.n_tiles, 256, 0, st>>>(w.keys_b, n, w.tile_count);
+  PTGS_LAUNCH_CHECK();
+  vox_scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_count, w.n_tiles, w.tile_base, w.total);
+  PTGS_LAUNCH_CHECK();
+  vox_mean_kernel<T><<<(unsigned)w.n_tiles, 256, 0, st>>>(x, y, z, offsets, indices, w.keys_b, w.vals_b,
+                                                         n, L, w.lay, w.tile_base, ds_x, ds_y, ds_z,
+                                                         ds_first, ds_offsets);
+  PTGS_LAUNCH_CHECK();
+  vox_fix_offsets_kernel<<<1, 32, 0, st>>>(offsets, L, w.total, ds_offsets);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+__global__ void vox_empty_kernel(int64_t* ds_offsets, int L, int32_t* status) {
+  for (int i = threadIdx.x; i <= L; i += blockDim.x) ds_offsets[i] = 0;
+  if (threadIdx.x == 0) *status = PTGS_OK;
+}
+
+}  // namespace ptgs
+
+using namespace ptgs;
+
+extern "C" {
+
+size_t ptgs_voxel_downsample_workspace_bytes(int64_t n_entries, int32_t n_blocks) {
+  if (n_blocks < 1) n_blocks = 1;
+  return carve_vox(nullptr, n_entries, n_blocks).bytes;
+}
+
+int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
+                          const void* z, const int64_t* offsets,
+                          const int32_t* indices, int64_t n_entries,
+                          int32_t n_blocks, double voxel_size, float* ds_x,
+                          float* ds_y, float* ds_z, int32_t* ds_first,
+                          int64_t* ds_offsets, int32_t* status_dev,
+                          void* workspace, size_t workspace_bytes,
+                          ptgs_stream_t stream) {
+  PTGS_REQUIRE(dtype == PTGS_F32 || dtype == PTGS_F64, "dtype");
+  PTGS_REQUIRE(n_entries >= 0 && n_entries < (1ll << 32), "n_entries");
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kVoxMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(voxel_size > 0.0, "voxel_size");
+  PTGS_REQUIRE(offsets && ds_offsets && status_dev, "arguments");
+  if (workspace_bytes < ptgs_voxel_downsample_workspace_bytes(n_entries, n_blocks)) {
+    set_error("voxel_downsample: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_entries == 0) {
+    vox_empty_kernel<<<1, 256, 0, st>>>(ds_offsets, n_blocks, status_dev);
+    PTGS_LAUNCH_CHECK();
+    return PTGS_OK;
+  }
+  if (dtype == PTGS_F32)
+    return voxel_impl<float>(x, y, z, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
+                             ds_z, ds_first, ds_offsets, status_dev, workspace, st);
+  return voxel_impl<double>(x, y, z, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
+                            ds_z, ds_first, ds_offsets, status_dev, workspace, st);
+}
+
+}  // extern "C"

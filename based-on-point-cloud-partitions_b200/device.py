@@ -1,0 +1,481 @@
+"""Device pipeline of the point-count partitioner: thin Python over the C ABI
+(include/ptgs.h).  torch is used for device memory and streams only.
+
+Stages (reference: scene/ptgs/shen_partition_utils.py:57-93, run_DataPartition):
+  A1 radius filter -> A2 bounds -> A3 balanced split -> A4 expansion ->
+  A5 camera assignment -> A6 voxel down-sampling -> A7-A9 visibility/selection.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import PTGS_F32, PTGS_F64, CAMERA_FLOATS, POLY_FLOATS, check
+
+# constants hard-coded by the reference (file:line in DESIGN.md)
+RADIUS, NB_POINTS = 1.0, 5            # shen_partition_utils.py:28-30
+LEAF_FACTOR, MAX_DEPTH = 1.2, 10      # density_partition.py:32, :163
+EXPAND_RATIO = 0.10                   # shen_partation_densify.py:222
+VOXEL_SIZE = 0.1                      # :928
+VISIBLE_RATE = 0.45                   # :930
+MIN_HITS = 3                          # :898
+NEAR_EPS = 1e-6
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def _dt(t):
+    return PTGS_F64 if t.dtype == torch.float64 else PTGS_F32
+
+
+@dataclass
+class VisibilityResult:
+    n_hit: torch.Tensor        # (P,) int32
+    area: torch.Tensor         # (P,) float64
+    ratio: torch.Tensor        # (P,) float64
+    keep: torch.Tensor         # (P,) uint8
+    flags: torch.Tensor        # (P,) uint8
+    cand_count: torch.Tensor   # (P,) int32
+    rounds: int = 1
+
+
+@dataclass
+class PartitionDeviceResult:
+    keep_mask: torch.Tensor            # (N,) uint8 (A1)
+    n_filtered: int
+    root_bounds: tuple
+    leaf_bounds: np.ndarray            # (L,4) float64 {minx,miny,maxx,maxy}
+    leaf_path: np.ndarray
+    leaf_depth: np.ndarray
+    leaf_count: np.ndarray
+    leaf_ids: list
+    boxes: np.ndarray                  # (L,4) float64 expanded {minx,miny,maxx,maxy}
+    pt_offsets: torch.Tensor           # (L+1,) int64, A4 CSR
+    pt_index: torch.Tensor             # int32
+    cam_offsets: torch.Tensor          # (L+1,) int64, A5 CSR
+    cam_index: torch.Tensor
+    ds_offsets: torch.Tensor = None    # A6
+    ds_x: torch.Tensor = None
+    ds_y: torch.Tensor = None
+    ds_z: torch.Tensor = None
+    ds_first: torch.Tensor = None
+    vis: VisibilityResult = None
+    kept_offsets: torch.Tensor = None  # A9 CSR
+    kept_index: torch.Tensor = None
+    timings_ms: dict = field(default_factory=dict)
+
+
+def leaf_id(path: int, depth: int) -> str:
+    """density_partition.py:28/:76/:86: root leaf -> "0"; otherwise the branch
+    bits, left = "0", right = "1", most significant first."""
+    if depth == 0:
+        return "0"
+    return format(int(path), "0%db" % depth)
+
+
+def expanded_boxes(leaf_bounds: np.ndarray) -> np.ndarray:
+    """shen_partation_densify.py:210-232 in Python floats (host, float64)."""
+    out = np.empty((len(leaf_bounds), 4), dtype=np.float64)
+    for i, (minx, miny, maxx, maxy) in enumerate(leaf_bounds.tolist()):
+        ew = (maxx - minx) * EXPAND_RATIO / 2
+        eh = (maxy - miny) * EXPAND_RATIO / 2
+        out[i] = (minx - ew, miny - eh, maxx + ew, maxy + eh)
+    return out
+
+
+# --------------------------------------------------------------------------
+# stage wrappers
+# --------------------------------------------------------------------------
+def aos_to_soa(xyz: torch.Tensor):
+    """(N,3) float32 device tensor -> planar x, y, z (padded for bulk copies)."""
+    lib = _lib.load()
+    assert xyz.is_cuda and xyz.dtype == torch.float32 and xyz.is_contiguous()
+    n = xyz.shape[0]
+    # rows must stay 16-byte aligned: pad the row pitch to a multiple of 4
+    pitch = (n + 8 + 3) // 4 * 4
+    buf = torch.zeros((3, pitch), dtype=torch.float32, device=xyz.device)
+    x, y, z = buf[0, :n], buf[1, :n], buf[2, :n]
+    check(lib.ptgs_aos_to_soa_f32(_ptr(xyz), n, _ptr(x), _ptr(y), _ptr(z), _stream()))
+    return x, y, z
+
+
+def manhattan_apply(x, y, z, man_trans: np.ndarray):
+    lib = _lib.load()
+    n = x.shape[0]
+    m = np.ascontiguousarray(man_trans, dtype=np.float64)
+    pitch = (n + 8 + 1) // 2 * 2
+    buf = torch.zeros((3, pitch), dtype=torch.float64, device=x.device)
+    ox, oy, oz = buf[0, :n], buf[1, :n], buf[2, :n]
+    check(lib.ptgs_manhattan_apply(_ptr(x), _ptr(y), _ptr(z), n,
+                                   m.ctypes.data_as(C.POINTER(C.c_double)), _ptr(ox), _ptr(oy),
+                                   _ptr(oz), _stream()))
+    return ox, oy, oz
+
+
+def radius_outlier_mask(x, y, z, radius=RADIUS, nb_points=NB_POINTS):
+    lib = _lib.load()
+    n = x.shape[0]
+    keep = torch.empty(n, dtype=torch.uint8, device=x.device)
+    n_keep = torch.zeros(1, dtype=torch.int64, device=x.device)
+    ws = _ws(lib.ptgs_radius_outlier_workspace_bytes(n), x.device)
+    check(lib.ptgs_radius_outlier_mask(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, float(radius),
+                                       int(nb_points), _ptr(keep), _ptr(n_keep), _ptr(ws),
+                                       ws.numel(), _stream()))
+    return keep, n_keep
+
+
+def compact_xy(x, y, keep):
+    lib = _lib.load()
+    n = x.shape[0]
+    ox = torch.empty(n, dtype=x.dtype, device=x.device)
+    oy = torch.empty(n, dtype=x.dtype, device=x.device)
+    n_out = torch.zeros(1, dtype=torch.int64, device=x.device)
+    ws = _ws(lib.ptgs_compact_xy_workspace_bytes(n), x.device)
+    check(lib.ptgs_compact_xy(_dt(x), _ptr(x), _ptr(y), _ptr(keep), n, _ptr(ox), _ptr(oy),
+                              _ptr(n_out), _ptr(ws), ws.numel(), _stream()))
+    return ox, oy, n_out
+
+
+def bounds_xy(x, y, n_dev):
+    lib = _lib.load()
+    b = torch.empty(4, dtype=torch.float64, device=x.device)
+    check(lib.ptgs_bounds_xy(_dt(x), _ptr(x), _ptr(y), _ptr(n_dev), x.shape[0], _ptr(b), _stream()))
+    return b
+
+
+def balanced_split(x, y, n_dev, root_bounds, threshold, max_depth=MAX_DEPTH, capacity_factor=1.25):
+    """A3.  Returns host arrays (bounds (L,4) f64, path, depth, count)."""
+    lib = _lib.load()
+    dev = x.device
+    ncap = x.shape[0]
+    max_leaves = 1 << max_depth
+    while True:
+        lb = torch.empty((max_leaves, 4), dtype=torch.float64, device=dev)
+        lp = torch.empty(max_leaves, dtype=torch.int32, device=dev)
+        ld = torch.empty(max_leaves, dtype=torch.int32, device=dev)
+        lc = torch.empty(max_leaves, dtype=torch.int64, device=dev)
+        nl = torch.zeros(1, dtype=torch.int32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        ws = _ws(lib.ptgs_balanced_split_workspace_bytes(_dt(x), ncap, capacity_factor, max_depth), dev)
+        check(lib.ptgs_balanced_split(_dt(x), _ptr(x), _ptr(y), _ptr(n_dev), ncap, _ptr(root_bounds),
+                                      float(threshold * LEAF_FACTOR), int(max_depth),
+                                      float(capacity_factor), _ptr(lb), _ptr(lp), _ptr(ld), _ptr(lc),
+                                      _ptr(nl), max_leaves, _ptr(status), _ptr(ws), ws.numel(),
+                                      _stream()))
+        st = int(status.item())
+        if st == _lib.PTGS_E_CAPACITY and capacity_factor < 64:
+            capacity_factor *= 2          # many points on split lines: duplicates grow the level
+            continue
+        if st != 0:
+            raise _lib.PtgsError(st, "balanced_split device status")
+        L = int(nl.item())
+        return (lb[:L].cpu().numpy(), lp[:L].cpu().numpy().astype(np.uint32),
+                ld[:L].cpu().numpy(), lc[:L].cpu().numpy())
+
+
+def expand_select(x, y, boxes: np.ndarray):
+    """A4.  boxes (L,4) float64 {minx,miny,maxx,maxy}; the bounds are rounded
+    to the cloud's dtype exactly as NumPy does for `f32_array >= python_float`
+    (shen_partation_densify.py:201-202)."""
+    lib = _lib.load()
+    dev = x.device
+    n, L = x.shape[0], len(boxes)
+    npdt = np.float64 if x.dtype == torch.float64 else np.float32
+    rects = np.stack([boxes[:, 0], boxes[:, 2], boxes[:, 1], boxes[:, 3]], axis=1).astype(npdt)
+    rects_d = torch.from_numpy(np.ascontiguousarray(rects)).to(dev)
+    counts = torch.empty(L, dtype=torch.int64, device=dev)
+    ws = _ws(lib.ptgs_expand_workspace_bytes(n, L), dev)
+    check(lib.ptgs_expand_count(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
+                                _ptr(ws), ws.numel(), _stream()))
+    total = int(counts.sum().item())
+    offsets = torch.empty(L + 1, dtype=torch.int64, device=dev)
+    indices = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+    check(lib.ptgs_expand_fill(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
+                               _ptr(offsets), _ptr(indices), total, _ptr(ws), ws.numel(), _stream()))
+    return offsets, indices[:total]
+
+
+def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device):
+    """A5.  centers (C,3) (float32 values widened to float64), boxes (L,4) f64."""
+    lib = _lib.load()
+    Cn, L = len(centers), len(boxes)
+    cen = torch.from_numpy(np.ascontiguousarray(centers, dtype=np.float64)).to(device)
+    bx = torch.from_numpy(np.ascontiguousarray(boxes, dtype=np.float64)).to(device)
+    offsets = torch.empty(L + 1, dtype=torch.int64, device=device)
+    cap = max(Cn * L, 1)
+    index = torch.empty(cap, dtype=torch.int32, device=device)
+    check(lib.ptgs_assign_cameras(_ptr(cen), Cn, _ptr(bx), L, _ptr(offsets), _ptr(index), cap, _stream()))
+    total = int(offsets[L].item())
+    return offsets, index[:total].clone()
+
+
+def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE):
+    """A6 over every block at once.  Voxels of a block come out in ascending
+    (vx,vy,vz) order; ds_first gives the reference's first-occurrence order."""
+    lib = _lib.load()
+    dev = x.device
+    L = offsets.shape[0] - 1
+    ne = indices.shape[0]
+    pitch = (ne + 8 + 3) // 4 * 4
+    buf = torch.zeros((3, pitch), dtype=torch.float32, device=dev)
+    ds_first = torch.empty(max(ne, 1), dtype=torch.int32, device=dev)
+    ds_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = _ws(lib.ptgs_voxel_downsample_workspace_bytes(ne, L), dev)
+    check(lib.ptgs_voxel_downsample(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(offsets), _ptr(indices),
+                                    ne, L, float(voxel), _ptr(buf[0]), _ptr(buf[1]), _ptr(buf[2]),
+                                    _ptr(ds_first), _ptr(ds_off), _ptr(status), _ptr(ws), ws.numel(),
+                                    _stream()))
+    m = int(ds_off[L].item())
+    return ds_off, buf[0, :m], buf[1, :m], buf[2, :m], ds_first[:m]
+
+
+def camera_records(R, T, FoVx, FoVy, width, height, front_axis=1) -> np.ndarray:
+    """(C,20) float32 camera records (include/ptgs.h) from the SimpleCamera
+    fields, using the same Python expressions as shen_partation_densify.py:
+    433-434 (float32 casts of R, T) and :457-461 (fx, fy, cx, cy in Python
+    floats, then float32)."""
+    import math
+    Cn = len(R)
+    rec = np.zeros((Cn, CAMERA_FLOATS), dtype=np.float32)
+    rec[:, 0:9] = np.asarray(R, dtype=np.float64).reshape(Cn, 9).astype(np.float32)
+    rec[:, 9:12] = np.asarray(T, dtype=np.float64).reshape(Cn, 3).astype(np.float32)
+    for i in range(Cn):
+        w, h = int(width[i]), int(height[i])
+        rec[i, 12] = np.float32(w / (2 * math.tan(float(FoVx[i]) / 2)))
+        rec[i, 13] = np.float32(h / (2 * math.tan(float(FoVy[i]) / 2)))
+        rec[i, 14] = np.float32(w / 2)
+        rec[i, 15] = np.float32(h / 2)
+        rec[i, 16] = np.float32(w)
+        rec[i, 17] = np.float32(h)
+    rec[:, 18] = np.float32(front_axis)
+    return rec
+
+
+def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
+    """Camera-list split factor of the sweep: enough work items for 148 SMs x 2
+    CTAs when there are few point tiles.  Results do not depend on it."""
+    tiles = max(1, (int(n_points_total) + 2047) // 2048 + n_blocks)
+    want = 148 * 2 * 4
+    return max(1, min(64, (want + tiles - 1) // tiles))
+
+
+def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
+               threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
+               cand_capacity=256, cam_split=None) -> VisibilityResult:
+    """A7-A9 for every (block, camera) pair: sweep 1 (counts, pivot, extremes),
+    inner polygons, sweep 2 (hull candidates), exact hull area, keep decision."""
+    lib = _lib.load()
+    dev = cameras_d.device
+    L = ds_offsets.shape[0] - 1
+    P = int(cam_index.shape[0])
+    n_hit = torch.empty(max(P, 1), dtype=torch.int32, device=dev)
+    pivot = torch.empty(max(P, 1), dtype=torch.int64, device=dev)
+    extreme = torch.empty(max(P, 1) * 8, dtype=torch.int64, device=dev)
+    cand_count = torch.empty(max(P, 1), dtype=torch.int32, device=dev)
+    area = torch.zeros(max(P, 1), dtype=torch.float64, device=dev)
+    ratio = torch.zeros(max(P, 1), dtype=torch.float64, device=dev)
+    keep = torch.zeros(max(P, 1), dtype=torch.uint8, device=dev)
+    flags = torch.zeros(max(P, 1), dtype=torch.uint8, device=dev)
+    if P == 0:
+        return VisibilityResult(n_hit[:0], area[:0], ratio[:0], keep[:0], flags[:0], cand_count[:0], 0)
+    if cam_split is None:
+        cam_split = pick_cam_split(int(ds_x.shape[0]), L)
+    ws = _ws(lib.ptgs_visibility_workspace_bytes(L), dev)
+    st = _stream()
+    check(lib.ptgs_visibility_init(P, _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(cand_count), st))
+    check(lib.ptgs_visibility_count(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
+                                    _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), cam_split,
+                                    _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(ws), ws.numel(), st))
+    poly = torch.empty((P, POLY_FLOATS), dtype=torch.float32, device=dev)
+    check(lib.ptgs_visibility_polygon(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
+                                      _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), _ptr(n_hit),
+                                      _ptr(pivot), _ptr(extreme), P, _ptr(poly), st))
+    caps = torch.full((P,), int(cand_capacity), dtype=torch.int64, device=dev)
+    rounds = 0
+    while True:
+        rounds += 1
+        cand_off = torch.zeros(P + 1, dtype=torch.int64, device=dev)
+        torch.cumsum(caps, 0, out=cand_off[1:])
+        total = int(cand_off[P].item())
+        cand_uv = torch.empty((max(total, 1), 2), dtype=torch.float32, device=dev)
+        check(lib.ptgs_visibility_init(P, None, None, None, _ptr(cand_count), st))
+        check(lib.ptgs_visibility_candidates(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
+                                             _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
+                                             cam_split, _ptr(poly), _ptr(cand_off), _ptr(cand_uv),
+                                             _ptr(cand_count), _ptr(ws), ws.numel(), st))
+        check(lib.ptgs_visibility_hull(_ptr(cand_uv), _ptr(cand_off), _ptr(cand_count), _ptr(n_hit), P,
+                                       _ptr(cam_index), _ptr(cameras_d), int(min_hits),
+                                       float(threshold), float(near_eps), _ptr(area), _ptr(ratio),
+                                       _ptr(keep), _ptr(flags), st))
+        over = cand_count.to(torch.int64) > caps
+        if not bool(over.any().item()):
+            break
+        if rounds > 3:
+            raise RuntimeError("visibility: candidate capacity did not converge")
+        # exact need is known (cand_count keeps counting past the capacity)
+        caps = torch.where(over, cand_count.to(torch.int64), torch.clamp(cand_count.to(torch.int64), min=1))
+    if bool((flags & 8).any().item()):
+        raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
+    return VisibilityResult(n_hit, area, ratio, keep, flags, cand_count, rounds)
+
+
+def select_cameras(keep, cam_offsets, cam_index):
+    lib = _lib.load()
+    dev = cam_offsets.device
+    L = cam_offsets.shape[0] - 1
+    kept_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
+    kept_idx = torch.empty(max(int(cam_index.shape[0]), 1), dtype=torch.int32, device=dev)
+    check(lib.ptgs_select_cameras(_ptr(keep), _ptr(cam_offsets), _ptr(cam_index), L, _ptr(kept_off),
+                                  _ptr(kept_idx), _stream()))
+    n = int(kept_off[L].item())
+    return kept_off, kept_idx[:n]
+
+
+def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen=False):
+    """Config 5 / Vast-style coverage: every point against cameras
+    [cam_first, cam_first + cam_count)."""
+    lib = _lib.load()
+    dev = px.device
+    if cam_count is None:
+        cam_count = cameras_d.shape[0] - cam_first
+    n = px.shape[0]
+    n_hit = torch.empty(max(cam_count, 1), dtype=torch.int32, device=dev)
+    seen = torch.empty(max(n, 1), dtype=torch.uint8, device=dev) if want_seen else None
+    check(lib.ptgs_coverage_sweep(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(cameras_d), int(cam_first),
+                                  int(cam_count), _ptr(n_hit), _ptr(seen), _stream()))
+    return (n_hit[:cam_count], seen[:n]) if want_seen else n_hit[:cam_count]
+
+
+class _Timer:
+    """CUDA-event stage timer on the current stream."""
+
+    def __init__(self, enabled):
+        self.enabled = enabled
+        self.marks = []
+
+    def mark(self, name):
+        if self.enabled:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.marks.append((name, e))
+
+    def result(self):
+        if not self.enabled or len(self.marks) < 2:
+            return {}
+        torch.cuda.synchronize()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self.marks[:-1], self.marks[1:]):
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        out["total"] = self.marks[0][1].elapsed_time(self.marks[-1][1])
+        return out
+
+
+def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np.ndarray,
+                     threshold: int, man_trans: np.ndarray | None = None, radius_filter: bool = True,
+                     do_visibility: bool = True, time_stages: bool = False,
+                     cam_shard: tuple | None = None, split_xyz: torch.Tensor | None = None
+                     ) -> PartitionDeviceResult:
+    """run_DataPartition (shen_partition_utils.py:57-93) on the device.
+
+    xyz         (N,3) float32 CUDA tensor: the scene cloud as fetchPly returns it.
+    cam_records (C,20) float32 host array (camera_records()).
+    cam_centers (C,3) host array, SimpleCamera.camera_center (float32 values).
+    man_trans   optional 4x4: the cloud is rotated first (float64 from there on);
+                the caller passes camera records / centres already in that frame.
+    split_xyz   optional (N,3) float32 tensor used for A1-A3 instead of `xyz`
+                (the reference's literal shen-path behaviour under man_trans:
+                the split reads the un-rotated PLY, shen_partition_utils.py:62).
+    cam_shard   (rank, world): this process evaluates only cameras
+                c % world == rank in the visibility pass (multi-GPU).
+    """
+    assert xyz.is_cuda
+    dev = xyz.device
+    tm = _Timer(time_stages)
+    tm.mark("start")
+    x, y, z = aos_to_soa(xyz)
+    if man_trans is not None:
+        x, y, z = manhattan_apply(x, y, z, man_trans)
+    tm.mark("layout")
+    if split_xyz is not None:
+        sx, sy, sz = aos_to_soa(split_xyz)
+    else:
+        sx, sy, sz = x, y, z
+    n = sx.shape[0]
+    if radius_filter:
+        keep_mask, n_keep = radius_outlier_mask(sx, sy, sz)
+    else:
+        keep_mask = torch.ones(n, dtype=torch.uint8, device=dev)
+        n_keep = torch.full((1,), n, dtype=torch.int64, device=dev)
+    tm.mark("A1_radius")
+    fx, fy, n_f = compact_xy(sx, sy, keep_mask)
+    root = bounds_xy(fx, fy, n_f)
+    tm.mark("A2_bounds")
+    lb, lp, ld, lc = balanced_split(fx, fy, n_f, root, threshold)
+    tm.mark("A3_split")
+    del fx, fy
+    boxes = expanded_boxes(lb)
+    pt_off, pt_idx = expand_select(x, y, boxes)
+    tm.mark("A4_expand")
+    cam_off, cam_idx = assign_cameras(cam_centers, boxes, dev)
+    if cam_shard is not None:
+        cam_off, cam_idx = shard_cameras(cam_off, cam_idx, *cam_shard)
+    tm.mark("A5_assign")
+    res = PartitionDeviceResult(
+        keep_mask=keep_mask, n_filtered=int(n_f.item()), root_bounds=tuple(root.cpu().tolist()),
+        leaf_bounds=lb, leaf_path=lp, leaf_depth=ld, leaf_count=lc,
+        leaf_ids=[leaf_id(p, d) for p, d in zip(lp.tolist(), ld.tolist())], boxes=boxes,
+        pt_offsets=pt_off, pt_index=pt_idx, cam_offsets=cam_off, cam_index=cam_idx)
+    if do_visibility:
+        ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx)
+        tm.mark("A6_voxel")
+        cams_d = torch.from_numpy(np.ascontiguousarray(cam_records, dtype=np.float32)).to(dev)
+        vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx)
+        tm.mark("A7_A8_visibility")
+        k_off, k_idx = select_cameras(vis.keep, cam_off, cam_idx)
+        tm.mark("A9_select")
+        res.ds_offsets, res.ds_x, res.ds_y, res.ds_z, res.ds_first = ds_off, dx, dy, dz, dfirst
+        res.vis, res.kept_offsets, res.kept_index = vis, k_off, k_idx
+    res.timings_ms = tm.result()
+    return res
+
+
+def shard_cameras(cam_off: torch.Tensor, cam_idx: torch.Tensor, rank: int, world: int):
+    """Keeps the cameras c % world == rank of every block's list (order kept)."""
+    if world <= 1:
+        return cam_off, cam_idx
+    L = cam_off.shape[0] - 1
+    mine = (cam_idx % world) == rank
+    seg = torch.repeat_interleave(torch.arange(L, device=cam_off.device),
+                                  (cam_off[1:] - cam_off[:-1]))
+    counts = torch.zeros(L, dtype=torch.int64, device=cam_off.device)
+    counts.index_add_(0, seg[mine], torch.ones(int(mine.sum().item()), dtype=torch.int64,
+                                               device=cam_off.device))
+    new_off = torch.zeros(L + 1, dtype=torch.int64, device=cam_off.device)
+    torch.cumsum(counts, 0, out=new_off[1:])
+    return new_off, cam_idx[mine].contiguous()
+
+
+def camera_centers(R, T) -> np.ndarray:
+    """SimpleCamera.camera_center (scene/cameras.py:56-58): -R^T T evaluated by
+    torch in float32 on the CPU, one camera at a time like the reference."""
+    out = np.empty((len(R), 3), dtype=np.float32)
+    for i in range(len(R)):
+        Rt = torch.tensor(np.asarray(R[i]), dtype=torch.float32)
+        Tt = torch.tensor(np.asarray(T[i]), dtype=torch.float32)
+        out[i] = (-torch.matmul(Rt.transpose(0, 1), Tt)).numpy()
+    return out

@@ -158,7 +158,8 @@ int ptgs_expand_count(int dtype, const void* x, const void* y, int64_t n,
                       void* workspace, size_t workspace_bytes,
                       ptgs_stream_t stream);
 int ptgs_expand_fill(int dtype, const void* x, const void* y, int64_t n,
-                     const void* rects, int32_t n_blocks, int64_t* offsets,
+                     const void* rects, int32_t n_blocks,
+                     const int64_t* counts, int64_t* offsets,
                      int32_t* indices, int64_t indices_capacity,
                      void* workspace, size_t workspace_bytes,
                      ptgs_stream_t stream);
@@ -225,43 +226,81 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  * ------------------------------------------------------------------ */
 #define PTGS_CAMERA_FLOATS 20
 
-/* Sweep: every point of block b against every camera listed for block b.
- * pair p = cam_offsets[b] + (position of the camera in the block's list).
- * Hits are appended to rec_{u,v,pair} (capacity rec_capacity); *n_records
- * (device int64) receives the TOTAL number of hits even when it exceeds the
- * capacity (the caller then re-runs with a larger buffer).
- * coord_absmax: max |coordinate| over the points (for the conservative
- * pre-filter slack).  */
-size_t ptgs_visibility_sweep_workspace_bytes(int32_t n_blocks);
-int ptgs_visibility_sweep(const float* px, const float* py, const float* pz,
+/* The visibility pass is two sweeps over the same (block, camera) pairs plus a
+ * per-pair hull.  pair p = cam_offsets[b] + (position of the camera in block
+ * b's list).  Point arrays px/py/pz hold every block's down-sampled points
+ * back to back (pt_offsets[L+1]); they must be 16-byte aligned and readable up
+ * to the next multiple of 4 elements past pt_offsets[L] (the tiles are staged
+ * with 16-byte granular bulk copies).
+ *
+ * Sweep 1 (ptgs_visibility_count): per pair
+ *   n_hit[p]   int32   number of in-image points (len(image_points), :898)
+ *   pivot[p]   uint64  (bits(v) << 32 | bits(u)) of the Graham pivot: lowest v,
+ *                      then lowest u (:509-511); ~0 when n_hit == 0
+ *   extreme[p][8] uint64  (ordered key << 32 | point position inside the block)
+ *                      of the extreme hit along the 8 directions
+ *                      +u, +(u+v), +v, +(v-u), -u, -(u+v), -v, +(u-v); 0 = none.
+ * All three are accumulated with atomics and must be pre-initialised by
+ * ptgs_visibility_init (also zeroes cand_count).
+ *
+ * ptgs_visibility_polygon: per pair the inner polygon (the extreme hits that
+ * survive the reference's pivot-row rule, see below) as <= 8 half planes.
+ *
+ * Sweep 2 (ptgs_visibility_candidates): re-projects and emits every hit that
+ * is (a) part of the point set the reference's scan effectively uses -- the
+ * pivot plus all hits with v > v_pivot: hits on the pivot's row are popped by
+ * the `cross <= 0` rule and the farthest of them is skipped by
+ * `sorted_points[1:]` (:513-527) -- and (b) not strictly inside the inner
+ * polygon.  cand_uv[cand_offsets[p] + k] (float2, k < capacity of the pair);
+ * cand_count[p] receives the number of candidates even when it exceeds the
+ * pair's capacity (the caller then re-runs the pair with a larger capacity).
+ *
+ * ptgs_visibility_hull: exact convex hull (float64 orientation tests with the
+ * reference's `cross <= 0` pop rule) of each pair's candidates, shoelace area
+ * in float64, ratio = area / (W*H); keep = n_hit > min_hits && ratio >= thr.
+ * flags: bit0 = |ratio - thr| <= near_eps; bit1 = another hit lies exactly on
+ * the first hull edge after the pivot (the one configuration in which the
+ * reference's result depends on libm atan2 ties); bit2 = candidate capacity
+ * overflow (result invalid, re-run); bit3 = hull larger than the kernel's
+ * vertex budget (result invalid).
+ * cam_split >= 1 splits every block's camera list into that many work items
+ * per point tile (load balance for small inputs); results do not depend on it.
+ */
+size_t ptgs_visibility_workspace_bytes(int32_t n_blocks);
+int ptgs_visibility_init(int64_t n_pairs, int32_t* n_hit, uint64_t* pivot,
+                         uint64_t* extreme, int32_t* cand_count,
+                         ptgs_stream_t stream);
+int ptgs_visibility_count(const float* px, const float* py, const float* pz,
                           const int64_t* pt_offsets, int32_t n_blocks,
                           const float* cameras, const int64_t* cam_offsets,
-                          const int32_t* cam_index, float coord_absmax,
-                          float* rec_u, float* rec_v, uint32_t* rec_pair,
-                          int64_t rec_capacity, int64_t* n_records,
+                          const int32_t* cam_index, int32_t cam_split,
+                          int32_t* n_hit, uint64_t* pivot, uint64_t* extreme,
                           void* workspace, size_t workspace_bytes,
                           ptgs_stream_t stream);
-
-/* Group the hit records by pair (counting sort): n_hit[n_pairs] (int32),
- * hit_offsets[n_pairs+1] (int64), hits_uv[n_records] (float2). */
-size_t ptgs_group_hits_workspace_bytes(int64_t n_pairs);
-int ptgs_group_hits(const float* rec_u, const float* rec_v,
-                    const uint32_t* rec_pair, int64_t n_records,
-                    int64_t n_pairs, int32_t* n_hit, int64_t* hit_offsets,
-                    float* hits_uv, void* workspace, size_t workspace_bytes,
-                    ptgs_stream_t stream);
-
-/* Hull area + keep decision per pair.  hits_uv is used as scratch (permuted).
- * pair_cam[n_pairs]: camera index of each pair (to fetch W,H).
- * area[n_pairs] float64 (reference Graham-scan semantics incl. its tie
- * handling), ratio = area / (W*H); keep = n_hit > min_hits && ratio >= thr;
- * near = |ratio - thr| <= near_eps. */
-int ptgs_hull_select(float* hits_uv, const int64_t* hit_offsets,
-                     const int32_t* n_hit, int64_t n_pairs,
-                     const int32_t* pair_cam, const float* cameras,
-                     int32_t min_hits, double ratio_threshold,
-                     double near_eps, double* area, double* ratio,
-                     uint8_t* keep, uint8_t* near, ptgs_stream_t stream);
+#define PTGS_POLY_FLOATS 28 /* [0]=n_edges [1]=v_pivot [2]=u_pivot [3]=margin, 8 x (a,b,c) */
+int ptgs_visibility_polygon(const float* px, const float* py, const float* pz,
+                            const int64_t* pt_offsets, int32_t n_blocks,
+                            const float* cameras, const int64_t* cam_offsets,
+                            const int32_t* cam_index, const int32_t* n_hit,
+                            const uint64_t* pivot, const uint64_t* extreme,
+                            int64_t n_pairs, float* poly,
+                            ptgs_stream_t stream);
+int ptgs_visibility_candidates(const float* px, const float* py,
+                               const float* pz, const int64_t* pt_offsets,
+                               int32_t n_blocks, const float* cameras,
+                               const int64_t* cam_offsets,
+                               const int32_t* cam_index, int32_t cam_split,
+                               const float* poly, const int64_t* cand_offsets,
+                               float* cand_uv, int32_t* cand_count,
+                               void* workspace, size_t workspace_bytes,
+                               ptgs_stream_t stream);
+int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
+                         const int32_t* cand_count, const int32_t* n_hit,
+                         int64_t n_pairs, const int32_t* pair_cam,
+                         const float* cameras, int32_t min_hits,
+                         double ratio_threshold, double near_eps, double* area,
+                         double* ratio, uint8_t* keep, uint8_t* flags,
+                         ptgs_stream_t stream);
 
 /* A9 selection: per block compaction of the kept cameras (ascending order of
  * the block's camera list).  kept_offsets[L+1] int64, kept_index capacity =
@@ -280,8 +319,8 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
  * ------------------------------------------------------------------ */
 int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         int64_t n, const float* cameras, int32_t cam_first,
-                        int32_t cam_count, float coord_absmax, int32_t* n_hit,
-                        uint8_t* seen, ptgs_stream_t stream);
+                        int32_t cam_count, int32_t* n_hit, uint8_t* seen,
+                        ptgs_stream_t stream);
 
 #ifdef __cplusplus
 }

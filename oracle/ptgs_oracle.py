@@ -290,7 +290,7 @@ def _fma32(a, b, c):
 
 def project_port(points, rec):
     """densify:429-471 in the arithmetic libptgs fixes (include/ptgs.h,
-    "One test"): float32, camera space by an FMA chain, IEEE division.
+    "One test"): float32, camera space by the SGEMM's FMA chain, IEEE division.
     Returns (hit mask over ALL points, u, v) -- u,v valid where hit."""
     p = np.asarray(points, dtype=np.float32)
     x, y, z = p[:, 0], p[:, 1], p[:, 2]
@@ -298,9 +298,13 @@ def project_port(points, rec):
     f = np.float32
 
     def row(i):
-        acc = _fma32(np.full_like(x, r[3 * i]), x, np.full_like(x, r[9 + i]))
+        # k-ordered accumulation of the 4x4 @ 4xN SGEMM (densify:444): r0*x,
+        # fma r1*y, fma r2*z, then + t (fma(t, 1, acc) is a plain add).  Checked
+        # bit-identical to torch's CPU matmul (tests/test_oracle_vs_reference.py).
+        acc = np.full_like(x, r[3 * i]) * x
         acc = _fma32(np.full_like(x, r[3 * i + 1]), y, acc)
-        return _fma32(np.full_like(x, r[3 * i + 2]), z, acc)
+        acc = _fma32(np.full_like(x, r[3 * i + 2]), z, acc)
+        return acc + np.full_like(x, r[9 + i])
     X, Y, Z = row(0), row(1), row(2)
     front = (Y > 0) if r[18] == f(1.0) else (Z > 0)
     with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
