@@ -210,7 +210,7 @@ int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
                              ptgs_stream_t stream) {
   PTGS_REQUIRE(n >= 0 && n < (1ll << 32), "n");
   PTGS_REQUIRE(radius > 0.0 && nb_points >= 0, "radius / nb_points");
-  PTGS_REQUIRE(keep && n_keep, "outputs");
+  PTGS_REQUIRE(n_keep && (keep || n == 0), "outputs");
   if (n == 0) {
     PTGS_CUDA_TRY(cudaMemsetAsync(n_keep, 0, 8, (cudaStream_t)stream));
     return PTGS_OK;
