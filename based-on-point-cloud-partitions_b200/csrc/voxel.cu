@@ -238,10 +238,12 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
       const int64_t rank = out + ex;
       const int b = shift_b >= 64 ? 0 : (int)(key >> shift_b);
       const uint32_t e0 = vals[i];
+      // np.add.reduce over axis 0 starts from the identity +0.0, so a voxel
+      // whose members are all -0.0 averages to +0.0
       T sx, sy, sz;
       {
         const int32_t p = indices[e0];
-        sx = x[p]; sy = y[p]; sz = z[p];
+        sx = T(0) + x[p]; sy = T(0) + y[p]; sz = T(0) + z[p];
       }
       int64_t j = i + 1;
       long long cnt = 1;
