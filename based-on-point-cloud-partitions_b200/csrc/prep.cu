@@ -44,6 +44,31 @@ __global__ void __launch_bounds__(256) aos_to_soa_kernel(
   }
 }
 
+// float64 rows (Manhattan-rotated clouds): 24-byte rows, one double2 + one
+// double load per point would misalign every other row, so each thread moves
+// 2 points = 3 aligned double2 loads.
+__global__ void __launch_bounds__(256) aos_to_soa_f64_kernel(
+    const double* __restrict__ xyz, int64_t n, double* __restrict__ x,
+    double* __restrict__ y, double* __restrict__ z) {
+  const int64_t n2 = n / 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const double2* in = reinterpret_cast<const double2*>(xyz);
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n2;
+       g += stride) {
+    const double2 a = __ldg(in + 3 * g), b = __ldg(in + 3 * g + 1),
+                  c = __ldg(in + 3 * g + 2);
+    reinterpret_cast<double2*>(x)[g] = make_double2(a.x, b.y);
+    reinterpret_cast<double2*>(y)[g] = make_double2(a.y, c.x);
+    reinterpret_cast<double2*>(z)[g] = make_double2(b.x, c.y);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
+    const int64_t i = n - 1;
+    x[i] = xyz[3 * i];
+    y[i] = xyz[3 * i + 1];
+    z[i] = xyz[3 * i + 2];
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Manhattan transform, f32 -> f64 (k-ordered fma accumulation, then + T).
 // ---------------------------------------------------------------------------
@@ -242,6 +267,19 @@ int ptgs_aos_to_soa_f32(const float* xyz, int64_t n, float* x, float* y,
                "pointers must be 16-byte aligned");
   int grid = grid_for(n / 4 + 1, 256, kNumSMs * 8);
   aos_to_soa_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz, n, x, y, z);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_aos_to_soa_f64(const double* xyz, int64_t n, double* x, double* y,
+                        double* z, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0, "n");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(((uintptr_t)xyz % 16 == 0) && ((uintptr_t)x % 16 == 0) &&
+                   ((uintptr_t)y % 16 == 0) && ((uintptr_t)z % 16 == 0),
+               "pointers must be 16-byte aligned");
+  int grid = grid_for(n / 2 + 1, 256, kNumSMs * 8);
+  aos_to_soa_f64_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz, n, x, y, z);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
     K kmax[3] = {0, 0, 0};
     if (valid) {
       b = find_block(s_off, L, e);
-      const int32_t i = indices[e];
+      const int32_t i = indices ? indices[e] : (int32_t)e;
       k[0] = KeyOf<T>::encode(x[i]); k[1] = KeyOf<T>::encode(y[i]); k[2] = KeyOf<T>::encode(z[i]);
       kmax[0] = k[0]; kmax[1] = k[1]; kmax[2] = k[2];
     }
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
     const int b = find_block(s_off, L, e);
-    const int32_t i = indices[e];
+    const int32_t i = indices ? indices[e] : (int32_t)e;
     const uint64_t vx = (uint64_t)VoxArith<T>::vid(x[i], bmin[3 * b], vs);
     const uint64_t vy = (uint64_t)VoxArith<T>::vid(y[i], bmin[3 * b + 1], vs);
     const uint64_t vz = (uint64_t)VoxArith<T>::vid(z[i], bmin[3 * b + 2], vs);
@@ -242,13 +242,13 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
       // whose members are all -0.0 averages to +0.0
       T sx, sy, sz;
       {
-        const int32_t p = indices[e0];
+        const int32_t p = indices ? indices[e0] : (int32_t)e0;
         sx = T(0) + x[p]; sy = T(0) + y[p]; sz = T(0) + z[p];
       }
       int64_t j = i + 1;
       long long cnt = 1;
       for (; j < n && keys[j] == key; ++j) {
-        const int32_t p = indices[vals[j]];
+        const int32_t p = indices ? indices[vals[j]] : (int32_t)vals[j];
         sx = sx + x[p]; sy = sy + y[p]; sz = sz + z[p];   // sequential, entry order
         ++cnt;
       }

@@ -103,13 +103,14 @@ def expanded_boxes(leaf_bounds: np.ndarray) -> np.ndarray:
 def aos_to_soa(xyz: torch.Tensor):
     """(N,3) float32 device tensor -> planar x, y, z (padded for bulk copies)."""
     lib = _lib.load()
-    assert xyz.is_cuda and xyz.dtype == torch.float32 and xyz.is_contiguous()
+    assert xyz.is_cuda and xyz.dtype in (torch.float32, torch.float64) and xyz.is_contiguous()
     n = xyz.shape[0]
     # rows must stay 16-byte aligned: pad the row pitch to a multiple of 4
     pitch = (n + 8 + 3) // 4 * 4
-    buf = torch.zeros((3, pitch), dtype=torch.float32, device=xyz.device)
+    buf = torch.zeros((3, pitch), dtype=xyz.dtype, device=xyz.device)
     x, y, z = buf[0, :n], buf[1, :n], buf[2, :n]
-    check(lib.ptgs_aos_to_soa_f32(_ptr(xyz), n, _ptr(x), _ptr(y), _ptr(z), _stream()))
+    fn = lib.ptgs_aos_to_soa_f32 if xyz.dtype == torch.float32 else lib.ptgs_aos_to_soa_f64
+    check(fn(_ptr(xyz), n, _ptr(x), _ptr(y), _ptr(z), _stream()))
     return x, y, z
 
 
@@ -223,13 +224,13 @@ def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device):
     return offsets, index[:total].clone()
 
 
-def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE):
+def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None):
     """A6 over every block at once.  Voxels of a block come out in ascending
     (vx,vy,vz) order; ds_first gives the reference's first-occurrence order."""
     lib = _lib.load()
     dev = x.device
     L = offsets.shape[0] - 1
-    ne = indices.shape[0]
+    ne = indices.shape[0] if indices is not None else int(n_entries)
     pitch = (ne + 8 + 3) // 4 * 4
     buf = torch.zeros((3, pitch), dtype=torch.float32, device=dev)
     ds_first = torch.empty(max(ne, 1), dtype=torch.int32, device=dev)
@@ -276,7 +277,7 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
-               cand_capacity=256, cam_split=None) -> VisibilityResult:
+               cand_capacity=256, cam_split=None, timer=None) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair: sweep 1 (counts, pivot, extremes),
     inner polygons, sweep 2 (hull candidates), exact hull area, keep decision."""
     lib = _lib.load()
@@ -297,14 +298,18 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         cam_split = pick_cam_split(int(ds_x.shape[0]), L)
     ws = _ws(lib.ptgs_visibility_workspace_bytes(L), dev)
     st = _stream()
+    mark = timer.mark if timer is not None else (lambda name: None)
     check(lib.ptgs_visibility_init(P, _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(cand_count), st))
+    mark("vis_init")
     check(lib.ptgs_visibility_count(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                     _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), cam_split,
                                     _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(ws), ws.numel(), st))
+    mark("vis_sweep1_count")
     poly = torch.empty((P, POLY_FLOATS), dtype=torch.float32, device=dev)
     check(lib.ptgs_visibility_polygon(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                       _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), _ptr(n_hit),
                                       _ptr(pivot), _ptr(extreme), P, _ptr(poly), st))
+    mark("vis_polygon")
     caps = torch.full((P,), int(cand_capacity), dtype=torch.int64, device=dev)
     rounds = 0
     while True:
@@ -318,10 +323,12 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                                              _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
                                              cam_split, _ptr(poly), _ptr(cand_off), _ptr(cand_uv),
                                              _ptr(cand_count), _ptr(ws), ws.numel(), st))
+        mark("vis_sweep2_candidates")
         check(lib.ptgs_visibility_hull(_ptr(cand_uv), _ptr(cand_off), _ptr(cand_count), _ptr(n_hit), P,
                                        _ptr(cam_index), _ptr(cameras_d), int(min_hits),
                                        float(threshold), float(near_eps), _ptr(area), _ptr(ratio),
                                        _ptr(keep), _ptr(flags), st))
+        mark("vis_hull")
         over = cand_count.to(torch.int64) > caps
         if not bool(over.any().item()):
             break
@@ -479,3 +486,54 @@ def camera_centers(R, T) -> np.ndarray:
         Tt = torch.tensor(np.asarray(T[i]), dtype=torch.float32)
         out[i] = (-torch.matmul(Rt.transpose(0, 1), Tt)).numpy()
     return out
+
+
+StageTimer = _Timer
+
+
+def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
+                       rank: int, world: int, group=None, timer=None, **kw) -> VisibilityResult:
+    """A7-A9 with the cameras sharded c % world == rank (north star: only the
+    visibility pass is partitioned; the per-pair result vectors are
+    all-gathered).  Returns the FULL per-pair result on every rank."""
+    from . import multigpu as M
+    if world <= 1:
+        return visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
+                          timer=timer, **kw)
+    my_off, my_idx, _ = M.shard_csr(cam_offsets, cam_index, rank, world)
+    if timer is not None:
+        timer.mark("vis_shard")
+    v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, my_off, my_idx, timer=timer, **kw)
+    rec = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
+    full = M.gather_records(rec, cam_index, world, group)
+    n_hit, ratio, area, keep, flags = M.unpack_records(full)
+    if timer is not None:
+        timer.mark("vis_allgather")
+    return VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
+
+
+def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
+                           cam_records: torch.Tensor, cam_offsets: np.ndarray,
+                           cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
+                           threshold=VISIBLE_RATE, rank=0, world=1, group=None):
+    """visibility_based_camera_selection (shen_partation_densify.py:911-954)
+    for HOST inputs: the expanded blocks' points back to back
+    (`block_points` (sum N_b, 3) float32/float64, ideally pinned), the camera
+    records and the block->camera CSR.  Uploads, down-samples (A6), runs the
+    visibility pass (A7-A9) and returns host arrays
+    (kept_offsets, kept_index, n_hit, ratio, keep, flags)."""
+    L = len(block_offsets) - 1
+    pts_d = block_points.to(device, non_blocking=True)
+    cams_d = cam_records.to(device, non_blocking=True)
+    off_d = torch.from_numpy(np.ascontiguousarray(block_offsets, dtype=np.int64)).to(device, non_blocking=True)
+    coff_d = torch.from_numpy(np.ascontiguousarray(cam_offsets, dtype=np.int64)).to(device, non_blocking=True)
+    cidx_d = torch.from_numpy(np.ascontiguousarray(cam_index, dtype=np.int32)).to(device, non_blocking=True)
+    x, y, z = aos_to_soa(pts_d)
+    n_e = int(block_offsets[L])
+    ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e)
+    vis = visibility_sharded(dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group,
+                             threshold=threshold)
+    k_off, k_idx = select_cameras(vis.keep, coff_d, cidx_d)
+    out = (k_off.cpu().numpy(), k_idx.cpu().numpy(), vis.n_hit.cpu().numpy(), vis.ratio.cpu().numpy(),
+           vis.keep.cpu().numpy(), vis.flags.cpu().numpy())
+    return out, int(ds_off[L].item())

@@ -1,0 +1,76 @@
+"""Camera-sharded visibility pass (one process per GPU, torch.distributed).
+
+The reference is single process; the north star shards
+only the visibility pass: every rank holds the same down-sampled blocks, rank r
+evaluates the cameras  c % world == r  of every block's list
+(shen_partation_densify.py:932-936 is the loop being split) and the small
+per-pair result vectors are all-gathered (NCCL over NVLink on the GPU box,
+gloo in the CPU tests).  Everything here is device agnostic torch; the
+compute callback is the CUDA visibility pass.
+"""
+from __future__ import annotations
+
+import torch
+
+# columns of the packed per-pair record (float64: every field is exact)
+REC_N_HIT, REC_RATIO, REC_AREA, REC_KEEP_FLAGS = 0, 1, 2, 3
+REC_COLS = 4
+
+
+def shard_mask(cam_idx: torch.Tensor, rank: int, world: int) -> torch.Tensor:
+    """Pairs (positions of the block->camera CSR) owned by `rank`."""
+    return (cam_idx % world) == rank
+
+
+def shard_csr(cam_off: torch.Tensor, cam_idx: torch.Tensor, rank: int, world: int):
+    """CSR restricted to the pairs of `rank` (order kept) + their positions in
+    the full pair list."""
+    if world <= 1:
+        pos = torch.arange(cam_idx.shape[0], device=cam_idx.device)
+        return cam_off, cam_idx, pos
+    L = cam_off.shape[0] - 1
+    mine = shard_mask(cam_idx, rank, world)
+    pos = torch.nonzero(mine).reshape(-1)
+    # per block count of owned pairs: searchsorted of the block boundaries in pos
+    new_off = torch.searchsorted(pos, cam_off[: L + 1].to(pos.dtype)).to(torch.int64)
+    return new_off.contiguous(), cam_idx[pos].contiguous(), pos
+
+
+def pack_records(n_hit, ratio, area, keep, flags) -> torch.Tensor:
+    rec = torch.empty((n_hit.shape[0], REC_COLS), dtype=torch.float64, device=n_hit.device)
+    rec[:, REC_N_HIT] = n_hit.to(torch.float64)
+    rec[:, REC_RATIO] = ratio
+    rec[:, REC_AREA] = area
+    rec[:, REC_KEEP_FLAGS] = keep.to(torch.float64) + 256.0 * flags.to(torch.float64)
+    return rec
+
+
+def unpack_records(rec: torch.Tensor):
+    n_hit = rec[:, REC_N_HIT].to(torch.int32)
+    kf = rec[:, REC_KEEP_FLAGS].to(torch.int64)
+    return n_hit, rec[:, REC_RATIO].contiguous(), rec[:, REC_AREA].contiguous(), \
+        (kf & 1).to(torch.uint8), (kf >> 8).to(torch.uint8)
+
+
+def gather_records(local: torch.Tensor, cam_idx: torch.Tensor, world: int, group=None) -> torch.Tensor:
+    """All-gather of the per-pair records.  `local` holds this rank's pairs in
+    shard order; returns the (P, REC_COLS) table in full pair order on every
+    rank.  cam_idx (the full, replicated list) fixes every rank's positions."""
+    import torch.distributed as dist
+    P = cam_idx.shape[0]
+    if world <= 1:
+        return local
+    owner = (cam_idx % world).to(torch.int64)
+    counts = torch.bincount(owner, minlength=world)
+    cap = int(counts.max().item()) if P else 0
+    cap = max(cap, 1)
+    send = torch.zeros((cap, REC_COLS), dtype=torch.float64, device=local.device)
+    send[: local.shape[0]] = local
+    recv = torch.empty((world * cap, REC_COLS), dtype=torch.float64, device=local.device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    # slot of pair p inside its owner's shard = rank of p among that owner's pairs
+    order = torch.argsort(owner, stable=True)
+    start = torch.cumsum(counts, 0) - counts
+    slot = torch.empty(P, dtype=torch.int64, device=local.device)
+    slot[order] = torch.arange(P, device=local.device) - start[owner[order]]
+    return recv[owner * cap + slot]

@@ -66,6 +66,11 @@ void ptgs_reset_launch_count(void);
 int ptgs_aos_to_soa_f32(const float* xyz, int64_t n, float* x, float* y,
                         float* z, ptgs_stream_t stream);
 
+/* Same for (N,3) float64 rows (the cloud after a Manhattan transform,
+ * scene/ptgs/shen_data_read.py:126-130, is float64). */
+int ptgs_aos_to_soa_f64(const double* xyz, int64_t n, double* x, double* y,
+                        double* z, ptgs_stream_t stream);
+
 /* A13 -- Manhattan transform of the point cloud,
  * scene/ptgs/shen_data_read.py:126-130 (fetchPly):
  *     new = R(3x3,f64) . p(f32->f64) + T        (f64 result)
@@ -187,7 +192,8 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
  *   arithmetic, :572), one output point per occupied voxel = the mean of its
  *   points accumulated sequentially in index order then divided by the
  *   count (:588-591), cast to float32 (:605).
- *   Inputs: planar coordinates, block CSR (offsets[L+1], indices).
+ *   Inputs: planar coordinates, block CSR (offsets[L+1], indices; indices may
+ *   be NULL = identity, i.e. the blocks' points are stored back to back).
  *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
  *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
  *   index list of the first point of the voxel.  Voxels of a block are
