@@ -143,8 +143,9 @@ __global__ void __launch_bounds__(1024) expand_scan_kernel(
 }
 
 // single CTA: offsets[L+1] = exclusive scan of counts.
-__global__ void __launch_bounds__(1024) offsets_kernel(const int64_t* __restrict__ counts,
-                                                       int L, int64_t* __restrict__ offsets) {
+// (counts may alias offsets: every element is read before its slot is written)
+__global__ void __launch_bounds__(1024) offsets_kernel(const int64_t* counts, int L,
+                                                       int64_t* offsets) {
   __shared__ long long sm[33];
   long long carry = 0;
   for (int s = 0; s < L; s += 1024) {
@@ -348,8 +349,7 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
   PTGS_REQUIRE(n_cameras >= 0 && n_blocks >= 1 && n_blocks <= kExpMaxBlocks, "sizes");
   PTGS_REQUIRE(boxes && cam_offsets && (centers || n_cameras == 0), "arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  int64_t* counts = nullptr;
-  PTGS_CUDA_TRY(cudaMallocAsync(&counts, sizeof(int64_t) * n_blocks, st));
+  int64_t* counts = cam_offsets;   // scanned in place
   assign_count_kernel<<<n_blocks, 256, 0, st>>>(centers, n_cameras, boxes, counts);
   PTGS_LAUNCH_CHECK();
   offsets_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, cam_offsets);
@@ -358,7 +358,6 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
     assign_fill_kernel<<<n_blocks, 256, 0, st>>>(centers, n_cameras, boxes, cam_offsets, cam_index, cam_capacity);
     PTGS_LAUNCH_CHECK();
   }
-  PTGS_CUDA_TRY(cudaFreeAsync(counts, st));
   return PTGS_OK;
 }
 
@@ -369,8 +368,7 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
   PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kExpMaxBlocks, "n_blocks");
   PTGS_REQUIRE(cam_offsets && kept_offsets, "arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  int64_t* counts = nullptr;
-  PTGS_CUDA_TRY(cudaMallocAsync(&counts, sizeof(int64_t) * n_blocks, st));
+  int64_t* counts = kept_offsets;  // scanned in place
   keep_count_kernel<<<n_blocks, 256, 0, st>>>(keep, cam_offsets, counts);
   PTGS_LAUNCH_CHECK();
   offsets_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, kept_offsets);
@@ -379,7 +377,6 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
     keep_fill_kernel<<<n_blocks, 256, 0, st>>>(keep, cam_offsets, cam_index, kept_offsets, kept_index);
     PTGS_LAUNCH_CHECK();
   }
-  PTGS_CUDA_TRY(cudaFreeAsync(counts, st));
   return PTGS_OK;
 }
 

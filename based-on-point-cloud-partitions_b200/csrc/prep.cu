@@ -155,7 +155,9 @@ __global__ void __launch_bounds__(256) bounds_kernel(
 template <typename T>
 __global__ void bounds_finish_kernel(const typename KeyOf<T>::type* keys,
                                      double* bounds) {
-  for (int i = 0; i < 4; ++i) bounds[i] = (double)KeyOf<T>::decode(keys[i]);
+  typename KeyOf<T>::type k[4];
+  for (int i = 0; i < 4; ++i) k[i] = keys[i];          // keys alias bounds
+  for (int i = 0; i < 4; ++i) bounds[i] = (double)KeyOf<T>::decode(k[i]);
 }
 
 // ---------------------------------------------------------------------------
@@ -230,12 +232,9 @@ template <typename T>
 static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
                        int64_t n_capacity, double* bounds, cudaStream_t st) {
   using K = typename KeyOf<T>::type;
-  // the 4 keys live in the output buffer itself? no: bounds is 4 doubles = 32 B,
-  // keys need 4*sizeof(K) <= 32 B -> reuse a small static-free scratch: the
-  // caller's bounds buffer is only 32 B, so run keys in a cudaMallocAsync'd
-  // block to stay re-entrant.
-  K* keys = nullptr;
-  PTGS_CUDA_TRY(cudaMallocAsync(&keys, 4 * sizeof(K), st));
+  // the 4 ordered keys (<= 32 B) are accumulated in the caller's 32-byte
+  // output buffer and decoded in place by one thread: no scratch allocation.
+  K* keys = reinterpret_cast<K*>(bounds);
   bounds_init_kernel<T><<<1, 1, 0, st>>>(keys);
   PTGS_LAUNCH_CHECK();
   int grid = grid_for(n_capacity, 256 * 8, kNumSMs * 8);
@@ -243,7 +242,6 @@ static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
   PTGS_LAUNCH_CHECK();
   bounds_finish_kernel<T><<<1, 1, 0, st>>>(keys, bounds);
   PTGS_LAUNCH_CHECK();
-  PTGS_CUDA_TRY(cudaFreeAsync(keys, st));
   return PTGS_OK;
 }
 

@@ -764,7 +764,8 @@ int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
 
 int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64_t n,
                         const float* cameras, int32_t cam_first, int32_t cam_count, int32_t* n_hit,
-                        uint8_t* seen, ptgs_stream_t stream) {
+                        uint8_t* seen, void* workspace, size_t workspace_bytes,
+                        ptgs_stream_t stream) {
   PTGS_REQUIRE(n >= 0 && cam_first >= 0 && cam_count >= 0 && n_hit, "arguments");
   PTGS_REQUIRE(aligned16(px) && aligned16(py) && aligned16(pz) && aligned16(cameras),
                "point / camera arrays must be 16-byte aligned");
@@ -772,8 +773,11 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64
   if (cam_count > 0) PTGS_CUDA_TRY(cudaMemsetAsync(n_hit, 0, sizeof(int32_t) * cam_count, st));
   if (seen && n > 0) PTGS_CUDA_TRY(cudaMemsetAsync(seen, 0, (size_t)n, st));
   if (n == 0 || cam_count == 0) return PTGS_OK;
-  int64_t* ws = nullptr;
-  PTGS_CUDA_TRY(cudaMallocAsync(&ws, 6 * sizeof(int64_t), st));
+  if (!workspace || workspace_bytes < ptgs_visibility_workspace_bytes(1)) {
+    set_error("coverage_sweep: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  int64_t* ws = (int64_t*)workspace;
   coverage_setup_kernel<<<1, 1, 0, st>>>(n, cam_count, ws, ws + 2);
   PTGS_LAUNCH_CHECK();
   // few tiles: split the camera list so that every SM has work
@@ -788,10 +792,7 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64
   a.cameras = cameras; a.cam_offsets = ws + 2; a.cam_index = nullptr; a.cam_first = cam_first;
   a.cam_split = (int32_t)split; a.item_prefix = ws + 4;
   a.n_hit = n_hit; a.seen = seen;
-  rc = launch_sweep<0>(a, st);
-  if (rc) return rc;
-  PTGS_CUDA_TRY(cudaFreeAsync(ws, st));
-  return PTGS_OK;
+  return launch_sweep<0>(a, st);
 }
 
 }  // extern "C"

@@ -363,8 +363,9 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
     n = px.shape[0]
     n_hit = torch.empty(max(cam_count, 1), dtype=torch.int32, device=dev)
     seen = torch.empty(max(n, 1), dtype=torch.uint8, device=dev) if want_seen else None
+    ws = _ws(lib.ptgs_visibility_workspace_bytes(1), dev)
     check(lib.ptgs_coverage_sweep(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(cameras_d), int(cam_first),
-                                  int(cam_count), _ptr(n_hit), _ptr(seen), _stream()))
+                                  int(cam_count), _ptr(n_hit), _ptr(seen), _ptr(ws), ws.numel(), _stream()))
     return (n_hit[:cam_count], seen[:n]) if want_seen else n_hit[:cam_count]
 
 

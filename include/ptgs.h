@@ -322,10 +322,12 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
  * camera cam_first..cam_first+cam_count-1; n_hit[cam_count] int32 (must be
  * zeroed by the caller... it is zeroed by the call); optional seen[n] uint8
  * (may be NULL): 1 when any camera of the range sees the point.
+ * workspace: ptgs_visibility_workspace_bytes(1) bytes.
  * ------------------------------------------------------------------ */
 int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         int64_t n, const float* cameras, int32_t cam_first,
                         int32_t cam_count, int32_t* n_hit, uint8_t* seen,
+                        void* workspace, size_t workspace_bytes,
                         ptgs_stream_t stream);
 
 #ifdef __cplusplus

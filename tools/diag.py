@@ -1,0 +1,49 @@
+"""Diagnostics on the GPU box: per-stage host/device timing and candidate statistics."""
+import sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import ptgs_b200
+from ptgs_b200 import device as D, workload as W
+
+name = sys.argv[1] if len(sys.argv) > 1 else "c2"
+scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
+hs = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
+dev = torch.device("cuda", 0)
+w = W.make(name, scale, height_scale=hs)
+recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+centers = D.camera_centers(w.R, w.T)
+xyz = torch.from_numpy(w.xyz).to(dev)
+
+
+def T(label, fn, rep=3):
+    out = None
+    for i in range(rep):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        out = fn()
+        torch.cuda.synchronize(); dt = time.perf_counter() - t0
+        print("%-28s run %d: %9.3f ms" % (label, i, dt * 1e3), flush=True)
+    return out
+
+res = T("partition_device", lambda: D.partition_device(xyz, recs, centers, w.threshold, man_trans=w.man_trans))
+x, y, z = D.aos_to_soa(xyz)
+if w.man_trans is not None:
+    x, y, z = T("manhattan", lambda: D.manhattan_apply(x, y, z, w.man_trans))
+keep, nk = T("radius", lambda: D.radius_outlier_mask(x, y, z))
+fx, fy, nf = T("compact", lambda: D.compact_xy(x, y, keep))
+root = T("bounds", lambda: D.bounds_xy(fx, fy, nf))
+lb, lp, ld, lc = T("split", lambda: D.balanced_split(fx, fy, nf, root, w.threshold))
+boxes = D.expanded_boxes(lb)
+off, idx = T("expand", lambda: D.expand_select(x, y, boxes))
+coff, cidx = T("assign", lambda: D.assign_cameras(centers, boxes, dev))
+ds = T("voxel", lambda: D.voxel_downsample(x, y, z, off, idx))
+cams_d = torch.from_numpy(recs).to(dev)
+vis = T("visibility", lambda: D.visibility(ds[1], ds[2], ds[3], ds[0], cams_d, coff, cidx))
+T("select", lambda: D.select_cameras(vis.keep, coff, cidx))
+nh = vis.n_hit.cpu().numpy(); cc = vis.cand_count.cpu().numpy(); rt = vis.ratio.cpu().numpy()
+print("leaves", len(lb), "pairs", len(nh), "rounds", vis.rounds)
+print("n_hit   pct[0,10,50,90,99,100]:", np.percentile(nh, [0, 10, 50, 90, 99, 100]))
+print("cand    pct[0,10,50,90,99,100]:", np.percentile(cc, [0, 10, 50, 90, 99, 100]))
+print("ratio   pct[0,10,50,90,99,100]:", np.percentile(rt, [0, 10, 50, 90, 99, 100]))
+print("kept fraction", float(vis.keep.float().mean()), "flags", np.bincount(vis.flags.cpu().numpy(), minlength=16)[:16])
+M = np.diff(ds[0].cpu().numpy()); Cb = np.diff(coff.cpu().numpy())
+print("M_b", M.min(), M.max(), "C_b", Cb.min(), Cb.max(), "tests", int((M * Cb).sum()))
