@@ -132,6 +132,53 @@ __device__ __forceinline__ uint32_t order_key(float f) {
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
 
+// ---- conservative tile cull ----------------------------------------------------
+// A tile's points lie in the axis aligned box (centre c, half extent e).  The
+// hit set of a camera is {front > 0} intersected with the double pyramid
+//   Z > 0:  uh >= 0, W*Z - uh > 0, vh >= 0, H*Z - vh > 0      (nappe +)
+//   Z < 0:  uh <= 0, W*Z - uh < 0, vh <= 0, H*Z - vh < 0      (nappe -, the
+//           mirrored points of SURVEY.md D5)
+// every constraint being a linear form g(p) = n.p + d of the world point.  Over
+// the box g ranges over [g(c) - |n|.e, g(c) + |n|.e]; a nappe is impossible when
+// one of its constraints fails on the whole box.  The float32 evaluation of the
+// real test differs from exact arithmetic by at most ~2^-21 * S in camera space
+// (S = magnitude of the coordinates involved); the margins below are 2^-16 * S,
+// a 32x safety factor (DESIGN.md "tile cull").  Comparisons are written so that
+// a NaN keeps the tile.
+struct Form { float mid, rad; };
+__device__ __forceinline__ Form form(float n0, float n1, float n2, float d, const float* b) {
+  Form f;
+  f.mid = fmaf(n0, b[0], fmaf(n1, b[1], fmaf(n2, b[2], d)));
+  f.rad = fmaf(fabsf(n0), b[3], fmaf(fabsf(n1), b[4], fabsf(n2) * b[5]));
+  return f;
+}
+__device__ __forceinline__ bool tile_may_hit(const Cam& c, const float* b) {
+  const float S = fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + b[3] + b[4] + b[5] +
+                  fmaxf(fabsf(c.tx), fmaxf(fabsf(c.ty), fabsf(c.tz)));
+  const float mF = S * (1.0f / 65536.0f);
+  const float mP = mF * (c.fx + c.fy + c.w + c.h + fabsf(c.cx) + fabsf(c.cy));
+  const Form Y = form(c.r10, c.r11, c.r12, c.ty, b);
+  const Form Z = form(c.r20, c.r21, c.r22, c.tz, b);
+  const Form F = (c.front_axis == 1.0f) ? Y : Z;
+  if (F.mid + F.rad < -mF) return false;
+  // uh = fx*X + cx*Z ; vh = fy*Y + cy*Z ; B = (W-cx)*Z - fx*X ; D = (H-cy)*Z - fy*Y
+  const float a0 = fmaf(c.fx, c.r00, c.cx * c.r20), a1 = fmaf(c.fx, c.r01, c.cx * c.r21),
+              a2 = fmaf(c.fx, c.r02, c.cx * c.r22), ad = fmaf(c.fx, c.tx, c.cx * c.tz);
+  const float c0 = fmaf(c.fy, c.r10, c.cy * c.r20), c1 = fmaf(c.fy, c.r11, c.cy * c.r21),
+              c2 = fmaf(c.fy, c.r12, c.cy * c.r22), cd = fmaf(c.fy, c.ty, c.cy * c.tz);
+  const Form A = form(a0, a1, a2, ad, b);
+  const Form Cc = form(c0, c1, c2, cd, b);
+  const Form B = form(fmaf(c.w, c.r20, -a0), fmaf(c.w, c.r21, -a1), fmaf(c.w, c.r22, -a2),
+                      fmaf(c.w, c.tz, -ad), b);
+  const Form D = form(fmaf(c.h, c.r20, -c0), fmaf(c.h, c.r21, -c1), fmaf(c.h, c.r22, -c2),
+                      fmaf(c.h, c.tz, -cd), b);
+  const bool plus = !(Z.mid + Z.rad < -mF) && !(A.mid + A.rad < -mP) && !(B.mid + B.rad < -mP) &&
+                    !(Cc.mid + Cc.rad < -mP) && !(D.mid + D.rad < -mP);
+  const bool minus = !(Z.mid - Z.rad > mF) && !(A.mid - A.rad > mP) && !(B.mid - B.rad > mP) &&
+                     !(Cc.mid - Cc.rad > mP) && !(D.mid - D.rad > mP);
+  return plus || minus;
+}
+
 // ---- work item schedule -----------------------------------------------------
 // item_prefix[b] = number of work items of the blocks before b; a block has
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
@@ -222,6 +269,10 @@ struct SweepSmem {
   long long cand_off[kSwCamChunk];                        // MODE 2
   int cand_cap[kSwCamChunk];                              // MODE 2
   int cnt[kSwCamChunk];
+  int act[kSwCamChunk];                                   // cameras that survive the tile cull
+  int nact;
+  float wbox[kSwThreads / 32][6];                         // per warp tile AABB
+  float box[6];                                           // centre xyz, half extent xyz (padded)
   alignas(8) uint64_t bar[2];
   int64_t prefix[kSwMaxBlocks + 1];
 };
@@ -277,7 +328,42 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         z[k] = ok ? S.tile[stage][2][shift + i] : qnan;
       }
     }
+    {
+      // tile AABB (fminf/fmaxf ignore the NaN padding)
+      const float inf = __int_as_float(0x7f800000);
+      float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+#pragma unroll
+      for (int k = 0; k < kSwP; ++k) {
+        lo[0] = fminf(lo[0], x[k]); hi[0] = fmaxf(hi[0], x[k]);
+        lo[1] = fminf(lo[1], y[k]); hi[1] = fmaxf(hi[1], y[k]);
+        lo[2] = fminf(lo[2], z[k]); hi[2] = fmaxf(hi[2], z[k]);
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          lo[a] = fminf(lo[a], __shfl_xor_sync(kFullMask, lo[a], d));
+          hi[a] = fmaxf(hi[a], __shfl_xor_sync(kFullMask, hi[a], d));
+        }
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { S.wbox[tid >> 5][a] = lo[a]; S.wbox[tid >> 5][3 + a] = hi[a]; }
+      }
+    }
     __syncthreads();   // every thread is done with stage^1 (previous item) and this stage
+    if (tid < 3) {
+      float lo = S.wbox[0][tid], hi = S.wbox[0][3 + tid];
+#pragma unroll
+      for (int w = 1; w < kSwThreads / 32; ++w) {
+        lo = fminf(lo, S.wbox[w][tid]);
+        hi = fmaxf(hi, S.wbox[w][3 + tid]);
+      }
+      // centre / half extent, padded for the rounding of these two operations
+      const float pad = (fabsf(lo) + fabsf(hi)) * (1.0f / 1048576.0f);
+      S.box[tid] = 0.5f * lo + 0.5f * hi;
+      S.box[3 + tid] = (0.5f * hi - 0.5f * lo) + pad;
+    }
     const int64_t next = item + gridDim.x;
     Item nxt;
     if (next < n_items) {
@@ -322,12 +408,31 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
       }
       __syncthreads();
+      // ---- cull: camera j of the chunk against the tile box (warp 0)
+      if (tid < 32) {
+        bool live = false;
+        if (tid < nc) live = tile_may_hit(load_cam(S.cam[tid]), S.box);
+        const unsigned m = __ballot_sync(kFullMask, live);
+        if (live) S.act[__popc(m & lanemask_lt())] = tid;
+        if (tid == 0) S.nact = __popc(m);
+      }
+      __syncthreads();
+      const int nact = S.nact;
 
-      // ---- sweep: 8 register points x nc cameras
-      for (int j = 0; j < nc; ++j) {
+      // ---- sweep: 8 register points x surviving cameras
+      for (int jj = 0; jj < nact; ++jj) {
+        const int j = S.act[jj];
         const Cam c = load_cam(S.cam[j]);
         const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
         int cnt = 0;
+        // MODE 1: per thread running pivot / directional extremes (registers)
+        unsigned long long t_pv = ~0ull;
+        float t_best[8];
+        uint32_t t_idx[8];
+        if (MODE == 1) {
+#pragma unroll
+          for (int d = 0; d < 8; ++d) { t_best[d] = -__int_as_float(0x7f800000); t_idx[d] = 0; }
+        }
 #pragma unroll
         for (int k = 0; k < kSwP; ++k) {
           const Proj p = project_pre(c, w1, h1, x[k], y[k], z[k]);
@@ -341,15 +446,13 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                 v = __fadd_rn(v, 0.0f);
                 const unsigned long long pk =
                     ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
-                const unsigned long long idx =
-                    (unsigned long long)(cur.tile * kSwTile + k * kSwThreads + tid);
+                t_pv = pk < t_pv ? pk : t_pv;
+                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + k * kSwThreads + tid);
                 const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                 const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
                 for (int d = 0; d < 8; ++d) {
-                  const unsigned long long e = ((unsigned long long)order_key(dir[d]) << 32) | idx;
-                  if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
+                  if (dir[d] > t_best[d]) { t_best[d] = dir[d]; t_idx[d] = idx; }
                 }
               }
               if (MODE == 2) {
@@ -381,6 +484,29 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         if (MODE != 2) {
           const int wsum = __reduce_add_sync(kFullMask, cnt);
           if (lane == 0 && wsum) atomicAdd(&S.cnt[j], wsum);
+          if (MODE == 1 && wsum) {
+            // warp reduction of the pivot (64-bit min as two 32-bit steps) and of
+            // the 8 extremes (redux.sync on the ordered key, lowest lane wins ties)
+            const uint32_t phi = (uint32_t)(t_pv >> 32);
+            const uint32_t mhi = __reduce_min_sync(kFullMask, phi);
+            const uint32_t plo = phi == mhi ? (uint32_t)t_pv : 0xffffffffu;
+            const uint32_t mlo = __reduce_min_sync(kFullMask, plo);
+            if (lane == 0) {
+              const unsigned long long pk = ((unsigned long long)mhi << 32) | mlo;
+              if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
+            }
+#pragma unroll
+            for (int d = 0; d < 8; ++d) {
+              const uint32_t key = order_key(t_best[d]);
+              const uint32_t mk = __reduce_max_sync(kFullMask, key);
+              const unsigned who = __ballot_sync(kFullMask, key == mk);
+              const uint32_t id = __shfl_sync(kFullMask, t_idx[d], __ffs(who) - 1);
+              if (lane == 0) {
+                const unsigned long long e = ((unsigned long long)mk << 32) | id;
+                if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
+              }
+            }
+          }
         }
       }
       __syncthreads();

@@ -11,7 +11,7 @@
 // (key, entry position), segment heads by neighbour compare + scan, and one
 // thread per occupied voxel walking its (tiny) run in entry order so the sum
 // is the same left-to-right float addition the reference performs.  Voxels
-// come out in ascending key order; `ds_first` (position of the voxel's first
+// come out in ascending key order (coarse cell major, see vox_key_kernel); `ds_first` (position of the voxel's first
 // point inside its block) recovers the reference's first-occurrence order.
 #include <cub/device/device_radix_sort.cuh>
 
@@ -20,6 +20,7 @@
 namespace ptgs {
 
 constexpr int kVoxMaxBlocks = 1024;
+constexpr int kVoxCoarseShift = 6;   // coarse cell = 64 voxels (6.4 units at voxel 0.1)
 
 struct VoxLayout {
   int32_t bits_b, bits_x, bits_y, bits_z;   // field widths
@@ -160,9 +161,18 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
     const uint64_t vx = (uint64_t)VoxArith<T>::vid(x[i], bmin[3 * b], vs);
     const uint64_t vy = (uint64_t)VoxArith<T>::vid(y[i], bmin[3 * b + 1], vs);
     const uint64_t vz = (uint64_t)VoxArith<T>::vid(z[i], bmin[3 * b + 2], vs);
+    // block | coarse cell (vx >> s, vy >> s) | fine (vx, vy) | vz : a bit
+    // permutation of (vx, vy, vz), so the voxel groups are unchanged and only
+    // their order moves -- cell-major order makes every run of consecutive
+    // voxels (a sweep tile) spatially compact, which the visibility sweep's
+    // tile culling relies on.
+    const int lx = l.bits_x < kVoxCoarseShift ? l.bits_x : kVoxCoarseShift;
+    const int ly = l.bits_y < kVoxCoarseShift ? l.bits_y : kVoxCoarseShift;
     uint64_t k = (uint64_t)b;
-    k = (k << l.bits_x) | vx;
-    k = (k << l.bits_y) | vy;
+    k = (k << (l.bits_x - lx)) | (vx >> lx);
+    k = (k << (l.bits_y - ly)) | (vy >> ly);
+    k = (k << lx) | (vx & ((1ull << lx) - 1));
+    k = (k << ly) | (vy & ((1ull << ly) - 1));
     k = (k << l.bits_z) | vz;
     keys[e] = k;
     vals[e] = (uint32_t)e;

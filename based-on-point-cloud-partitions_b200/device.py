@@ -277,7 +277,7 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
-               cand_capacity=256, cam_split=None, timer=None) -> VisibilityResult:
+               cand_capacity=2048, cam_split=None, timer=None) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair: sweep 1 (counts, pivot, extremes),
     inner polygons, sweep 2 (hull candidates), exact hull area, keep decision."""
     lib = _lib.load()

@@ -166,12 +166,21 @@ def make_scene(n_points: int, n_cameras: int, threshold: int, seed: int,
                                 manhattan_deg=manhattan_deg))
 
 
+# Camera height multiplier applied to SURVEY.md 8(d)'s h = 0.225*sqrt(thr/rho).
+# With the formula's own height (x1) 98 % of the assigned cameras pass the 0.45
+# hull-area test at c2; SURVEY asks for a kept fraction of 20-80 % and allows
+# only `h` to change: x3 gives about 60 % (BASELINE.md records the measured
+# fraction per configuration).
+HEIGHT_SCALE = 3.0
+
+
 def make_config(name: str, scale: float = 1.0, **kw) -> SynthScene:
     """One of the BASELINE.json configurations (c1..c5); `scale` < 1 shrinks
     both the point and the camera count (same density, same camera height)."""
     N, C, thr, seed, obl, man = CONFIGS[name]
     N = max(1000, int(N * scale))
     C = max(4, int(C * scale))
+    kw.setdefault("height_scale", HEIGHT_SCALE)
     sc = make_scene(N, C, thr if scale == 1.0 else kw.pop("threshold", thr), seed,
                     oblique_fraction=obl, manhattan_deg=man, **kw)
     sc.meta["config"] = name

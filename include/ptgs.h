@@ -197,8 +197,9 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
  *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
  *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
  *   index list of the first point of the voxel.  Voxels of a block are
- *   emitted in ascending (vx,vy,vz) order; the reference's first-occurrence
- *   order is ds_first ascending (ptgs_voxel_reference_order).
+ *   emitted grouped by coarse XY cell (64 x 64 voxels, cell-major) so that
+ *   consecutive output points are spatially compact; the reference's
+ *   first-occurrence order is ds_first ascending.
  *   status_dev: PTGS_E_RANGE when a voxel index exceeds the key layout.
  * ------------------------------------------------------------------ */
 size_t ptgs_voxel_downsample_workspace_bytes(int64_t n_entries,

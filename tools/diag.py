@@ -7,9 +7,9 @@ from ptgs_b200 import device as D, workload as W
 
 name = sys.argv[1] if len(sys.argv) > 1 else "c2"
 scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
-hs = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
+hs = float(sys.argv[3]) if len(sys.argv) > 3 else None
 dev = torch.device("cuda", 0)
-w = W.make(name, scale, height_scale=hs)
+w = W.make(name, scale, **({} if hs is None else dict(height_scale=hs)))
 recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
 centers = D.camera_centers(w.R, w.T)
 xyz = torch.from_numpy(w.xyz).to(dev)
