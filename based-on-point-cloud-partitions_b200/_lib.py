@@ -47,13 +47,15 @@ SIGNATURES = {
     "ptgs_visibility_init": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_visibility_count": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                         _vp, _vp, _sz, _vp]),
-    "ptgs_visibility_polygon": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
-                                          _i64, _vp, _vp]),
-    "ptgs_visibility_candidates": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp,
+    "ptgs_visibility_bounds": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
+                                         _i64, _i32, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
+                                         _vp, _vp, _vp]),
+    "ptgs_visibility_plan": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp]),
+    "ptgs_visibility_candidates": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                              _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
-                                       _vp, _vp, _vp, _vp]),
-    "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp]),
+                                       _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
     "ptgs_coverage_sweep": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
 }
 

@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(256) keep_count_kernel(
 __global__ void __launch_bounds__(256) keep_fill_kernel(
     const uint8_t* __restrict__ keep, const int64_t* __restrict__ cam_offsets,
     const int32_t* __restrict__ cam_index, const int64_t* __restrict__ kept_offsets,
-    int32_t* __restrict__ kept_index) {
+    int32_t* __restrict__ kept_index, int32_t* __restrict__ kept_pos) {
   __shared__ int sm[33];
   const int b = blockIdx.x;
   const int64_t a = cam_offsets[b], e = cam_offsets[b + 1];
@@ -290,7 +290,10 @@ __global__ void __launch_bounds__(256) keep_fill_kernel(
     const int f = (i < e && keep[i]) ? 1 : 0;
     int tot;
     int ex = block_exclusive_sum<int, 256>(f, sm, &tot);
-    if (f) kept_index[out + ex] = cam_index[i];
+    if (f) {
+      kept_index[out + ex] = cam_index[i];
+      if (kept_pos) kept_pos[out + ex] = (int32_t)i;
+    }
     out += tot;
   }
 }
@@ -364,7 +367,7 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
 int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
                         const int32_t* cam_index, int32_t n_blocks,
                         int64_t* kept_offsets, int32_t* kept_index,
-                        ptgs_stream_t stream) {
+                        int32_t* kept_pos, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kExpMaxBlocks, "n_blocks");
   PTGS_REQUIRE(cam_offsets && kept_offsets, "arguments");
   cudaStream_t st = (cudaStream_t)stream;
@@ -374,7 +377,8 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
   offsets_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, kept_offsets);
   PTGS_LAUNCH_CHECK();
   if (kept_index) {
-    keep_fill_kernel<<<n_blocks, 256, 0, st>>>(keep, cam_offsets, cam_index, kept_offsets, kept_index);
+    keep_fill_kernel<<<n_blocks, 256, 0, st>>>(keep, cam_offsets, cam_index, kept_offsets, kept_index,
+                                               kept_pos);
     PTGS_LAUNCH_CHECK();
   }
   return PTGS_OK;

@@ -220,6 +220,7 @@ struct SweepArgs {
   uint64_t* pivot;                // MODE 1
   uint64_t* extreme;              // MODE 1
   // MODE 2
+  const int32_t* pair_map;        // optional: pair slot of the (sub-)CSR -> pair id for poly / cand_*
   const float* poly;
   const int64_t* cand_offsets;
   float2* cand_uv;
@@ -268,6 +269,7 @@ struct SweepSmem {
   unsigned long long pivot[kSwCamChunk];                  // MODE 1
   long long cand_off[kSwCamChunk];                        // MODE 2
   int cand_cap[kSwCamChunk];                              // MODE 2
+  int pair_of[kSwCamChunk];                               // MODE 2
   int cnt[kSwCamChunk];
   int act[kSwCamChunk];                                   // cameras that survive the tile cull
   int nact;
@@ -389,8 +391,10 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       if (MODE == 2) {
         for (int i = tid; i < nc * (kPolyFloats / 4); i += kSwThreads) {
           const int j = i / (kPolyFloats / 4), q = i % (kPolyFloats / 4);
-          reinterpret_cast<float4*>(S.poly[j])[q] = __ldg(
-              reinterpret_cast<const float4*>(a.poly + (cam_base + c0 + j) * kPolyFloats) + q);
+          const int64_t slot = cam_base + c0 + j;
+          const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
+          reinterpret_cast<float4*>(S.poly[j])[q] =
+              __ldg(reinterpret_cast<const float4*>(a.poly + pair * kPolyFloats) + q);
         }
       }
       if (tid < nc) {
@@ -401,10 +405,12 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           for (int d = 0; d < 8; ++d) S.ext[tid][d] = 0ull;
         }
         if (MODE == 2) {
-          const int64_t pair = cam_base + c0 + tid;
+          const int64_t slot = cam_base + c0 + tid;
+          const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
           const int64_t o0 = a.cand_offsets[pair], o1 = a.cand_offsets[pair + 1];
           S.cand_off[tid] = o0;
           S.cand_cap[tid] = (int)(o1 - o0);
+          S.pair_of[tid] = (int)pair;
         }
       }
       __syncthreads();
@@ -472,8 +478,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                     inside = inside && (f > margin);
                   }
                   if (!inside) {
-                    const int64_t pair = cam_base + c0 + j;
-                    const int slot = atomicAdd(a.cand_count + pair, 1);
+                    const int slot = atomicAdd(a.cand_count + S.pair_of[j], 1);
                     if (slot < S.cand_cap[j]) a.cand_uv[S.cand_off[j] + slot] = make_float2(u, v);
                   }
                 }
@@ -538,20 +543,65 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
   }
 }
 
-// ---- inner polygon per pair --------------------------------------------------
-__global__ void __launch_bounds__(128) polygon_kernel(
+// ---- inner / outer polygon, area bounds and early decision per pair --------------
+// Sutherland-Hodgman clip of a convex polygon (<= 16 vertices) by a*u + b*v <= c.
+__device__ int clip_halfplane(const double* px, const double* py, int n, double a, double b,
+                              double c, double* qx, double* qy) {
+  int m = 0;
+  for (int i = 0; i < n; ++i) {
+    const int k = (i + 1 == n) ? 0 : i + 1;
+    const double fi = a * px[i] + b * py[i] - c, fk = a * px[k] + b * py[k] - c;
+    const bool in_i = fi <= 0.0, in_k = fk <= 0.0;
+    if (in_i && m < 16) { qx[m] = px[i]; qy[m] = py[i]; ++m; }
+    if (in_i != in_k && m < 16) {
+      const double t = fi / (fi - fk);
+      qx[m] = px[i] + t * (px[k] - px[i]);
+      qy[m] = py[i] + t * (py[k] - py[i]);
+      ++m;
+    }
+  }
+  return m;
+}
+__device__ double shoelace(const double* px, const double* py, int n) {
+  if (n < 3) return 0.0;
+  double acc = 0.0;
+  for (int i = 0; i < n; ++i) {
+    const int k = (i + 1 == n) ? 0 : i + 1;
+    acc += px[i] * py[k] - px[k] * py[i];
+  }
+  return 0.5 * fabs(acc);
+}
+__device__ __forceinline__ float key_to_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// Per pair: the inner polygon (extreme hits that belong to the point set the
+// reference scans) -> lower bound of the reference's hull area; the outer
+// octagon (the 8 supporting lines of sweep 1, inflated for the float32 rounding
+// of u+v / u-v) -> upper bound.  A pair whose bounds fall on one side of the
+// threshold by more than near_eps is decided here (flags bit4: `ratio` holds the
+// deciding bound, not the exact value); the rest get need = 1 and go through
+// sweep 2 + the exact hull.  exact_all != 0 sends every pair with enough hits
+// through the exact path.
+__global__ void __launch_bounds__(128) bounds_kernel(
     const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz,
     const int64_t* __restrict__ pt_offsets, int L, const float* __restrict__ cameras,
     const int64_t* __restrict__ cam_offsets, const int32_t* __restrict__ cam_index,
     const int32_t* __restrict__ n_hit, const uint64_t* __restrict__ pivot,
-    const uint64_t* __restrict__ extreme, float* __restrict__ poly) {
+    const uint64_t* __restrict__ extreme, int min_hits, double thr, double near_eps,
+    int exact_all, float* __restrict__ poly, double* __restrict__ ratio_lo,
+    double* __restrict__ ratio_hi, uint8_t* __restrict__ need, double* __restrict__ area_out,
+    double* __restrict__ ratio_out, uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out) {
   const int64_t n_pairs = cam_offsets[L];
   const int64_t pair = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pair >= n_pairs) return;
   float* out = poly + pair * kPolyFloats;
   for (int i = 0; i < kPolyFloats; ++i) out[i] = 0.0f;
   out[1] = -1.0f; out[2] = -1.0f;     // no hit has a negative coordinate
-  if (n_hit[pair] <= 0) return;
+  const int nh = n_hit[pair];
+  need[pair] = 0; area_out[pair] = 0.0; ratio_out[pair] = 0.0; keep_out[pair] = 0; flags_out[pair] = 0;
+  ratio_lo[pair] = 0.0; ratio_hi[pair] = 0.0;
+  if (nh <= 0) return;
   int lo = 0, hi = L - 1;             // block of the pair
   while (lo < hi) {
     const int mid = (lo + hi + 1) >> 1;
@@ -563,13 +613,16 @@ __global__ void __launch_bounds__(128) polygon_kernel(
   const uint64_t pv = pivot[pair];
   const float vp = __uint_as_float((uint32_t)(pv >> 32)), up = __uint_as_float((uint32_t)pv);
   out[1] = vp; out[2] = up;
-  const float D = fmaxf(c.w, c.h);
-  out[3] = 4e-6f * D * D;             // > the float32 evaluation error of the half planes
-  double vx[8], vy[8];
+  const float Dm = fmaxf(c.w, c.h);
+  out[3] = 4e-6f * Dm * Dm;           // > the float32 evaluation error of the half planes
+  double vx[8], vy[8], sup[8];
   int m = 0;
   for (int d = 0; d < 8; ++d) {
     const uint64_t e = extreme[pair * 8 + d];
+    sup[d] = 0.0;
     if (!e) continue;
+    const double hval = (double)key_to_float((uint32_t)(e >> 32));
+    sup[d] = hval + fabs(hval) * (1.0 / 4194304.0) + 1e-30;   // outward, covers fl(u+v)
     const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
     const Proj p = project_pre(c, w1, h1, px[gi], py[gi], pz[gi]);
     float u, v;
@@ -580,15 +633,65 @@ __global__ void __launch_bounds__(128) polygon_kernel(
     vx[m] = u; vy[m] = v; ++m;
   }
   while (m > 1 && vx[m - 1] == vx[0] && vy[m - 1] == vy[0]) --m;
-  if (m < 3) return;
-  for (int i = 0; i < m; ++i) {
-    const int k = (i + 1 == m) ? 0 : i + 1;
-    const double ea = -(vy[k] - vy[i]), eb = vx[k] - vx[i];
-    out[4 + 3 * i] = (float)ea;
-    out[5 + 3 * i] = (float)eb;
-    out[6 + 3 * i] = (float)(-(ea * vx[i] + eb * vy[i]));
+  double a_in = 0.0;
+  if (m >= 3) {
+    for (int i = 0; i < m; ++i) {
+      const int k = (i + 1 == m) ? 0 : i + 1;
+      const double ea = -(vy[k] - vy[i]), eb = vx[k] - vx[i];
+      out[4 + 3 * i] = (float)ea;
+      out[5 + 3 * i] = (float)eb;
+      out[6 + 3 * i] = (float)(-(ea * vx[i] + eb * vy[i]));
+    }
+    out[0] = (float)m;
+    a_in = shoelace(vx, vy, m);
   }
-  out[0] = (float)m;
+  // outer octagon: u <= s0, u+v <= s1, v <= s2, v-u <= s3, -u <= s4, -(u+v) <= s5, -v <= s6, u-v <= s7
+  double ax[16], ay[16], bx[16], by[16];
+  ax[0] = -sup[4]; ay[0] = -sup[6];
+  ax[1] = sup[0];  ay[1] = -sup[6];
+  ax[2] = sup[0];  ay[2] = sup[2];
+  ax[3] = -sup[4]; ay[3] = sup[2];
+  int n = 4;
+  n = clip_halfplane(ax, ay, n, 1.0, 1.0, sup[1], bx, by);
+  n = clip_halfplane(bx, by, n, -1.0, 1.0, sup[3], ax, ay);
+  n = clip_halfplane(ax, ay, n, -1.0, -1.0, sup[5], bx, by);
+  n = clip_halfplane(bx, by, n, 1.0, -1.0, sup[7], ax, ay);
+  const double a_out = shoelace(ax, ay, n) * (1.0 + 1e-12);
+  const double wh = (double)c.w * (double)c.h;
+  const double rlo = a_in / wh, rhi = a_out / wh;
+  ratio_lo[pair] = rlo; ratio_hi[pair] = rhi;
+  if (nh <= min_hits) return;                                  // densify:898 -> dropped
+  if (!exact_all && rlo >= thr + near_eps) {
+    keep_out[pair] = 1; ratio_out[pair] = rlo; area_out[pair] = a_in; flags_out[pair] = 16;
+  } else if (!exact_all && rhi < thr - near_eps) {
+    ratio_out[pair] = rhi; area_out[pair] = a_out; flags_out[pair] = 16;
+  } else {
+    need[pair] = 1;
+  }
+}
+
+// candidate capacity plan: cap = need ? (caps_in ? caps_in : min(n_hit, cap_max)) : 0,
+// cand_offsets = exclusive scan (single CTA).
+__global__ void __launch_bounds__(1024) cand_plan_kernel(
+    const int32_t* __restrict__ n_hit, const uint8_t* __restrict__ need,
+    const int32_t* __restrict__ caps_in, int64_t n_pairs, int cap_max,
+    int64_t* __restrict__ cand_offsets) {
+  __shared__ long long sm[33];
+  long long carry = 0;
+  for (int64_t s = 0; s < n_pairs; s += 1024) {
+    const int64_t i = s + threadIdx.x;
+    long long v = 0;
+    if (i < n_pairs && need[i]) {
+      const int h = caps_in ? caps_in[i] : n_hit[i];
+      v = (caps_in || h < cap_max) ? h : cap_max;
+      if (v < 1) v = 1;
+    }
+    long long tot;
+    const long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
+    if (i < n_pairs) cand_offsets[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) cand_offsets[n_pairs] = carry;
 }
 
 // ---- exact hull + area per pair ----------------------------------------------
@@ -612,13 +715,15 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     const int32_t* __restrict__ cand_count, const int32_t* __restrict__ n_hit, int64_t n_pairs,
     const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
     double thr, double near_eps, double* __restrict__ area_out, double* __restrict__ ratio_out,
-    uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out) {
+    uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out,
+    const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev) {
   __shared__ float2 buf[kHullBuf];
   __shared__ float2 lower[kHullChain];
   __shared__ float2 upper[kHullChain];
   __shared__ int s_h, s_nl, s_nu, s_flags, s_col;
-  const int64_t pair = blockIdx.x;
-  if (pair >= n_pairs) return;
+  if (blockIdx.x >= n_pairs) return;
+  if (n_sub_dev && (int64_t)blockIdx.x >= *n_sub_dev) return;
+  const int64_t pair = pair_map ? (int64_t)pair_map[blockIdx.x] : (int64_t)blockIdx.x;
   const int tid = threadIdx.x;
   const int64_t off = cand_offsets[pair];
   const int cap = (int)(cand_offsets[pair + 1] - off);
@@ -827,18 +932,34 @@ int ptgs_visibility_count(const float* px, const float* py, const float* pz,
   return launch_sweep<1>(a, st);
 }
 
-int ptgs_visibility_polygon(const float* px, const float* py, const float* pz,
-                            const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
-                            const int64_t* cam_offsets, const int32_t* cam_index,
-                            const int32_t* n_hit, const uint64_t* pivot, const uint64_t* extreme,
-                            int64_t n_pairs, float* poly, ptgs_stream_t stream) {
+int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
+                           const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
+                           const int64_t* cam_offsets, const int32_t* cam_index,
+                           const int32_t* n_hit, const uint64_t* pivot, const uint64_t* extreme,
+                           int64_t n_pairs, int32_t min_hits, double ratio_threshold,
+                           double near_eps, int32_t exact_all, float* poly, double* ratio_lo,
+                           double* ratio_hi, uint8_t* need, double* area, double* ratio,
+                           uint8_t* keep, uint8_t* flags, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
   PTGS_REQUIRE(n_pairs >= 0, "n_pairs");
   if (n_pairs == 0) return PTGS_OK;
-  PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && n_hit && pivot && extreme && poly,
+  PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && n_hit && pivot && extreme && poly &&
+                   ratio_lo && ratio_hi && need && area && ratio && keep && flags,
                "arguments");
-  polygon_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-      px, py, pz, pt_offsets, n_blocks, cameras, cam_offsets, cam_index, n_hit, pivot, extreme, poly);
+  bounds_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      px, py, pz, pt_offsets, n_blocks, cameras, cam_offsets, cam_index, n_hit, pivot, extreme,
+      min_hits, ratio_threshold, near_eps, exact_all, poly, ratio_lo, ratio_hi, need, area, ratio,
+      keep, flags);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need, const int32_t* caps_in,
+                         int64_t n_pairs, int32_t cap_max, int64_t* cand_offsets,
+                         ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_pairs >= 0 && n_hit && need && cand_offsets && cap_max >= 1, "arguments");
+  cand_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_hit, need, caps_in, n_pairs, cap_max,
+                                                       cand_offsets);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
@@ -846,9 +967,9 @@ int ptgs_visibility_polygon(const float* px, const float* py, const float* pz,
 int ptgs_visibility_candidates(const float* px, const float* py, const float* pz,
                                const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
                                const int64_t* cam_offsets, const int32_t* cam_index,
-                               int32_t cam_split, const float* poly, const int64_t* cand_offsets,
-                               float* cand_uv, int32_t* cand_count, void* workspace,
-                               size_t workspace_bytes, ptgs_stream_t stream) {
+                               int32_t cam_split, const int32_t* pair_map, const float* poly,
+                               const int64_t* cand_offsets, float* cand_uv, int32_t* cand_count,
+                               void* workspace, size_t workspace_bytes, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
   PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && poly && cand_offsets && cand_count,
                "arguments");
@@ -868,7 +989,7 @@ int ptgs_visibility_candidates(const float* px, const float* py, const float* pz
   a.px = px; a.py = py; a.pz = pz; a.pt_offsets = pt_offsets; a.n_blocks = n_blocks;
   a.cameras = cameras; a.cam_offsets = cam_offsets; a.cam_index = cam_index;
   a.cam_split = cam_split; a.item_prefix = item_prefix;
-  a.poly = poly; a.cand_offsets = cand_offsets; a.cand_uv = (float2*)cand_uv; a.cand_count = cand_count;
+  a.pair_map = pair_map; a.poly = poly; a.cand_offsets = cand_offsets; a.cand_uv = (float2*)cand_uv; a.cand_count = cand_count;
   return launch_sweep<2>(a, st);
 }
 
@@ -876,14 +997,15 @@ int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* cand_count, const int32_t* n_hit, int64_t n_pairs,
                          const int32_t* pair_cam, const float* cameras, int32_t min_hits,
                          double ratio_threshold, double near_eps, double* area, double* ratio,
-                         uint8_t* keep, uint8_t* flags, ptgs_stream_t stream) {
+                         uint8_t* keep, uint8_t* flags, const int32_t* pair_map,
+                         const int64_t* n_sub_dev, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_pairs >= 0 && n_pairs < (1ll << 31), "n_pairs");
   if (n_pairs == 0) return PTGS_OK;
   PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
                "arguments");
   hull_kernel<<<(unsigned)n_pairs, kHullThreads, 0, (cudaStream_t)stream>>>(
       (const float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-      ratio_threshold, near_eps, area, ratio, keep, flags);
+      ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

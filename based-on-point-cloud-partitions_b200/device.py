@@ -51,6 +51,9 @@ class VisibilityResult:
     flags: torch.Tensor        # (P,) uint8
     cand_count: torch.Tensor   # (P,) int32
     rounds: int = 1
+    ratio_lo: torch.Tensor = None   # (P,) float64 lower / upper bound of the ratio
+    ratio_hi: torch.Tensor = None
+    n_exact: int = None             # pairs that went through the exact hull
 
 
 @dataclass
@@ -277,23 +280,34 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
-               cand_capacity=2048, cam_split=None, timer=None) -> VisibilityResult:
-    """A7-A9 for every (block, camera) pair: sweep 1 (counts, pivot, extremes),
-    inner polygons, sweep 2 (hull candidates), exact hull area, keep decision."""
+               cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False) -> VisibilityResult:
+    """A7-A9 for every (block, camera) pair.
+
+    sweep 1 (hit counts, pivot, 8 extremes) -> area bounds + early decision ->
+    for the undecided pairs only: sweep 2 (hull candidates) + exact hull area.
+    exact_ratio=True sends every pair with > min_hits hits through the exact
+    hull (ratio is then the reference's value for every pair; otherwise decided
+    pairs carry the deciding bound and flags bit4).  One host synchronisation
+    at the end (candidate-capacity check)."""
     lib = _lib.load()
     dev = cameras_d.device
     L = ds_offsets.shape[0] - 1
     P = int(cam_index.shape[0])
-    n_hit = torch.empty(max(P, 1), dtype=torch.int32, device=dev)
-    pivot = torch.empty(max(P, 1), dtype=torch.int64, device=dev)
-    extreme = torch.empty(max(P, 1) * 8, dtype=torch.int64, device=dev)
-    cand_count = torch.empty(max(P, 1), dtype=torch.int32, device=dev)
-    area = torch.zeros(max(P, 1), dtype=torch.float64, device=dev)
-    ratio = torch.zeros(max(P, 1), dtype=torch.float64, device=dev)
-    keep = torch.zeros(max(P, 1), dtype=torch.uint8, device=dev)
-    flags = torch.zeros(max(P, 1), dtype=torch.uint8, device=dev)
+    Pa = max(P, 1)
+    n_hit = torch.empty(Pa, dtype=torch.int32, device=dev)
+    area = torch.empty(Pa, dtype=torch.float64, device=dev)
+    ratio = torch.empty(Pa, dtype=torch.float64, device=dev)
+    keep = torch.empty(Pa, dtype=torch.uint8, device=dev)
+    flags = torch.empty(Pa, dtype=torch.uint8, device=dev)
+    cand_count = torch.empty(Pa, dtype=torch.int32, device=dev)
     if P == 0:
         return VisibilityResult(n_hit[:0], area[:0], ratio[:0], keep[:0], flags[:0], cand_count[:0], 0)
+    pivot = torch.empty(P, dtype=torch.int64, device=dev)
+    extreme = torch.empty(P * 8, dtype=torch.int64, device=dev)
+    ratio_lo = torch.empty(P, dtype=torch.float64, device=dev)
+    ratio_hi = torch.empty(P, dtype=torch.float64, device=dev)
+    need = torch.empty(P, dtype=torch.uint8, device=dev)
+    poly = torch.empty((P, POLY_FLOATS), dtype=torch.float32, device=dev)
     if cam_split is None:
         cam_split = pick_cam_split(int(ds_x.shape[0]), L)
     ws = _ws(lib.ptgs_visibility_workspace_bytes(L), dev)
@@ -305,52 +319,78 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                                     _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), cam_split,
                                     _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(ws), ws.numel(), st))
     mark("vis_sweep1_count")
-    poly = torch.empty((P, POLY_FLOATS), dtype=torch.float32, device=dev)
-    check(lib.ptgs_visibility_polygon(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
-                                      _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), _ptr(n_hit),
-                                      _ptr(pivot), _ptr(extreme), P, _ptr(poly), st))
-    mark("vis_polygon")
-    caps = torch.full((P,), int(cand_capacity), dtype=torch.int64, device=dev)
+    check(lib.ptgs_visibility_bounds(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
+                                     _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), _ptr(n_hit),
+                                     _ptr(pivot), _ptr(extreme), P, int(min_hits), float(threshold),
+                                     float(near_eps), 1 if exact_ratio else 0, _ptr(poly), _ptr(ratio_lo),
+                                     _ptr(ratio_hi), _ptr(need), _ptr(area), _ptr(ratio), _ptr(keep),
+                                     _ptr(flags), st))
+    mark("vis_bounds")
+    sub_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
+    sub_idx = torch.empty(P, dtype=torch.int32, device=dev)
+    sub_pos = torch.empty(P, dtype=torch.int32, device=dev)
+    cand_off = torch.empty(P + 1, dtype=torch.int64, device=dev)
+    caps_in = None
     rounds = 0
+    n_exact = None
     while True:
         rounds += 1
-        cand_off = torch.zeros(P + 1, dtype=torch.int64, device=dev)
-        torch.cumsum(caps, 0, out=cand_off[1:])
-        total = int(cand_off[P].item())
+        # sub-list of the pairs that need the exact hull (device side, no sync)
+        check(lib.ptgs_select_cameras(_ptr(need), _ptr(cam_offsets), _ptr(cam_index), L, _ptr(sub_off),
+                                      _ptr(sub_idx), _ptr(sub_pos), st))
+        check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), P, int(cand_capacity),
+                                       _ptr(cand_off), st))
+        if caps_in is None:
+            total = P * int(cand_capacity)            # upper bound, no sync needed
+        else:
+            total = int(cand_off[P].item())
         cand_uv = torch.empty((max(total, 1), 2), dtype=torch.float32, device=dev)
         check(lib.ptgs_visibility_init(P, None, None, None, _ptr(cand_count), st))
+        mark("vis_plan")
         check(lib.ptgs_visibility_candidates(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
-                                             _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
-                                             cam_split, _ptr(poly), _ptr(cand_off), _ptr(cand_uv),
+                                             _ptr(cameras_d), _ptr(sub_off), _ptr(sub_idx), cam_split,
+                                             _ptr(sub_pos), _ptr(poly), _ptr(cand_off), _ptr(cand_uv),
                                              _ptr(cand_count), _ptr(ws), ws.numel(), st))
         mark("vis_sweep2_candidates")
         check(lib.ptgs_visibility_hull(_ptr(cand_uv), _ptr(cand_off), _ptr(cand_count), _ptr(n_hit), P,
                                        _ptr(cam_index), _ptr(cameras_d), int(min_hits),
                                        float(threshold), float(near_eps), _ptr(area), _ptr(ratio),
-                                       _ptr(keep), _ptr(flags), st))
+                                       _ptr(keep), _ptr(flags), _ptr(sub_pos), _ptr(sub_off[L:]), st))
         mark("vis_hull")
-        over = cand_count.to(torch.int64) > caps
-        if not bool(over.any().item()):
+        # the one synchronisation: [overflowed pairs, hull budget exceeded, exact pairs]
+        bad = need.bool() & ((flags & 4) != 0)
+        stat = torch.stack([bad.sum(), ((flags & 8) != 0).sum(), sub_off[L]]).cpu()
+        if n_exact is None:
+            n_exact = int(stat[2])
+        if int(stat[1]):
+            raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
+        if int(stat[0]) == 0:
             break
         if rounds > 3:
             raise RuntimeError("visibility: candidate capacity did not converge")
-        # exact need is known (cand_count keeps counting past the capacity)
-        caps = torch.where(over, cand_count.to(torch.int64), torch.clamp(cand_count.to(torch.int64), min=1))
-    if bool((flags & 8).any().item()):
-        raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
-    return VisibilityResult(n_hit, area, ratio, keep, flags, cand_count, rounds)
+        # re-run only the overflowed pairs with their exact candidate counts
+        need = bad.to(torch.uint8)
+        caps_in = cand_count.clone()
+    mark("vis_check")
+    res = VisibilityResult(n_hit, area, ratio, keep, flags, cand_count, rounds)
+    res.ratio_lo, res.ratio_hi, res.n_exact = ratio_lo, ratio_hi, n_exact
+    return res
 
 
-def select_cameras(keep, cam_offsets, cam_index):
+def select_cameras(keep, cam_offsets, cam_index, want_pos=False, sync=True):
+    """A9: per block compaction of the kept cameras (device CSR)."""
     lib = _lib.load()
     dev = cam_offsets.device
     L = cam_offsets.shape[0] - 1
     kept_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
     kept_idx = torch.empty(max(int(cam_index.shape[0]), 1), dtype=torch.int32, device=dev)
+    kept_pos = torch.empty_like(kept_idx) if want_pos else None
     check(lib.ptgs_select_cameras(_ptr(keep), _ptr(cam_offsets), _ptr(cam_index), L, _ptr(kept_off),
-                                  _ptr(kept_idx), _stream()))
+                                  _ptr(kept_idx), _ptr(kept_pos), _stream()))
+    if not sync:
+        return (kept_off, kept_idx, kept_pos) if want_pos else (kept_off, kept_idx)
     n = int(kept_off[L].item())
-    return kept_off, kept_idx[:n]
+    return (kept_off, kept_idx[:n], kept_pos[:n]) if want_pos else (kept_off, kept_idx[:n])
 
 
 def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen=False):
@@ -396,8 +436,8 @@ class _Timer:
 def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np.ndarray,
                      threshold: int, man_trans: np.ndarray | None = None, radius_filter: bool = True,
                      do_visibility: bool = True, time_stages: bool = False,
-                     cam_shard: tuple | None = None, split_xyz: torch.Tensor | None = None
-                     ) -> PartitionDeviceResult:
+                     cam_shard: tuple | None = None, split_xyz: torch.Tensor | None = None,
+                     exact_ratio: bool = False) -> PartitionDeviceResult:
     """run_DataPartition (shen_partition_utils.py:57-93) on the device.
 
     xyz         (N,3) float32 CUDA tensor: the scene cloud as fetchPly returns it.
@@ -410,6 +450,8 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
                 the split reads the un-rotated PLY, shen_partition_utils.py:62).
     cam_shard   (rank, world): this process evaluates only cameras
                 c % world == rank in the visibility pass (multi-GPU).
+    exact_ratio every pair's exact hull ratio (default: pairs decided by the
+                area bounds skip the exact hull, see visibility()).
     """
     assert xyz.is_cuda
     dev = xyz.device
@@ -452,7 +494,7 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
         ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx)
         tm.mark("A6_voxel")
         cams_d = torch.from_numpy(np.ascontiguousarray(cam_records, dtype=np.float32)).to(dev)
-        vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx)
+        vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx, exact_ratio=exact_ratio)
         tm.mark("A7_A8_visibility")
         k_off, k_idx = select_cameras(vis.keep, cam_off, cam_idx)
         tm.mark("A9_select")

@@ -250,15 +250,30 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  * All three are accumulated with atomics and must be pre-initialised by
  * ptgs_visibility_init (also zeroes cand_count).
  *
- * ptgs_visibility_polygon: per pair the inner polygon (the extreme hits that
- * survive the reference's pivot-row rule, see below) as <= 8 half planes.
+ * ptgs_visibility_bounds: per pair
+ *   - the inner polygon (the extreme hits that survive the reference's
+ *     pivot-row rule, see below) as <= 8 half planes -> `poly`, and its area
+ *     / (W*H) -> ratio_lo: a lower bound of the reference's ratio;
+ *   - the outer octagon (intersection of the 8 supporting half planes of sweep
+ *     1) -> ratio_hi: an upper bound;
+ *   - the early decision: n_hit <= min_hits -> dropped (:898); ratio_lo >=
+ *     thr + near_eps -> kept; ratio_hi < thr - near_eps -> dropped.  Decided
+ *     pairs get keep / ratio (= the deciding bound) / area and flags bit4; the
+ *     others get need[p] = 1 and must go through sweep 2 + the exact hull.
+ *     exact_all != 0 disables the early decision (every pair with enough hits
+ *     gets its exact ratio).
+ * ptgs_visibility_plan: cand_offsets[P+1] = exclusive scan of the candidate
+ *   capacities: need ? (caps_in ? caps_in[p] : min(n_hit[p], cap_max)) : 0.
  *
  * Sweep 2 (ptgs_visibility_candidates): re-projects and emits every hit that
  * is (a) part of the point set the reference's scan effectively uses -- the
  * pivot plus all hits with v > v_pivot: hits on the pivot's row are popped by
  * the `cross <= 0` rule and the farthest of them is skipped by
  * `sorted_points[1:]` (:513-527) -- and (b) not strictly inside the inner
- * polygon.  cand_uv[cand_offsets[p] + k] (float2, k < capacity of the pair);
+ * polygon.  The (block, camera) lists given to sweep 2 may be a sub-list of the
+ * pairs (the undecided ones); pair_map[slot] then names the pair id p of every
+ * slot of that sub-list (NULL = identity), poly / cand_offsets / cand_count are
+ * always indexed by p.  cand_uv[cand_offsets[p] + k] (float2, k < capacity of the pair);
  * cand_count[p] receives the number of candidates even when it exceeds the
  * pair's capacity (the caller then re-runs the pair with a larger capacity).
  *
@@ -269,7 +284,9 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  * the first hull edge after the pivot (the one configuration in which the
  * reference's result depends on libm atan2 ties); bit2 = candidate capacity
  * overflow (result invalid, re-run); bit3 = hull larger than the kernel's
- * vertex budget (result invalid).
+ * vertex budget (result invalid); bit4 = decided from the bounds (set by
+ * ptgs_visibility_bounds).  One CTA per entry of pair_map (NULL = every pair);
+ * n_pairs bounds the grid, *n_sub_dev (device, may be NULL) the live entries.
  * cam_split >= 1 splits every block's camera list into that many work items
  * per point tile (load balance for small inputs); results do not depend on it.
  */
@@ -285,19 +302,28 @@ int ptgs_visibility_count(const float* px, const float* py, const float* pz,
                           void* workspace, size_t workspace_bytes,
                           ptgs_stream_t stream);
 #define PTGS_POLY_FLOATS 28 /* [0]=n_edges [1]=v_pivot [2]=u_pivot [3]=margin, 8 x (a,b,c) */
-int ptgs_visibility_polygon(const float* px, const float* py, const float* pz,
-                            const int64_t* pt_offsets, int32_t n_blocks,
-                            const float* cameras, const int64_t* cam_offsets,
-                            const int32_t* cam_index, const int32_t* n_hit,
-                            const uint64_t* pivot, const uint64_t* extreme,
-                            int64_t n_pairs, float* poly,
-                            ptgs_stream_t stream);
+int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
+                           const int64_t* pt_offsets, int32_t n_blocks,
+                           const float* cameras, const int64_t* cam_offsets,
+                           const int32_t* cam_index, const int32_t* n_hit,
+                           const uint64_t* pivot, const uint64_t* extreme,
+                           int64_t n_pairs, int32_t min_hits,
+                           double ratio_threshold, double near_eps,
+                           int32_t exact_all, float* poly, double* ratio_lo,
+                           double* ratio_hi, uint8_t* need, double* area,
+                           double* ratio, uint8_t* keep, uint8_t* flags,
+                           ptgs_stream_t stream);
+int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need,
+                         const int32_t* caps_in, int64_t n_pairs,
+                         int32_t cap_max, int64_t* cand_offsets,
+                         ptgs_stream_t stream);
 int ptgs_visibility_candidates(const float* px, const float* py,
                                const float* pz, const int64_t* pt_offsets,
                                int32_t n_blocks, const float* cameras,
                                const int64_t* cam_offsets,
                                const int32_t* cam_index, int32_t cam_split,
-                               const float* poly, const int64_t* cand_offsets,
+                               const int32_t* pair_map, const float* poly,
+                               const int64_t* cand_offsets,
                                float* cand_uv, int32_t* cand_count,
                                void* workspace, size_t workspace_bytes,
                                ptgs_stream_t stream);
@@ -307,15 +333,17 @@ int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
                          const float* cameras, int32_t min_hits,
                          double ratio_threshold, double near_eps, double* area,
                          double* ratio, uint8_t* keep, uint8_t* flags,
+                         const int32_t* pair_map, const int64_t* n_sub_dev,
                          ptgs_stream_t stream);
 
 /* A9 selection: per block compaction of the kept cameras (ascending order of
  * the block's camera list).  kept_offsets[L+1] int64, kept_index capacity =
- * cam_offsets[L]. */
+ * cam_offsets[L]; kept_pos (may be NULL, same capacity) receives the pair
+ * position (index into cam_index) of every kept entry. */
 int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
                         const int32_t* cam_index, int32_t n_blocks,
                         int64_t* kept_offsets, int32_t* kept_index,
-                        ptgs_stream_t stream);
+                        int32_t* kept_pos, ptgs_stream_t stream);
 
 /* ------------------------------------------------------------------ *
  * Coverage sweep (config 5; the camera x all-points pass of the Vast path,

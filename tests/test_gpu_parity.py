@@ -154,10 +154,14 @@ def test_voxel_downsample():
 
 
 def _vis_compare(vis, ds_lists, cam_lists, recs, thr=O.VISIBLE_RATE):
+    """Per pair against the oracle.  Exact pairs: ratio to 1e-12; pairs decided
+    from the area bounds (flags bit4): keep identical and lo <= exact <= hi."""
     n_hit = vis.n_hit.cpu().numpy()
     ratio = vis.ratio.cpu().numpy()
     keep = vis.keep.cpu().numpy().astype(bool)
     flags = vis.flags.cpu().numpy()
+    rlo = vis.ratio_lo.cpu().numpy()
+    rhi = vis.ratio_hi.cpu().numpy()
     p = 0
     n_kept = 0
     for b, cl in enumerate(cam_lists):
@@ -167,9 +171,18 @@ def _vis_compare(vis, ds_lists, cam_lists, recs, thr=O.VISIBLE_RATE):
             if flags[p] & 2:          # first-ray collinear: atan2-tie dependent, reported apart
                 p += 1
                 continue
-            assert abs(ratio[p] - rt) <= 1e-12 * max(1.0, abs(rt)), (b, c, ratio[p], rt)
-            if not (flags[p] & 1):
+            if nh > O.MIN_HITS:
+                hit, u, v = O.project_port(ds_lists[b], recs[c])
+                collinear = O.first_ray_collinear(np.stack([u[hit], v[hit]], 1).astype(np.float64))
+                if not collinear:
+                    assert rlo[p] <= rt * (1 + 1e-12) + 1e-15, (b, c, rlo[p], rt)
+                    assert rhi[p] >= rt * (1 - 1e-12), (b, c, rhi[p], rt)
+            if flags[p] & 16:
                 assert keep[p] == kp, (b, c, ratio[p], rt)
+            else:
+                assert abs(ratio[p] - rt) <= 1e-12 * max(1.0, abs(rt)), (b, c, ratio[p], rt)
+                if not (flags[p] & 1):
+                    assert keep[p] == kp, (b, c, ratio[p], rt)
             n_kept += int(kp)
             p += 1
     assert p == len(n_hit)
@@ -184,7 +197,8 @@ def test_visibility_blocks(seed, obl):
     assert np.array_equal(recs[3], O.camera_record(cams.R[3], cams.T[3], cams.FoVx[3], cams.FoVy[3],
                                                    sc.width, sc.height))
     centers = D.camera_centers(cams.R, cams.T)
-    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold)
+    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, exact_ratio=True)
+    assert not bool((res.vis.flags & 16).any())
     ds_off = res.ds_offsets.cpu().numpy()
     ds = np.stack([res.ds_x.cpu().numpy(), res.ds_y.cpu().numpy(), res.ds_z.cpu().numpy()], 1)
     ds_lists = [ds[ds_off[b]:ds_off[b + 1]] for b in range(len(ds_off) - 1)]
@@ -205,6 +219,20 @@ def test_visibility_blocks(seed, obl):
     k2 = _vis_compare(vis2, ds_lists, cam_lists, recs, thr=0.93)
     assert 0 < k2 < len(vis2.keep)
     assert torch.equal(vis2.n_hit, res.vis.n_hit)
+    # default mode: pairs decided by the area bounds skip the exact hull; the
+    # keep decisions are identical to the exact pass for every threshold
+    for thr in (0.2, O.VISIBLE_RATE, 0.7, 0.93):
+        ve = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets,
+                          res.cam_index, threshold=thr, exact_ratio=True)
+        vd = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets,
+                          res.cam_index, threshold=thr)
+        assert torch.equal(ve.keep, vd.keep), thr
+        assert vd.n_exact <= ve.n_exact
+        ex = (vd.flags & 16) == 0
+        assert torch.equal(ve.ratio[ex], vd.ratio[ex])
+        assert bool((vd.ratio_lo <= ve.ratio * (1 + 1e-12) + 1e-15).all())
+        assert bool((vd.ratio_hi >= ve.ratio * (1 - 1e-12)).all())
+    _vis_compare(vd, ds_lists, cam_lists, recs, thr=0.93)
 
 
 def _unit_camera(W=64.0, H=64.0, front_axis=1):
@@ -223,7 +251,7 @@ def _run_single(points, recs):
     cams = torch.from_numpy(np.stack(recs)).to(DEV)
     coff = torch.tensor([0, len(recs)], dtype=torch.int64, device=DEV)
     cidx = torch.arange(len(recs), dtype=torch.int32, device=DEV)
-    return D.visibility(x, y, z, off, cams, coff, cidx, cand_capacity=8), pts
+    return D.visibility(x, y, z, off, cams, coff, cidx, cand_capacity=8, exact_ratio=True), pts
 
 
 def test_visibility_adversarial_hulls():
@@ -293,7 +321,7 @@ def test_full_partition_vs_oracle():
     cams = scene_cameras(sc)
     recs = D.camera_records(cams.R, cams.T, cams.FoVx, cams.FoVy, cams.width, cams.height)
     centers = D.camera_centers(cams.R, cams.T)
-    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold)
+    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, exact_ratio=True)
     want = O.run_partition(sc.xyz, cams, sc.threshold, centers=centers)
     assert np.array_equal(res.keep_mask.cpu().numpy().astype(bool), want.keep_mask)
     assert res.root_bounds == want.root_bounds
@@ -313,4 +341,8 @@ def test_full_partition_vs_oracle():
     kept = _csr_lists(res.kept_offsets, res.kept_index)
     if ok.all():
         for g, w in zip(kept, want.kept_cameras):
+            assert set(g.tolist()) == set(w.tolist())
+        # the default (bounds-decided) mode selects the same cameras
+        res2 = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold)
+        for g, w in zip(_csr_lists(res2.kept_offsets, res2.kept_index), want.kept_cameras):
             assert set(g.tolist()) == set(w.tolist())
