@@ -674,30 +674,42 @@ __global__ void __launch_bounds__(128) bounds_kernel(
 // cand_offsets = exclusive scan (single CTA).
 __global__ void __launch_bounds__(1024) cand_plan_kernel(
     const int32_t* __restrict__ n_hit, const uint8_t* __restrict__ need,
-    const int32_t* __restrict__ caps_in, int64_t n_pairs, int cap_max,
-    int64_t* __restrict__ cand_offsets) {
+    const int32_t* __restrict__ caps_in, const float* __restrict__ poly, int64_t n_pairs,
+    int cap_max, int64_t pool, int64_t* __restrict__ cand_offsets) {
   __shared__ long long sm[33];
   long long carry = 0;
   for (int64_t s = 0; s < n_pairs; s += 1024) {
     const int64_t i = s + threadIdx.x;
     long long v = 0;
     if (i < n_pairs && need[i]) {
-      const int h = caps_in ? caps_in[i] : n_hit[i];
-      v = (caps_in || h < cap_max) ? h : cap_max;
+      if (caps_in) {
+        v = caps_in[i];
+      } else {
+        // candidates are a fraction of the hits (a third for the worst shapes
+        // measured): half of them, at least cap_max, never more than the hits
+        const int h = n_hit[i];
+        const int want = (h >> 1) > cap_max ? (h >> 1) : cap_max;
+        v = h < want ? h : want;
+        // no inner polygon (degenerate extremes): every hit is a candidate
+        if (poly && poly[i * kPolyFloats] == 0.0f) v = h;
+      }
       if (v < 1) v = 1;
     }
     long long tot;
     const long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
-    if (i < n_pairs) cand_offsets[i] = carry + ex;
+    // offsets clamped to the pool: pairs past it get a shrunken (or empty)
+    // segment, overflow and are re-run by the caller
+    if (i < n_pairs) cand_offsets[i] = (carry + ex) < pool ? (carry + ex) : pool;
     carry += tot;
   }
-  if (threadIdx.x == 0) cand_offsets[n_pairs] = carry;
+  if (threadIdx.x == 0) cand_offsets[n_pairs] = carry < pool ? carry : pool;
 }
 
 // ---- exact hull + area per pair ----------------------------------------------
 constexpr int kHullThreads = 128;
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
+constexpr int kHullFilterMin = 192; // candidates above which the directional pre-filter runs
 
 __device__ __forceinline__ bool lex_less(float2 a, float2 b) {
   return a.x < b.x || (a.x == b.x && a.y < b.y);
@@ -710,8 +722,105 @@ __device__ __forceinline__ double cross3(float2 a, float2 b, float2 c) {
   return __dsub_rn(__dmul_rn(abx, acy), __dmul_rn(aby, acx));
 }
 
+// ---- directional pre-filter of a pair's candidates (in place) ---------------------
+// One round: the extreme candidates along 64 evenly spaced directions (warp w
+// owns 16 of them) form, in direction order, a closed chain; a point strictly
+// to the left of every edge of that chain has winding number >= 1 about it, so
+// it lies inside the convex hull of the chain's vertices and can never be a
+// hull vertex (nor touch the reference's `cross <= 0` rule).  Such points are
+// dropped; everything within `margin` of an edge is kept.  The float32 edge
+// evaluation and margin are those of sweep 2 (ptgs_visibility_bounds).
+constexpr int kFiltDirs = 64;
+struct FilterSmem {
+  float2 dir[kFiltDirs];
+  int idx[kFiltDirs];
+  float2 vert[kFiltDirs];
+  float ea[kFiltDirs], eb[kFiltDirs], ec[kFiltDirs];
+  int m;
+  int out;
+  int scan[33];
+};
+
+__device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  // 1. extremes
+  float best[16];
+  int bi[16];
+#pragma unroll
+  for (int d = 0; d < 16; ++d) { best[d] = -__int_as_float(0x7f800000); bi[d] = 0; }
+  for (int i = lane; i < n; i += 32) {
+    const float2 q = cu[i];
+#pragma unroll
+    for (int d = 0; d < 16; ++d) {
+      const float2 dv = F.dir[w * 16 + d];
+      const float dot = fmaf(q.x, dv.x, q.y * dv.y);
+      if (dot > best[d]) { best[d] = dot; bi[d] = i; }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 16; ++d) {
+    const uint32_t key = order_key(best[d]);
+    const uint32_t mk = __reduce_max_sync(kFullMask, key);
+    const unsigned who = __ballot_sync(kFullMask, key == mk);
+    const int id = __shfl_sync(kFullMask, bi[d], __ffs(who) - 1);
+    if (lane == 0) F.idx[w * 16 + d] = id;
+  }
+  __syncthreads();
+  if (tid < kFiltDirs) F.vert[tid] = cu[F.idx[tid]];
+  __syncthreads();
+  if (tid == 0) {
+    // distinct consecutive vertices, edges as float half planes a*u + b*v + c
+    float2 v[kFiltDirs];
+    int m = 0;
+    for (int k = 0; k < kFiltDirs; ++k) {
+      const float2 q = F.vert[k];
+      if (m && v[m - 1].x == q.x && v[m - 1].y == q.y) continue;
+      v[m++] = q;
+    }
+    while (m > 1 && v[m - 1].x == v[0].x && v[m - 1].y == v[0].y) --m;
+    if (m >= 3) {
+      for (int i = 0; i < m; ++i) {
+        const int k = (i + 1 == m) ? 0 : i + 1;
+        const double a = -((double)v[k].y - (double)v[i].y), b = (double)v[k].x - (double)v[i].x;
+        F.ea[i] = (float)a;
+        F.eb[i] = (float)b;
+        F.ec[i] = (float)(-(a * (double)v[i].x + b * (double)v[i].y));
+      }
+    }
+    F.m = m >= 3 ? m : 0;
+    F.out = 0;
+  }
+  __syncthreads();
+  const int m = F.m;
+  if (m == 0) return n;
+  // 2. filter + in-place compaction, 128 points per step (reads of a step finish
+  //    before its writes, which land at or before the step's first position)
+  for (int base = 0; base < n; base += kHullThreads) {
+    const int i = base + tid;
+    float2 q = make_float2(0.f, 0.f);
+    int kp = 0;
+    if (i < n) {
+      q = cu[i];
+      bool inside = true;
+      for (int e = 0; e < m && inside; ++e) {
+        const float f = __fadd_rn(__fadd_rn(__fmul_rn(F.ea[e], q.x), __fmul_rn(F.eb[e], q.y)), F.ec[e]);
+        inside = f > margin;
+      }
+      kp = inside ? 0 : 1;
+    }
+    int tot;
+    const int ex = block_exclusive_sum<int, kHullThreads>(kp, F.scan, &tot);
+    const int o = F.out;
+    if (kp) cu[o + ex] = q;
+    __syncthreads();
+    if (tid == 0) F.out = o + tot;
+    __syncthreads();
+  }
+  return F.out;
+}
+
 __global__ void __launch_bounds__(kHullThreads) hull_kernel(
-    const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
+    float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
     const int32_t* __restrict__ cand_count, const int32_t* __restrict__ n_hit, int64_t n_pairs,
     const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
     double thr, double near_eps, double* __restrict__ area_out, double* __restrict__ ratio_out,
@@ -729,10 +838,38 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
   const int cap = (int)(cand_offsets[pair + 1] - off);
   int K = cand_count[pair];
   int flags = 0;
-  if (K > cap) { flags |= 4; K = cap; }
+  if (K > cap) {
+    // candidate capacity overflow: the result would be invalid, the caller
+    // re-runs the pair with cand_count[pair] slots
+    if (tid == 0) {
+      area_out[pair] = 0.0; ratio_out[pair] = 0.0; keep_out[pair] = 0; flags_out[pair] = 4;
+    }
+    return;
+  }
   if (tid == 0) { s_h = 0; s_flags = 0; s_col = 0; }
   __syncthreads();
   const float inf = __int_as_float(0x7f800000);
+  float2* cu = cand_uv + off;
+  if (K > kHullFilterMin) {
+    __shared__ FilterSmem F;
+    if (tid < kFiltDirs) {
+      float sn, cs;
+      sincospif((float)tid * (2.0f / kFiltDirs), &sn, &cs);
+      F.dir[tid] = make_float2(cs, sn);
+    }
+    __syncthreads();
+    const float* rec = cameras + (int64_t)pair_cam[pair] * kCamFloats;
+    const float Dm = fmaxf(rec[16], rec[17]);
+    const float margin = 4e-6f * Dm * Dm;
+    for (int it = 0; it < 4 && K > kHullFilterMin; ++it) {
+      const int kn = filter_round(cu, K, margin, F);
+      const bool progress = kn < K - K / 8;
+      K = kn;
+      if (!progress) break;
+    }
+    __threadfence_block();
+    __syncthreads();
+  }
   int pos = 0;
   bool single_round = true;
   int rounds = 0;
@@ -744,7 +881,7 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     int n2 = 1;
     while (n2 < n) n2 <<= 1;
     for (int i = tid; i < n2 - h; i += kHullThreads)
-      buf[h + i] = (i < m) ? cand_uv[off + pos + i] : make_float2(inf, inf);
+      buf[h + i] = (i < m) ? cu[pos + i] : make_float2(inf, inf);
     __syncthreads();
     // bitonic sort of buf[0..n2) by (u, v)
     for (int k = 2; k <= n2; k <<= 1) {
@@ -955,11 +1092,13 @@ int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
 }
 
 int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need, const int32_t* caps_in,
-                         int64_t n_pairs, int32_t cap_max, int64_t* cand_offsets,
-                         ptgs_stream_t stream) {
-  PTGS_REQUIRE(n_pairs >= 0 && n_hit && need && cand_offsets && cap_max >= 1, "arguments");
-  cand_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_hit, need, caps_in, n_pairs, cap_max,
-                                                       cand_offsets);
+                         const float* poly, int64_t n_pairs, int32_t cap_max,
+                         int64_t pool_capacity,
+                         int64_t* cand_offsets, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_pairs >= 0 && n_hit && need && cand_offsets && cap_max >= 1 && pool_capacity >= 0,
+               "arguments");
+  cand_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_hit, need, caps_in, poly, n_pairs,
+                                                       cap_max, pool_capacity, cand_offsets);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
@@ -993,7 +1132,7 @@ int ptgs_visibility_candidates(const float* px, const float* py, const float* pz
   return launch_sweep<2>(a, st);
 }
 
-int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
+int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* cand_count, const int32_t* n_hit, int64_t n_pairs,
                          const int32_t* pair_cam, const float* cameras, int32_t min_hits,
                          double ratio_threshold, double near_eps, double* area, double* ratio,
@@ -1004,7 +1143,7 @@ int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
   PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
                "arguments");
   hull_kernel<<<(unsigned)n_pairs, kHullThreads, 0, (cudaStream_t)stream>>>(
-      (const float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
+      (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
       ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;

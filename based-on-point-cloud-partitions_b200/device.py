@@ -280,7 +280,8 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
-               cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False) -> VisibilityResult:
+               cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False,
+               cand_pool=None) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair.
 
     sweep 1 (hit counts, pivot, 8 extremes) -> area bounds + early decision ->
@@ -338,12 +339,13 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         # sub-list of the pairs that need the exact hull (device side, no sync)
         check(lib.ptgs_select_cameras(_ptr(need), _ptr(cam_offsets), _ptr(cam_index), L, _ptr(sub_off),
                                       _ptr(sub_idx), _ptr(sub_pos), st))
-        check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), P, int(cand_capacity),
-                                       _ptr(cand_off), st))
         if caps_in is None:
-            total = P * int(cand_capacity)            # upper bound, no sync needed
+            # fixed pool (no sync): pairs that do not fit overflow and are re-run
+            total = max(P * 256, 32 << 20) if cand_pool is None else int(cand_pool)
         else:
-            total = int(cand_off[P].item())
+            total = int(caps_in[need.bool()].sum().item())
+        check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), _ptr(poly), P, int(cand_capacity),
+                                       total, _ptr(cand_off), st))
         cand_uv = torch.empty((max(total, 1), 2), dtype=torch.float32, device=dev)
         check(lib.ptgs_visibility_init(P, None, None, None, _ptr(cand_count), st))
         mark("vis_plan")

@@ -263,7 +263,10 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  *     exact_all != 0 disables the early decision (every pair with enough hits
  *     gets its exact ratio).
  * ptgs_visibility_plan: cand_offsets[P+1] = exclusive scan of the candidate
- *   capacities: need ? (caps_in ? caps_in[p] : min(n_hit[p], cap_max)) : 0.
+ *   capacities: need ? (caps_in ? caps_in[p] : min(n_hit[p], max(cap_max,
+ *   n_hit[p]/2))) : 0 (n_hit[p] when the pair has no inner polygon: poly,
+ *   may be NULL), every offset clamped to pool_capacity (the size of the
+ *   caller's cand_uv pool in candidates; pairs that do not fit overflow).
  *
  * Sweep 2 (ptgs_visibility_candidates): re-projects and emits every hit that
  * is (a) part of the point set the reference's scan effectively uses -- the
@@ -277,7 +280,8 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  * cand_count[p] receives the number of candidates even when it exceeds the
  * pair's capacity (the caller then re-runs the pair with a larger capacity).
  *
- * ptgs_visibility_hull: exact convex hull (float64 orientation tests with the
+ * ptgs_visibility_hull (cand_uv is compacted in place by a directional
+ * pre-filter that drops candidates strictly inside the hull): exact convex hull (float64 orientation tests with the
  * reference's `cross <= 0` pop rule) of each pair's candidates, shoelace area
  * in float64, ratio = area / (W*H); keep = n_hit > min_hits && ratio >= thr.
  * flags: bit0 = |ratio - thr| <= near_eps; bit1 = another hit lies exactly on
@@ -314,9 +318,10 @@ int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
                            double* ratio, uint8_t* keep, uint8_t* flags,
                            ptgs_stream_t stream);
 int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need,
-                         const int32_t* caps_in, int64_t n_pairs,
-                         int32_t cap_max, int64_t* cand_offsets,
-                         ptgs_stream_t stream);
+                         const int32_t* caps_in, const float* poly,
+                         int64_t n_pairs, int32_t cap_max,
+                         int64_t pool_capacity,
+                         int64_t* cand_offsets, ptgs_stream_t stream);
 int ptgs_visibility_candidates(const float* px, const float* py,
                                const float* pz, const int64_t* pt_offsets,
                                int32_t n_blocks, const float* cameras,
@@ -327,7 +332,7 @@ int ptgs_visibility_candidates(const float* px, const float* py,
                                float* cand_uv, int32_t* cand_count,
                                void* workspace, size_t workspace_bytes,
                                ptgs_stream_t stream);
-int ptgs_visibility_hull(const float* cand_uv, const int64_t* cand_offsets,
+int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* cand_count, const int32_t* n_hit,
                          int64_t n_pairs, const int32_t* pair_cam,
                          const float* cameras, int32_t min_hits,

@@ -251,7 +251,7 @@ def _run_single(points, recs):
     cams = torch.from_numpy(np.stack(recs)).to(DEV)
     coff = torch.tensor([0, len(recs)], dtype=torch.int64, device=DEV)
     cidx = torch.arange(len(recs), dtype=torch.int32, device=DEV)
-    return D.visibility(x, y, z, off, cams, coff, cidx, cand_capacity=8, exact_ratio=True), pts
+    return D.visibility(x, y, z, off, cams, coff, cidx, cand_capacity=8, exact_ratio=True, cand_pool=300), pts
 
 
 def test_visibility_adversarial_hulls():

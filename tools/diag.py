@@ -47,3 +47,14 @@ print("ratio   pct[0,10,50,90,99,100]:", np.percentile(rt, [0, 10, 50, 90, 99, 1
 print("kept fraction", float(vis.keep.float().mean()), "flags", np.bincount(vis.flags.cpu().numpy(), minlength=16)[:16])
 M = np.diff(ds[0].cpu().numpy()); Cb = np.diff(coff.cpu().numpy())
 print("M_b", M.min(), M.max(), "C_b", Cb.min(), Cb.max(), "tests", int((M * Cb).sum()))
+ex = (vis.flags.cpu().numpy() & 16) == 0
+print("rounds", vis.rounds, "n_exact", vis.n_exact, "sum cand (exact pairs)", int(cc[ex].sum()), "max", int(cc.max()),
+      "sum min(nh,max(2048,nh/4)) over exact", int(np.minimum(nh[ex], np.maximum(2048, nh[ex] // 4)).sum()))
+gap = (vis.ratio_hi - vis.ratio_lo).cpu().numpy()
+print("bound gap pct[50,90,99,100]", np.percentile(gap, [50, 90, 99, 100]))
+tm = D.StageTimer(True); tm.mark("start")
+D.visibility(ds[1], ds[2], ds[3], ds[0], cams_d, coff, cidx, timer=tm)
+print({k: round(v, 3) for k, v in tm.result().items()})
+i = int(np.argmax(cc))
+print("worst pair", i, "n_hit", nh[i], "cand", cc[i], "rlo", float(vis.ratio_lo[i]), "rhi", float(vis.ratio_hi[i]),
+      "ratio", rt[i], "flags", int(vis.flags[i]))
