@@ -709,7 +709,7 @@ __global__ void __launch_bounds__(1024) cand_plan_kernel(
 constexpr int kHullThreads = 128;
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
-constexpr int kHullFilterMin = 192; // candidates above which the directional pre-filter runs
+constexpr int kHullFilterMin = 128; // candidates above which the directional pre-filter runs
 
 __device__ __forceinline__ bool lex_less(float2 a, float2 b) {
   return a.x < b.x || (a.x == b.x && a.y < b.y);
@@ -748,13 +748,23 @@ __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
   int bi[16];
 #pragma unroll
   for (int d = 0; d < 16; ++d) { best[d] = -__int_as_float(0x7f800000); bi[d] = 0; }
-  for (int i = lane; i < n; i += 32) {
-    const float2 q = cu[i];
+  // 4 independent loads in flight per lane (the loop is latency bound otherwise)
+  for (int i0 = lane; i0 < n; i0 += 128) {
+    float2 q[4];
 #pragma unroll
-    for (int d = 0; d < 16; ++d) {
-      const float2 dv = F.dir[w * 16 + d];
-      const float dot = fmaf(q.x, dv.x, q.y * dv.y);
-      if (dot > best[d]) { best[d] = dot; bi[d] = i; }
+    for (int r = 0; r < 4; ++r) {
+      const int i = i0 + 32 * r;
+      q[r] = i < n ? cu[i] : cu[i0];
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int i = (i0 + 32 * r) < n ? (i0 + 32 * r) : i0;
+#pragma unroll
+      for (int d = 0; d < 16; ++d) {
+        const float2 dv = F.dir[w * 16 + d];
+        const float dot = fmaf(q[r].x, dv.x, q[r].y * dv.y);
+        if (dot > best[d]) { best[d] = dot; bi[d] = i; }
+      }
     }
   }
 #pragma unroll
@@ -795,23 +805,36 @@ __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
   if (m == 0) return n;
   // 2. filter + in-place compaction, 128 points per step (reads of a step finish
   //    before its writes, which land at or before the step's first position)
-  for (int base = 0; base < n; base += kHullThreads) {
-    const int i = base + tid;
-    float2 q = make_float2(0.f, 0.f);
-    int kp = 0;
-    if (i < n) {
-      q = cu[i];
+  // 4 consecutive points per thread and step (order preserving)
+  constexpr int kPer = 4;
+  for (int base = 0; base < n; base += kHullThreads * kPer) {
+    float2 q[kPer];
+    int kp[kPer];
+    int mine = 0;
+#pragma unroll
+    for (int r = 0; r < kPer; ++r) {
+      const int i = base + tid * kPer + r;
+      q[r] = i < n ? cu[i] : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int r = 0; r < kPer; ++r) {
+      const int i = base + tid * kPer + r;
       bool inside = true;
       for (int e = 0; e < m && inside; ++e) {
-        const float f = __fadd_rn(__fadd_rn(__fmul_rn(F.ea[e], q.x), __fmul_rn(F.eb[e], q.y)), F.ec[e]);
+        const float f =
+            __fadd_rn(__fadd_rn(__fmul_rn(F.ea[e], q[r].x), __fmul_rn(F.eb[e], q[r].y)), F.ec[e]);
         inside = f > margin;
       }
-      kp = inside ? 0 : 1;
+      kp[r] = (i < n && !inside) ? 1 : 0;
+      mine += kp[r];
     }
     int tot;
-    const int ex = block_exclusive_sum<int, kHullThreads>(kp, F.scan, &tot);
+    const int ex = block_exclusive_sum<int, kHullThreads>(mine, F.scan, &tot);
     const int o = F.out;
-    if (kp) cu[o + ex] = q;
+    int w0 = o + ex;
+#pragma unroll
+    for (int r = 0; r < kPer; ++r)
+      if (kp[r]) cu[w0++] = q[r];
     __syncthreads();
     if (tid == 0) F.out = o + tot;
     __syncthreads();
@@ -852,20 +875,23 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
   float2* cu = cand_uv + off;
   if (K > kHullFilterMin) {
     __shared__ FilterSmem F;
-    if (tid < kFiltDirs) {
-      float sn, cs;
-      sincospif((float)tid * (2.0f / kFiltDirs), &sn, &cs);
-      F.dir[tid] = make_float2(cs, sn);
-    }
-    __syncthreads();
     const float* rec = cameras + (int64_t)pair_cam[pair] * kCamFloats;
     const float Dm = fmaxf(rec[16], rec[17]);
     const float margin = 4e-6f * Dm * Dm;
-    for (int it = 0; it < 4 && K > kHullFilterMin; ++it) {
+    // every round uses the 64 directions shifted by another fraction of the
+    // angular step, so successive rounds cut with different polygons
+    const float frac[6] = {0.0f, 0.5f, 0.25f, 0.75f, 0.125f, 0.625f};
+    for (int it = 0; it < 6 && K > kHullFilterMin; ++it) {
+      if (tid < kFiltDirs) {
+        float sn, cs;
+        sincospif(((float)tid + frac[it]) * (2.0f / kFiltDirs), &sn, &cs);
+        F.dir[tid] = make_float2(cs, sn);
+      }
+      __syncthreads();
       const int kn = filter_round(cu, K, margin, F);
-      const bool progress = kn < K - K / 8;
+      const bool progress = kn < K - K / 16;
       K = kn;
-      if (!progress) break;
+      if (!progress && it >= 2) break;
     }
     __threadfence_block();
     __syncthreads();
@@ -897,21 +923,38 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
         __syncthreads();
       }
     }
-    if (tid == 0) {
-      // Andrew's monotone chain; pop on cross <= 0 (densify:522)
-      int nl = 0, nu = 0;
+    // Andrew's monotone chain; pop on cross <= 0 (densify:522).  The lower and
+    // the upper chain are independent: warp 0 / warp 1, one lane each, with the
+    // two topmost stack entries kept in registers.
+    if (tid == 0 || tid == 32) {
+      const bool lo_chain = tid == 0;
+      float2* st = lo_chain ? lower : upper;
+      int ns = 0;
       bool overflow = false;
+      float2 t1 = make_float2(0.f, 0.f), t2 = t1;   // st[ns-1], st[ns-2]
       for (int i = 0; i < n; ++i) {
         const float2 p = buf[i];
-        while (nl >= 2 && cross3(lower[nl - 2], lower[nl - 1], p) <= 0.0) --nl;
-        if (nl == 1 && lower[0].x == p.x && lower[0].y == p.y) --nl;
-        if (nl < kHullChain) lower[nl++] = p; else overflow = true;
-        while (nu >= 2 && cross3(upper[nu - 2], upper[nu - 1], p) >= 0.0) --nu;
-        if (nu == 1 && upper[0].x == p.x && upper[0].y == p.y) --nu;
-        if (nu < kHullChain) upper[nu++] = p; else overflow = true;
+        while (ns >= 2) {
+          const double c = cross3(t2, t1, p);
+          if (lo_chain ? (c <= 0.0) : (c >= 0.0)) {
+            --ns;
+            t1 = t2;
+            if (ns >= 2) t2 = st[ns - 2];
+          } else {
+            break;
+          }
+        }
+        if (ns == 1 && t1.x == p.x && t1.y == p.y) --ns;
+        if (ns < kHullChain) {
+          st[ns++] = p;
+          t2 = t1;
+          t1 = p;
+        } else {
+          overflow = true;
+        }
       }
-      if (overflow) s_flags |= 8;
-      s_nl = nl; s_nu = nu;
+      if (overflow) atomicOr(&s_flags, 8);
+      if (lo_chain) s_nl = ns; else s_nu = ns;
     }
     __syncthreads();
     pos += m;
