@@ -158,9 +158,15 @@ def test_graham_scan(ref):
         assert got == pytest.approx(float(want), rel=1e-13, abs=1e-15)
 
 
-def test_visibility_selection(ref, tmp_path):
+def test_visibility_selection(ref, tmp_path, monkeypatch):
     """End of the path: the reference's own visibility_based_camera_selection
-    (thread pool, pkl + COLMAP output) against the oracle's decisions."""
+    (thread pool, pkl + COLMAP output) against the oracle's decisions.  The
+    reference projects with device='cuda' by default (densify:410) and swallows
+    the resulting exception on a CPU-only box (densify:907-910), dropping every
+    camera; the default is redirected to 'cpu' here, nothing else changes."""
+    orig = ref.densify.project_points_to_camera
+    monkeypatch.setattr(ref.densify, "project_points_to_camera",
+                        lambda points, camera, device="cpu": orig(points, camera, device="cpu"))
     sc = small_scene(n=30000, c=30, thr=8000, seed=16, height_scale=2.0)
     cams, rcams = _ref_cameras(ref, sc)
     p64 = sc.xyz.astype(np.float64)
