@@ -1,0 +1,95 @@
+"""world_size-2 (and 3) test of the camera-sharded visibility exchange on CPU
+(gloo): shard_csr -> per-rank records -> gather_records must reproduce the
+single-process per-pair table in full pair order on every rank.  The compute
+callback is replaced by a deterministic function of (block, camera) -- the
+CUDA visibility pass itself is covered by the `gpu` tests."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import ptgs_b200  # noqa: F401
+from ptgs_b200 import multigpu as M
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _make_csr(seed, L=13, C=57):
+    rng = np.random.default_rng(seed)
+    lists = [np.sort(rng.choice(C, size=rng.integers(0, 12), replace=False)) for _ in range(L)]
+    lists[3] = np.zeros(0, np.int64)                      # an empty block
+    off = np.zeros(L + 1, np.int64)
+    off[1:] = np.cumsum([len(l) for l in lists])
+    idx = np.concatenate(lists).astype(np.int32)
+    return torch.from_numpy(off), torch.from_numpy(idx)
+
+
+def _fake_records(off, idx):
+    """Deterministic per-pair 'visibility result' from (block, camera)."""
+    L = off.shape[0] - 1
+    blk = torch.repeat_interleave(torch.arange(L), off[1:] - off[:-1])
+    cam = idx.to(torch.int64)
+    n_hit = (blk * 1000 + cam).to(torch.int32)
+    ratio = (cam.to(torch.float64) + 0.5) / 64.0 + blk.to(torch.float64) * 1e-9
+    area = ratio * 1920000.0
+    keep = (ratio >= 0.45).to(torch.uint8)
+    flags = ((cam % 5 == 0).to(torch.uint8) * 16) | (blk % 2).to(torch.uint8)
+    return n_hit, ratio, area, keep, flags
+
+
+def _worker(rank, world, port, seed, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        off, idx = _make_csr(seed)
+        my_off, my_idx, pos = M.shard_csr(off, idx, rank, world)
+        # shard invariants
+        assert bool(((my_idx % world) == rank).all())
+        assert int(my_off[-1]) == my_idx.shape[0] == pos.shape[0]
+        assert torch.equal(idx[pos], my_idx)
+        nh, rt, ar, kp, fl = _fake_records(my_off, my_idx)
+        full = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world)
+        got = M.unpack_records(full)
+        want = _fake_records(off, idx)
+        for g, w in zip(got, want):
+            assert torch.equal(g, w), "rank %d: gathered table differs" % rank
+        torch.save([g.clone() for g in got], os.path.join(out_dir, "r%d.pt" % rank))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,seed", [(2, 1), (2, 2), (3, 3)])
+def test_sharded_records_gloo(world, seed, tmp_path):
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, seed, str(tmp_path)), nprocs=world, join=True)
+    tabs = [torch.load(os.path.join(tmp_path, "r%d.pt" % r)) for r in range(world)]
+    for t in tabs[1:]:
+        for a, b in zip(tabs[0], t):
+            assert torch.equal(a, b)
+
+
+def test_shard_csr_single_process_identity():
+    off, idx = _make_csr(9)
+    o, i, pos = M.shard_csr(off, idx, 0, 1)
+    assert torch.equal(o, off) and torch.equal(i, idx) and torch.equal(pos, torch.arange(idx.shape[0]))
+    # the shards of a world partition the pair list
+    for world in (2, 4, 8):
+        seen = torch.zeros(idx.shape[0], dtype=torch.int64)
+        for r in range(world):
+            o, i, pos = M.shard_csr(off, idx, r, world)
+            seen[pos] += 1
+            cnt = o[1:] - o[:-1]
+            blk = torch.repeat_interleave(torch.arange(off.shape[0] - 1), off[1:] - off[:-1])
+            assert torch.equal(cnt, torch.bincount(blk[pos], minlength=off.shape[0] - 1))
+        assert bool((seen == 1).all())
