@@ -47,6 +47,7 @@ print("ratio   pct[0,10,50,90,99,100]:", np.percentile(rt, [0, 10, 50, 90, 99, 1
 print("kept fraction", float(vis.keep.float().mean()), "flags", np.bincount(vis.flags.cpu().numpy(), minlength=16)[:16])
 M = np.diff(ds[0].cpu().numpy()); Cb = np.diff(coff.cpu().numpy())
 print("M_b", M.min(), M.max(), "C_b", Cb.min(), Cb.max(), "tests", int((M * Cb).sum()))
+print("hits", int(nh.sum()), "hit rate", float(nh.sum()) / float((M * Cb).sum()))
 ex = (vis.flags.cpu().numpy() & 16) == 0
 print("rounds", vis.rounds, "n_exact", vis.n_exact, "sum cand (exact pairs)", int(cc[ex].sum()), "max", int(cc.max()),
       "sum min(nh,max(2048,nh/4)) over exact", int(np.minimum(nh[ex], np.maximum(2048, nh[ex] // 4)).sum()))
