@@ -46,7 +46,10 @@ SIGNATURES = {
     "ptgs_visibility_workspace_bytes": (_sz, [_i32]),
     "ptgs_visibility_init": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_visibility_count": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
-                                        _vp, _vp, _sz, _vp]),
+                                        _vp, _vp, _vp, _sz, _vp]),
+    "ptgs_visibility_sample": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i64, _vp]),
+    "ptgs_visibility_krect": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _f64,
+                                        _vp, _vp]),
     "ptgs_visibility_bounds": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
                                          _i64, _i32, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
                                          _vp, _vp, _vp]),
@@ -56,6 +59,7 @@ SIGNATURES = {
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
                                        _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),
     "ptgs_coverage_sweep": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
 }
 

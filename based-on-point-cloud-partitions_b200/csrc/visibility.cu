@@ -179,6 +179,66 @@ __device__ __forceinline__ bool tile_may_hit(const Cam& c, const float* b) {
   return plus || minus;
 }
 
+// ---- division-free classification (MODE 0 / 1) ------------------------------------
+// A rectangle {|u - cu| <= hu, |v - cv| <= hv} of the image plane is tested in
+// homogeneous form, |uh - cu*Z| <= hu*|Z|, which holds for both nappes (Z < 0
+// flips both sides).  Two rectangles per camera (der[0..3] = "in", der[4..7] =
+// "out"):
+//   out  = the image, slightly inflated: a point outside it cannot be a hit.
+//          hit  =>  0 <= RN(uh/Z) < W  =>  |uh/Z - hW| <= W - hW  with hW =
+//          pred(W)/2; the inflation 2^-20 covers W - hW = hW(1 + <=2^-22), the
+//          single rounding of the fma and of the product (2^-24 each); the
+//          1e-30 slack covers underflow and uh = Z = 0 (-> exact path -> NaN).
+//   in   = a rectangle all of whose points are hits that need no further work:
+//          MODE 0: the image deflated by 2^-20 (strict compare, so |Z| = 0 never
+//          passes); MODE 1: the per-pair interior rectangle K of ptgs_visibility_krect
+//          (>= 1 pixel inside the convex hull of known hits, hence inside the
+//          image and never a pivot / directional extreme).
+// Points in "in" are counted; points in "out" but not "in" take the exact path
+// (IEEE divisions, the reference's compares); the rest are misses.
+__device__ __forceinline__ void make_rects(const Cam& c, const float* krect, int mode, float* der) {
+  const float pW = (c.w > 0.0f) ? __uint_as_float(__float_as_uint(c.w) - 1u) : 0.0f;
+  const float pH = (c.h > 0.0f) ? __uint_as_float(__float_as_uint(c.h) - 1u) : 0.0f;
+  const float hW = 0.5f * pW, hH = 0.5f * pH;
+  const float up = 1.0f + 9.5367431640625e-07f, dn = 1.0f - 9.5367431640625e-07f;   // 1 +- 2^-20
+  der[4] = hW; der[5] = hH; der[6] = hW * up; der[7] = hH * up;
+  if (mode == 0) {
+    der[0] = hW; der[1] = hH; der[2] = hW * dn; der[3] = hH * dn;
+  } else if (krect) {
+    der[0] = krect[0]; der[1] = krect[1]; der[2] = krect[2]; der[3] = krect[3];
+  } else {
+    der[0] = 0.0f; der[1] = 0.0f; der[2] = -1.0f; der[3] = -1.0f;
+  }
+}
+
+// Is every point of the tile box strictly inside the "in" rectangle of the
+// positive nappe and in front?  Same interval arithmetic and margins as
+// tile_may_hit; the four edge forms are built from combined coefficients.
+__device__ __forceinline__ bool tile_all_in(const Cam& c, const float* der, const float* b) {
+  if (!(der[2] > 0.0f) || !(der[3] > 0.0f)) return false;
+  const float S = fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + b[3] + b[4] + b[5] +
+                  fmaxf(fabsf(c.tx), fmaxf(fabsf(c.ty), fabsf(c.tz)));
+  const float mF = S * (1.0f / 65536.0f);
+  const float mP = mF * (c.fx + c.fy + c.w + c.h + fabsf(c.cx) + fabsf(c.cy));
+  const Form Y = form(c.r10, c.r11, c.r12, c.ty, b);
+  const Form Z = form(c.r20, c.r21, c.r22, c.tz, b);
+  const Form F = (c.front_axis == 1.0f) ? Y : Z;
+  if (!(F.mid - F.rad > mF) || !(Z.mid - Z.rad > mF)) return false;
+  const float u1 = der[0] - der[2], u2 = der[0] + der[2], v1 = der[1] - der[3], v2 = der[1] + der[3];
+  // uh - u1*Z >= 0, u2*Z - uh >= 0, vh - v1*Z >= 0, v2*Z - vh >= 0 over the box
+  const float e1 = c.cx - u1, e2 = u2 - c.cx, g1 = c.cy - v1, g2 = v2 - c.cy;
+  const Form A1 = form(fmaf(c.fx, c.r00, e1 * c.r20), fmaf(c.fx, c.r01, e1 * c.r21),
+                       fmaf(c.fx, c.r02, e1 * c.r22), fmaf(c.fx, c.tx, e1 * c.tz), b);
+  const Form A2 = form(fmaf(-c.fx, c.r00, e2 * c.r20), fmaf(-c.fx, c.r01, e2 * c.r21),
+                       fmaf(-c.fx, c.r02, e2 * c.r22), fmaf(-c.fx, c.tx, e2 * c.tz), b);
+  const Form B1 = form(fmaf(c.fy, c.r10, g1 * c.r20), fmaf(c.fy, c.r11, g1 * c.r21),
+                       fmaf(c.fy, c.r12, g1 * c.r22), fmaf(c.fy, c.ty, g1 * c.tz), b);
+  const Form B2 = form(fmaf(-c.fy, c.r10, g2 * c.r20), fmaf(-c.fy, c.r11, g2 * c.r21),
+                       fmaf(-c.fy, c.r12, g2 * c.r22), fmaf(-c.fy, c.ty, g2 * c.tz), b);
+  return (A1.mid - A1.rad > mP) && (A2.mid - A2.rad > mP) && (B1.mid - B1.rad > mP) &&
+         (B2.mid - B2.rad > mP);
+}
+
 // ---- work item schedule -----------------------------------------------------
 // item_prefix[b] = number of work items of the blocks before b; a block has
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
@@ -219,6 +279,7 @@ struct SweepArgs {
   uint8_t* seen;                  // MODE 0, optional
   uint64_t* pivot;                // MODE 1
   uint64_t* extreme;              // MODE 1
+  const float* krect;             // MODE 1, optional: per pair (cu, cv, hu, hv) interior rectangle
   // MODE 2
   const int32_t* pair_map;        // optional: pair slot of the (sub-)CSR -> pair id for poly / cand_*
   const float* poly;
@@ -260,6 +321,10 @@ __device__ __forceinline__ Item decode_item(const SweepArgs& a, const int64_t* s
   return it;
 }
 
+// diagnostics (ptgs_debug_sweep_stats): point-camera tests before / after the
+// tile cull, summed over every sweep launch since the last reset
+__device__ unsigned long long g_sweep_stats[4];
+
 // ---- the sweep ---------------------------------------------------------------
 struct SweepSmem {
   alignas(128) float tile[2][3][kSwStageFloats];
@@ -271,8 +336,11 @@ struct SweepSmem {
   int cand_cap[kSwCamChunk];                              // MODE 2
   int pair_of[kSwCamChunk];                               // MODE 2
   int cnt[kSwCamChunk];
-  int act[kSwCamChunk];                                   // cameras that survive the tile cull
+  int act[kSwThreads];                                    // cameras of the round that survive the tile cull
+  long long lpos[kSwCamChunk];                            // list position of the staged cameras
   int nact;
+  int tile_seen;                                          // MODE 0: a camera contains the whole tile
+  alignas(16) float der[kSwCamChunk][8];                  // MODE 0/1: fast-in / not-miss rectangles
   float wbox[kSwThreads / 32][6];                         // per warp tile AABB
   float box[6];                                           // centre xyz, half extent xyz (padded)
   alignas(8) uint64_t bar[2];
@@ -378,34 +446,88 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
 
     const int64_t cam_base = a.cam_offsets[cur.b];
     unsigned seen_mask = 0;
-    for (int64_t c0 = cur.cam_lo; c0 < cur.cam_hi; c0 += kSwCamChunk) {
-      const int nc = (int)((cur.cam_hi - c0) < kSwCamChunk ? (cur.cam_hi - c0) : kSwCamChunk);
-      // ---- stage the camera chunk
+    if (MODE == 0 && tid == 0) S.tile_seen = 0;   // ordered by the chunk loop's barriers
+    // The item's cameras are culled against the tile box by all threads at once
+    // (rounds of kSwThreads cameras), the survivors are compacted into S.act and
+    // swept in chunks of kSwCamChunk; tiles that lie wholly inside a camera's "in"
+    // rectangle are counted right here.
+    for (int64_t r0 = cur.cam_lo; r0 < cur.cam_hi; r0 += kSwThreads) {
+      const int nr = (int)((cur.cam_hi - r0) < kSwThreads ? (cur.cam_hi - r0) : kSwThreads);
+      if (tid == 0) S.nact = 0;
+      __syncthreads();                       // S.box / S.nact visible, previous round finished
+      if (tid < nr) {
+        const int64_t lpos = r0 + tid;       // position inside the block's camera list
+        const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
+        float rec[kCamFloats];
+#pragma unroll
+        for (int q = 0; q < kCamFloats / 4; ++q)
+          reinterpret_cast<float4*>(rec)[q] =
+              __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
+        const Cam cj = load_cam(rec);
+        bool live = tile_may_hit(cj, S.box);
+        if (MODE != 2 && live) {
+          float der[8];
+          const float* kr = nullptr;
+          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * 4;
+          make_rects(cj, kr, MODE, der);
+          if (tile_all_in(cj, der, S.box)) {
+            // every point of the tile is a hit that needs no further work
+            const int64_t pair = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
+            atomicAdd(a.n_hit + pair, cur.cnt);
+            if (MODE == 0) S.tile_seen = 1;
+            live = false;
+          }
+        }
+        if (live) S.act[atomicAdd(&S.nact, 1)] = (int)(lpos - cur.cam_lo);
+      }
+      __syncthreads();
+      const int nact_all = S.nact;
+      if (tid == 0) {
+        atomicAdd(&g_sweep_stats[0], (unsigned long long)nr * (unsigned)cur.cnt);
+        atomicAdd(&g_sweep_stats[1], (unsigned long long)nact_all * (unsigned)cur.cnt);
+      }
+    for (int c0 = 0; c0 < nact_all; c0 += kSwCamChunk) {
+      const int nc = (nact_all - c0) < kSwCamChunk ? (nact_all - c0) : kSwCamChunk;
+      // ---- stage the chunk of surviving cameras
       for (int i = tid; i < nc * (kCamFloats / 4); i += kSwThreads) {
         const int j = i / (kCamFloats / 4), q = i % (kCamFloats / 4);
-        const int64_t pos = cam_base + c0 + j;
-        const int64_t cam = a.cam_index ? (int64_t)a.cam_index[pos] : (int64_t)a.cam_first + (c0 + j);
+        const int64_t lpos = cur.cam_lo + S.act[c0 + j];
+        const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
         reinterpret_cast<float4*>(S.cam[j])[q] =
             __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
       }
       if (MODE == 2) {
         for (int i = tid; i < nc * (kPolyFloats / 4); i += kSwThreads) {
           const int j = i / (kPolyFloats / 4), q = i % (kPolyFloats / 4);
-          const int64_t slot = cam_base + c0 + j;
+          const int64_t slot = cam_base + cur.cam_lo + S.act[c0 + j];
           const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
           reinterpret_cast<float4*>(S.poly[j])[q] =
               __ldg(reinterpret_cast<const float4*>(a.poly + pair * kPolyFloats) + q);
         }
       }
       if (tid < nc) {
+        const int64_t lpos = cur.cam_lo + S.act[c0 + tid];
+        S.lpos[tid] = lpos;
         S.cnt[tid] = 0;
         if (MODE == 1) {
           S.pivot[tid] = ~0ull;
 #pragma unroll
           for (int d = 0; d < 8; ++d) S.ext[tid][d] = 0ull;
         }
+        if (MODE != 2) {
+          const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
+          const float* rp = a.cameras + cam * kCamFloats;
+          Cam cj;                                  // make_rects only reads w, h
+          cj.w = __ldg(rp + 16); cj.h = __ldg(rp + 17);
+          float der[8];
+          const float* kr = nullptr;
+          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * 4;
+          make_rects(cj, kr, MODE, der);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) S.der[tid][q] = der[q];
+        }
         if (MODE == 2) {
-          const int64_t slot = cam_base + c0 + tid;
+          const int64_t slot = cam_base + lpos;
           const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
           const int64_t o0 = a.cand_offsets[pair], o1 = a.cand_offsets[pair + 1];
           S.cand_off[tid] = o0;
@@ -414,20 +536,112 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
       }
       __syncthreads();
-      // ---- cull: camera j of the chunk against the tile box (warp 0)
-      if (tid < 32) {
-        bool live = false;
-        if (tid < nc) live = tile_may_hit(load_cam(S.cam[tid]), S.box);
-        const unsigned m = __ballot_sync(kFullMask, live);
-        if (live) S.act[__popc(m & lanemask_lt())] = tid;
-        if (tid == 0) S.nact = __popc(m);
-      }
-      __syncthreads();
-      const int nact = S.nact;
+      const int nact = nc;
 
       // ---- sweep: 8 register points x surviving cameras
+      if (MODE != 2) {
+        for (int jj = 0; jj < nact; ++jj) {
+          const int j = jj;
+          const Cam c = load_cam(S.cam[j]);
+          const float4 din = *reinterpret_cast<const float4*>(&S.der[j][0]);
+          const float4 dout = *reinterpret_cast<const float4*>(&S.der[j][4]);
+          const bool front_y = c.front_axis == 1.0f;
+          int cnt = 0;
+          unsigned slow = 0;
+#pragma unroll
+          for (int k = 0; k < kSwP; ++k) {
+            const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
+            const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
+            const float Z = cam_row(c.r20, c.r21, c.r22, c.tz, x[k], y[k], z[k]);
+            const float uh = __fmaf_rn(c.cx, Z, __fmul_rn(c.fx, X));
+            const float vh = __fmaf_rn(c.cy, Z, __fmul_rn(c.fy, Y));
+            const float az = fabsf(Z);
+            const bool front = (front_y ? Y : Z) > 0.0f;
+            const bool in = front && (fabsf(__fmaf_rn(-din.x, Z, uh)) < __fmul_rn(din.z, az)) &&
+                            (fabsf(__fmaf_rn(-din.y, Z, vh)) < __fmul_rn(din.w, az));
+            bool nm;
+            if (MODE == 0) {   // same centre: one fma per axis serves both rectangles
+              nm = front && (fabsf(__fmaf_rn(-din.x, Z, uh)) <= __fmaf_rn(dout.z, az, 1e-30f)) &&
+                   (fabsf(__fmaf_rn(-din.y, Z, vh)) <= __fmaf_rn(dout.w, az, 1e-30f));
+            } else {
+              nm = front && (fabsf(__fmaf_rn(-dout.x, Z, uh)) <= __fmaf_rn(dout.z, az, 1e-30f)) &&
+                   (fabsf(__fmaf_rn(-dout.y, Z, vh)) <= __fmaf_rn(dout.w, az, 1e-30f));
+            }
+            cnt += in ? 1 : 0;
+            if (MODE == 0 && in) seen_mask |= 1u << k;
+            slow |= (nm && !in) ? (1u << k) : 0u;
+          }
+          // ---- exact path for the points between the two rectangles
+          bool any_slow = false;
+          unsigned long long t_pv = ~0ull;
+          float t_best[8];
+          uint32_t t_idx[8];
+          if (MODE == 1) {
+#pragma unroll
+            for (int d = 0; d < 8; ++d) { t_best[d] = -__int_as_float(0x7f800000); t_idx[d] = 0; }
+          }
+          if (__any_sync(kFullMask, slow != 0)) {
+#pragma unroll
+            for (int k = 0; k < kSwP; ++k) {
+              const bool mine = (slow >> k) & 1u;
+              if (!__any_sync(kFullMask, mine)) continue;
+              if (mine) {
+                const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
+                const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
+                Proj p;
+                p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, x[k], y[k], z[k]);
+                p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
+                p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
+                float u, v;
+                if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
+                  ++cnt;
+                  if (MODE == 0) seen_mask |= 1u << k;
+                  if (MODE == 1) {
+                    any_slow = true;
+                    u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                    v = __fadd_rn(v, 0.0f);
+                    const unsigned long long pk =
+                        ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                    t_pv = pk < t_pv ? pk : t_pv;
+                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + k * kSwThreads + tid);
+                    const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
+                    const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
+#pragma unroll
+                    for (int d = 0; d < 8; ++d) {
+                      if (dir[d] > t_best[d]) { t_best[d] = dir[d]; t_idx[d] = idx; }
+                    }
+                  }
+                }
+              }
+            }
+          }
+          const int wsum = __reduce_add_sync(kFullMask, cnt);
+          if (lane == 0 && wsum) atomicAdd(&S.cnt[j], wsum);
+          if (MODE == 1 && __any_sync(kFullMask, any_slow)) {
+            const uint32_t phi = (uint32_t)(t_pv >> 32);
+            const uint32_t mhi = __reduce_min_sync(kFullMask, phi);
+            const uint32_t plo = phi == mhi ? (uint32_t)t_pv : 0xffffffffu;
+            const uint32_t mlo = __reduce_min_sync(kFullMask, plo);
+            if (lane == 0) {
+              const unsigned long long pk = ((unsigned long long)mhi << 32) | mlo;
+              if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
+            }
+#pragma unroll
+            for (int d = 0; d < 8; ++d) {
+              const uint32_t key = order_key(t_best[d]);
+              const uint32_t mk = __reduce_max_sync(kFullMask, key);
+              const unsigned who = __ballot_sync(kFullMask, key == mk);
+              const uint32_t id = __shfl_sync(kFullMask, t_idx[d], __ffs(who) - 1);
+              if (lane == 0) {
+                const unsigned long long e = ((unsigned long long)mk << 32) | id;
+                if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
+              }
+            }
+          }
+        }
+      } else {
       for (int jj = 0; jj < nact; ++jj) {
-        const int j = S.act[jj];
+        const int j = jj;
         const Cam c = load_cam(S.cam[j]);
         const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
         int cnt = 0;
@@ -514,13 +728,14 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           }
         }
       }
+      }
       __syncthreads();
 
       // ---- flush the chunk's accumulators
       if (MODE != 2 && tid < nc) {
         const int cn = S.cnt[tid];
         if (cn) {
-          const int64_t pair = (MODE == 0 && !a.cam_index) ? (c0 + tid) : (cam_base + c0 + tid);
+          const int64_t pair = (MODE == 0 && !a.cam_index) ? S.lpos[tid] : (cam_base + S.lpos[tid]);
           atomicAdd(a.n_hit + pair, cn);
           if (MODE == 1) {
             atomicMin(reinterpret_cast<unsigned long long*>(a.pivot) + pair, S.pivot[tid]);
@@ -534,10 +749,13 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       }
       __syncthreads();
     }
+    }
     if (MODE == 0 && a.seen) {
+      const bool all = S.tile_seen != 0;   // written before the last barrier of the chunk loop
 #pragma unroll
       for (int k = 0; k < kSwP; ++k)
-        if (seen_mask & (1u << k)) a.seen[cur.start + k * kSwThreads + tid] = 1;
+        if ((all && k * kSwThreads + tid < cur.cnt) || (seen_mask & (1u << k)))
+          a.seen[cur.start + k * kSwThreads + tid] = 1;
     }
     cur = nxt;
   }
@@ -1043,6 +1261,107 @@ __global__ void coverage_setup_kernel(int64_t n, int32_t cam_count, int64_t* pt_
   cam_off[0] = 0; cam_off[1] = cam_count;
 }
 
+// ---- interior rectangle K per pair (MODE 1 fast path) ---------------------------------
+// Sweep 1 is first run on a 1-in-`stride` sample of every block.  The extreme
+// hits of the sample span a convex polygon Q inside the convex hull of all
+// hits; K is an axis-parallel rectangle inside Q (the bounding box of Q scaled
+// about Q's vertex centroid until a corner touches an edge), shrunk by
+// `margin_px`.  Every point of K is a hit (K lies inside the image, the margin
+// is >> the float32 evaluation error of the homogeneous test) and is strictly
+// inside the hull of the hits, so it can be neither the Graham pivot nor an
+// extreme along any direction: the full sweep only counts such points.
+__global__ void __launch_bounds__(1024) sample_offsets_kernel(
+    const int64_t* __restrict__ pt_offsets, int L, int stride, int64_t* __restrict__ s_offsets) {
+  __shared__ long long sm[33];
+  long long carry = 0;
+  for (int s0 = 0; s0 < L; s0 += 1024) {
+    const int b = s0 + threadIdx.x;
+    long long v = 0;
+    if (b < L) v = (pt_offsets[b + 1] - pt_offsets[b] + stride - 1) / stride;
+    long long tot;
+    const long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
+    if (b < L) s_offsets[b] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) s_offsets[L] = carry;
+}
+
+__global__ void __launch_bounds__(256) sample_gather_kernel(
+    const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz,
+    const int64_t* __restrict__ pt_offsets, const int64_t* __restrict__ s_offsets, int L, int stride,
+    int64_t capacity, float* __restrict__ sx, float* __restrict__ sy, float* __restrict__ sz) {
+  __shared__ int64_t so[kSwMaxBlocks + 1];
+  for (int i = threadIdx.x; i <= L; i += blockDim.x) so[i] = s_offsets[i];
+  __syncthreads();
+  const int64_t n = so[L] < capacity ? so[L] : capacity;
+  const int64_t step = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
+    int lo = 0, hi = L - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (so[mid] <= i) lo = mid; else hi = mid - 1;
+    }
+    const int64_t src = pt_offsets[lo] + (i - so[lo]) * stride;
+    sx[i] = px[src]; sy[i] = py[src]; sz[i] = pz[src];
+  }
+}
+
+__global__ void __launch_bounds__(128) krect_kernel(
+    const float* __restrict__ sx, const float* __restrict__ sy, const float* __restrict__ sz,
+    const int64_t* __restrict__ s_offsets, int L, const float* __restrict__ cameras,
+    const int64_t* __restrict__ cam_offsets, const int32_t* __restrict__ cam_index,
+    const int32_t* __restrict__ n_hit_s, const uint64_t* __restrict__ extreme_s, double margin_px,
+    float* __restrict__ krect) {
+  const int64_t n_pairs = cam_offsets[L];
+  const int64_t pair = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= n_pairs) return;
+  float* out = krect + pair * 4;
+  out[0] = 0.0f; out[1] = 0.0f; out[2] = -1.0f; out[3] = -1.0f;
+  if (n_hit_s[pair] < 3) return;
+  int lo = 0, hi = L - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (cam_offsets[mid] <= pair) lo = mid; else hi = mid - 1;
+  }
+  const int64_t p0 = s_offsets[lo];
+  const Cam c = load_cam(cameras + (int64_t)cam_index[pair] * kCamFloats);
+  double vx[8], vy[8];
+  int m = 0;
+  for (int d = 0; d < 8; ++d) {
+    const uint64_t e = extreme_s[pair * 8 + d];
+    if (!e) continue;
+    const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
+    const Proj p = project_pre(c, 0.0f, 0.0f, sx[gi], sy[gi], sz[gi]);
+    float u, v;
+    if (!project_exact(c, p, u, v)) continue;
+    if (m && vx[m - 1] == (double)u && vy[m - 1] == (double)v) continue;
+    vx[m] = u; vy[m] = v; ++m;
+  }
+  while (m > 1 && vx[m - 1] == vx[0] && vy[m - 1] == vy[0]) --m;
+  if (m < 3) return;
+  double gu = 0.0, gv = 0.0, u0 = vx[0], u1 = vx[0], v0 = vy[0], v1 = vy[0];
+  for (int i = 0; i < m; ++i) {
+    gu += vx[i]; gv += vy[i];
+    u0 = fmin(u0, vx[i]); u1 = fmax(u1, vx[i]); v0 = fmin(v0, vy[i]); v1 = fmax(v1, vy[i]);
+  }
+  gu /= m; gv /= m;
+  const double ha = 0.5 * (u1 - u0), hb = 0.5 * (v1 - v0);
+  double t = 1.0;
+  for (int i = 0; i < m; ++i) {
+    const int k = (i + 1 == m) ? 0 : i + 1;
+    const double nx = -(vy[k] - vy[i]), ny = vx[k] - vx[i];      // inward normal (CCW polygon)
+    const double fg = nx * (gu - vx[i]) + ny * (gv - vy[i]);
+    const double reach = fabs(nx) * ha + fabs(ny) * hb;
+    if (!(fg > 0.0)) return;                                      // degenerate / not CCW: no K
+    if (reach > 0.0) t = fmin(t, fg / reach);
+  }
+  const double hu = t * ha * (1.0 - 1e-6) - margin_px, hv = t * hb * (1.0 - 1e-6) - margin_px;
+  if (!(hu > 0.0) || !(hv > 0.0)) return;
+  // stay strictly inside the image whatever the rounding to float
+  if (gu - hu < 1.0 || gv - hv < 1.0 || gu + hu > (double)c.w - 1.0 || gv + hv > (double)c.h - 1.0) return;
+  out[0] = (float)gu; out[1] = (float)gv; out[2] = (float)hu; out[3] = (float)hv;
+}
+
 // ---- host side -----------------------------------------------------------------
 template <int MODE>
 static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
@@ -1088,8 +1407,8 @@ int ptgs_visibility_init(int64_t n_pairs, int32_t* n_hit, uint64_t* pivot, uint6
 int ptgs_visibility_count(const float* px, const float* py, const float* pz,
                           const int64_t* pt_offsets, int32_t n_blocks, const float* cameras,
                           const int64_t* cam_offsets, const int32_t* cam_index, int32_t cam_split,
-                          int32_t* n_hit, uint64_t* pivot, uint64_t* extreme, void* workspace,
-                          size_t workspace_bytes, ptgs_stream_t stream) {
+                          int32_t* n_hit, uint64_t* pivot, uint64_t* extreme, const float* krect,
+                          void* workspace, size_t workspace_bytes, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
   PTGS_REQUIRE(pt_offsets && cameras && cam_offsets && cam_index && n_hit && pivot && extreme,
                "arguments");
@@ -1108,8 +1427,44 @@ int ptgs_visibility_count(const float* px, const float* py, const float* pz,
   a.px = px; a.py = py; a.pz = pz; a.pt_offsets = pt_offsets; a.n_blocks = n_blocks;
   a.cameras = cameras; a.cam_offsets = cam_offsets; a.cam_index = cam_index;
   a.cam_split = cam_split; a.item_prefix = item_prefix;
-  a.n_hit = n_hit; a.pivot = pivot; a.extreme = extreme;
+  a.n_hit = n_hit; a.pivot = pivot; a.extreme = extreme; a.krect = krect;
   return launch_sweep<1>(a, st);
+}
+
+int ptgs_visibility_sample(const float* px, const float* py, const float* pz,
+                           const int64_t* pt_offsets, int32_t n_blocks, int32_t stride, float* sx,
+                           float* sy, float* sz, int64_t* s_offsets, int64_t capacity,
+                           ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(stride >= 1 && capacity >= 0 && pt_offsets && s_offsets, "arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  sample_offsets_kernel<<<1, 1024, 0, st>>>(pt_offsets, n_blocks, stride, s_offsets);
+  PTGS_LAUNCH_CHECK();
+  if (capacity == 0) return PTGS_OK;
+  PTGS_REQUIRE(px && py && pz && sx && sy && sz, "arguments");
+  int64_t g = (capacity + 255) / 256;
+  if (g > kNumSMs * 8) g = kNumSMs * 8;
+  sample_gather_kernel<<<(int)g, 256, 0, st>>>(px, py, pz, pt_offsets, s_offsets, n_blocks, stride,
+                                               capacity, sx, sy, sz);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_visibility_krect(const float* sx, const float* sy, const float* sz,
+                          const int64_t* s_offsets, int32_t n_blocks, const float* cameras,
+                          const int64_t* cam_offsets, const int32_t* cam_index,
+                          const int32_t* n_hit_s, const uint64_t* extreme_s, int64_t n_pairs,
+                          double margin_px, float* krect, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kSwMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(n_pairs >= 0 && margin_px >= 0.5, "n_pairs / margin_px (>= 0.5 pixel)");
+  if (n_pairs == 0) return PTGS_OK;
+  PTGS_REQUIRE(s_offsets && cameras && cam_offsets && cam_index && n_hit_s && extreme_s && krect,
+               "arguments");
+  krect_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      sx, sy, sz, s_offsets, n_blocks, cameras, cam_offsets, cam_index, n_hit_s, extreme_s,
+      margin_px, krect);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
 }
 
 int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
@@ -1189,6 +1544,20 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
       (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
       ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev);
   PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset) {
+  unsigned long long h[4] = {0, 0, 0, 0};
+  PTGS_CUDA_TRY(cudaDeviceSynchronize());
+  if (out4) {
+    PTGS_CUDA_TRY(cudaMemcpyFromSymbol(h, g_sweep_stats, sizeof(h)));
+    for (int i = 0; i < 4; ++i) out4[i] = h[i];
+  }
+  if (reset) {
+    unsigned long long z[4] = {0, 0, 0, 0};
+    PTGS_CUDA_TRY(cudaMemcpyToSymbol(g_sweep_stats, z, sizeof(z)));
+  }
   return PTGS_OK;
 }
 

@@ -26,6 +26,8 @@ struct VoxLayout {
   int32_t bits_b, bits_x, bits_y, bits_z;   // field widths
   int32_t total_bits;
   int32_t max_vx, max_vy, max_vz;
+  int32_t bits_m;    // width of the coarse-cell field (Morton interleave of cx, cy when it fits)
+  int32_t morton;
 };
 
 template <typename T> struct VoxArith;
@@ -132,7 +134,16 @@ __global__ void __launch_bounds__(1024) vox_layout_kernel(
     VoxLayout l;
     l.bits_b = nbits(L - 1);
     l.bits_x = nbits(smax[0]); l.bits_y = nbits(smax[1]); l.bits_z = nbits(smax[2]);
-    l.total_bits = l.bits_b + l.bits_x + l.bits_y + l.bits_z;
+    {
+      // coarse cells (vx >> 6, vy >> 6) are Morton-interleaved when the padding fits in 64 bits
+      const int nx = l.bits_x > kVoxCoarseShift ? l.bits_x - kVoxCoarseShift : 0;
+      const int ny = l.bits_y > kVoxCoarseShift ? l.bits_y - kVoxCoarseShift : 0;
+      const int nm = 2 * (nx > ny ? nx : ny);
+      const int rest = l.bits_b + l.bits_x + l.bits_y + l.bits_z - nx - ny;
+      l.morton = (rest + nm <= 64) ? 1 : 0;
+      l.bits_m = l.morton ? nm : nx + ny;
+      l.total_bits = rest + l.bits_m;
+    }
     const bool ok = smax[0] < 0x7fffffffll && smax[1] < 0x7fffffffll && smax[2] < 0x7fffffffll &&
                     l.total_bits <= 64;
     l.max_vx = (int32_t)min(smax[0], 0x7fffffffll);
@@ -161,19 +172,31 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
     const uint64_t vx = (uint64_t)VoxArith<T>::vid(x[i], bmin[3 * b], vs);
     const uint64_t vy = (uint64_t)VoxArith<T>::vid(y[i], bmin[3 * b + 1], vs);
     const uint64_t vz = (uint64_t)VoxArith<T>::vid(z[i], bmin[3 * b + 2], vs);
-    // block | coarse cell (vx >> s, vy >> s) | fine (vx, vy) | vz : a bit
-    // permutation of (vx, vy, vz), so the voxel groups are unchanged and only
-    // their order moves -- cell-major order makes every run of consecutive
-    // voxels (a sweep tile) spatially compact, which the visibility sweep's
-    // tile culling relies on.
+    // block | coarse layer (vz >> s) | coarse cell (vx >> s, vy >> s, Morton
+    // interleaved) | fine (vx, vy, vz): an injective re-arrangement of the bits
+    // of (vx, vy, vz), so the voxel groups are unchanged and only their order
+    // moves.  Layer-major, then Z-order over the 6.4-unit cells, makes every
+    // run of consecutive voxels (a sweep tile) compact in all three axes --
+    // the visibility sweep's tile culling and whole-tile accept rely on it
+    // (a box that is tall in z projects to a large image footprint).
     const int lx = l.bits_x < kVoxCoarseShift ? l.bits_x : kVoxCoarseShift;
     const int ly = l.bits_y < kVoxCoarseShift ? l.bits_y : kVoxCoarseShift;
+    const int lz = l.bits_z < kVoxCoarseShift ? l.bits_z : kVoxCoarseShift;
+    const uint64_t cx = vx >> lx, cy = vy >> ly;
+    uint64_t cell;
+    if (l.morton) {
+      cell = 0;
+      for (int i = 0; i < l.bits_m / 2; ++i)
+        cell |= (((cx >> i) & 1ull) << (2 * i + 1)) | (((cy >> i) & 1ull) << (2 * i));
+    } else {
+      cell = (cx << (l.bits_y - ly)) | cy;
+    }
     uint64_t k = (uint64_t)b;
-    k = (k << (l.bits_x - lx)) | (vx >> lx);
-    k = (k << (l.bits_y - ly)) | (vy >> ly);
+    k = (k << (l.bits_z - lz)) | (vz >> lz);
+    k = (k << l.bits_m) | cell;
     k = (k << lx) | (vx & ((1ull << lx) - 1));
     k = (k << ly) | (vy & ((1ull << ly) - 1));
-    k = (k << l.bits_z) | vz;
+    k = (k << lz) | (vz & ((1ull << lz) - 1));
     keys[e] = k;
     vals[e] = (uint32_t)e;
   }
@@ -224,7 +247,7 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
     int32_t* __restrict__ ds_first, int64_t* __restrict__ ds_offsets) {
   __shared__ int s[33];
   const VoxLayout l = *lay;
-  const int shift_b = l.bits_x + l.bits_y + l.bits_z;
+  const int shift_b = l.total_bits - l.bits_b;
   const int64_t base = (int64_t)blockIdx.x * kHeadTile;
   int64_t out = tile_base[blockIdx.x];
 #pragma unroll 1

@@ -24,6 +24,8 @@ VOXEL_SIZE = 0.1                      # :928
 VISIBLE_RATE = 0.45                   # :930
 MIN_HITS = 3                          # :898
 NEAR_EPS = 1e-6
+SAMPLE_STRIDE = 32                    # sweep-1 sample used for the interior rectangles
+KRECT_MARGIN_PX = 1.0
 
 
 def _ptr(t):
@@ -281,7 +283,7 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
                cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False,
-               cand_pool=None) -> VisibilityResult:
+               cand_pool=None, interior=True, sample_stride=SAMPLE_STRIDE) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair.
 
     sweep 1 (hit counts, pivot, 8 extremes) -> area bounds + early decision ->
@@ -289,7 +291,12 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
     exact_ratio=True sends every pair with > min_hits hits through the exact
     hull (ratio is then the reference's value for every pair; otherwise decided
     pairs carry the deciding bound and flags bit4).  One host synchronisation
-    at the end (candidate-capacity check)."""
+    at the end (candidate-capacity check).
+
+    interior=True first runs sweep 1 on a 1-in-`sample_stride` sample of every
+    block and derives, per pair, a rectangle strictly inside the convex hull
+    of the sample's hits; the full sweep only counts the points that project
+    into it (no divisions, no extreme tracking).  Results are identical."""
     lib = _lib.load()
     dev = cameras_d.device
     L = ds_offsets.shape[0] - 1
@@ -316,9 +323,33 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
     mark = timer.mark if timer is not None else (lambda name: None)
     check(lib.ptgs_visibility_init(P, _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(cand_count), st))
     mark("vis_init")
+    krect = None
+    if interior:
+        n_pts = int(ds_x.shape[0])
+        cap = (n_pts // int(sample_stride) + L + 8 + 3) & ~3   # >= sum ceil(M_b / stride); rows stay 16 B aligned
+        smp = torch.empty((3, cap + 8), dtype=torch.float32, device=dev)
+        s_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
+        n_hit_s = torch.empty(P, dtype=torch.int32, device=dev)
+        pivot_s = torch.empty(P, dtype=torch.int64, device=dev)
+        extreme_s = torch.empty(P * 8, dtype=torch.int64, device=dev)
+        krect = torch.empty((P, 4), dtype=torch.float32, device=dev)
+        check(lib.ptgs_visibility_sample(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
+                                         int(sample_stride), _ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]),
+                                         _ptr(s_off), cap, st))
+        check(lib.ptgs_visibility_init(P, _ptr(n_hit_s), _ptr(pivot_s), _ptr(extreme_s), None, st))
+        check(lib.ptgs_visibility_count(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
+                                        _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
+                                        pick_cam_split(cap, L), _ptr(n_hit_s), _ptr(pivot_s),
+                                        _ptr(extreme_s), None, _ptr(ws), ws.numel(), st))
+        check(lib.ptgs_visibility_krect(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
+                                        _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
+                                        _ptr(n_hit_s), _ptr(extreme_s), P, float(KRECT_MARGIN_PX),
+                                        _ptr(krect), st))
+        mark("vis_interior_rects")
     check(lib.ptgs_visibility_count(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                     _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), cam_split,
-                                    _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(ws), ws.numel(), st))
+                                    _ptr(n_hit), _ptr(pivot), _ptr(extreme), _ptr(krect), _ptr(ws),
+                                    ws.numel(), st))
     mark("vis_sweep1_count")
     check(lib.ptgs_visibility_bounds(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                      _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), _ptr(n_hit),

@@ -303,8 +303,30 @@ int ptgs_visibility_count(const float* px, const float* py, const float* pz,
                           const float* cameras, const int64_t* cam_offsets,
                           const int32_t* cam_index, int32_t cam_split,
                           int32_t* n_hit, uint64_t* pivot, uint64_t* extreme,
-                          void* workspace, size_t workspace_bytes,
-                          ptgs_stream_t stream);
+                          const float* krect, void* workspace,
+                          size_t workspace_bytes, ptgs_stream_t stream);
+/* Interior rectangles for sweep 1 (optional acceleration, results unchanged).
+ * ptgs_visibility_sample gathers every `stride`-th point of each block
+ * (s_offsets[L+1], sx/sy/sz with room for `capacity` >= sum ceil(M_b / stride)
+ * points, padded like the point arrays above).  Run ptgs_visibility_count on
+ * the sample (krect = NULL) and hand its n_hit / extreme to
+ * ptgs_visibility_krect: per pair, krect[p] = (cu, cv, hu, hv), an
+ * axis-parallel rectangle of the image plane at least margin_px (>= 0.5)
+ * inside the convex hull of the sample's hits (hu < 0: none).  Passed to the
+ * full ptgs_visibility_count, points projecting into it are only counted:
+ * they are hits, and they cannot be the Graham pivot (:509-511) or a
+ * directional extreme. */
+int ptgs_visibility_sample(const float* px, const float* py, const float* pz,
+                           const int64_t* pt_offsets, int32_t n_blocks,
+                           int32_t stride, float* sx, float* sy, float* sz,
+                           int64_t* s_offsets, int64_t capacity,
+                           ptgs_stream_t stream);
+int ptgs_visibility_krect(const float* sx, const float* sy, const float* sz,
+                          const int64_t* s_offsets, int32_t n_blocks,
+                          const float* cameras, const int64_t* cam_offsets,
+                          const int32_t* cam_index, const int32_t* n_hit_s,
+                          const uint64_t* extreme_s, int64_t n_pairs,
+                          double margin_px, float* krect, ptgs_stream_t stream);
 #define PTGS_POLY_FLOATS 28 /* [0]=n_edges [1]=v_pivot [2]=u_pivot [3]=margin, 8 x (a,b,c) */
 int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
                            const int64_t* pt_offsets, int32_t n_blocks,
@@ -363,6 +385,11 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         int32_t cam_count, int32_t* n_hit, uint8_t* seen,
                         void* workspace, size_t workspace_bytes,
                         ptgs_stream_t stream);
+
+/* Diagnostics (synchronising; HOST pointer): out4[0] = point-camera tests
+ * presented to the sweeps since the last reset, out4[1] = tests left after the
+ * tile / frustum cull, out4[2..3] reserved.  reset != 0 zeroes the counters. */
+int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset);
 
 #ifdef __cplusplus
 }
