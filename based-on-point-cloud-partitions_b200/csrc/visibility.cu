@@ -25,10 +25,11 @@ constexpr int kSwThreads = 256;
 constexpr int kSwP = 8;                          // points per thread
 constexpr int kSwTile = kSwThreads * kSwP;       // 2048 points per tile
 constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
-constexpr int kSwCamChunk = 32;                  // cameras staged per round
+constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups)
 constexpr int kSwMaxBlocks = 1024;
 constexpr int kCamFloats = PTGS_CAMERA_FLOATS;   // 20
 constexpr int kPolyFloats = PTGS_POLY_FLOATS;    // 28
+constexpr int kKrectFloats = PTGS_KRECT_FLOATS;  // 32
 
 // ---- mbarrier / bulk copy (TMA) -------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -239,6 +240,45 @@ __device__ __forceinline__ bool tile_all_in(const Cam& c, const float* der, cons
          (B2.mid - B2.rad > mP);
 }
 
+// Same question for the interior polygon Q of a pair (krect record: [4] = number
+// of edges, [8 + 3e ..] = (a, b, c) with a*u + b*v + c >= 0 inside, |(a, b)| = 1,
+// c already reduced by the safety margin): a*uh + b*vh + c*Z >= 0 over the box.
+// Returns the mask of polygon edges that are NOT satisfied by every point of the
+// box (0xffffffff: no polygon); `fz` = front > 0 and Z > 0 hold on the whole box.
+// Mask 0 with fz: every point of the box projects into Q.  A point with front > 0
+// and Z > 0 that satisfies the masked edges projects into Q as well.
+__device__ __forceinline__ unsigned poly_undecided(const Cam& c, const float* kq, const float* b,
+                                                   bool& fz) {
+  fz = false;
+  const int ne = (int)kq[4];
+  if (ne < 3) return 0xffffffffu;
+  const float S = fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + b[3] + b[4] + b[5] +
+                  fmaxf(fabsf(c.tx), fmaxf(fabsf(c.ty), fabsf(c.tz)));
+  const float mF = S * (1.0f / 65536.0f);
+  const float mP = mF * (c.fx + c.fy + c.w + c.h + fabsf(c.cx) + fabsf(c.cy));
+  const Form Y = form(c.r10, c.r11, c.r12, c.ty, b);
+  const Form Z = form(c.r20, c.r21, c.r22, c.tz, b);
+  const Form F = (c.front_axis == 1.0f) ? Y : Z;
+  fz = (F.mid - F.rad > mF) && (Z.mid - Z.rad > mF);
+  // uh = A.p + ad, vh = C.p + cd as linear forms of the world point
+  const float a0 = fmaf(c.fx, c.r00, c.cx * c.r20), a1 = fmaf(c.fx, c.r01, c.cx * c.r21),
+              a2 = fmaf(c.fx, c.r02, c.cx * c.r22), ad = fmaf(c.fx, c.tx, c.cx * c.tz);
+  const float c0 = fmaf(c.fy, c.r10, c.cy * c.r20), c1 = fmaf(c.fy, c.r11, c.cy * c.r21),
+              c2 = fmaf(c.fy, c.r12, c.cy * c.r22), cd = fmaf(c.fy, c.ty, c.cy * c.tz);
+  unsigned und = 0;
+  for (int e = 0; e < ne; ++e) {
+    const float ea = kq[8 + 3 * e], eb = kq[9 + 3 * e], ec = kq[10 + 3 * e];
+    const Form G = form(fmaf(ea, a0, fmaf(eb, c0, ec * c.r20)), fmaf(ea, a1, fmaf(eb, c1, ec * c.r21)),
+                        fmaf(ea, a2, fmaf(eb, c2, ec * c.r22)), fmaf(ea, ad, fmaf(eb, cd, ec * c.tz)), b);
+    if (!(G.mid - G.rad > mP)) und |= 1u << e;
+  }
+  return und;
+}
+__device__ __forceinline__ bool tile_all_in_poly(const Cam& c, const float* kq, const float* b) {
+  bool fz;
+  return poly_undecided(c, kq, b, fz) == 0u && fz;
+}
+
 // ---- work item schedule -----------------------------------------------------
 // item_prefix[b] = number of work items of the blocks before b; a block has
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
@@ -323,21 +363,23 @@ __device__ __forceinline__ Item decode_item(const SweepArgs& a, const int64_t* s
 
 // diagnostics (ptgs_debug_sweep_stats): point-camera tests before / after the
 // tile cull, summed over every sweep launch since the last reset
-__device__ unsigned long long g_sweep_stats[4];
+__device__ unsigned long long g_sweep_stats[8];
+#ifdef PTGS_SWEEP_STATS_FINE   // counters [2..7] sit on the hot path: diagnostics builds only
+#define PTGS_FINE_STAT(i, v) atomicAdd(&g_sweep_stats[i], (unsigned long long)(v))
+#else
+#define PTGS_FINE_STAT(i, v) ((void)0)
+#endif
 
 // ---- the sweep ---------------------------------------------------------------
 struct SweepSmem {
   alignas(128) float tile[2][3][kSwStageFloats];
   alignas(16) float cam[kSwCamChunk][kCamFloats];
-  alignas(16) float poly[kSwCamChunk][kPolyFloats];       // MODE 2
-  unsigned long long ext[kSwCamChunk][8];                 // MODE 1
-  unsigned long long pivot[kSwCamChunk];                  // MODE 1
+  alignas(16) float poly[kSwCamChunk][kKrectFloats];      // MODE 2: inner polygon; MODE 1: krect record
   long long cand_off[kSwCamChunk];                        // MODE 2
   int cand_cap[kSwCamChunk];                              // MODE 2
   int pair_of[kSwCamChunk];                               // MODE 2
-  int cnt[kSwCamChunk];
   int act[kSwThreads];                                    // cameras of the round that survive the tile cull
-  long long lpos[kSwCamChunk];                            // list position of the staged cameras
+  long long pair[kSwCamChunk];                            // output slot (pair id / camera) of the staged cameras
   int nact;
   int tile_seen;                                          // MODE 0: a camera contains the whole tile
   alignas(16) float der[kSwCamChunk][8];                  // MODE 0/1: fast-in / not-miss rectangles
@@ -386,12 +428,14 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
     mbar_wait(&S.bar[stage], phase[stage]);
     phase[stage] ^= 1;
     float x[kSwP], y[kSwP], z[kSwP];
+    float wb[6];        // this warp's box: centre xyz, half extent xyz (its 256 points are contiguous)
+    const int wcnt = min(max(cur.cnt - (tid & ~31) * kSwP, 0), 32 * kSwP);
     {
       const int shift = (int)(cur.start & 3);
       const float qnan = __int_as_float(0x7fc00000);
 #pragma unroll
       for (int k = 0; k < kSwP; ++k) {
-        const int i = k * kSwThreads + tid;
+        const int i = (tid & ~31) * kSwP + k * 32 + lane;   // warp w owns points [256 w, 256 w + 256)
         const bool ok = i < cur.cnt;
         x[k] = ok ? S.tile[stage][0][shift + i] : qnan;   // NaN never hits
         y[k] = ok ? S.tile[stage][1][shift + i] : qnan;
@@ -419,6 +463,12 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       if (lane == 0) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) { S.wbox[tid >> 5][a] = lo[a]; S.wbox[tid >> 5][3 + a] = hi[a]; }
+      }
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const float pad = (fabsf(lo[a]) + fabsf(hi[a])) * (1.0f / 1048576.0f);
+        wb[a] = 0.5f * lo[a] + 0.5f * hi[a];
+        wb[3 + a] = (0.5f * hi[a] - 0.5f * lo[a]) + pad;
       }
     }
     __syncthreads();   // every thread is done with stage^1 (previous item) and this stage
@@ -468,12 +518,13 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         if (MODE != 2 && live) {
           float der[8];
           const float* kr = nullptr;
-          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * 4;
+          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * kKrectFloats;
           make_rects(cj, kr, MODE, der);
-          if (tile_all_in(cj, der, S.box)) {
+          if ((MODE == 1 && kr) ? tile_all_in_poly(cj, kr, S.box) : tile_all_in(cj, der, S.box)) {
             // every point of the tile is a hit that needs no further work
             const int64_t pair = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
             atomicAdd(a.n_hit + pair, cur.cnt);
+            PTGS_FINE_STAT(5, cur.cnt);
             if (MODE == 0) S.tile_seen = 1;
             live = false;
           }
@@ -505,15 +556,18 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
               __ldg(reinterpret_cast<const float4*>(a.poly + pair * kPolyFloats) + q);
         }
       }
+      if (MODE == 1) {
+        for (int i = tid; i < nc * (kKrectFloats / 4); i += kSwThreads) {
+          const int j = i / (kKrectFloats / 4), q = i % (kKrectFloats / 4);
+          const int64_t slot = cam_base + cur.cam_lo + S.act[c0 + j];
+          reinterpret_cast<float4*>(S.poly[j])[q] =
+              a.krect ? __ldg(reinterpret_cast<const float4*>(a.krect + slot * kKrectFloats) + q)
+                      : make_float4(0.0f, 0.0f, -1.0f, -1.0f);
+        }
+      }
       if (tid < nc) {
         const int64_t lpos = cur.cam_lo + S.act[c0 + tid];
-        S.lpos[tid] = lpos;
-        S.cnt[tid] = 0;
-        if (MODE == 1) {
-          S.pivot[tid] = ~0ull;
-#pragma unroll
-          for (int d = 0; d < 8; ++d) S.ext[tid][d] = 0ull;
-        }
+        S.pair[tid] = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
         if (MODE != 2) {
           const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
           const float* rp = a.cameras + cam * kCamFloats;
@@ -521,7 +575,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           cj.w = __ldg(rp + 16); cj.h = __ldg(rp + 17);
           float der[8];
           const float* kr = nullptr;
-          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * 4;
+          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * kKrectFloats;
           make_rects(cj, kr, MODE, der);
 #pragma unroll
           for (int q = 0; q < 8; ++q) S.der[tid][q] = der[q];
@@ -536,18 +590,59 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
       }
       __syncthreads();
-      const int nact = nc;
+      for (int g0 = 0; g0 < nc; g0 += 32) {
+      // ---- per-warp classification: lane j tests camera j of the chunk against the
+      // box of the warp's own 256 contiguous points (a few voxel-cells wide):
+      // outside -> skipped, wholly inside the "in" rectangle -> counted, else swept.
+      unsigned pm = 0;
+      unsigned und = 0xffffffffu;      // MODE 1, lane j: polygon edges of camera j that cut the warp's box
+      if (wcnt > 0) {
+        bool may = false, allin = false;
+        if (g0 + lane < nc) {
+          const Cam cj = load_cam(S.cam[g0 + lane]);
+          may = tile_may_hit(cj, wb);
+          if (MODE == 1 && may) {
+            bool fz;
+            und = poly_undecided(cj, S.poly[g0 + lane], wb, fz);
+            allin = und == 0u && fz;
+          }
+          if (MODE == 0 && may) allin = tile_all_in(cj, S.der[g0 + lane], wb);
+          if (allin) atomicAdd(a.n_hit + S.pair[g0 + lane], wcnt);
+        }
+        pm = __ballot_sync(kFullMask, may && !allin);
+        if (MODE == 0 && __ballot_sync(kFullMask, allin) != 0u) seen_mask = 0xffu;
+        if (lane == 0) {
+          PTGS_FINE_STAT(MODE == 2 ? 3 : 2, (unsigned long long)__popc(pm) * (unsigned)wcnt);
+        }
+        {
+          const unsigned am = __ballot_sync(kFullMask, allin);
+          if (lane == 0 && am) PTGS_FINE_STAT(4, (unsigned long long)__popc(am) * (unsigned)wcnt);
+        }
+      }
 
       // ---- sweep: 8 register points x surviving cameras
       if (MODE != 2) {
-        for (int jj = 0; jj < nact; ++jj) {
-          const int j = jj;
+        for (unsigned pmm = pm; pmm; pmm &= pmm - 1) {
+          const int jl = __ffs(pmm) - 1, j = g0 + jl;
           const Cam c = load_cam(S.cam[j]);
           const float4 din = *reinterpret_cast<const float4*>(&S.der[j][0]);
           const float4 dout = *reinterpret_cast<const float4*>(&S.der[j][4]);
           const bool front_y = c.front_axis == 1.0f;
           int cnt = 0;
           unsigned slow = 0;
+          // MODE 1: when at most two polygon edges cut the warp's box, "inside those
+          // edges" replaces the interior rectangle as the count-only region
+          bool use_edges = false;
+          float e1a = 0.0f, e1b = 0.0f, e1c = 0.0f, e2a = 0.0f, e2b = 0.0f, e2c = 0.0f;
+          if (MODE == 1) {
+            const unsigned uj = __shfl_sync(kFullMask, und, jl);
+            if (uj != 0xffffffffu && uj != 0u && __popc(uj) <= 2) {
+              use_edges = true;
+              const int ea = __ffs(uj) - 1, eb = 31 - __clz(uj);
+              e1a = S.poly[j][8 + 3 * ea]; e1b = S.poly[j][9 + 3 * ea]; e1c = S.poly[j][10 + 3 * ea];
+              e2a = S.poly[j][8 + 3 * eb]; e2b = S.poly[j][9 + 3 * eb]; e2c = S.poly[j][10 + 3 * eb];
+            }
+          }
 #pragma unroll
           for (int k = 0; k < kSwP; ++k) {
             const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
@@ -557,8 +652,15 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
             const float vh = __fmaf_rn(c.cy, Z, __fmul_rn(c.fy, Y));
             const float az = fabsf(Z);
             const bool front = (front_y ? Y : Z) > 0.0f;
-            const bool in = front && (fabsf(__fmaf_rn(-din.x, Z, uh)) < __fmul_rn(din.z, az)) &&
-                            (fabsf(__fmaf_rn(-din.y, Z, vh)) < __fmul_rn(din.w, az));
+            bool in;
+            if (MODE == 1 && use_edges) {
+              in = front && (Z > 0.0f) &&
+                   (__fmaf_rn(e1a, uh, __fmaf_rn(e1b, vh, __fmul_rn(e1c, Z))) > 0.0f) &&
+                   (__fmaf_rn(e2a, uh, __fmaf_rn(e2b, vh, __fmul_rn(e2c, Z))) > 0.0f);
+            } else {
+              in = front && (fabsf(__fmaf_rn(-din.x, Z, uh)) < __fmul_rn(din.z, az)) &&
+                   (fabsf(__fmaf_rn(-din.y, Z, vh)) < __fmul_rn(din.w, az));
+            }
             bool nm;
             if (MODE == 0) {   // same centre: one fma per axis serves both rectangles
               nm = front && (fabsf(__fmaf_rn(-din.x, Z, uh)) <= __fmaf_rn(dout.z, az, 1e-30f)) &&
@@ -581,10 +683,12 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
             for (int d = 0; d < 8; ++d) { t_best[d] = -__int_as_float(0x7f800000); t_idx[d] = 0; }
           }
           if (__any_sync(kFullMask, slow != 0)) {
+            if (lane == 0) PTGS_FINE_STAT(6, 1);
 #pragma unroll
             for (int k = 0; k < kSwP; ++k) {
               const bool mine = (slow >> k) & 1u;
               if (!__any_sync(kFullMask, mine)) continue;
+              if (lane == 0) PTGS_FINE_STAT(7, 1);
               if (mine) {
                 const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
                 const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
@@ -603,7 +707,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                     const unsigned long long pk =
                         ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
                     t_pv = pk < t_pv ? pk : t_pv;
-                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + k * kSwThreads + tid);
+                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + (tid & ~31) * kSwP + k * 32 + lane);
                     const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                     const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
@@ -615,33 +719,40 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
               }
             }
           }
+          // results go straight to the pair's global slots: warps never wait for each other
+          const int64_t pair = S.pair[j];
           const int wsum = __reduce_add_sync(kFullMask, cnt);
-          if (lane == 0 && wsum) atomicAdd(&S.cnt[j], wsum);
+          if (lane == 0 && wsum) atomicAdd(a.n_hit + pair, wsum);
           if (MODE == 1 && __any_sync(kFullMask, any_slow)) {
             const uint32_t phi = (uint32_t)(t_pv >> 32);
             const uint32_t mhi = __reduce_min_sync(kFullMask, phi);
             const uint32_t plo = phi == mhi ? (uint32_t)t_pv : 0xffffffffu;
             const uint32_t mlo = __reduce_min_sync(kFullMask, plo);
+            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
             if (lane == 0) {
               const unsigned long long pk = ((unsigned long long)mhi << 32) | mlo;
-              if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
+              if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
             }
+            // the 8 extremes: lane d reduces nothing, every lane contributes to 8 redux
+            unsigned long long mine_e = 0ull;
 #pragma unroll
             for (int d = 0; d < 8; ++d) {
               const uint32_t key = order_key(t_best[d]);
               const uint32_t mk = __reduce_max_sync(kFullMask, key);
               const unsigned who = __ballot_sync(kFullMask, key == mk);
               const uint32_t id = __shfl_sync(kFullMask, t_idx[d], __ffs(who) - 1);
-              if (lane == 0) {
-                const unsigned long long e = ((unsigned long long)mk << 32) | id;
-                if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
-              }
+              if (lane == d) mine_e = ((unsigned long long)mk << 32) | id;
             }
+            // -inf (no hit along d in this warp) has key 0x007fffff: never beats a real entry
+            if (lane < 8 && (uint32_t)(mine_e >> 32) > 0x007fffffu &&
+                mine_e > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
+              atomicMax(gex + lane, mine_e);
           }
         }
       } else {
-      for (int jj = 0; jj < nact; ++jj) {
-        const int j = jj;
+      for (unsigned pmm = pm; pmm; pmm &= pmm - 1) {
+        const int jl = __ffs(pmm) - 1, j = g0 + jl;
         const Cam c = load_cam(S.cam[j]);
         const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
         int cnt = 0;
@@ -667,7 +778,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                 const unsigned long long pk =
                     ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
                 t_pv = pk < t_pv ? pk : t_pv;
-                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + k * kSwThreads + tid);
+                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + (tid & ~31) * kSwP + k * 32 + lane);
                 const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                 const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
@@ -700,62 +811,20 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
             }
           }
         }
-        if (MODE != 2) {
-          const int wsum = __reduce_add_sync(kFullMask, cnt);
-          if (lane == 0 && wsum) atomicAdd(&S.cnt[j], wsum);
-          if (MODE == 1 && wsum) {
-            // warp reduction of the pivot (64-bit min as two 32-bit steps) and of
-            // the 8 extremes (redux.sync on the ordered key, lowest lane wins ties)
-            const uint32_t phi = (uint32_t)(t_pv >> 32);
-            const uint32_t mhi = __reduce_min_sync(kFullMask, phi);
-            const uint32_t plo = phi == mhi ? (uint32_t)t_pv : 0xffffffffu;
-            const uint32_t mlo = __reduce_min_sync(kFullMask, plo);
-            if (lane == 0) {
-              const unsigned long long pk = ((unsigned long long)mhi << 32) | mlo;
-              if (pk < S.pivot[j]) atomicMin(&S.pivot[j], pk);
-            }
-#pragma unroll
-            for (int d = 0; d < 8; ++d) {
-              const uint32_t key = order_key(t_best[d]);
-              const uint32_t mk = __reduce_max_sync(kFullMask, key);
-              const unsigned who = __ballot_sync(kFullMask, key == mk);
-              const uint32_t id = __shfl_sync(kFullMask, t_idx[d], __ffs(who) - 1);
-              if (lane == 0) {
-                const unsigned long long e = ((unsigned long long)mk << 32) | id;
-                if (e > S.ext[j][d]) atomicMax(&S.ext[j][d], e);
-              }
-            }
-          }
-        }
       }
       }
-      __syncthreads();
+      }   // lane groups
 
-      // ---- flush the chunk's accumulators
-      if (MODE != 2 && tid < nc) {
-        const int cn = S.cnt[tid];
-        if (cn) {
-          const int64_t pair = (MODE == 0 && !a.cam_index) ? S.lpos[tid] : (cam_base + S.lpos[tid]);
-          atomicAdd(a.n_hit + pair, cn);
-          if (MODE == 1) {
-            atomicMin(reinterpret_cast<unsigned long long*>(a.pivot) + pair, S.pivot[tid]);
-#pragma unroll
-            for (int d = 0; d < 8; ++d)
-              if (S.ext[tid][d])
-                atomicMax(reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8 + d,
-                          S.ext[tid][d]);
-          }
-        }
-      }
-      __syncthreads();
+      // staging arrays are rewritten by the next chunk (rare: > kSwCamChunk surviving cameras)
+      if (c0 + kSwCamChunk < nact_all) __syncthreads();
     }
     }
     if (MODE == 0 && a.seen) {
       const bool all = S.tile_seen != 0;   // written before the last barrier of the chunk loop
 #pragma unroll
       for (int k = 0; k < kSwP; ++k)
-        if ((all && k * kSwThreads + tid < cur.cnt) || (seen_mask & (1u << k)))
-          a.seen[cur.start + k * kSwThreads + tid] = 1;
+        if ((tid & ~31) * kSwP + k * 32 + lane < cur.cnt && (all || (seen_mask & (1u << k))))
+          a.seen[cur.start + (tid & ~31) * kSwP + k * 32 + lane] = 1;
     }
     cur = nxt;
   }
@@ -1315,8 +1384,9 @@ __global__ void __launch_bounds__(128) krect_kernel(
   const int64_t n_pairs = cam_offsets[L];
   const int64_t pair = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pair >= n_pairs) return;
-  float* out = krect + pair * 4;
-  out[0] = 0.0f; out[1] = 0.0f; out[2] = -1.0f; out[3] = -1.0f;
+  float* out = krect + pair * kKrectFloats;
+  for (int i = 0; i < kKrectFloats; ++i) out[i] = 0.0f;
+  out[2] = -1.0f; out[3] = -1.0f;
   if (n_hit_s[pair] < 3) return;
   int lo = 0, hi = L - 1;
   while (lo < hi) {
@@ -1355,6 +1425,17 @@ __global__ void __launch_bounds__(128) krect_kernel(
     if (!(fg > 0.0)) return;                                      // degenerate / not CCW: no K
     if (reach > 0.0) t = fmin(t, fg / reach);
   }
+  // the polygon itself, every edge moved inwards by margin_px (unit normals);
+  // its vertices are hits, so it lies inside the image
+  for (int i = 0; i < m; ++i) {
+    const int k = (i + 1 == m) ? 0 : i + 1;
+    const double nx = -(vy[k] - vy[i]), ny = vx[k] - vx[i];
+    const double len = sqrt(nx * nx + ny * ny);
+    out[8 + 3 * i] = (float)(nx / len);
+    out[9 + 3 * i] = (float)(ny / len);
+    out[10 + 3 * i] = (float)(-(nx * vx[i] + ny * vy[i]) / len - margin_px - 1e-3 * (fabs(vx[i]) + fabs(vy[i])) * 1e-3);
+  }
+  out[4] = (float)m;
   const double hu = t * ha * (1.0 - 1e-6) - margin_px, hv = t * hb * (1.0 - 1e-6) - margin_px;
   if (!(hu > 0.0) || !(hv > 0.0)) return;
   // stay strictly inside the image whatever the rounding to float
@@ -1365,7 +1446,7 @@ __global__ void __launch_bounds__(128) krect_kernel(
 // ---- host side -----------------------------------------------------------------
 template <int MODE>
 static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
-  static_assert(sizeof(SweepSmem) < 100 * 1024, "two CTAs per SM");
+  static_assert(sizeof(SweepSmem) < 112 * 1024, "two CTAs per SM");
   PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(SweepSmem)));
   sweep_kernel<MODE><<<kNumSMs * 2, kSwThreads, sizeof(SweepSmem), st>>>(a);
@@ -1548,14 +1629,14 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
 }
 
 int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset) {
-  unsigned long long h[4] = {0, 0, 0, 0};
+  unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   PTGS_CUDA_TRY(cudaDeviceSynchronize());
   if (out4) {
     PTGS_CUDA_TRY(cudaMemcpyFromSymbol(h, g_sweep_stats, sizeof(h)));
-    for (int i = 0; i < 4; ++i) out4[i] = h[i];
+    for (int i = 0; i < 8; ++i) out4[i] = h[i];
   }
   if (reset) {
-    unsigned long long z[4] = {0, 0, 0, 0};
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     PTGS_CUDA_TRY(cudaMemcpyToSymbol(g_sweep_stats, z, sizeof(z)));
   }
   return PTGS_OK;

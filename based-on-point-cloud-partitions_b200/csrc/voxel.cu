@@ -194,9 +194,13 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
     uint64_t k = (uint64_t)b;
     k = (k << (l.bits_z - lz)) | (vz >> lz);
     k = (k << l.bits_m) | cell;
-    k = (k << lx) | (vx & ((1ull << lx) - 1));
-    k = (k << ly) | (vy & ((1ull << ly) - 1));
-    k = (k << lz) | (vz & ((1ull << lz) - 1));
+    // fine bits: 3-D Morton, so that 256 / 32 consecutive voxels (a warp's share
+    // of a sweep tile / one register slot of a warp) are compact cubes
+    for (int i = kVoxCoarseShift - 1; i >= 0; --i) {
+      if (i < lx) k = (k << 1) | ((vx >> i) & 1ull);
+      if (i < ly) k = (k << 1) | ((vy >> i) & 1ull);
+      if (i < lz) k = (k << 1) | ((vz >> i) & 1ull);
+    }
     keys[e] = k;
     vals[e] = (uint32_t)e;
   }

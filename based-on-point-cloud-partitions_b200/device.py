@@ -332,7 +332,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         n_hit_s = torch.empty(P, dtype=torch.int32, device=dev)
         pivot_s = torch.empty(P, dtype=torch.int64, device=dev)
         extreme_s = torch.empty(P * 8, dtype=torch.int64, device=dev)
-        krect = torch.empty((P, 4), dtype=torch.float32, device=dev)
+        krect = torch.empty((P, 32), dtype=torch.float32, device=dev)     # PTGS_KRECT_FLOATS
         check(lib.ptgs_visibility_sample(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                          int(sample_stride), _ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]),
                                          _ptr(s_off), cap, st))

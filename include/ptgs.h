@@ -310,12 +310,17 @@ int ptgs_visibility_count(const float* px, const float* py, const float* pz,
  * (s_offsets[L+1], sx/sy/sz with room for `capacity` >= sum ceil(M_b / stride)
  * points, padded like the point arrays above).  Run ptgs_visibility_count on
  * the sample (krect = NULL) and hand its n_hit / extreme to
- * ptgs_visibility_krect: per pair, krect[p] = (cu, cv, hu, hv), an
- * axis-parallel rectangle of the image plane at least margin_px (>= 0.5)
- * inside the convex hull of the sample's hits (hu < 0: none).  Passed to the
- * full ptgs_visibility_count, points projecting into it are only counted:
+ * ptgs_visibility_krect: per pair a record of PTGS_KRECT_FLOATS floats,
+ *   [0..3]  (cu, cv, hu, hv): an axis-parallel rectangle of the image plane
+ *           (hu < 0: none),
+ *   [4]     number of edges m of a convex polygon (0: none), [5..7] zero,
+ *   [8+3e..] (a, b, c) of edge e: a*u + b*v + c >= 0 inside, |(a, b)| = 1,
+ * both at least margin_px (>= 0.5) inside the convex hull of the sample's
+ * hits.  Passed to the full ptgs_visibility_count, points projecting into the
+ * rectangle and point boxes projecting into the polygon are only counted:
  * they are hits, and they cannot be the Graham pivot (:509-511) or a
  * directional extreme. */
+#define PTGS_KRECT_FLOATS 32
 int ptgs_visibility_sample(const float* px, const float* py, const float* pz,
                            const int64_t* pt_offsets, int32_t n_blocks,
                            int32_t stride, float* sx, float* sy, float* sz,
@@ -386,9 +391,12 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         void* workspace, size_t workspace_bytes,
                         ptgs_stream_t stream);
 
-/* Diagnostics (synchronising; HOST pointer): out4[0] = point-camera tests
- * presented to the sweeps since the last reset, out4[1] = tests left after the
- * tile / frustum cull, out4[2..3] reserved.  reset != 0 zeroes the counters. */
+/* Diagnostics (synchronising; HOST pointer to 8 counters since the last
+ * reset): [0] point-camera tests presented to the sweeps, [1] left after the
+ * CTA-level tile cull, [2] swept per point (sweep 1 / coverage), [3] swept per
+ * point (sweep 2), [4] accepted per warp box, [5] accepted per tile box,
+ * [6] (warp, camera) passes that entered the exact path, [7] 32-point groups
+ * on the exact path.  reset != 0 zeroes the counters. */
 int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset);
 
 #ifdef __cplusplus

@@ -55,13 +55,13 @@ gap = (vis.ratio_hi - vis.ratio_lo).cpu().numpy()
 print("bound gap pct[50,90,99,100]", np.percentile(gap, [50, 90, 99, 100]))
 import ctypes
 from ptgs_b200 import _lib
-lib = _lib.load(); st4 = (ctypes.c_uint64 * 4)()
+lib = _lib.load(); st4 = (ctypes.c_uint64 * 8)()
 lib.ptgs_debug_sweep_stats(None, 1)
 tm = D.StageTimer(True); tm.mark("start")
 D.visibility(ds[1], ds[2], ds[3], ds[0], cams_d, coff, cidx, timer=tm)
 print({k: round(v, 3) for k, v in tm.result().items()})
 lib.ptgs_debug_sweep_stats(st4, 0)
-print("sweep tests presented (both sweeps)", st4[0], "after cull", st4[1], "survive", st4[1] / max(1, st4[0]))
+print("sweep stats [presented, after CTA cull, swept s1, swept s2, warp all-in, tile all-in, slow passes, slow groups]", list(st4))
 i = int(np.argmax(cc))
 print("worst pair", i, "n_hit", nh[i], "cand", cc[i], "rlo", float(vis.ratio_lo[i]), "rhi", float(vis.ratio_hi[i]),
       "ratio", rt[i], "flags", int(vis.flags[i]))
