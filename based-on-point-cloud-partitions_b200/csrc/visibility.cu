@@ -284,7 +284,7 @@ __device__ __forceinline__ bool tile_all_in_poly(const Cam& c, const float* kq, 
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
 __global__ void __launch_bounds__(1024) sweep_schedule_kernel(
     const int64_t* __restrict__ pt_offsets, const int64_t* __restrict__ cam_offsets, int L,
-    int cam_split, int64_t* __restrict__ item_prefix) {
+    int cam_split, int64_t* __restrict__ item_prefix, int n_ctas) {
   __shared__ long long sm[33];
   long long carry = 0;
   for (int s = 0; s < L; s += 1024) {
@@ -301,7 +301,10 @@ __global__ void __launch_bounds__(1024) sweep_schedule_kernel(
     if (b < L) item_prefix[b] = carry + ex;
     carry += tot;
   }
-  if (threadIdx.x == 0) item_prefix[L] = carry;
+  if (threadIdx.x == 0) {
+    item_prefix[L] = carry;
+    item_prefix[L + 1] = n_ctas;   // dynamic work counter: CTA i starts on item i
+  }
 }
 
 struct SweepArgs {
@@ -381,6 +384,7 @@ struct SweepSmem {
   int act[kSwThreads];                                    // cameras of the round that survive the tile cull
   long long pair[kSwCamChunk];                            // output slot (pair id / camera) of the staged cameras
   int nact;
+  long long next_item;
   int tile_seen;                                          // MODE 0: a camera contains the whole tile
   alignas(16) float der[kSwCamChunk][8];                  // MODE 0/1: fast-in / not-miss rectangles
   float wbox[kSwThreads / 32][6];                         // per warp tile AABB
@@ -423,7 +427,9 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
   }
   uint32_t phase[2] = {0, 0};
   int stage = 0;
-  for (; item < n_items; item += gridDim.x, stage ^= 1) {
+  unsigned long long* work_counter =
+      reinterpret_cast<unsigned long long*>(const_cast<int64_t*>(a.item_prefix)) + a.n_blocks + 1;
+  for (; item < n_items; stage ^= 1) {
     // ---- tile -> registers
     mbar_wait(&S.bar[stage], phase[stage]);
     phase[stage] ^= 1;
@@ -484,13 +490,15 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       S.box[tid] = 0.5f * lo + 0.5f * hi;
       S.box[3 + tid] = (0.5f * hi - 0.5f * lo) + pad;
     }
-    const int64_t next = item + gridDim.x;
-    Item nxt;
-    if (next < n_items) {
-      nxt = decode_item(a, S.prefix, next);
-      if (tid == 0) {
+    // dynamic schedule: the next item comes from a global counter (items differ
+    // widely in cost); its tile is requested right away
+    if (tid == 0) {
+      const int64_t nx = (int64_t)atomicAdd(work_counter, 1ull);
+      S.next_item = nx;
+      if (nx < n_items) {
+        const Item nxt0 = decode_item(a, S.prefix, nx);
         fence_proxy_async();
-        issue(nxt, stage ^ 1);
+        issue(nxt0, stage ^ 1);
       }
     }
 
@@ -826,7 +834,8 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         if ((tid & ~31) * kSwP + k * 32 + lane < cur.cnt && (all || (seen_mask & (1u << k))))
           a.seen[cur.start + (tid & ~31) * kSwP + k * 32 + lane] = 1;
     }
-    cur = nxt;
+    item = S.next_item;            // published by the barriers of the camera loop
+    if (item < n_items) cur = decode_item(a, S.prefix, item);
   }
 }
 
@@ -1456,7 +1465,8 @@ static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
 
 static int schedule(const int64_t* pt_offsets, const int64_t* cam_offsets, int32_t L,
                     int32_t cam_split, int64_t* item_prefix, cudaStream_t st) {
-  sweep_schedule_kernel<<<1, 1024, 0, st>>>(pt_offsets, cam_offsets, L, cam_split, item_prefix);
+  sweep_schedule_kernel<<<1, 1024, 0, st>>>(pt_offsets, cam_offsets, L, cam_split, item_prefix,
+                                            kNumSMs * 2);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

@@ -591,25 +591,80 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
 def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
                            cam_records: torch.Tensor, cam_offsets: np.ndarray,
                            cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
-                           threshold=VISIBLE_RATE, rank=0, world=1, group=None):
+                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2):
     """visibility_based_camera_selection (shen_partation_densify.py:911-954)
     for HOST inputs: the expanded blocks' points back to back
     (`block_points` (sum N_b, 3) float32/float64, ideally pinned), the camera
     records and the block->camera CSR.  Uploads, down-samples (A6), runs the
     visibility pass (A7-A9) and returns host arrays
-    (kept_offsets, kept_index, n_hit, ratio, keep, flags)."""
+    (kept_offsets, kept_index, n_hit, ratio, keep, flags).
+
+    The blocks are cut into `groups` runs of consecutive blocks of about equal
+    size; all uploads are queued on a copy stream up front and group g is
+    processed on the current stream as soon as its points have landed, so the
+    PCIe transfer of group g+1 overlaps the kernels of group g."""
     L = len(block_offsets) - 1
-    pts_d = block_points.to(device, non_blocking=True)
-    cams_d = cam_records.to(device, non_blocking=True)
-    off_d = torch.from_numpy(np.ascontiguousarray(block_offsets, dtype=np.int64)).to(device, non_blocking=True)
-    coff_d = torch.from_numpy(np.ascontiguousarray(cam_offsets, dtype=np.int64)).to(device, non_blocking=True)
-    cidx_d = torch.from_numpy(np.ascontiguousarray(cam_index, dtype=np.int32)).to(device, non_blocking=True)
-    x, y, z = aos_to_soa(pts_d)
-    n_e = int(block_offsets[L])
-    ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e)
-    vis = visibility_sharded(dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group,
-                             threshold=threshold)
-    k_off, k_idx = select_cameras(vis.keep, coff_d, cidx_d)
-    out = (k_off.cpu().numpy(), k_idx.cpu().numpy(), vis.n_hit.cpu().numpy(), vis.ratio.cpu().numpy(),
-           vis.keep.cpu().numpy(), vis.flags.cpu().numpy())
-    return out, int(ds_off[L].item())
+    block_offsets = np.ascontiguousarray(block_offsets, dtype=np.int64)
+    cam_offsets = np.ascontiguousarray(cam_offsets, dtype=np.int64)
+    cam_index = np.ascontiguousarray(cam_index, dtype=np.int32)
+    n_total = int(block_offsets[L])
+    # group boundaries: consecutive blocks, ~equal point counts
+    G = max(1, min(int(groups), L))
+    cuts = [0]
+    for g in range(1, G):
+        b = int(np.searchsorted(block_offsets, n_total * g / G, side="left"))
+        cuts.append(min(max(b, cuts[-1]), L))
+    cuts.append(L)
+    spans = [(cuts[i], cuts[i + 1]) for i in range(G) if cuts[i + 1] > cuts[i]]
+    main = torch.cuda.current_stream(device)
+    copy = _copy_stream(device)
+    copy.wait_stream(main)
+    staged = []
+    with torch.cuda.stream(copy):
+        cams_d = cam_records.to(device, non_blocking=True)
+        for (b0, b1) in spans:
+            p0, p1 = int(block_offsets[b0]), int(block_offsets[b1])
+            pts_d = block_points[p0:p1].to(device, non_blocking=True)
+            off_d = torch.from_numpy(block_offsets[b0:b1 + 1] - p0).to(device, non_blocking=True)
+            c0, c1 = int(cam_offsets[b0]), int(cam_offsets[b1])
+            coff_d = torch.from_numpy(cam_offsets[b0:b1 + 1] - c0).to(device, non_blocking=True)
+            cidx_d = torch.from_numpy(cam_index[c0:c1]).to(device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy)
+            staged.append((pts_d, off_d, coff_d, cidx_d, ev, p1 - p0, b1 - b0))
+    parts, n_ds = [], 0
+    for (pts_d, off_d, coff_d, cidx_d, ev, n_e, nb) in staged:
+        main.wait_event(ev)
+        for t in (pts_d, off_d, coff_d, cidx_d, cams_d):
+            t.record_stream(main)
+        x, y, z = aos_to_soa(pts_d)
+        ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e)
+        vis = visibility_sharded(dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group,
+                                 threshold=threshold)
+        k_off, k_idx = select_cameras(vis.keep, coff_d, cidx_d, sync=False)
+        parts.append((k_off, k_idx, vis, ds_off, nb))
+    # one round of D2H at the end
+    k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1, np.int64)], [], [], [], [], []
+    base = 0
+    for (k_off, k_idx, vis, ds_off, nb) in parts:
+        ko = k_off.cpu().numpy()
+        k_offs.append(ko[1:] + base)
+        k_idxs.append(k_idx[: int(ko[nb])].cpu().numpy())
+        base += int(ko[nb])
+        nh.append(vis.n_hit.cpu().numpy()); rt.append(vis.ratio.cpu().numpy())
+        kp.append(vis.keep.cpu().numpy()); fl.append(vis.flags.cpu().numpy())
+        n_ds += int(ds_off[nb].item())
+    cat = lambda xs, dt: np.concatenate(xs) if xs else np.zeros(0, dt)
+    out = (np.concatenate(k_offs), cat(k_idxs, np.int32), cat(nh, np.int32), cat(rt, np.float64),
+           cat(kp, np.uint8), cat(fl, np.uint8))
+    return out, n_ds
+
+
+_COPY_STREAMS = {}
+
+
+def _copy_stream(device):
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    if key not in _COPY_STREAMS:
+        _COPY_STREAMS[key] = torch.cuda.Stream(device=device)
+    return _COPY_STREAMS[key]
