@@ -279,6 +279,38 @@ __device__ __forceinline__ bool tile_all_in_poly(const Cam& c, const float* kq, 
   return poly_undecided(c, kq, b, fz) == 0u && fz;
 }
 
+// MODE 2: does every point of the box project strictly inside the pair's inner
+// polygon (poly record of ptgs_visibility_bounds: [0] = edges, [3] = margin,
+// [4 + 3e ..] = (a, b, c), inside when a*u + b*v + c > margin)?  Such points are
+// not hull candidates, so the warp skips the camera.
+__device__ __forceinline__ bool inner_all_in(const Cam& c, const float* pl, const float* b) {
+  const int ne = (int)pl[0];
+  if (ne < 3) return false;
+  const float S = fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + b[3] + b[4] + b[5] +
+                  fmaxf(fabsf(c.tx), fmaxf(fabsf(c.ty), fabsf(c.tz)));
+  const float mF = S * (1.0f / 65536.0f);
+  const Form Y = form(c.r10, c.r11, c.r12, c.ty, b);
+  const Form Z = form(c.r20, c.r21, c.r22, c.tz, b);
+  const Form F = (c.front_axis == 1.0f) ? Y : Z;
+  if (!(F.mid - F.rad > mF) || !(Z.mid - Z.rad > mF)) return false;
+  const float a0 = fmaf(c.fx, c.r00, c.cx * c.r20), a1 = fmaf(c.fx, c.r01, c.cx * c.r21),
+              a2 = fmaf(c.fx, c.r02, c.cx * c.r22), ad = fmaf(c.fx, c.tx, c.cx * c.tz);
+  const float c0 = fmaf(c.fy, c.r10, c.cy * c.r20), c1 = fmaf(c.fy, c.r11, c.cy * c.r21),
+              c2 = fmaf(c.fy, c.r12, c.cy * c.r22), cd = fmaf(c.fy, c.ty, c.cy * c.tz);
+  const float margin = pl[3];
+  bool in = true;
+  for (int e = 0; e < ne; ++e) {
+    const float ea = pl[4 + 3 * e], eb = pl[5 + 3 * e];
+    // twice the margin: the per-point test evaluates f in float32 with its own error
+    const float ec = pl[6 + 3 * e] - 2.0f * margin;
+    const float mPe = mF * (fabsf(ea) * (c.fx + fabsf(c.cx)) + fabsf(eb) * (c.fy + fabsf(c.cy)) + fabsf(ec));
+    const Form G = form(fmaf(ea, a0, fmaf(eb, c0, ec * c.r20)), fmaf(ea, a1, fmaf(eb, c1, ec * c.r21)),
+                        fmaf(ea, a2, fmaf(eb, c2, ec * c.r22)), fmaf(ea, ad, fmaf(eb, cd, ec * c.tz)), b);
+    in = in && (G.mid - G.rad > mPe);
+  }
+  return in;
+}
+
 // ---- work item schedule -----------------------------------------------------
 // item_prefix[b] = number of work items of the blocks before b; a block has
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
@@ -615,7 +647,8 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
             allin = und == 0u && fz;
           }
           if (MODE == 0 && may) allin = tile_all_in(cj, S.der[g0 + lane], wb);
-          if (allin) atomicAdd(a.n_hit + S.pair[g0 + lane], wcnt);
+          if (MODE == 2 && may) allin = inner_all_in(cj, S.poly[g0 + lane], wb);   // nothing to emit
+          if (MODE != 2 && allin) atomicAdd(a.n_hit + S.pair[g0 + lane], wcnt);
         }
         pm = __ballot_sync(kFullMask, may && !allin);
         if (MODE == 0 && __ballot_sync(kFullMask, allin) != 0u) seen_mask = 0xffu;
