@@ -49,15 +49,22 @@ __device__ __forceinline__ long long cell_of(double v, double vmin, double inv_c
   return c < 0 ? 0 : (c >= nmax ? nmax - 1 : c);
 }
 
+// order-preserving 32-bit image of float(z): inside a column the points are
+// sorted by height, so a query only walks the slab |dz| <= r of each column
+__device__ __forceinline__ uint32_t zkey_of(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) column_key_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, int64_t n, GridSpec g,
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, int64_t n, GridSpec g,
     uint64_t* __restrict__ keys, uint32_t* __restrict__ idx) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     long long ix = cell_of((double)x[i], g.xmin, g.inv_cell, g.nx);
     long long iy = cell_of((double)y[i], g.ymin, g.inv_cell, g.ny);
-    keys[i] = (uint64_t)(ix * g.ny + iy);
+    keys[i] = ((uint64_t)(ix * g.ny + iy) << 32) | zkey_of((float)z[i]);   // float(z): monotone in z
     idx[i] = (uint32_t)i;
   }
 }
@@ -93,7 +100,7 @@ __global__ void __launch_bounds__(256) radius_count_kernel(
   int kept = 0;
   if (p < n) {
     const double xi = (double)sx[p], yi = (double)sy[p], zi = (double)sz[p];
-    const uint64_t key = keys[p];
+    const uint64_t key = keys[p] >> 32;
     const long long ix = (long long)(key / (uint64_t)g.ny);
     const long long iy = (long long)(key % (uint64_t)g.ny);
     const long long y0 = iy > 0 ? iy - 1 : 0;
@@ -103,9 +110,9 @@ __global__ void __launch_bounds__(256) radius_count_kernel(
       long long cx = ix + dx;
       if (cx < 0 || cx >= g.nx) continue;
       const uint64_t klo = (uint64_t)(cx * g.ny + y0), khi = (uint64_t)(cx * g.ny + y1);
-      int64_t j = lower_bound_u64(keys, n, klo);
+      int64_t j = lower_bound_u64(keys, n, klo << 32);
       for (; j < n && cnt <= nb; ++j) {
-        if (__ldg(keys + j) > khi) break;
+        if ((__ldg(keys + j) >> 32) > khi) break;
         double ddx = __dsub_rn((double)sx[j], xi);
         double ddy = __dsub_rn((double)sy[j], yi);
         double ddz = __dsub_rn((double)sz[j], zi);
@@ -120,6 +127,79 @@ __global__ void __launch_bounds__(256) radius_count_kernel(
   int s = warp_sum(kept);
   if (lane_id() == 0 && s) atomicAdd(n_keep, (unsigned long long)s);
 }
+
+
+// cell_start[k] = first sorted position whose key is >= k (k in [0, ncell]); one
+// thread per sorted point fills the gap of (possibly empty) cells that ends at
+// its own key.
+__global__ void __launch_bounds__(256) cell_start_kernel(const uint64_t* __restrict__ keys, int64_t n,
+                                                         uint64_t ncell, uint32_t* __restrict__ cs) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t k = keys[i] >> 32;
+  if (i == 0) {
+    for (uint64_t c = 0; c <= k; ++c) cs[c] = 0u;
+  } else {
+    const uint64_t kp = keys[i - 1] >> 32;
+    for (uint64_t c = kp + 1; c <= k; ++c) cs[c] = (uint32_t)i;
+  }
+  if (i == n - 1)
+    for (uint64_t c = k + 1; c <= ncell; ++c) cs[c] = (uint32_t)n;
+}
+
+// Neighbour count with the cell table: the point's own cell first (most likely
+// to hold close neighbours, so the `> nb_points` early exit comes soonest), then
+// the 8 surrounding cells.
+template <typename T>
+__global__ void __launch_bounds__(256) radius_count_cells_kernel(
+    const T* __restrict__ sx, const T* __restrict__ sy, const T* __restrict__ sz,
+    const uint64_t* __restrict__ keys, const uint32_t* __restrict__ idx,
+    const uint32_t* __restrict__ cs, int64_t n, GridSpec g, double r2, int nb,
+    uint8_t* __restrict__ keep, unsigned long long* __restrict__ n_keep) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int kept = 0;
+  if (p < n) {
+    const double xi = (double)sx[p], yi = (double)sy[p], zi = (double)sz[p];
+    const uint64_t key = keys[p] >> 32;
+    const long long ix = (long long)(key / (uint64_t)g.ny);
+    const long long iy = (long long)(key % (uint64_t)g.ny);
+    // height slab in the (rounded-to-float) sort order: conservative by one float step
+    const double rr = sqrt(r2);
+    const uint32_t zlo = zkey_of(__double2float_rd(zi - rr)) - 1u;
+    const uint32_t zhi = zkey_of(__double2float_ru(zi + rr)) + 1u;
+    int cnt = 0;
+    // visiting order: (0,0), then the 4 edge neighbours, then the 4 corners
+    const int ox[9] = {0, 0, 0, -1, 1, -1, -1, 1, 1};
+    const int oy[9] = {0, -1, 1, 0, 0, -1, 1, -1, 1};
+#pragma unroll 1
+    for (int c = 0; c < 9 && cnt <= nb; ++c) {
+      const long long cx = ix + ox[c], cy = iy + oy[c];
+      if (cx < 0 || cx >= g.nx || cy < 0 || cy >= g.ny) continue;
+      const uint64_t k = (uint64_t)(cx * g.ny + cy);
+      const uint32_t j1 = __ldg(cs + k + 1);
+      uint32_t lo = __ldg(cs + k), hi = j1;
+      while (lo < hi) {                      // first point of the column inside the slab
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uint32_t)__ldg(keys + mid) < zlo) lo = mid + 1; else hi = mid;
+      }
+      for (uint32_t j = lo; j < j1 && cnt <= nb; ++j) {
+        if ((uint32_t)__ldg(keys + j) > zhi) break;
+        double ddx = __dsub_rn((double)sx[j], xi);
+        double ddy = __dsub_rn((double)sy[j], yi);
+        double ddz = __dsub_rn((double)sz[j], zi);
+        double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)),
+                              __dmul_rn(ddz, ddz));
+        cnt += (d2 < r2) ? 1 : 0;
+      }
+    }
+    kept = cnt > nb;
+    keep[idx[p]] = (uint8_t)kept;
+  }
+  int s = warp_sum(kept);
+  if (lane_id() == 0 && s) atomicAdd(n_keep, (unsigned long long)s);
+}
+
+static inline uint64_t cell_table_capacity(int64_t n) { return (uint64_t)4 * (uint64_t)n + (1ull << 20); }
 
 static inline int grid_for(int64_t n, int per_block, int max_blocks) {
   int64_t b = (n + per_block - 1) / per_block;
@@ -149,6 +229,7 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
   T* sx = cv.take<T>(n); T* sy = cv.take<T>(n); T* sz = cv.take<T>(n);
   size_t tb = sort_temp_bytes(n);
   void* sort_tmp = cv.take<char>(tb);
+  uint32_t* cell_start = cv.take<uint32_t>(cell_table_capacity(n) + 2);
 
   const unsigned long long init[4] = {~0ull, ~0ull, 0ull, 0ull};
   PTGS_CUDA_TRY(cudaMemcpyAsync(mm, init, sizeof(init), cudaMemcpyHostToDevice, st));
@@ -171,18 +252,32 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
     set_error("radius_outlier: grid %lld x %lld out of range", g.nx, g.ny);
     return PTGS_E_RANGE;
   }
+  if ((double)g.nx * (double)g.ny >= 2147483648.0) {
+    set_error("radius_outlier: grid %lld x %lld has more than 2^31 columns", g.nx, g.ny);
+    return PTGS_E_RANGE;
+  }
   int bits = 1;
-  while (bits < 64 && ((unsigned long long)(g.nx * g.ny - 1) >> bits)) ++bits;
-  column_key_kernel<T><<<g1, 256, 0, st>>>(x, y, n, g, keys_a, idx_a);
+  while (bits < 32 && ((unsigned long long)(g.nx * g.ny - 1) >> bits)) ++bits;
+  bits += 32;                                // column | height key
+  column_key_kernel<T><<<g1, 256, 0, st>>>(x, y, z, n, g, keys_a, idx_a);
   PTGS_LAUNCH_CHECK();
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, idx_b,
                                                 (int64_t)n, 0, bits, st));
   count_launch(2 + (bits + 7) / 8);
   gather_sorted_kernel<T><<<g1, 256, 0, st>>>(x, y, z, idx_b, n, sx, sy, sz);
   PTGS_LAUNCH_CHECK();
-  radius_count_kernel<T><<<(int)((n + 255) / 256), 256, 0, st>>>(
-      sx, sy, sz, keys_b, idx_b, n, g, radius * radius, nb, keep,
-      (unsigned long long*)n_keep);
+  const uint64_t ncell = (uint64_t)g.nx * (uint64_t)g.ny;
+  if (ncell <= cell_table_capacity(n)) {
+    cell_start_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(keys_b, n, ncell, cell_start);
+    PTGS_LAUNCH_CHECK();
+    radius_count_cells_kernel<T><<<(int)((n + 255) / 256), 256, 0, st>>>(
+        sx, sy, sz, keys_b, idx_b, cell_start, n, g, radius * radius, nb, keep,
+        (unsigned long long*)n_keep);
+  } else {   // very sparse grid (far outliers): binary search per column
+    radius_count_kernel<T><<<(int)((n + 255) / 256), 256, 0, st>>>(
+        sx, sy, sz, keys_b, idx_b, n, g, radius * radius, nb, keep,
+        (unsigned long long*)n_keep);
+  }
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
@@ -200,6 +295,7 @@ size_t ptgs_radius_outlier_workspace_bytes(int64_t n) {
   b += 2 * align_up((size_t)n * 4, 256);      // idx
   b += 3 * align_up((size_t)n * 8, 256);      // sorted coords (f64 worst case)
   b += align_up(sort_temp_bytes(n), 256) + 4096;
+  b += align_up((size_t)(cell_table_capacity(n) + 2) * 4, 256);   // cell table
   return b;
 }
 

@@ -98,11 +98,19 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
           K o = __shfl_xor_sync(kFullMask, lo, d); lo = o < lo ? o : lo;
           K p = __shfl_xor_sync(kFullMask, hi, d); hi = p > hi ? p : hi;
         }
-        if (lane_id() == 0) { amin(mm + 6 * b0 + a, lo); amax(mm + 6 * b0 + 3 + a, hi); }
+        // monotone slots: a (possibly stale) plain read can only cause a redundant
+        // atomic, never a missed one; after the first tiles almost nothing improves
+        if (lane_id() == 0) {
+          if (lo < __ldcg(mm + 6 * b0 + a)) amin(mm + 6 * b0 + a, lo);
+          if (hi > __ldcg(mm + 6 * b0 + 3 + a)) amax(mm + 6 * b0 + 3 + a, hi);
+        }
       }
     } else if (valid) {
 #pragma unroll
-      for (int a = 0; a < 3; ++a) { amin(mm + 6 * b + a, k[a]); amax(mm + 6 * b + 3 + a, kmax[a]); }
+      for (int a = 0; a < 3; ++a) {
+        if (k[a] < __ldcg(mm + 6 * b + a)) amin(mm + 6 * b + a, k[a]);
+        if (kmax[a] > __ldcg(mm + 6 * b + 3 + a)) amax(mm + 6 * b + 3 + a, kmax[a]);
+      }
     }
   }
 }

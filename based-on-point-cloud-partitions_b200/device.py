@@ -576,12 +576,12 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
     if world <= 1:
         return visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                           timer=timer, **kw)
-    my_off, my_idx, _ = M.shard_csr(cam_offsets, cam_index, rank, world)
+    my_off, my_idx, my_pos = M.shard_csr(cam_offsets, cam_index, rank, world)
     if timer is not None:
         timer.mark("vis_shard")
     v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, my_off, my_idx, timer=timer, **kw)
     rec = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
-    full = M.gather_records(rec, cam_index, world, group)
+    full = M.gather_records(rec, cam_index, world, group, pos=my_pos)
     n_hit, ratio, area, keep, flags = M.unpack_records(full)
     if timer is not None:
         timer.mark("vis_allgather")

@@ -52,25 +52,26 @@ def unpack_records(rec: torch.Tensor):
         (kf & 1).to(torch.uint8), (kf >> 8).to(torch.uint8)
 
 
-def gather_records(local: torch.Tensor, cam_idx: torch.Tensor, world: int, group=None) -> torch.Tensor:
+def gather_records(local: torch.Tensor, cam_idx: torch.Tensor, world: int, group=None,
+                   pos: torch.Tensor | None = None, rank: int | None = None) -> torch.Tensor:
     """All-gather of the per-pair records.  `local` holds this rank's pairs in
-    shard order; returns the (P, REC_COLS) table in full pair order on every
-    rank.  cam_idx (the full, replicated list) fixes every rank's positions."""
+    shard order, `pos` their positions in the full pair list (shard_csr);
+    returns the (P, REC_COLS) table in full pair order on every rank.
+
+    Every rank sends a P-row table with its records at their global positions
+    and zeros elsewhere; the gathered tables are summed (each pair has exactly
+    one owner, x + 0.0 is exact).  P rows x 32 B x world is tiny (c4: ~13 MB over
+    NVLink), and no count exchange / host synchronisation is needed."""
     import torch.distributed as dist
     P = cam_idx.shape[0]
     if world <= 1:
         return local
-    owner = (cam_idx % world).to(torch.int64)
-    counts = torch.bincount(owner, minlength=world)
-    cap = int(counts.max().item()) if P else 0
-    cap = max(cap, 1)
-    send = torch.zeros((cap, REC_COLS), dtype=torch.float64, device=local.device)
-    send[: local.shape[0]] = local
-    recv = torch.empty((world * cap, REC_COLS), dtype=torch.float64, device=local.device)
+    if pos is None:
+        if rank is None:
+            rank = dist.get_rank(group)
+        pos = torch.nonzero(shard_mask(cam_idx, rank, world)).reshape(-1)
+    send = torch.zeros((max(P, 1), REC_COLS), dtype=torch.float64, device=local.device)
+    send[pos] = local
+    recv = torch.empty((world * max(P, 1), REC_COLS), dtype=torch.float64, device=local.device)
     dist.all_gather_into_tensor(recv, send, group=group)
-    # slot of pair p inside its owner's shard = rank of p among that owner's pairs
-    order = torch.argsort(owner, stable=True)
-    start = torch.cumsum(counts, 0) - counts
-    slot = torch.empty(P, dtype=torch.int64, device=local.device)
-    slot[order] = torch.arange(P, device=local.device) - start[owner[order]]
-    return recv[owner * cap + slot]
+    return recv.view(world, max(P, 1), REC_COLS).sum(dim=0)[:P]

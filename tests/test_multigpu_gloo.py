@@ -59,7 +59,9 @@ def _worker(rank, world, port, seed, out_dir):
         assert int(my_off[-1]) == my_idx.shape[0] == pos.shape[0]
         assert torch.equal(idx[pos], my_idx)
         nh, rt, ar, kp, fl = _fake_records(my_off, my_idx)
-        full = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world)
+        full = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world, pos=pos)
+        full2 = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world, rank=rank)
+        assert torch.equal(full, full2)
         got = M.unpack_records(full)
         want = _fake_records(off, idx)
         for g, w in zip(got, want):
