@@ -710,26 +710,33 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
               nm = front && (fabsf(__fmaf_rn(-dout.x, Z, uh)) <= __fmaf_rn(dout.z, az, 1e-30f)) &&
                    (fabsf(__fmaf_rn(-dout.y, Z, vh)) <= __fmaf_rn(dout.w, az, 1e-30f));
             }
-            cnt += in ? 1 : 0;
+            cnt += __popc(__ballot_sync(kFullMask, in));      // warp-uniform count, no reduction later
             if (MODE == 0 && in) seen_mask |= 1u << k;
             slow |= (nm && !in) ? (1u << k) : 0u;
           }
-          // ---- exact path for the points between the two rectangles
-          bool any_slow = false;
-          unsigned long long t_pv = ~0ull;
-          float t_best[8];
-          uint32_t t_idx[8];
-          if (MODE == 1) {
-#pragma unroll
-            for (int d = 0; d < 8; ++d) { t_best[d] = -__int_as_float(0x7f800000); t_idx[d] = 0; }
-          }
+          // ---- exact path for the points between the two regions.  Pivot and
+          // extremes go straight to the pair's global slots: the current values are
+          // read once per pass (a stale value only causes a redundant atomic) and
+          // only a hit that improves one of them issues an atomic.
+          const int64_t pair = S.pair[j];
           if (__any_sync(kFullMask, slow != 0)) {
             if (lane == 0) PTGS_FINE_STAT(6, 1);
+            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
+            unsigned long long cur_pv = ~0ull;
+            uint32_t cur_key[8];
+            if (MODE == 1) {
+              cur_pv = *reinterpret_cast<volatile unsigned long long*>(gpv);
+#pragma unroll
+              for (int d = 0; d < 8; ++d)
+                cur_key[d] = (uint32_t)(*reinterpret_cast<volatile unsigned long long*>(gex + d) >> 32);
+            }
 #pragma unroll
             for (int k = 0; k < kSwP; ++k) {
               const bool mine = (slow >> k) & 1u;
               if (!__any_sync(kFullMask, mine)) continue;
               if (lane == 0) PTGS_FINE_STAT(7, 1);
+              bool hit = false;
               if (mine) {
                 const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
                 const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
@@ -739,57 +746,32 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                 p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
                 float u, v;
                 if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
-                  ++cnt;
+                  hit = true;
                   if (MODE == 0) seen_mask |= 1u << k;
                   if (MODE == 1) {
-                    any_slow = true;
                     u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
                     v = __fadd_rn(v, 0.0f);
                     const unsigned long long pk =
                         ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                    t_pv = pk < t_pv ? pk : t_pv;
+                    if (pk < cur_pv) { atomicMin(gpv, pk); cur_pv = pk; }
                     const uint32_t idx = (uint32_t)(cur.tile * kSwTile + (tid & ~31) * kSwP + k * 32 + lane);
                     const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                     const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
                     for (int d = 0; d < 8; ++d) {
-                      if (dir[d] > t_best[d]) { t_best[d] = dir[d]; t_idx[d] = idx; }
+                      const uint32_t key = order_key(dir[d]);
+                      if (key >= cur_key[d]) {      // >=: an equal value with a larger index still wins
+                        atomicMax(gex + d, ((unsigned long long)key << 32) | idx);
+                        cur_key[d] = key;
+                      }
                     }
                   }
                 }
               }
+              cnt += __popc(__ballot_sync(kFullMask, hit));
             }
           }
-          // results go straight to the pair's global slots: warps never wait for each other
-          const int64_t pair = S.pair[j];
-          const int wsum = __reduce_add_sync(kFullMask, cnt);
-          if (lane == 0 && wsum) atomicAdd(a.n_hit + pair, wsum);
-          if (MODE == 1 && __any_sync(kFullMask, any_slow)) {
-            const uint32_t phi = (uint32_t)(t_pv >> 32);
-            const uint32_t mhi = __reduce_min_sync(kFullMask, phi);
-            const uint32_t plo = phi == mhi ? (uint32_t)t_pv : 0xffffffffu;
-            const uint32_t mlo = __reduce_min_sync(kFullMask, plo);
-            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
-            if (lane == 0) {
-              const unsigned long long pk = ((unsigned long long)mhi << 32) | mlo;
-              if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
-            }
-            // the 8 extremes: lane d reduces nothing, every lane contributes to 8 redux
-            unsigned long long mine_e = 0ull;
-#pragma unroll
-            for (int d = 0; d < 8; ++d) {
-              const uint32_t key = order_key(t_best[d]);
-              const uint32_t mk = __reduce_max_sync(kFullMask, key);
-              const unsigned who = __ballot_sync(kFullMask, key == mk);
-              const uint32_t id = __shfl_sync(kFullMask, t_idx[d], __ffs(who) - 1);
-              if (lane == d) mine_e = ((unsigned long long)mk << 32) | id;
-            }
-            // -inf (no hit along d in this warp) has key 0x007fffff: never beats a real entry
-            if (lane < 8 && (uint32_t)(mine_e >> 32) > 0x007fffffu &&
-                mine_e > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
-              atomicMax(gex + lane, mine_e);
-          }
+          if (lane == 0 && cnt) atomicAdd(a.n_hit + pair, cnt);
         }
       } else {
       for (unsigned pmm = pm; pmm; pmm &= pmm - 1) {

@@ -142,6 +142,17 @@ def max_over_ranks(v, world, dev):
     return float(t.item())
 
 
+def sweep_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one sweep_kernel<1> launch on
+    the bench workload, from the committed ncu capture (profiles/r01_sweep_traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "r01_sweep_traffic.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import ptgs_b200  # noqa: F401
     from ptgs_b200 import _lib, device as D, workload as W
@@ -239,14 +250,18 @@ def run_ours(args):
     out["roofline"] = {
         "kernel": "sweep_kernel<1> (ptgs_visibility_count)", "bound": "hbm",
         "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_kind": peak_kind,
+        "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": sweep_traffic_bytes(),
+        "peak_kind": peak_kind,
         "algorithmic_bytes": alg_bytes, "kernel_ms": k_ms,
-        "note": "the sweep re-uses every staged point tile for all cameras of the block: it is FP32-issue bound, see fp32",
+        "note": "the sweep re-uses every staged point tile for all cameras of the block, so its HBM traffic "
+                "is 12 B/point by construction and the binding roof is FP32 issue (see fp32; DESIGN.md 4.1); "
+                "`traffic` = dram read+write bytes of one launch from the ncu --set full capture in profiles/",
         "fp32": {"slots_per_test": SLOTS_PER_TEST,
                  "achieved_lane_ops_per_s": shard_tests * SLOTS_PER_TEST / (k_ms * 1e-3),
                  "peak_lane_ops_per_s": lane_peak,
                  "frac": shard_tests * SLOTS_PER_TEST / (k_ms * 1e-3) / lane_peak,
-                 "peak_kind": "148 SMs x 128 lanes x sm_max_mhz (nominal issue rate)"},
+                 "peak_kind": "148 SMs x 128 lanes x sm_max_mhz (nominal issue rate)",
+                 "note": "algorithmic tests (pairs culled per tile / per warp box count as done) x 34 slots"},
     }
     ctx = dict(w=w, res=res, recs=recs, centers=centers, xyz_pinned=xyz_pinned, xyz=xyz, dev=dev,
                tests=tests, world=world, rank=rank, flush=flush, lib=lib, D=D)
