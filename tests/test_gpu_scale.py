@@ -1,0 +1,127 @@
+"""GPU tests at BASELINE.json sizes and multi-rank equivalence.
+
+* config 1 (1 M points / 300 cameras / threshold 500 000, the reference's own
+  CPU-runnable case): leaves, expanded blocks, camera assignment and every
+  pair's hit count against the oracle (bit-exact); keep decisions against the
+  oracle's exact hull ratio for a sample of pairs and through the bound
+  invariants (ratio_lo <= exact <= ratio_hi) for all of them.
+* size-independent properties at a larger size: determinism (two runs are
+  identical), default (bound-decided) mode == exact mode, and camera sharding
+  for world sizes 2 / 3 / 8 (ranks run one after the other on this GPU)
+  == the unsharded result."""
+import numpy as np
+import pytest
+import torch
+
+import ptgs_oracle as O
+from helpers import scene_cameras
+import ptgs_b200  # noqa: F401
+from ptgs_b200 import device as D, multigpu as M, workload as W
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _lists(off, idx):
+    off = off.cpu().numpy()
+    idx = idx.cpu().numpy()
+    return [idx[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+
+def test_config1_against_oracle():
+    w = W.make("c1", 1.0)
+    recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+    centers = D.camera_centers(w.R, w.T)
+    res = D.partition_device(torch.from_numpy(w.xyz).to(DEV), recs, centers, w.threshold)
+    cams = O.CameraSet(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+    want = O.run_partition(w.xyz, cams, w.threshold, centers=centers, visibility=False)
+    assert np.array_equal(res.keep_mask.cpu().numpy().astype(bool), want.keep_mask)
+    assert res.leaf_ids == [l.partition_id for l in want.leaves] and len(res.leaf_ids) >= 2
+    assert [tuple(b) for b in res.leaf_bounds.tolist()] == [l.bounds for l in want.leaves]
+    for g, wv in zip(_lists(res.pt_offsets, res.pt_index), want.block_index):
+        assert np.array_equal(g, wv)
+    cam_lists = _lists(res.cam_offsets, res.cam_index)
+    for g, wv in zip(cam_lists, want.cam_index):
+        assert np.array_equal(g, wv)
+    # voxel down-sampling of every block, bit for bit (set comparison through first-occurrence order)
+    ds_off = res.ds_offsets.cpu().numpy()
+    ds = np.stack([res.ds_x.cpu().numpy(), res.ds_y.cpu().numpy(), res.ds_z.cpu().numpy()], 1)
+    n_hit = res.vis.n_hit.cpu().numpy()
+    keep = res.vis.keep.cpu().numpy().astype(bool)
+    flags = res.vis.flags.cpu().numpy()
+    rlo = res.vis.ratio_lo.cpu().numpy()
+    rhi = res.vis.ratio_hi.cpu().numpy()
+    p = 0
+    rng = np.random.default_rng(0)
+    checked = 0
+    for b, cl in enumerate(cam_lists):
+        d = ds[ds_off[b]:ds_off[b + 1]]
+        wd = O.voxel_downsample(w.xyz[want.block_index[b]])
+        assert len(d) == len(wd)
+        du, wu = d.view(np.uint32), wd.view(np.uint32)
+        du = du[np.lexsort((du[:, 2], du[:, 1], du[:, 0]))]
+        wu = wu[np.lexsort((wu[:, 2], wu[:, 1], wu[:, 0]))]
+        assert np.array_equal(du, wu)
+        for c in cl:
+            hit, u, v = O.project_port(d, recs[c])
+            assert n_hit[p] == int(hit.sum()), (b, c)
+            assert rlo[p] <= rhi[p] + 1e-12
+            if n_hit[p] > O.MIN_HITS and not (flags[p] & 3) and rng.random() < 0.04:
+                rt = O.run_graham_scan(np.stack([u[hit], v[hit]], 1).astype(np.float64),
+                                       float(recs[c][16]), float(recs[c][17]))
+                if not O.first_ray_collinear(np.stack([u[hit], v[hit]], 1).astype(np.float64)):
+                    assert rlo[p] <= rt * (1 + 1e-12) + 1e-15 and rhi[p] >= rt * (1 - 1e-12), (b, c)
+                    assert keep[p] == (rt >= O.VISIBLE_RATE), (b, c, rt)
+                    checked += 1
+            if n_hit[p] <= O.MIN_HITS:
+                assert not keep[p]
+            p += 1
+    assert p == len(n_hit) and checked >= 3
+    assert 0 < keep.sum() < len(keep)
+
+
+def _scene_state(scale=0.2):
+    w = W.make("c3", scale)                      # many leaves (deep recursion config)
+    recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+    centers = D.camera_centers(w.R, w.T)
+    res = D.partition_device(torch.from_numpy(w.xyz).to(DEV), recs, centers, w.threshold, man_trans=w.man_trans)
+    return w, recs, res
+
+
+def test_determinism_and_modes():
+    w, recs, res = _scene_state()
+    assert len(res.leaf_ids) >= 16
+    cams_d = torch.from_numpy(recs).to(DEV)
+    args = (res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets, res.cam_index)
+    a = D.visibility(*args)
+    b = D.visibility(*args)
+    for f in ("n_hit", "keep", "flags", "ratio"):
+        assert torch.equal(getattr(a, f), getattr(b, f)), f
+    e = D.visibility(*args, exact_ratio=True)
+    n = D.visibility(*args, interior=False)          # without the interior-region fast path
+    assert torch.equal(a.n_hit, e.n_hit) and torch.equal(a.keep, e.keep)
+    assert torch.equal(a.n_hit, n.n_hit) and torch.equal(a.keep, n.keep) and torch.equal(a.ratio, n.ratio)
+    assert bool((a.ratio_lo <= e.ratio * (1 + 1e-12) + 1e-15).all())
+    assert bool((a.ratio_hi >= e.ratio * (1 - 1e-12)).all())
+    assert 0 < int(a.keep.sum()) < a.keep.numel()
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_camera_sharding_equals_single_gpu(world):
+    """Rank r evaluates cameras c % world == r (multigpu.shard_csr); scattering every
+    rank's records to their global pair positions reproduces the unsharded table."""
+    w, recs, res = _scene_state()
+    cams_d = torch.from_numpy(recs).to(DEV)
+    full = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets, res.cam_index)
+    P = res.cam_index.shape[0]
+    table = torch.zeros((P, M.REC_COLS), dtype=torch.float64, device=DEV)
+    seen = torch.zeros(P, dtype=torch.int32, device=DEV)
+    for r in range(world):
+        off, idx, pos = M.shard_csr(res.cam_offsets, res.cam_index, r, world)
+        v = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, off, idx)
+        table[pos] = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
+        seen[pos] += 1
+    assert bool((seen == 1).all())
+    n_hit, ratio, area, keep, flags = M.unpack_records(table)
+    assert torch.equal(n_hit, full.n_hit) and torch.equal(keep, full.keep) and torch.equal(flags, full.flags)
+    assert torch.equal(ratio, full.ratio)
