@@ -73,46 +73,64 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
   __shared__ int64_t s_off[kVoxMaxBlocks + 1];
   for (int i = threadIdx.x; i <= L; i += blockDim.x) s_off[i] = offsets[i];
   __syncthreads();
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t start = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  for (int64_t e0 = start - threadIdx.x % 32; e0 < n_entries; e0 += stride) {
-    const int64_t e = e0 + (threadIdx.x & 31);
-    const bool valid = e < n_entries;
+  // every warp walks ONE contiguous run of entries and keeps a running per-lane
+  // min / max for as long as the run stays inside one block; the six atomics
+  // are issued once per (warp, block) instead of once per 32 entries
+  const int64_t n_warps = (int64_t)gridDim.x * (blockDim.x / 32);
+  const int64_t per_warp = ((n_entries + n_warps - 1) / n_warps + 31) / 32 * 32;
+  const int64_t w0 = ((int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32) * per_warp;
+  const int64_t w1 = w0 + per_warp < n_entries ? w0 + per_warp : n_entries;
+  const int lane = threadIdx.x & 31;
+  int b_run = -1;
+  K rlo[3] = {~K(0), ~K(0), ~K(0)}, rhi[3] = {0, 0, 0};
+  auto flush = [&]() {
+    if (b_run < 0) return;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      K lo = rlo[a], hi = rhi[a];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        K o = __shfl_xor_sync(kFullMask, lo, d); lo = o < lo ? o : lo;
+        K p = __shfl_xor_sync(kFullMask, hi, d); hi = p > hi ? p : hi;
+      }
+      if (lane == 0) {
+        if (lo < __ldcg(mm + 6 * b_run + a)) amin(mm + 6 * b_run + a, lo);
+        if (hi > __ldcg(mm + 6 * b_run + 3 + a)) amax(mm + 6 * b_run + 3 + a, hi);
+      }
+      rlo[a] = ~K(0); rhi[a] = 0;
+    }
+  };
+  for (int64_t e0 = w0; e0 < w1; e0 += 32) {
+    const int64_t e = e0 + lane;
+    const bool valid = e < w1;
     int b = -1;
     K k[3] = {~K(0), ~K(0), ~K(0)};
-    K kmax[3] = {0, 0, 0};
     if (valid) {
       b = find_block(s_off, L, e);
       const int32_t i = indices ? indices[e] : (int32_t)e;
       k[0] = KeyOf<T>::encode(x[i]); k[1] = KeyOf<T>::encode(y[i]); k[2] = KeyOf<T>::encode(z[i]);
-      kmax[0] = k[0]; kmax[1] = k[1]; kmax[2] = k[2];
     }
     const int b0 = __shfl_sync(kFullMask, b, 0);
     const bool uniform = __all_sync(kFullMask, b == b0 || !valid) && b0 >= 0;
     if (uniform) {
+      if (b0 != b_run) { flush(); b_run = b0; }
+      if (valid) {
 #pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        K lo = k[a], hi = kmax[a];
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-          K o = __shfl_xor_sync(kFullMask, lo, d); lo = o < lo ? o : lo;
-          K p = __shfl_xor_sync(kFullMask, hi, d); hi = p > hi ? p : hi;
-        }
-        // monotone slots: a (possibly stale) plain read can only cause a redundant
-        // atomic, never a missed one; after the first tiles almost nothing improves
-        if (lane_id() == 0) {
-          if (lo < __ldcg(mm + 6 * b0 + a)) amin(mm + 6 * b0 + a, lo);
-          if (hi > __ldcg(mm + 6 * b0 + 3 + a)) amax(mm + 6 * b0 + 3 + a, hi);
-        }
+        for (int a = 0; a < 3; ++a) { rlo[a] = k[a] < rlo[a] ? k[a] : rlo[a]; rhi[a] = k[a] > rhi[a] ? k[a] : rhi[a]; }
       }
-    } else if (valid) {
+    } else {
+      // the 32 entries straddle a block boundary (at most L - 1 times overall)
+      flush(); b_run = -1;
+      if (valid) {
 #pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        if (k[a] < __ldcg(mm + 6 * b + a)) amin(mm + 6 * b + a, k[a]);
-        if (kmax[a] > __ldcg(mm + 6 * b + 3 + a)) amax(mm + 6 * b + 3 + a, kmax[a]);
+        for (int a = 0; a < 3; ++a) {
+          if (k[a] < __ldcg(mm + 6 * b + a)) amin(mm + 6 * b + a, k[a]);
+          if (k[a] > __ldcg(mm + 6 * b + 3 + a)) amax(mm + 6 * b + 3 + a, k[a]);
+        }
       }
     }
   }
+  flush();
 }
 
 // single CTA: decode per block min, global max voxel index per axis, layout.
