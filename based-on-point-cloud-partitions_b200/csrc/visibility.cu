@@ -417,6 +417,8 @@ struct SweepSmem {
   long long pair[kSwCamChunk];                            // output slot (pair id / camera) of the staged cameras
   int nact;
   long long next_item;
+  int qn, qhead;                                          // (warp run, camera) work queue of the chunk
+  unsigned q[(kSwThreads / 32) * kSwCamChunk];            // run << 24 | camera slot << 12 | edge mask (0xfff: none)
   int tile_seen;                                          // MODE 0: a camera contains the whole tile
   alignas(16) float der[kSwCamChunk][8];                  // MODE 0/1: fast-in / not-miss rectangles
   float wbox[kSwThreads / 32][6];                         // per warp tile AABB
@@ -468,6 +470,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
     float x[kSwP], y[kSwP], z[kSwP];
     float wb[6];        // this warp's box: centre xyz, half extent xyz (its 256 points are contiguous)
     const int wcnt = min(max(cur.cnt - (tid & ~31) * kSwP, 0), 32 * kSwP);
+    int have_run = tid >> 5;   // which 256-point run of the tile the registers hold
     {
       const int shift = (int)(cur.start & 3);
       const float qnan = __int_as_float(0x7fc00000);
@@ -605,6 +608,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                       : make_float4(0.0f, 0.0f, -1.0f, -1.0f);
         }
       }
+      if (tid == 0) { S.qn = 0; S.qhead = 0; }
       if (tid < nc) {
         const int64_t lpos = cur.cam_lo + S.act[c0 + tid];
         S.pair[tid] = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
@@ -652,6 +656,17 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
         pm = __ballot_sync(kFullMask, may && !allin);
         if (MODE == 0 && __ballot_sync(kFullMask, allin) != 0u) seen_mask = 0xffu;
+        // the cameras that cut this run go to the CTA's queue: any warp may sweep them
+        if (pm) {
+          int base = 0;
+          if (lane == 0) base = atomicAdd(&S.qn, __popc(pm));
+          base = __shfl_sync(kFullMask, base, 0);
+          if (may && !allin) {
+            const unsigned um = (MODE == 1 && und != 0xffffffffu) ? (und & 0xffu) : 0xfffu;
+            S.q[base + __popc(pm & lanemask_lt())] =
+                ((unsigned)(tid >> 5) << 24) | ((unsigned)(g0 + lane) << 12) | um;
+          }
+        }
         if (lane == 0) {
           PTGS_FINE_STAT(MODE == 2 ? 3 : 2, (unsigned long long)__popc(pm) * (unsigned)wcnt);
         }
@@ -661,10 +676,36 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
       }
 
-      // ---- sweep: 8 register points x surviving cameras
+      }   // lane groups (phase 1: classification)
+      __syncthreads();
+
+      // ---- phase 2: the queued (run, camera) pairs are swept by whichever warp is
+      // free (runs of a tile differ widely in how many cameras cut them); a warp
+      // that takes another run's pair reloads that run's points from the tile
+      const int qn = S.qn;
+      for (;;) {
+        int qi = 0;
+        if (lane == 0) qi = atomicAdd(&S.qhead, 1);
+        qi = __shfl_sync(kFullMask, qi, 0);
+        if (qi >= qn) break;
+        const unsigned ent = S.q[qi];
+        const int run = (int)(ent >> 24), j = (int)((ent >> 12) & 0xfffu);
+        const unsigned uj = (ent & 0xfffu) == 0xfffu ? 0xffffffffu : (ent & 0xfffu);
+        if (run != have_run) {
+          const int shift = (int)(cur.start & 3);
+          const float qnan = __int_as_float(0x7fc00000);
+#pragma unroll
+          for (int k = 0; k < kSwP; ++k) {
+            const int i = run * (32 * kSwP) + k * 32 + lane;
+            const bool ok = i < cur.cnt;
+            x[k] = ok ? S.tile[stage][0][shift + i] : qnan;
+            y[k] = ok ? S.tile[stage][1][shift + i] : qnan;
+            z[k] = ok ? S.tile[stage][2][shift + i] : qnan;
+          }
+          have_run = run;
+        }
       if (MODE != 2) {
-        for (unsigned pmm = pm; pmm; pmm &= pmm - 1) {
-          const int jl = __ffs(pmm) - 1, j = g0 + jl;
+        {
           const Cam c = load_cam(S.cam[j]);
           const float4 din = *reinterpret_cast<const float4*>(&S.der[j][0]);
           const float4 dout = *reinterpret_cast<const float4*>(&S.der[j][4]);
@@ -676,7 +717,6 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           bool use_edges = false;
           float e1a = 0.0f, e1b = 0.0f, e1c = 0.0f, e2a = 0.0f, e2b = 0.0f, e2c = 0.0f;
           if (MODE == 1) {
-            const unsigned uj = __shfl_sync(kFullMask, und, jl);
             if (uj != 0xffffffffu && uj != 0u && __popc(uj) <= 2) {
               use_edges = true;
               const int ea = __ffs(uj) - 1, eb = 31 - __clz(uj);
@@ -711,7 +751,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                    (fabsf(__fmaf_rn(-dout.y, Z, vh)) <= __fmaf_rn(dout.w, az, 1e-30f));
             }
             cnt += __popc(__ballot_sync(kFullMask, in));      // warp-uniform count, no reduction later
-            if (MODE == 0 && in) seen_mask |= 1u << k;
+            if (MODE == 0 && in && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
             slow |= (nm && !in) ? (1u << k) : 0u;
           }
           // ---- exact path for the points between the two regions.  Pivot and
@@ -747,14 +787,14 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                 float u, v;
                 if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
                   hit = true;
-                  if (MODE == 0) seen_mask |= 1u << k;
+                  if (MODE == 0 && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
                   if (MODE == 1) {
                     u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
                     v = __fadd_rn(v, 0.0f);
                     const unsigned long long pk =
                         ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
                     if (pk < cur_pv) { atomicMin(gpv, pk); cur_pv = pk; }
-                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + (tid & ~31) * kSwP + k * 32 + lane);
+                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + k * 32 + lane);
                     const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                     const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
@@ -774,8 +814,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           if (lane == 0 && cnt) atomicAdd(a.n_hit + pair, cnt);
         }
       } else {
-      for (unsigned pmm = pm; pmm; pmm &= pmm - 1) {
-        const int jl = __ffs(pmm) - 1, j = g0 + jl;
+      {
         const Cam c = load_cam(S.cam[j]);
         const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
         int cnt = 0;
@@ -801,7 +840,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                 const unsigned long long pk =
                     ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
                 t_pv = pk < t_pv ? pk : t_pv;
-                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + (tid & ~31) * kSwP + k * 32 + lane);
+                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + k * 32 + lane);
                 const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                 const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
@@ -836,7 +875,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
         }
       }
       }
-      }   // lane groups
+      }   // queue
 
       // staging arrays are rewritten by the next chunk (rare: > kSwCamChunk surviving cameras)
       if (c0 + kSwCamChunk < nact_all) __syncthreads();

@@ -65,3 +65,12 @@ print("sweep stats [presented, after CTA cull, swept s1, swept s2, warp all-in, 
 i = int(np.argmax(cc))
 print("worst pair", i, "n_hit", nh[i], "cand", cc[i], "rlo", float(vis.ratio_lo[i]), "rhi", float(vis.ratio_hi[i]),
       "ratio", rt[i], "flags", int(vis.flags[i]))
+for stride in (16, 32, 64, 128, 256):
+    best = None
+    for rep in range(3):
+        tm = D.StageTimer(True); tm.mark("start")
+        D.visibility(ds[1], ds[2], ds[3], ds[0], cams_d, coff, cidx, timer=tm, sample_stride=stride)
+        r = tm.result()
+        t = r["vis_interior_rects"] + r["vis_sweep1_count"]
+        best = t if best is None else min(best, t)
+    print("sample stride %4d: interior + sweep1 = %.3f ms (last: %.3f + %.3f)" % (stride, best, r["vis_interior_rects"], r["vis_sweep1_count"]))
