@@ -1056,7 +1056,8 @@ __global__ void __launch_bounds__(1024) cand_plan_kernel(
 }
 
 // ---- exact hull + area per pair ----------------------------------------------
-constexpr int kHullThreads = 128;
+constexpr int kHullThreads = 512;   // a pair's chain of passes is latency bound: 4 warps per scheduler
+constexpr int kHullParts = kHullThreads / 128;   // point partitions of the directional scan
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
 constexpr int kHullFilterMin = 128; // candidates above which the directional pre-filter runs
@@ -1089,17 +1090,19 @@ struct FilterSmem {
   int m;
   int out;
   int scan[33];
+  uint32_t pkey[kHullParts][kFiltDirs];
+  int pidx[kHullParts][kFiltDirs];
 };
 
 __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  // 1. extremes
+  const int tid = threadIdx.x, lane = tid & 31, w = (tid >> 5) & 3, part = tid >> 7;
+  // 1. extremes: warp (w, part) scans every kHullParts-th 128-point slice for the 16 directions of group w
   float best[16];
   int bi[16];
 #pragma unroll
   for (int d = 0; d < 16; ++d) { best[d] = -__int_as_float(0x7f800000); bi[d] = 0; }
   // 4 independent loads in flight per lane (the loop is latency bound otherwise)
-  for (int i0 = lane; i0 < n; i0 += 128) {
+  for (int i0 = lane + 128 * part; i0 < n; i0 += 128 * kHullParts) {
     float2 q[4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
@@ -1123,7 +1126,16 @@ __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
     const uint32_t mk = __reduce_max_sync(kFullMask, key);
     const unsigned who = __ballot_sync(kFullMask, key == mk);
     const int id = __shfl_sync(kFullMask, bi[d], __ffs(who) - 1);
-    if (lane == 0) F.idx[w * 16 + d] = id;
+    if (lane == 0) { F.pkey[part][w * 16 + d] = mk; F.pidx[part][w * 16 + d] = id; }
+  }
+  __syncthreads();
+  if (tid < kFiltDirs) {
+    uint32_t bk = F.pkey[0][tid];
+    int bid = F.pidx[0][tid];
+#pragma unroll
+    for (int p = 1; p < kHullParts; ++p)
+      if (F.pkey[p][tid] > bk) { bk = F.pkey[p][tid]; bid = F.pidx[p][tid]; }
+    F.idx[tid] = bid;
   }
   __syncthreads();
   if (tid < kFiltDirs) F.vert[tid] = cu[F.idx[tid]];
