@@ -1,0 +1,182 @@
+// libptgs: spatial (3-D Morton) ordering of a planar float32 cloud.
+//
+// The coverage sweep (config 5 / the Vast path's camera x all-points pass,
+// scene/ptgs/data_partition.py:385-424, :505) gets its points in file order.
+// The sweep culls cameras per 2048-point tile and per 256-point warp run, which
+// only works when consecutive points are neighbours in space: this pass sorts
+// the cloud by the Morton code of a 2^16-cell-per-axis cubic grid over its
+// bounding box (one cell size for all axes) and returns the permutation, so
+// per-point outputs can be written back in the caller's order.  The order only
+// affects speed: hit counts and seen flags do not depend on it.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace ptgs {
+
+constexpr int kOrderBits = 16;   // per axis -> 48-bit keys, 6 radix passes
+
+__global__ void __launch_bounds__(256) order_minmax_kernel(
+    const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z, int64_t n,
+    uint32_t* __restrict__ mm /* min xyz, max xyz as order-preserving keys */) {
+  const float inf = __int_as_float(0x7f800000);
+  float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v[3] = {x[i], y[i], z[i]};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      if (fabsf(v[a]) < inf) {               // NaN / inf do not shape the grid
+        lo[a] = fminf(lo[a], v[a]);
+        hi[a] = fmaxf(hi[a], v[a]);
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(kFullMask, lo[a], d));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(kFullMask, hi[a], d));
+    }
+  }
+  if (lane_id() == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      atomicMin(mm + a, KeyOf<float>::encode(lo[a]));
+      atomicMax(mm + 3 + a, KeyOf<float>::encode(hi[a]));
+    }
+  }
+}
+
+// bit i of v -> bit 3 i
+__device__ __forceinline__ uint64_t spread3(uint32_t v) {
+  uint64_t x = v & 0x1fffffu;
+  x = (x | (x << 32)) & 0x1f00000000ffffull;
+  x = (x | (x << 16)) & 0x1f0000ff0000ffull;
+  x = (x | (x << 8)) & 0x100f00f00f00f00full;
+  x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
+  x = (x | (x << 2)) & 0x1249249249249249ull;
+  return x;
+}
+
+__global__ void __launch_bounds__(256) order_key_kernel(
+    const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z, int64_t n,
+    const uint32_t* __restrict__ mm, uint64_t* __restrict__ keys, uint32_t* __restrict__ idx) {
+  float lo[3], ext = 0.0f;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = KeyOf<float>::decode(mm[a]);
+    const float e = KeyOf<float>::decode(mm[3 + a]) - lo[a];
+    ext = (e > ext) ? e : ext;               // empty axis: +inf - (-inf) is never > ext ... NaN compares false
+  }
+  const float cells = (float)(1u << kOrderBits);
+  const float inv = (ext > 0.0f && ext < __int_as_float(0x7f800000)) ? cells / ext : 0.0f;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v[3] = {x[i], y[i], z[i]};
+    uint32_t c[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const float f = (v[a] - lo[a]) * inv;
+      const float g = (f >= 0.0f) ? f : 0.0f;                     // NaN, -inf -> cell 0
+      c[a] = (g < cells) ? (uint32_t)g : ((1u << kOrderBits) - 1);
+    }
+    keys[i] = spread3(c[0]) | (spread3(c[1]) << 1) | (spread3(c[2]) << 2);
+    idx[i] = (uint32_t)i;
+  }
+}
+
+__global__ void __launch_bounds__(256) order_gather_kernel(
+    const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z,
+    const uint32_t* __restrict__ perm, int64_t n, float* __restrict__ sx, float* __restrict__ sy,
+    float* __restrict__ sz) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint32_t j = perm[i];
+    sx[i] = x[j]; sy[i] = y[j]; sz[i] = z[j];
+  }
+}
+
+__global__ void __launch_bounds__(256) unpermute_u8_kernel(
+    const uint8_t* __restrict__ src, const uint32_t* __restrict__ perm, int64_t n,
+    uint8_t* __restrict__ dst) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[perm[i]] = src[i];
+}
+
+static size_t order_sort_temp_bytes(int64_t n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0,
+                                  3 * kOrderBits);
+  return bytes;
+}
+
+static inline int order_grid(int64_t n) {
+  int64_t b = (n + 2047) / 2048;
+  if (b < 1) b = 1;
+  if (b > kNumSMs * 8) b = kNumSMs * 8;
+  return (int)b;
+}
+
+}  // namespace ptgs
+
+using namespace ptgs;
+
+extern "C" {
+
+size_t ptgs_spatial_order_workspace_bytes(int64_t n) {
+  if (n < 1) n = 1;
+  size_t b = 512;
+  b += 2 * align_up((size_t)n * 8, 256);      // keys in / out
+  b += align_up((size_t)n * 4, 256);          // identity index
+  b += align_up(order_sort_temp_bytes(n), 256) + 4096;
+  return b;
+}
+
+int ptgs_spatial_order(const float* px, const float* py, const float* pz, int64_t n, float* sx,
+                       float* sy, float* sz, uint32_t* perm, void* workspace,
+                       size_t workspace_bytes, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && n < 4294967296ll, "spatial_order: n must be in [0, 2^32)");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(px && py && pz && sx && sy && sz && perm && workspace, "spatial_order: null pointer");
+  if (workspace_bytes < ptgs_spatial_order_workspace_bytes(n)) {
+    set_error("spatial_order: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver cv(workspace);
+  uint32_t* mm = cv.take<uint32_t>(8);
+  uint64_t* keys_a = cv.take<uint64_t>(n);
+  uint64_t* keys_b = cv.take<uint64_t>(n);
+  uint32_t* idx_a = cv.take<uint32_t>(n);
+  size_t tb = order_sort_temp_bytes(n);
+  void* sort_tmp = cv.take<char>(tb);
+  const uint32_t init[8] = {~0u, ~0u, ~0u, 0u, 0u, 0u, 0u, 0u};
+  PTGS_CUDA_TRY(cudaMemcpyAsync(mm, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  const int g = order_grid(n);
+  order_minmax_kernel<<<g, 256, 0, st>>>(px, py, pz, n, mm);
+  PTGS_LAUNCH_CHECK();
+  order_key_kernel<<<g, 256, 0, st>>>(px, py, pz, n, mm, keys_a, idx_a);
+  PTGS_LAUNCH_CHECK();
+  PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, perm,
+                                                (int64_t)n, 0, 3 * kOrderBits, st));
+  count_launch(2 + (3 * kOrderBits + 7) / 8);
+  order_gather_kernel<<<g, 256, 0, st>>>(px, py, pz, perm, n, sx, sy, sz);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_unpermute_u8(const uint8_t* src, const uint32_t* perm, int64_t n, uint8_t* dst,
+                      ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0, "unpermute_u8: n < 0");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(src && perm && dst, "unpermute_u8: null pointer");
+  unpermute_u8_kernel<<<order_grid(n), 256, 0, (cudaStream_t)stream>>>(src, perm, n, dst);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+}  // extern "C"

@@ -426,19 +426,46 @@ def select_cameras(keep, cam_offsets, cam_index, want_pos=False, sync=True):
     return (kept_off, kept_idx[:n], kept_pos[:n]) if want_pos else (kept_off, kept_idx[:n])
 
 
-def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen=False):
-    """Config 5 / Vast-style coverage: every point against cameras
-    [cam_first, cam_first + cam_count)."""
+def spatial_order(px, py, pz):
+    """Morton-ordered copy of a planar float32 cloud + the permutation
+    (sorted[i] = input[perm[i]]); ptgs_spatial_order."""
+    lib = _lib.load()
+    dev = px.device
+    n = px.shape[0]
+    sx, sy, sz = (torch.empty(max(n, 1), dtype=torch.float32, device=dev) for _ in range(3))
+    perm = torch.empty(max(n, 1), dtype=torch.int32, device=dev)       # uint32 payload
+    ws = _ws(lib.ptgs_spatial_order_workspace_bytes(n), dev)
+    check(lib.ptgs_spatial_order(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(sx), _ptr(sy), _ptr(sz), _ptr(perm),
+                                 _ptr(ws), ws.numel(), _stream()))
+    return sx[:n], sy[:n], sz[:n], perm[:n]
+
+
+def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen=False,
+                   spatial_order_points=True, ordered=None):
+    """Config 5 / Vast-style coverage (data_partition.py:385-424, :505): every point against
+    cameras [cam_first, cam_first + cam_count).  The cloud is first put into Morton order
+    (`spatial_order`) so that the sweep can cull cameras per tile; `ordered` takes the result of
+    an earlier `spatial_order(px, py, pz)` call to reuse it across camera ranges.  Results do
+    not depend on the order (seen flags come back in the caller's point order)."""
     lib = _lib.load()
     dev = px.device
     if cam_count is None:
         cam_count = cameras_d.shape[0] - cam_first
     n = px.shape[0]
+    perm = None
+    if ordered is not None:
+        px, py, pz, perm = ordered
+    elif spatial_order_points and n > 0:
+        px, py, pz, perm = spatial_order(px, py, pz)
     n_hit = torch.empty(max(cam_count, 1), dtype=torch.int32, device=dev)
     seen = torch.empty(max(n, 1), dtype=torch.uint8, device=dev) if want_seen else None
     ws = _ws(lib.ptgs_visibility_workspace_bytes(1), dev)
     check(lib.ptgs_coverage_sweep(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(cameras_d), int(cam_first),
                                   int(cam_count), _ptr(n_hit), _ptr(seen), _ptr(ws), ws.numel(), _stream()))
+    if want_seen and perm is not None and n > 0:
+        out = torch.empty_like(seen)
+        check(lib.ptgs_unpermute_u8(_ptr(seen), _ptr(perm), n, _ptr(out), _stream()))
+        seen = out
     return (n_hit[:cam_count], seen[:n]) if want_seen else n_hit[:cam_count]
 
 

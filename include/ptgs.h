@@ -391,6 +391,24 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         void* workspace, size_t workspace_bytes,
                         ptgs_stream_t stream);
 
+/* ------------------------------------------------------------------ *
+ * Spatial order for the coverage sweep (the Vast path's cloud arrives in file
+ * order; scene/ptgs/data_partition.py:505 projects all of it per camera).
+ * Sorts the planar float32 cloud by the 3-D Morton code of a 2^16-cells-per-
+ * axis cubic grid over its bounding box: sx/sy/sz[n] = the points in that
+ * order, perm[n] uint32 = their indices in the input (n < 2^32).  Only the
+ * speed of ptgs_coverage_sweep depends on the order, never its results.
+ * ptgs_unpermute_u8: dst[perm[i]] = src[i] (per-point flags back to the
+ * caller's order).
+ * ------------------------------------------------------------------ */
+size_t ptgs_spatial_order_workspace_bytes(int64_t n);
+int ptgs_spatial_order(const float* px, const float* py, const float* pz,
+                       int64_t n, float* sx, float* sy, float* sz,
+                       uint32_t* perm, void* workspace, size_t workspace_bytes,
+                       ptgs_stream_t stream);
+int ptgs_unpermute_u8(const uint8_t* src, const uint32_t* perm, int64_t n,
+                      uint8_t* dst, ptgs_stream_t stream);
+
 /* Diagnostics (synchronising; HOST pointer to 8 counters since the last
  * reset): [0] point-camera tests presented to the sweeps, [1] left after the
  * CTA-level tile cull, [2] swept per point (sweep 1 / coverage), [3] swept per

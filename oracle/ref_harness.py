@@ -166,7 +166,15 @@ def load():
     gm.BasicPointCloud = BasicPointCloud
     sys.modules["scene.gaussian_model"] = gm
 
+    # a drop-in module of the same name (compat/) must not stand in for the reference
+    ref_ptgs = os.path.join(REF_ROOT, "scene", "ptgs")
+    for name in ("shen_partation_densify", "shen_partition_utils", "density_partition", "shen_data_read"):
+        m = sys.modules.get(name)
+        if m is not None and not os.path.abspath(getattr(m, "__file__", "") or "").startswith(ref_ptgs):
+            del sys.modules[name]
     densify = importlib.import_module("shen_partation_densify")
+    if not os.path.abspath(densify.__file__).startswith(ref_ptgs):
+        raise ImportError("shen_partation_densify resolved to %s, not the reference" % densify.__file__)
     _loaded.update(
         densify=densify,
         density_partition=importlib.import_module("density_partition"),

@@ -69,10 +69,31 @@ def test_no_cpu_fallback():
         P.quad_tree_partition(np.zeros((10, 3)), P.Rect(0, 0, 1, 1), 5)
 
 
-def test_compat_module_names():
-    sys.path.insert(0, os.path.join(ROOT, "compat"))
-    import shen_partation_densify as d
-    import shen_partition_utils as u
+@pytest.fixture
+def compat_modules():
+    """compat/ first on sys.path for one test only (the reference harness imports the
+    reference's modules of the same names)."""
+    path = os.path.join(ROOT, "compat")
+    names = ("shen_partation_densify", "shen_partition_utils")
+    saved = {n: sys.modules.pop(n) for n in names if n in sys.modules}
+    types_ = (P.BasicPointCloud, P.Partition, P.CameraPose)
+    mods = [t.__module__ for t in types_]          # the compat module renames them for pickle
+    sys.path.insert(0, path)
+    try:
+        import shen_partation_densify as d
+        import shen_partition_utils as u
+        yield d, u
+    finally:
+        sys.path.remove(path)
+        for n in names:
+            sys.modules.pop(n, None)
+        sys.modules.update(saved)
+        for t, m in zip(types_, mods):
+            t.__module__ = m
+
+
+def test_compat_module_names(compat_modules):
+    d, u = compat_modules
     assert d.Partition.__module__ == "shen_partation_densify"
     for name in ("quad_tree_partition", "expand_partitions", "assign_cameras_to_partitions",
                  "visibility_based_camera_selection", "downsample_point_cloud", "save_partition_as_pkl"):

@@ -314,6 +314,36 @@ def test_coverage_sweep():
     part = D.coverage_sweep(x, y, z, cams_d, cam_first=5, cam_count=11)
     assert np.array_equal(part.cpu().numpy(), want[5:16])
     assert want.sum() > 1000
+    # file order (no spatial sort) and a reused ordering give the same answers
+    n2, s2 = D.coverage_sweep(x, y, z, cams_d, want_seen=True, spatial_order_points=False)
+    assert torch.equal(n2, n_hit) and torch.equal(s2, seen)
+    od = D.spatial_order(x, y, z)
+    n3, s3 = D.coverage_sweep(x, y, z, cams_d, want_seen=True, ordered=od)
+    assert torch.equal(n3, n_hit) and torch.equal(s3, seen)
+
+
+def test_spatial_order_is_a_permutation_and_local():
+    rng = np.random.default_rng(7)
+    n = 300001
+    pts = rng.uniform(-50, 50, size=(n, 3)).astype(np.float32)
+    pts[:, 2] *= 0.1
+    pts[5] = [np.nan, 1.0, 2.0]            # non-finite coordinates must not break the grid
+    pts[6] = [np.inf, -np.inf, 0.0]
+    x, y, z = (torch.from_numpy(np.ascontiguousarray(pts[:, a])).to(DEV) for a in range(3))
+    sx, sy, sz, perm = D.spatial_order(x, y, z)
+    p = perm.cpu().numpy().view(np.uint32).astype(np.int64)
+    assert np.array_equal(np.sort(p), np.arange(n))
+    got = np.stack([sx.cpu().numpy(), sy.cpu().numpy(), sz.cpu().numpy()], 1)
+    assert np.array_equal(got.view(np.uint32), pts[p].view(np.uint32))
+    # locality: 256-point runs of the sorted cloud are far smaller than the cloud
+    fin = np.isfinite(got).all(1)
+    runs = got[: (n // 256) * 256].reshape(-1, 256, 3)
+    ok = fin[: (n // 256) * 256].reshape(-1, 256).all(1)
+    ext = (runs.max(1) - runs.min(1))[ok]
+    assert np.median(ext[:, 0]) < 10.0 and np.median(ext[:, 1]) < 10.0
+    # empty input
+    e = torch.empty(0, dtype=torch.float32, device=DEV)
+    assert D.spatial_order(e, e, e)[3].numel() == 0
 
 
 def test_full_partition_vs_oracle():

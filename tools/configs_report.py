@@ -46,10 +46,16 @@ for name in names:
         x, y, z = D.aos_to_soa(xyz)
         cams_d = torch.from_numpy(recs).to(dev)
         C = len(recs) if c5_cams is None else min(c5_cams, len(recs))
-        n_hit, ms = timed(lambda: D.coverage_sweep(x, y, z, cams_d, cam_first=0, cam_count=C), reps=2)
+        od, oms = timed(lambda: D.spatial_order(x, y, z), reps=2)
+        n_hit, ms = timed(lambda: D.coverage_sweep(x, y, z, cams_d, cam_first=0, cam_count=C, ordered=od), reps=2)
         tests = float(len(w.xyz)) * C
-        line.update({"cameras_swept": C, "tests": tests, "sweep_ms": round(ms, 3), "tests_per_s": tests / (ms * 1e-3),
+        line.update({"cameras_swept": C, "tests": tests, "spatial_order_ms": round(oms, 3), "sweep_ms": round(ms, 3),
+                     "tests_per_s": tests / ((ms + oms) * 1e-3),
                      "hits": int(n_hit.sum().item()), "cameras_with_hits": int((n_hit > 0).sum().item())})
+        if "--c5-file-order" in sys.argv:
+            n2, ms2 = timed(lambda: D.coverage_sweep(x, y, z, cams_d, cam_first=0, cam_count=C,
+                                                     spatial_order_points=False), reps=1)
+            line.update({"file_order_sweep_ms": round(ms2, 3), "file_order_equal": bool(torch.equal(n2, n_hit))})
     else:
         centers = D.camera_centers(w.R, w.T)
         res, ms = timed(lambda: D.partition_device(xyz, recs, centers, w.threshold, man_trans=w.man_trans,
