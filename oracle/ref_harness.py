@@ -52,7 +52,7 @@ class _Polygon:
     geom_type = "Polygon"
 
     def __init__(self, shell=None, holes=None):
-        pts = [(float(p[0]), float(p[1])) for p in (shell or [])]
+        pts = [(float(p[0]), float(p[1])) for p in (shell if shell is not None else [])]
         self._pts = pts
         self.exterior = _Exterior(pts) if pts else None
 
@@ -68,8 +68,41 @@ class _Polygon:
 
     @property
     def area(self):
+        if getattr(self, "_general", False):      # ring of a convex polygon: shoelace
+            a = 0.0
+            n = len(self._pts)
+            for i in range(n):
+                x0, y0 = self._pts[i]
+                x1, y1 = self._pts[(i + 1) % n]
+                a += x0 * y1 - x1 * y0
+            return abs(a) * 0.5
         minx, miny, maxx, maxy = self.bounds
         return (maxx - minx) * (maxy - miny)
+
+    def intersection(self, other):
+        """Convex ring (self) clipped by the bounds rectangle of `other` -- the only use the
+        Vast path makes of shapely (graham_scan.py:92-94: hull polygon & box(0, 0, W, H)).
+        Third-party restatement (shapely is not in the reference tree): Sutherland-Hodgman."""
+        minx, miny, maxx, maxy = other.bounds
+        ring = list(self._pts)
+        for axis, bound, keep_le in ((0, minx, False), (0, maxx, True), (1, miny, False), (1, maxy, True)):
+            out = []
+            n = len(ring)
+            for i in range(n):
+                p, q = ring[i], ring[(i + 1) % n]
+                fp = (p[axis] - bound) if keep_le else (bound - p[axis])
+                fq = (q[axis] - bound) if keep_le else (bound - q[axis])
+                if fp <= 0.0:
+                    out.append(p)
+                if (fp <= 0.0) != (fq <= 0.0):
+                    t = fp / (fp - fq)
+                    out.append((p[0] + t * (q[0] - p[0]), p[1] + t * (q[1] - p[1])))
+            ring = out
+            if not ring:
+                break
+        r = _Polygon(ring)
+        r._general = True
+        return r
 
     def __repr__(self):
         return "RectPolygon(%r)" % (self.bounds,)
@@ -130,13 +163,13 @@ def load():
     _mod("shapely.strtree", STRtree=_Anything)
     _mod("shapely.ops")
     shp.geometry = geo
-    plt = _mod("matplotlib.pyplot")
+    plt = _mod("matplotlib.pyplot", subplots=lambda *a, **k: (_Anything(), _Anything()))
     mpl = _mod("matplotlib", pyplot=plt)
     _mod("matplotlib.patches")
     _mod("matplotlib.font_manager")
     mpl.use = lambda *a, **k: None
     _mod("open3d")
-    _mod("plyfile", PlyData=_Anything, PlyElement=_Anything)
+    _mod("plyfile", PlyData=_Anything(), PlyElement=_Anything())
     _mod("simple_knn")
     _mod("simple_knn._C", distCUDA2=_Anything())
     _mod("diff_gaussian_rasterization")
@@ -178,6 +211,8 @@ def load():
     _loaded.update(
         densify=densify,
         density_partition=importlib.import_module("density_partition"),
+        vast_data_partition=importlib.import_module("scene.ptgs.data_partition"),
+        vast_graham_scan=importlib.import_module("scene.ptgs.graham_scan"),
         save_partition=importlib.import_module("scene.ptgs.save_partition"),
         read_write_model=importlib.import_module("scene.ptgs.read_write_model"),
         cameras=importlib.import_module("scene.cameras"),

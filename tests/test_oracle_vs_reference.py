@@ -190,3 +190,67 @@ def test_visibility_selection(ref, tmp_path, monkeypatch):
         assert os.path.exists(vis_dir / p.partition_id / ("partition_%s.pkl" % p.partition_id))
     total = sum(len(c) for c in want.cam_index)
     assert 0 < n_kept <= total
+
+
+# ------------------------------------------------------------------ Vast path (A14)
+def _vast_reference(ref, pts, colors, vc, tmp_path, m, n, extend_rate, visible_rate):
+    from types import SimpleNamespace
+    from helpers import VastCamera
+    dp = ref.vast_data_partition
+    cams = [VastCamera(vc.R[c], vc.T[c], float(vc.FoVx[c]), float(vc.FoVy[c]), int(vc.width[c]),
+                       int(vc.height[c]), vc.names[c], vc.center[c]) for c in range(len(vc.names))]
+    pcd = dp.BasicPointCloud(points=pts, colors=colors, normals=np.zeros_like(pts))
+    return dp.ProgressiveDataPartitioning(SimpleNamespace(point_cloud=pcd), cams, str(tmp_path), m, n,
+                                          extend_rate, visible_rate)
+
+
+@pytest.mark.parametrize("seed,m,n,rate", [(71, 2, 2, 0.25), (72, 3, 2, 0.1)])
+def test_vast_path(ref, tmp_path, seed, m, n, rate):
+    import ptgs_oracle_vast as OV
+    from helpers import vast_inputs
+    sc = small_scene(n=24000, c=41, thr=6000, seed=seed, oblique_fraction=0.5)
+    pts, colors, vc = vast_inputs(sc)
+    want = _vast_reference(ref, pts, colors, vc, tmp_path, m, n, 0.2, rate)
+    parts, sel = OV.run_vast(pts, vc, m, n, 0.2, rate)
+    assert len(want.partition_scene) == m * n == len(parts)
+    name_to_idx = {nm: i for i, nm in enumerate(vc.names)}
+    n_added = 0
+    for w, p, (cam_list, uniq, first, added) in zip(want.partition_scene, parts, sel):
+        assert w.partition_id == p.partition_id
+        assert list(w.ori_camera_bbox) == list(p.ori_camera_bbox)
+        assert list(w.extend_camera_bbox) == list(p.extend_camera_bbox)
+        assert list(w.ori_point_bbox) == list(p.ori_point_bbox)
+        assert list(w.extend_point_bbox) == list(p.extend_point_bbox)
+        assert [name_to_idx[cp.camera.image_name] for cp in w.cameras] == list(cam_list)
+        assert np.array_equal(w.point_cloud.points, uniq)
+        assert np.array_equal(w.point_cloud.colors, colors[first])
+        n_added += len(added)
+    assert n_added > 0
+
+
+def test_vast_airspace_rate(ref):
+    """The 8-corner rate against the reference's point_in_image + run_graham_scan."""
+    import ptgs_oracle_vast as OV
+    from helpers import VastCamera, vast_inputs
+    sc = small_scene(n=2000, c=30, thr=6000, seed=73, oblique_fraction=0.5)
+    pts, colors, vc = vast_inputs(sc)
+    dp, gs = ref.vast_data_partition, ref.vast_graham_scan
+    self_ = dp.ProgressiveDataPartitioning.__new__(dp.ProgressiveDataPartitioning)
+    rng = np.random.default_rng(5)
+    nz = 0
+    for c in range(len(vc.names)):
+        lo = rng.uniform(-40, 0, 3).astype(np.float32)
+        hi = (lo + rng.uniform(5, 60, 3)).astype(np.float32)
+        bbox = [lo[0], hi[0], lo[1], hi[1], lo[2], hi[2]]
+        cam = VastCamera(vc.R[c], vc.T[c], float(vc.FoVx[c]), float(vc.FoVy[c]), int(vc.width[c]),
+                         int(vc.height[c]), vc.names[c], vc.center[c])
+        proj = {}
+        for key, point in self_.get_8_corner_points(bbox).items():
+            pi, _, _ = self_.point_in_image(cam, np.array([point]))
+            if len(pi):
+                proj[key] = pi[0]
+        want = gs.run_graham_scan(list(proj.values()), cam.image_width, cam.image_height)["intersection_rate"]
+        got = OV.airspace_rate(vc, c, OV.corner_points(bbox))
+        assert abs(got - want) <= 1e-9 * max(1.0, abs(want)), (c, got, want)
+        nz += want > 0
+    assert nz >= 5
