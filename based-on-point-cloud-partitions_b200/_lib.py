@@ -63,6 +63,14 @@ SIGNATURES = {
     "ptgs_spatial_order_workspace_bytes": (_sz, [_i64]),
     "ptgs_spatial_order": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_unpermute_u8": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
+    "ptgs_vast_point_range": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _sz, _vp]),
+    "ptgs_vast_airspace": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "ptgs_vast_begin_block": (C.c_int, [_vp, _i64, _vp]),
+    "ptgs_vast_coverage_workspace_bytes": (_sz, [_i64, _i32]),
+    "ptgs_vast_coverage": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _sz, _vp]),
+    "ptgs_vast_mark_own": (C.c_int, [_vp, _i64, _i32, _vp, _vp]),
+    "ptgs_vast_unique_workspace_bytes": (_sz, [_i64]),
+    "ptgs_vast_unique": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
     "ptgs_coverage_sweep": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
 }
 

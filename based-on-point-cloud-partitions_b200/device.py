@@ -469,6 +469,88 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
     return (n_hit[:cam_count], seen[:n]) if want_seen else n_hit[:cam_count]
 
 
+# ---------------------------------------------------------------- A14: the camera-grid (Vast) path
+VAST_CAMERA_DOUBLES = 20
+
+
+def vast_camera_records(R, T, FoVx, FoVy, width, height) -> np.ndarray:
+    """(C,20) float64 records for the ptgs_vast_* entry points, with the Python expressions of
+    point_in_image (scene/ptgs/data_partition.py:388-407): w2c = R^T, fx = W / (2 tan(FoVx/2)),
+    cx = W // 2, cy = H // 2."""
+    import math
+    Cn = len(R)
+    rec = np.zeros((Cn, VAST_CAMERA_DOUBLES), dtype=np.float64)
+    for i in range(Cn):
+        w, h = int(width[i]), int(height[i])
+        rec[i, 0:9] = np.transpose(np.asarray(R[i], dtype=np.float64)).reshape(9)
+        rec[i, 9:12] = np.asarray(T[i], dtype=np.float64)
+        rec[i, 12] = w / (2 * math.tan(float(FoVx[i]) / 2))
+        rec[i, 13] = h / (2 * math.tan(float(FoVy[i]) / 2))
+        rec[i, 14] = w // 2
+        rec[i, 15] = h // 2
+        rec[i, 16] = w
+        rec[i, 17] = h
+    return rec
+
+
+def vast_point_range(x, y, z, offsets, indices) -> np.ndarray:
+    """get_point_range (data_partition.py:285-293) of every block of a CSR -> (B,6) float64 on the host."""
+    lib = _lib.load()
+    dev = x.device
+    B = offsets.shape[0] - 1
+    out = torch.empty((B, 6), dtype=torch.float64, device=dev)
+    ws = _ws(B * 48, dev)
+    check(lib.ptgs_vast_point_range(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(offsets), _ptr(indices), B,
+                                    _ptr(out), _ptr(ws), ws.numel(), _stream()))
+    return out.cpu().numpy()
+
+
+def vast_airspace(cams_d, boxes: np.ndarray, pair_block: np.ndarray, pair_cam: np.ndarray) -> np.ndarray:
+    """8-corner visibility rate of every (block box, camera) pair (data_partition.py:478-488)."""
+    lib = _lib.load()
+    dev = cams_d.device
+    P = len(pair_block)
+    if P == 0:
+        return np.zeros(0)
+    boxes_d = torch.from_numpy(np.ascontiguousarray(boxes, dtype=np.float64)).to(dev)
+    pb = torch.from_numpy(np.ascontiguousarray(pair_block, dtype=np.int32)).to(dev)
+    pc = torch.from_numpy(np.ascontiguousarray(pair_cam, dtype=np.int32)).to(dev)
+    rate = torch.empty(P, dtype=torch.float64, device=dev)
+    check(lib.ptgs_vast_airspace(_ptr(cams_d), _ptr(boxes_d), _ptr(pb), _ptr(pc), P, _ptr(rate), _stream()))
+    return rate.cpu().numpy()
+
+
+def vast_block_cloud(x, y, z, cams_d, own_index, sources):
+    """Coverage-based point selection + row dedup for one destination block
+    (data_partition.py:441-557).  own_index: int32 cloud indices of the block's own (extended)
+    cloud; sources: [(block_index int32 tensor, [camera ids accepted from that block, in order])]
+    in the reference's block order.  Returns the cloud indices of the unique rows
+    (lexicographic row order, first occurrence) as an int32 tensor."""
+    lib = _lib.load()
+    dev = x.device
+    n = x.shape[0]
+    first_pos = torch.empty(max(n, 1), dtype=torch.int64, device=dev)      # uint64 payload
+    check(lib.ptgs_vast_begin_block(_ptr(first_pos), n, _stream()))
+    seq = 0
+    for idx_j, cam_ids in sources:
+        k = len(cam_ids)
+        if k == 0 or idx_j.shape[0] == 0:
+            seq += k
+            continue
+        cl = torch.from_numpy(np.ascontiguousarray(cam_ids, dtype=np.int32)).to(dev)
+        ws = _ws(lib.ptgs_vast_coverage_workspace_bytes(idx_j.shape[0], k), dev)
+        check(lib.ptgs_vast_coverage(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(idx_j), idx_j.shape[0], _ptr(cams_d),
+                                     _ptr(cl), k, seq, _ptr(first_pos), _ptr(ws), ws.numel(), _stream()))
+        seq += k
+    check(lib.ptgs_vast_mark_own(_ptr(own_index), own_index.shape[0], seq, _ptr(first_pos), _stream()))
+    uniq = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    n_uniq = torch.zeros(1, dtype=torch.int64, device=dev)
+    ws = _ws(lib.ptgs_vast_unique_workspace_bytes(n), dev)
+    check(lib.ptgs_vast_unique(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, _ptr(first_pos), _ptr(uniq), n,
+                               _ptr(n_uniq), _ptr(ws), ws.numel(), _stream()))
+    return uniq[:int(n_uniq.item())]
+
+
 class _Timer:
     """CUDA-event stage timer on the current stream."""
 

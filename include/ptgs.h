@@ -409,6 +409,67 @@ int ptgs_spatial_order(const float* px, const float* py, const float* pz,
 int ptgs_unpermute_u8(const uint8_t* src, const uint32_t* perm, int64_t n,
                       uint8_t* dst, ptgs_stream_t stream);
 
+/* ------------------------------------------------------------------ *
+ * A14 -- the camera-grid ("Vast") partitioner, scene/ptgs/data_partition.py.
+ * The XZ box selection of extract_point_cloud (:276-283) is ptgs_expand_count /
+ * ptgs_expand_fill called with (x, z) and rects {x0, x1, z0, z1}.  Everything
+ * below computes in float64 in NumPy's operation order (the reference's
+ * point_in_image, :385-424, is host NumPy).
+ *
+ * Camera records: PTGS_VAST_CAMERA_DOUBLES doubles per camera =
+ *   {w2c rotation row-major [9] (= camera.R transposed, :389-391), T [3],
+ *    fx, fy (:393-394), cx = W//2, cy = H//2 (:404-407), W, H, 0, 0}.
+ *
+ * ptgs_vast_point_range: get_point_range (:285-293) of every block of a CSR
+ *   (offsets[B+1] int64, indices int32 into the cloud): range[B][6] =
+ *   {min x, max x, min y, max y, min z, max z}; workspace >= 48 B bytes.
+ * ptgs_vast_airspace: for pair p, the 8 corners (:368-382) of
+ *   boxes[pair_block[p]] (6 doubles, same layout as `range`) projected into
+ *   camera pair_cam[p]; corners with camera z <= 0 are dropped; area of
+ *   (convex hull & [0,W]x[0,H]) / (W H), 0 with fewer than 3 distinct corners
+ *   (:478-488, graham_scan.py:65-105).
+ * Coverage of one destination block i (:441-557), in this order:
+ *   ptgs_vast_begin_block   first_pos[n_cloud] (uint64) := ~0
+ *   ptgs_vast_coverage      once per source block j, for the cameras of j
+ *     accepted for i (cam_list, in the reference's order; seq_base = number of
+ *     cameras accepted before): point_in_image of block j's cloud
+ *     (block_index[n_block_points] int32 into the cloud, ascending).  A point
+ *     in front of the camera and inside the image (x against H, y against W,
+ *     :417-422) selects the block's point number `rank` = its position among
+ *     the points in front (:412, :505-506), and
+ *     first_pos[block_index[rank]] = min(., (seq << 32) | rank).
+ *   ptgs_vast_mark_own      block i's own points, seq = total number of
+ *     accepted cameras (they come last in the concatenation, :537-539)
+ *   ptgs_vast_unique        np.unique(rows, axis=0, return_index=True) (:545):
+ *     uniq_index[*n_unique_dev] = cloud indices of the distinct (x, y, z) rows
+ *     in lexicographic order, each the first occurrence in concatenation
+ *     order.  Synchronises the stream once (the number of selected points
+ *     sizes the sorts); PTGS_E_CAPACITY when it exceeds `capacity`.
+ * ------------------------------------------------------------------ */
+#define PTGS_VAST_CAMERA_DOUBLES 20
+int ptgs_vast_point_range(int dtype, const void* x, const void* y, const void* z,
+                          const int64_t* offsets, const int32_t* indices,
+                          int32_t n_blocks, double* range, void* workspace,
+                          size_t workspace_bytes, ptgs_stream_t stream);
+int ptgs_vast_airspace(const double* cameras, const double* boxes,
+                       const int32_t* pair_block, const int32_t* pair_cam,
+                       int64_t n_pairs, double* rate, ptgs_stream_t stream);
+int ptgs_vast_begin_block(uint64_t* first_pos, int64_t n, ptgs_stream_t stream);
+size_t ptgs_vast_coverage_workspace_bytes(int64_t n_block_points, int32_t n_cameras);
+int ptgs_vast_coverage(int dtype, const void* x, const void* y, const void* z,
+                       const int32_t* block_index, int64_t n_block_points,
+                       const double* cameras, const int32_t* cam_list,
+                       int32_t n_cameras, int32_t seq_base, uint64_t* first_pos,
+                       void* workspace, size_t workspace_bytes,
+                       ptgs_stream_t stream);
+int ptgs_vast_mark_own(const int32_t* block_index, int64_t n_block_points,
+                       int32_t seq, uint64_t* first_pos, ptgs_stream_t stream);
+size_t ptgs_vast_unique_workspace_bytes(int64_t n);
+int ptgs_vast_unique(int dtype, const void* x, const void* y, const void* z,
+                     int64_t n, const uint64_t* first_pos, int32_t* uniq_index,
+                     int64_t capacity, int64_t* n_unique_dev, void* workspace,
+                     size_t workspace_bytes, ptgs_stream_t stream);
+
 /* Diagnostics (synchronising; HOST pointer to 8 counters since the last
  * reset): [0] point-camera tests presented to the sweeps, [1] left after the
  * CTA-level tile cull, [2] swept per point (sweep 1 / coverage), [3] swept per

@@ -207,6 +207,34 @@ def selection_case(ref):
     return d
 
 
+def vast_case(ref):
+    """A14: the reference's camera-grid partitioner (scene/ptgs/data_partition.py), run unchanged."""
+    from types import SimpleNamespace
+    from helpers import VastCamera, vast_inputs
+    n, c, seed, m, n_region, er, vr = 20000, 37, 75, 2, 2, 0.2, 0.25
+    sc = small_scene(n=n, c=c, thr=6000, seed=seed, oblique_fraction=0.5)
+    pts, colors, vc = vast_inputs(sc)
+    dp = ref.vast_data_partition
+    cams = [VastCamera(vc.R[k], vc.T[k], float(vc.FoVx[k]), float(vc.FoVy[k]), int(vc.width[k]),
+                       int(vc.height[k]), vc.names[k], vc.center[k]) for k in range(c)]
+    pcd = dp.BasicPointCloud(points=pts, colors=colors, normals=np.zeros_like(pts))
+    with tempfile.TemporaryDirectory() as tmp:
+        out = dp.ProgressiveDataPartitioning(SimpleNamespace(point_cloud=pcd), cams, tmp, m, n_region, er, vr)
+    res = out.partition_scene
+    d = dict(n=np.int64(n), c=np.int64(c), seed=np.int64(seed), m=np.int64(m), n_region=np.int64(n_region),
+             extend_rate=np.float64(er), visible_rate=np.float64(vr),
+             ids=np.array([p.partition_id for p in res], dtype="U16"),
+             ori_camera_bbox=np.array([p.ori_camera_bbox for p in res], np.float64),
+             extend_camera_bbox=np.array([p.extend_camera_bbox for p in res], np.float64),
+             ori_point_bbox=np.array([p.ori_point_bbox for p in res], np.float64),
+             extend_point_bbox=np.array([p.extend_point_bbox for p in res], np.float64))
+    for b, p in enumerate(res):
+        d["cams_%d" % b] = np.array([vc.names.index(cp.camera.image_name) for cp in p.cameras], np.int64)
+        d["points_%d" % b] = p.point_cloud.points
+        d["colors_%d" % b] = p.point_cloud.colors
+    return d
+
+
 def main():
     if not H.available():
         raise SystemExit("make_golden.py needs /root/reference (build container only)")
@@ -219,6 +247,7 @@ def main():
     np.savez_compressed(os.path.join(GOLDEN, "projection.npz"), **projection_case(ref))
     np.savez_compressed(os.path.join(GOLDEN, "graham.npz"), **graham_cases(ref))
     np.savez_compressed(os.path.join(GOLDEN, "selection.npz"), **selection_case(ref))
+    np.savez_compressed(os.path.join(GOLDEN, "vast.npz"), **vast_case(ref))
     for f in sorted(os.listdir(GOLDEN)):
         print("%-28s %8d B" % (f, os.path.getsize(os.path.join(GOLDEN, f))))
 
