@@ -754,22 +754,19 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
             if (MODE == 0 && in && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
             slow |= (nm && !in) ? (1u << k) : 0u;
           }
-          // ---- exact path for the points between the two regions.  Pivot and
-          // extremes go straight to the pair's global slots: the current values are
-          // read once per pass (a stale value only causes a redundant atomic) and
-          // only a hit that improves one of them issues an atomic.
+          // ---- exact path for the points between the two regions.  Each lane keeps
+          // its best pivot / directional extremes of the pass in registers; one warp
+          // reduction per pass then sends at most 9 atomics (lane d owns direction d)
+          // to the pair's global slots, and only for values that improve them.
           const int64_t pair = S.pair[j];
           if (__any_sync(kFullMask, slow != 0)) {
             if (lane == 0) PTGS_FINE_STAT(6, 1);
-            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
-            unsigned long long cur_pv = ~0ull;
-            uint32_t cur_key[8];
+            unsigned long long t_pv = ~0ull;
+            float t_best[8];
+            unsigned t_k = 0;                 // 4 bits per direction: the slot k that holds t_best[d]
             if (MODE == 1) {
-              cur_pv = *reinterpret_cast<volatile unsigned long long*>(gpv);
 #pragma unroll
-              for (int d = 0; d < 8; ++d)
-                cur_key[d] = (uint32_t)(*reinterpret_cast<volatile unsigned long long*>(gex + d) >> 32);
+              for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
             }
 #pragma unroll
             for (int k = 0; k < kSwP; ++k) {
@@ -793,22 +790,45 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
                     v = __fadd_rn(v, 0.0f);
                     const unsigned long long pk =
                         ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                    if (pk < cur_pv) { atomicMin(gpv, pk); cur_pv = pk; }
-                    const uint32_t idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + k * 32 + lane);
+                    t_pv = pk < t_pv ? pk : t_pv;
                     const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
                     const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
 #pragma unroll
                     for (int d = 0; d < 8; ++d) {
-                      const uint32_t key = order_key(dir[d]);
-                      if (key >= cur_key[d]) {      // >=: an equal value with a larger index still wins
-                        atomicMax(gex + d, ((unsigned long long)key << 32) | idx);
-                        cur_key[d] = key;
+                      // >=: among equal values the larger point index (= later k) wins
+                      if (dir[d] >= t_best[d]) {
+                        t_best[d] = dir[d];
+                        t_k = (t_k & ~(0xfu << (4 * d))) | ((unsigned)k << (4 * d));
                       }
                     }
                   }
                 }
               }
               cnt += __popc(__ballot_sync(kFullMask, hit));
+            }
+            if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
+              unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+              unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
+              const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + lane);
+              const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
+              const uint32_t mh = __reduce_min_sync(kFullMask, ph);
+              const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
+              unsigned long long mine_val = 0;
+#pragma unroll
+              for (int d = 0; d < 8; ++d) {
+                const uint32_t key = order_key(t_best[d]);          // -inf (no hit in this lane) is below every hit
+                const uint32_t kmax = __reduce_max_sync(kFullMask, key);
+                const uint32_t idx = base_idx + ((t_k >> (4 * d)) & 0xfu) * 32u;
+                const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? idx : 0u);
+                if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
+              }
+              if (lane < 8) {
+                if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
+                  atomicMax(gex + lane, mine_val);
+              } else if (lane == 8) {
+                const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
+                if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
+              }
             }
           }
           if (lane == 0 && cnt) atomicAdd(a.n_hit + pair, cnt);

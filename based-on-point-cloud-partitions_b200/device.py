@@ -677,15 +677,21 @@ StageTimer = _Timer
 
 
 def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
-                       rank: int, world: int, group=None, timer=None, **kw) -> VisibilityResult:
-    """A7-A9 with the cameras sharded c % world == rank (north star: only the
-    visibility pass is partitioned; the per-pair result vectors are
-    all-gathered).  Returns the FULL per-pair result on every rank."""
+                       rank: int, world: int, group=None, timer=None, shard="ranges", **kw) -> VisibilityResult:
+    """A7-A9 with the (block, camera) pairs sharded over the ranks (north star: only the
+    visibility pass is partitioned; the per-pair result vectors are all-gathered).
+    shard="ranges": contiguous equal-cost ranges of the pair list (multigpu.shard_csr_ranges);
+    shard="modulo": cameras c % world == rank of every block (multigpu.shard_csr).
+    Returns the FULL per-pair result on every rank."""
     from . import multigpu as M
     if world <= 1:
         return visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                           timer=timer, **kw)
-    my_off, my_idx, my_pos = M.shard_csr(cam_offsets, cam_index, rank, world)
+    if shard == "ranges":
+        my_off, my_idx, my_pos = M.shard_csr_ranges(cam_offsets, cam_index, rank, world,
+                                                    ds_offsets[1:] - ds_offsets[:-1])
+    else:
+        my_off, my_idx, my_pos = M.shard_csr(cam_offsets, cam_index, rank, world)
     if timer is not None:
         timer.mark("vis_shard")
     v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, my_off, my_idx, timer=timer, **kw)

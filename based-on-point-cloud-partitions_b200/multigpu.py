@@ -36,6 +36,53 @@ def shard_csr(cam_off: torch.Tensor, cam_idx: torch.Tensor, rank: int, world: in
     return new_off.contiguous(), cam_idx[pos].contiguous(), pos
 
 
+def shard_csr_ranges(cam_off: torch.Tensor, cam_idx: torch.Tensor, rank: int, world: int,
+                     block_cost: torch.Tensor):
+    """Like shard_csr, but rank r owns a CONTIGUOUS range of the pair list whose cost
+    (pair cost = the block's down-sampled point count, `block_cost[L]`) is 1/world of the
+    total: whole blocks plus at most two partial camera lists per rank, so the per-tile work
+    of the sweep (tile load, box, cull) is not repeated on every rank as it is with the
+    modulo sharding.  Every rank evaluates the same expressions on the same data, so the
+    ranges tile the pair list exactly."""
+    P = cam_idx.shape[0]
+    if world <= 1:
+        return cam_off, cam_idx, torch.arange(P, device=cam_idx.device)
+    lo, hi = range_bounds(cam_off.cpu().numpy(), block_cost.cpu().numpy(), rank, world)
+    # the range is contiguous: the shard is a view of the pair list and a clamped offset table
+    new_off = (cam_off.clamp(lo, hi) - lo).to(torch.int64)
+    pos = torch.arange(lo, hi, device=cam_idx.device)
+    return new_off.contiguous(), cam_idx[lo:hi], pos
+
+
+def range_bounds(cam_off_h, block_cost_h, rank: int, world: int):
+    """[lo, hi) of rank's pair range (host arithmetic on the L-sized tables, exact in integers):
+    pair p of block b has exclusive cumulative cost  S_b + (p - cam_off[b]) * M_b;  rank r owns the
+    pairs with  total * r <= cost * world < total * (r + 1)."""
+    L = len(cam_off_h) - 1
+    cnt = [int(cam_off_h[b + 1] - cam_off_h[b]) for b in range(L)]
+    M = [int(block_cost_h[b]) for b in range(L)]
+    total = sum(c * m for c, m in zip(cnt, M))
+
+    def first_at_least(t):          # first pair whose exclusive cost * world >= t  (t = total * r)
+        s = 0
+        for b in range(L):
+            if cnt[b] == 0:
+                continue
+            if M[b] == 0:
+                if s * world >= t:
+                    return int(cam_off_h[b])
+                continue
+            if (s + (cnt[b] - 1) * M[b]) * world >= t:
+                need = t - s * world                        # k * M[b] * world >= need
+                k = max(0, -(-need // (M[b] * world)))
+                return int(cam_off_h[b]) + k
+            s += cnt[b] * M[b]
+        return int(cam_off_h[L])
+    lo = first_at_least(total * rank)
+    hi = first_at_least(total * (rank + 1)) if rank + 1 < world else int(cam_off_h[L])
+    return lo, hi
+
+
 def pack_records(n_hit, ratio, area, keep, flags) -> torch.Tensor:
     rec = torch.empty((n_hit.shape[0], REC_COLS), dtype=torch.float64, device=n_hit.device)
     rec[:, REC_N_HIT] = n_hit.to(torch.float64)

@@ -236,7 +236,7 @@ def run_ours(args):
             "leaves": L, "pairs": pairs, "tests_per_step": tests,
             "downsampled_points": int(M_b.sum()), "kept_cameras": n_kept,
             "kept_fraction": n_kept / max(pairs, 1),
-            "parallelism": "cameras sharded c %% %d, per-pair records all-gathered" % world if world > 1 else "single GPU",
+            "parallelism": "(block, camera) pairs sharded in %d contiguous equal-cost ranges, per-pair records all-gathered" % world if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MB write)",
         },
         "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall,

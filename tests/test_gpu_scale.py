@@ -107,9 +107,11 @@ def test_determinism_and_modes():
 
 
 @pytest.mark.parametrize("world", [2, 3, 8])
-def test_camera_sharding_equals_single_gpu(world):
-    """Rank r evaluates cameras c % world == r (multigpu.shard_csr); scattering every
-    rank's records to their global pair positions reproduces the unsharded table."""
+@pytest.mark.parametrize("mode", ["ranges", "modulo"])
+def test_camera_sharding_equals_single_gpu(world, mode):
+    """Rank r evaluates its share of the pairs (contiguous equal-cost ranges, or cameras
+    c % world == r); scattering every rank's records to their global pair positions
+    reproduces the unsharded table."""
     w, recs, res = _scene_state()
     cams_d = torch.from_numpy(recs).to(DEV)
     full = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets, res.cam_index)
@@ -117,7 +119,11 @@ def test_camera_sharding_equals_single_gpu(world):
     table = torch.zeros((P, M.REC_COLS), dtype=torch.float64, device=DEV)
     seen = torch.zeros(P, dtype=torch.int32, device=DEV)
     for r in range(world):
-        off, idx, pos = M.shard_csr(res.cam_offsets, res.cam_index, r, world)
+        if mode == "ranges":
+            off, idx, pos = M.shard_csr_ranges(res.cam_offsets, res.cam_index, r, world,
+                                               res.ds_offsets[1:] - res.ds_offsets[:-1])
+        else:
+            off, idx, pos = M.shard_csr(res.cam_offsets, res.cam_index, r, world)
         v = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, off, idx)
         table[pos] = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
         seen[pos] += 1

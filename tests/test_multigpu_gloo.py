@@ -47,6 +47,10 @@ def _fake_records(off, idx):
     return n_hit, ratio, area, keep, flags
 
 
+def _block_cost(L, seed):
+    return torch.from_numpy(np.random.default_rng(100 + seed).integers(1, 5000, L).astype(np.int64))
+
+
 def _worker(rank, world, port, seed, out_dir):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -66,6 +70,15 @@ def _worker(rank, world, port, seed, out_dir):
         want = _fake_records(off, idx)
         for g, w in zip(got, want):
             assert torch.equal(g, w), "rank %d: gathered table differs" % rank
+        # contiguous equal-cost ranges (the default sharding of the visibility pass)
+        r_off, r_idx, r_pos = M.shard_csr_ranges(off, idx, rank, world, _block_cost(off.shape[0] - 1, seed))
+        assert int(r_off[-1]) == r_idx.shape[0] == r_pos.shape[0] and torch.equal(idx[r_pos], r_idx)
+        if r_pos.numel():
+            assert torch.equal(r_pos, torch.arange(int(r_pos[0]), int(r_pos[-1]) + 1))
+        nh, rt, ar, kp, fl = _fake_records(r_off, r_idx)
+        full3 = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world, pos=r_pos)
+        for g, w in zip(M.unpack_records(full3), want):
+            assert torch.equal(g, w), "rank %d: gathered table differs (ranges)" % rank
         torch.save([g.clone() for g in got], os.path.join(out_dir, "r%d.pt" % rank))
     finally:
         dist.destroy_process_group()
@@ -95,3 +108,15 @@ def test_shard_csr_single_process_identity():
             blk = torch.repeat_interleave(torch.arange(off.shape[0] - 1), off[1:] - off[:-1])
             assert torch.equal(cnt, torch.bincount(blk[pos], minlength=off.shape[0] - 1))
         assert bool((seen == 1).all())
+        # ranges: a partition of the pair list into contiguous pieces of near-equal cost
+        cost = _block_cost(off.shape[0] - 1, 9)
+        seen = torch.zeros(idx.shape[0], dtype=torch.int64)
+        loads = []
+        blk = torch.repeat_interleave(torch.arange(off.shape[0] - 1), off[1:] - off[:-1])
+        for r in range(world):
+            o, i, pos = M.shard_csr_ranges(off, idx, r, world, cost)
+            seen[pos] += 1
+            loads.append(int(cost[blk[pos]].sum()))
+            assert torch.equal(o[1:] - o[:-1], torch.bincount(blk[pos], minlength=off.shape[0] - 1))
+        assert bool((seen == 1).all())
+        assert max(loads) - min(loads) <= 2 * int(cost.max())
