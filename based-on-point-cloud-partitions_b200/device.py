@@ -275,6 +275,9 @@ def camera_records(R, T, FoVx, FoVy, width, height, front_axis=1) -> np.ndarray:
 def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
     """Camera-list split factor of the sweep: enough work items for 148 SMs x 2
     CTAs when there are few point tiles.  Results do not depend on it."""
+    import os
+    if os.environ.get("PTGS_CAM_SPLIT"):          # diagnostics: results do not depend on it
+        return int(os.environ["PTGS_CAM_SPLIT"])
     tiles = max(1, (int(n_points_total) + 2047) // 2048 + n_blocks)
     want = 148 * 2 * 4
     return max(1, min(64, (want + tiles - 1) // tiles))
