@@ -416,6 +416,8 @@ struct SweepSmem {
   int act[kSwThreads];                                    // cameras of the round that survive the tile cull
   long long pair[kSwCamChunk];                            // output slot (pair id / camera) of the staged cameras
   int nact;
+  int tag_b;                                              // block / first camera whose whole camera range is staged
+  long long tag_lo;                                       //   (-1: none) -- see `cached` in the sweep
   long long next_item;
   int qn, qhead;                                          // (warp run, camera) work queue of the chunk
   unsigned q[(kSwThreads / 32) * kSwCamChunk];            // run << 24 | camera slot << 12 | edge mask (0xfff: none)
@@ -435,6 +437,8 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
 
   for (int i = tid; i <= a.n_blocks; i += kSwThreads) S.prefix[i] = a.item_prefix[i];
   if (tid == 0) {
+    S.tag_b = -1;
+    S.tag_lo = -1;
     mbar_init(&S.bar[0], 1);
     mbar_init(&S.bar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -544,48 +548,12 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
     // (rounds of kSwThreads cameras), the survivors are compacted into S.act and
     // swept in chunks of kSwCamChunk; tiles that lie wholly inside a camera's "in"
     // rectangle are counted right here.
-    for (int64_t r0 = cur.cam_lo; r0 < cur.cam_hi; r0 += kSwThreads) {
-      const int nr = (int)((cur.cam_hi - r0) < kSwThreads ? (cur.cam_hi - r0) : kSwThreads);
-      if (tid == 0) S.nact = 0;
-      __syncthreads();                       // S.box / S.nact visible, previous round finished
-      if (tid < nr) {
-        const int64_t lpos = r0 + tid;       // position inside the block's camera list
-        const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
-        float rec[kCamFloats];
-#pragma unroll
-        for (int q = 0; q < kCamFloats / 4; ++q)
-          reinterpret_cast<float4*>(rec)[q] =
-              __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
-        const Cam cj = load_cam(rec);
-        bool live = tile_may_hit(cj, S.box);
-        if (MODE != 2 && live) {
-          float der[8];
-          const float* kr = nullptr;
-          if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * kKrectFloats;
-          make_rects(cj, kr, MODE, der);
-          if ((MODE == 1 && kr) ? tile_all_in_poly(cj, kr, S.box) : tile_all_in(cj, der, S.box)) {
-            // every point of the tile is a hit that needs no further work
-            const int64_t pair = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
-            atomicAdd(a.n_hit + pair, cur.cnt);
-            PTGS_FINE_STAT(5, cur.cnt);
-            if (MODE == 0) S.tile_seen = 1;
-            live = false;
-          }
-        }
-        if (live) S.act[atomicAdd(&S.nact, 1)] = (int)(lpos - cur.cam_lo);
-      }
-      __syncthreads();
-      const int nact_all = S.nact;
-      if (tid == 0) {
-        atomicAdd(&g_sweep_stats[0], (unsigned long long)nr * (unsigned)cur.cnt);
-        atomicAdd(&g_sweep_stats[1], (unsigned long long)nact_all * (unsigned)cur.cnt);
-      }
-    for (int c0 = 0; c0 < nact_all; c0 += kSwCamChunk) {
-      const int nc = (nact_all - c0) < kSwCamChunk ? (nact_all - c0) : kSwCamChunk;
-      // ---- stage the chunk of surviving cameras
+    // Stages cameras [first, first + count) of the item's list (positions S.act[c0 + j] - or
+    // cur.cam_lo + j when `direct`) with everything the sweep needs per camera.
+    auto stage_cameras = [&](int c0, int nc, bool direct) {
       for (int i = tid; i < nc * (kCamFloats / 4); i += kSwThreads) {
         const int j = i / (kCamFloats / 4), q = i % (kCamFloats / 4);
-        const int64_t lpos = cur.cam_lo + S.act[c0 + j];
+        const int64_t lpos = cur.cam_lo + (direct ? j : S.act[c0 + j]);
         const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
         reinterpret_cast<float4*>(S.cam[j])[q] =
             __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
@@ -593,7 +561,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       if (MODE == 2) {
         for (int i = tid; i < nc * (kPolyFloats / 4); i += kSwThreads) {
           const int j = i / (kPolyFloats / 4), q = i % (kPolyFloats / 4);
-          const int64_t slot = cam_base + cur.cam_lo + S.act[c0 + j];
+          const int64_t slot = cam_base + cur.cam_lo + (direct ? j : S.act[c0 + j]);
           const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
           reinterpret_cast<float4*>(S.poly[j])[q] =
               __ldg(reinterpret_cast<const float4*>(a.poly + pair * kPolyFloats) + q);
@@ -602,15 +570,14 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       if (MODE == 1) {
         for (int i = tid; i < nc * (kKrectFloats / 4); i += kSwThreads) {
           const int j = i / (kKrectFloats / 4), q = i % (kKrectFloats / 4);
-          const int64_t slot = cam_base + cur.cam_lo + S.act[c0 + j];
+          const int64_t slot = cam_base + cur.cam_lo + (direct ? j : S.act[c0 + j]);
           reinterpret_cast<float4*>(S.poly[j])[q] =
               a.krect ? __ldg(reinterpret_cast<const float4*>(a.krect + slot * kKrectFloats) + q)
                       : make_float4(0.0f, 0.0f, -1.0f, -1.0f);
         }
       }
-      if (tid == 0) { S.qn = 0; S.qhead = 0; }
       if (tid < nc) {
-        const int64_t lpos = cur.cam_lo + S.act[c0 + tid];
+        const int64_t lpos = cur.cam_lo + (direct ? tid : S.act[c0 + tid]);
         S.pair[tid] = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
         if (MODE != 2) {
           const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
@@ -633,7 +600,76 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           S.pair_of[tid] = (int)pair;
         }
       }
+    };
+    // An item whose whole camera range fits the staging arrays keeps it there for as long as
+    // the CTA stays on the same (block, range): consecutive items are mostly tiles of the same
+    // block, so the camera / interior-region records are read from global memory once per block
+    // and not three dependent L2 round trips per tile.
+    const bool cached = (cur.cam_hi - cur.cam_lo) <= kSwCamChunk;
+    if (cached) {
+      const bool fresh = (S.tag_b == cur.b) && (S.tag_lo == cur.cam_lo);   // ordered by the barrier above
+      if (!fresh) stage_cameras(0, (int)(cur.cam_hi - cur.cam_lo), true);
       __syncthreads();
+      if (tid == 0) { S.tag_b = cur.b; S.tag_lo = cur.cam_lo; }
+    } else if (tid == 0) {
+      S.tag_b = -1;                      // the staging arrays are about to be overwritten chunk by chunk
+    }
+    for (int64_t r0 = cur.cam_lo; r0 < cur.cam_hi; r0 += kSwThreads) {
+      const int nr = (int)((cur.cam_hi - r0) < kSwThreads ? (cur.cam_hi - r0) : kSwThreads);
+      if (tid == 0) S.nact = 0;
+      __syncthreads();                       // S.box / S.nact visible, previous round finished
+      if (tid < nr) {
+        const int64_t lpos = r0 + tid;       // position inside the block's camera list
+        Cam cj;
+        if (cached) {
+          cj = load_cam(S.cam[tid]);
+        } else {
+          const int64_t cam = a.cam_index ? (int64_t)a.cam_index[cam_base + lpos] : (int64_t)a.cam_first + lpos;
+          float rec[kCamFloats];
+#pragma unroll
+          for (int q = 0; q < kCamFloats / 4; ++q)
+            reinterpret_cast<float4*>(rec)[q] =
+                __ldg(reinterpret_cast<const float4*>(a.cameras + cam * kCamFloats) + q);
+          cj = load_cam(rec);
+        }
+        bool live = tile_may_hit(cj, S.box);
+        if (MODE != 2 && live) {
+          bool all_in;
+          if (cached) {
+            all_in = (MODE == 1 && a.krect) ? tile_all_in_poly(cj, S.poly[tid], S.box)
+                                            : tile_all_in(cj, S.der[tid], S.box);
+          } else {
+            float der[8];
+            const float* kr = nullptr;
+            if (MODE == 1 && a.krect) kr = a.krect + (cam_base + lpos) * kKrectFloats;
+            make_rects(cj, kr, MODE, der);
+            all_in = (MODE == 1 && kr) ? tile_all_in_poly(cj, kr, S.box) : tile_all_in(cj, der, S.box);
+          }
+          if (all_in) {
+            // every point of the tile is a hit that needs no further work
+            const int64_t pair = (MODE == 0 && !a.cam_index) ? lpos : (cam_base + lpos);
+            atomicAdd(a.n_hit + pair, cur.cnt);
+            PTGS_FINE_STAT(5, cur.cnt);
+            if (MODE == 0) S.tile_seen = 1;
+            live = false;
+          }
+        }
+        if (live) S.act[atomicAdd(&S.nact, 1)] = (int)(lpos - cur.cam_lo);
+      }
+      __syncthreads();
+      const int nact_all = S.nact;
+      if (tid == 0) {
+        atomicAdd(&g_sweep_stats[0], (unsigned long long)nr * (unsigned)cur.cnt);
+        atomicAdd(&g_sweep_stats[1], (unsigned long long)nact_all * (unsigned)cur.cnt);
+      }
+    for (int c0 = 0; c0 < nact_all; c0 += kSwCamChunk) {
+      const int nc = (nact_all - c0) < kSwCamChunk ? (nact_all - c0) : kSwCamChunk;
+      // ---- stage the chunk of surviving cameras (already resident when `cached`)
+      if (!cached) stage_cameras(c0, nc, false);
+      if (tid == 0) { S.qn = 0; S.qhead = 0; }
+      __syncthreads();
+      // staged slot of the i-th survivor of the chunk
+      auto slot_of = [&](int i) { return cached ? S.act[c0 + i] : i; };
       for (int g0 = 0; g0 < nc; g0 += 32) {
       // ---- per-warp classification: lane j tests camera j of the chunk against the
       // box of the warp's own 256 contiguous points (a few voxel-cells wide):
@@ -642,17 +678,19 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
       unsigned und = 0xffffffffu;      // MODE 1, lane j: polygon edges of camera j that cut the warp's box
       if (wcnt > 0) {
         bool may = false, allin = false;
+        int sl = 0;                      // staged slot of this lane's camera
         if (g0 + lane < nc) {
-          const Cam cj = load_cam(S.cam[g0 + lane]);
+          sl = slot_of(g0 + lane);
+          const Cam cj = load_cam(S.cam[sl]);
           may = tile_may_hit(cj, wb);
           if (MODE == 1 && may) {
             bool fz;
-            und = poly_undecided(cj, S.poly[g0 + lane], wb, fz);
+            und = poly_undecided(cj, S.poly[sl], wb, fz);
             allin = und == 0u && fz;
           }
-          if (MODE == 0 && may) allin = tile_all_in(cj, S.der[g0 + lane], wb);
-          if (MODE == 2 && may) allin = inner_all_in(cj, S.poly[g0 + lane], wb);   // nothing to emit
-          if (MODE != 2 && allin) atomicAdd(a.n_hit + S.pair[g0 + lane], wcnt);
+          if (MODE == 0 && may) allin = tile_all_in(cj, S.der[sl], wb);
+          if (MODE == 2 && may) allin = inner_all_in(cj, S.poly[sl], wb);   // nothing to emit
+          if (MODE != 2 && allin) atomicAdd(a.n_hit + S.pair[sl], wcnt);
         }
         pm = __ballot_sync(kFullMask, may && !allin);
         if (MODE == 0 && __ballot_sync(kFullMask, allin) != 0u) seen_mask = 0xffu;
@@ -664,7 +702,7 @@ __global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
           if (may && !allin) {
             const unsigned um = (MODE == 1 && und != 0xffffffffu) ? (und & 0xffu) : 0xfffu;
             S.q[base + __popc(pm & lanemask_lt())] =
-                ((unsigned)(tid >> 5) << 24) | ((unsigned)(g0 + lane) << 12) | um;
+                ((unsigned)(tid >> 5) << 24) | ((unsigned)sl << 12) | um;
           }
         }
         if (lane == 0) {
