@@ -94,8 +94,19 @@ class ProgressiveDataPartitioning:
         pts = np.ascontiguousarray(self.pcd.points)
         if pts.dtype not in (np.float32, np.float64):
             pts = pts.astype(np.float64)
-        self._x, self._y, self._z = D.aos_to_soa(torch.from_numpy(pts).to(dev))
+        self._pts_d = torch.from_numpy(pts).to(dev)
+        self._x, self._y, self._z = D.aos_to_soa(self._pts_d)
+        # colours / normals ride along so that block clouds are gathered on the device
+        # (a NumPy fancy index of ~10^7 rows in coordinate order costs seconds per block)
+        self._col_d = torch.from_numpy(np.ascontiguousarray(self.pcd.colors)).to(dev)
+        self._nrm_d = torch.from_numpy(np.ascontiguousarray(self.pcd.normals)).to(dev)
         self._dev = dev
+
+    def _gather(self, idx_d):
+        """points / colors / normals rows `idx_d` (device int tensor) -> host arrays in the cloud's dtypes."""
+        i = idx_d.to(torch.int64)
+        return (self._pts_d.index_select(0, i).cpu().numpy(), self._col_d.index_select(0, i).cpu().numpy(),
+                self._nrm_d.index_select(0, i).cpu().numpy())
 
     def _store_ply(self, path, xyz, rgb):
         if self.write_outputs:
@@ -184,31 +195,30 @@ class ProgressiveDataPartitioning:
         o_rng = D.vast_point_range(self._x, self._y, self._z, o_off, o_idx)
         e_rng = D.vast_point_range(self._x, self._y, self._z, e_off, e_idx)
         o_off_h, e_off_h = o_off.cpu().numpy(), e_off.cpu().numpy()
-        o_idx_h, e_idx_h = o_idx.cpu().numpy(), e_idx.cpu().numpy()
         self._ext_index = [e_idx[e_off_h[b]:e_off_h[b + 1]] for b in range(len(ids))]
         sc = pcd.points.dtype.type
         out = []
         n_ori = n_ext = 0
         for b, pid in enumerate(ids):
-            io = o_idx_h[o_off_h[b]:o_off_h[b + 1]]
-            ie = e_idx_h[e_off_h[b]:e_off_h[b + 1]]
-            if len(io) == 0 or len(ie) == 0:
+            n_o, n_e = int(o_off_h[b + 1] - o_off_h[b]), int(e_off_h[b + 1] - e_off_h[b])
+            if n_o == 0 or n_e == 0:
                 raise ValueError("min() arg is an empty sequence")       # get_point_range of an empty block (:289)
             self._store_ply(os.path.join(self.partition_ori_dir, "%s_camera_centers.ply" % pid),
                             np.array([cp.pose for cp in partition_dict[pid]]), np.zeros((len(partition_dict[pid]), 3)))
             self._store_ply(os.path.join(self.partition_extend_dir, "%s_camera_centers.ply" % pid),
                             np.array([cp.pose for cp in cam_lists[b]]), np.zeros((len(cam_lists[b]), 3)))
-            pts_e, col_e, nrm_e = pcd.points[ie], pcd.colors[ie], pcd.normals[ie]
+            pts_e, col_e, nrm_e = self._gather(self._ext_index[b])
             out.append(CameraPartition(partition_id=pid, cameras=cam_lists[b],
                                        point_cloud=BasicPointCloud(pts_e, col_e, nrm_e),
                                        ori_camera_bbox=ori_boxes[b], extend_camera_bbox=ext_boxes[b],
                                        extend_rate=self.extend_rate,
                                        ori_point_bbox=[sc(v) for v in o_rng[b]],
                                        extend_point_bbox=[sc(v) for v in e_rng[b]]))
-            n_ori += len(io)
-            n_ext += len(ie)
+            n_ori += n_o
+            n_ext += n_e
             if self.write_outputs:
-                self._store_ply(os.path.join(self.partition_ori_dir, "%s.ply" % pid), pcd.points[io], pcd.colors[io])
+                pts_o, col_o, _ = self._gather(o_idx[o_off_h[b]:o_off_h[b + 1]])
+                self._store_ply(os.path.join(self.partition_ori_dir, "%s.ply" % pid), pts_o, col_o)
                 self._store_ply(os.path.join(self.partition_extend_dir, "%s_extend.ply" % pid), pts_e, col_e)
         print("Total ori point number: %d\n" % pcd.points.shape[0], "Total before extend point number: %d\n" % n_ori,
               "Total extend point number: %d\n" % n_ext)
@@ -291,8 +301,8 @@ class ProgressiveDataPartitioning:
                             % (pid_i, total_added, len(cameras)))
                 self._store_ply(os.path.join(self.partition_visible_dir, "%s_camera_centers.ply" % pid_i),
                                 np.array([cp.pose for cp in cameras]), np.zeros((len(cameras), 3)))
-            uniq = D.vast_block_cloud(self._x, self._y, self._z, cams_d, self._ext_index[i], sources).cpu().numpy()
-            new_points, new_colors, new_normals = pcd.points[uniq], pcd.colors[uniq], pcd.normals[uniq]
+            uniq = D.vast_block_cloud(self._x, self._y, self._z, cams_d, self._ext_index[i], sources)
+            new_points, new_colors, new_normals = self._gather(uniq)
             out.append(part_i._replace(cameras=cameras,
                                        point_cloud=BasicPointCloud(new_points, new_colors, new_normals)))
             self._store_ply(os.path.join(self.partition_visible_dir, "%s_visible.ply" % pid_i), new_points, new_colors)
