@@ -39,6 +39,10 @@ SIGNATURES = {
     "ptgs_expand_count": (C.c_int, [C.c_int, _vp, _vp, _i64, _vp, _i32, _vp, _vp, _sz, _vp]),
     "ptgs_expand_fill": (C.c_int, [C.c_int, _vp, _vp, _i64, _vp, _i32, _vp, _vp, _vp, _i64, _vp,
                                    _sz, _vp]),
+    "ptgs_expand_count_grid": (C.c_int, [C.c_int, _vp, _vp, _i64, _vp, _i32, C.POINTER(C.c_double), _vp, _vp, _vp,
+                                         _vp, _sz, _vp]),
+    "ptgs_expand_fill_grid": (C.c_int, [C.c_int, _vp, _vp, _i64, _vp, _i32, C.POINTER(C.c_double), _vp, _vp, _vp,
+                                        _vp, _vp, _i64, _vp, _sz, _vp]),
     "ptgs_assign_cameras": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _i64, _vp]),
     "ptgs_voxel_downsample_workspace_bytes": (_sz, [_i64, _i32]),
     "ptgs_voxel_downsample": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f64, _vp,

@@ -221,6 +221,164 @@ static int expand_fill_impl(const void* x, const void* y, int64_t n, const void*
 }
 
 // ---------------------------------------------------------------------------
+// A4 with many blocks: the same selection through a uniform cell grid.  The caller
+// supplies, per cell of a G x G grid over the rectangles' bounding box, the list of
+// rectangles that can contain a point of that cell (a superset, built on the host
+// with a one-cell margin); a point is tested against its cell's candidates only
+// (N * L tests -> N * ~2), with the very same closed compares.  Tile / warp bookkeeping
+// is that of expand_kernel; because the lanes of a warp now look at different
+// rectangles, counts use shared-memory atomics on the warp's private counters and the
+// fill pass ranks the 32 points of a sub-group through a per-warp bit mask per
+// rectangle (bit = lane), which keeps every block's index list ascending.
+struct CellGrid {
+  double x0, y0, inv_x, inv_y;
+  int G;
+};
+
+template <typename T>
+__device__ __forceinline__ void cell_range(const CellGrid& g, const int32_t* __restrict__ cell_off, bool valid,
+                                           T px, T py, int& beg, int& end) {
+  beg = end = 0;
+  if (valid && px == px && py == py) {          // NaN lies in no rectangle
+    double fx = floor(((double)px - g.x0) * g.inv_x), fy = floor(((double)py - g.y0) * g.inv_y);
+    const double gm = (double)(g.G - 1);
+    fx = fx < 0.0 ? 0.0 : (fx > gm ? gm : fx);  // points outside the grid fail the exact tests anyway
+    fy = fy < 0.0 ? 0.0 : (fy > gm ? gm : fy);
+    const int c = (int)fy * g.G + (int)fx;
+    beg = cell_off[c];
+    end = cell_off[c + 1];
+  }
+}
+
+template <typename T, bool FILL>
+__global__ void __launch_bounds__(kExpWarps * 32) expand_grid_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, int64_t n,
+    const Rect4<T>* __restrict__ rects, int L, CellGrid g, const int32_t* __restrict__ cell_off,
+    const int32_t* __restrict__ cell_list, int64_t n_tiles, uint32_t* __restrict__ tile_cnt,
+    const int64_t* __restrict__ tile_base, int32_t* __restrict__ indices) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Rect4<T>* srect = reinterpret_cast<Rect4<T>*>(smem_raw);         // [L]
+  long long* sbase = reinterpret_cast<long long*>(srect + L);      // [L] tile bases (FILL)
+  uint32_t* wcnt = reinterpret_cast<uint32_t*>(sbase + L);         // [kExpWarps][L]
+  uint32_t* wmask = wcnt + (size_t)L * kExpWarps;                  // [kExpWarps][L], FILL only
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t tile = blockIdx.x;
+  for (int i = threadIdx.x; i < L; i += blockDim.x) {
+    srect[i] = rects[i];
+    if (FILL) sbase[i] = tile_base[(size_t)i * n_tiles + tile];
+  }
+  for (int i = threadIdx.x; i < L * kExpWarps * (FILL ? 2 : 1); i += blockDim.x) wcnt[i] = 0;
+  __syncthreads();
+  const int64_t wbase = tile * kExpTile + (int64_t)warp * (32 * kExpPerLane);
+  uint32_t* mycnt = wcnt + warp * L;
+  uint32_t* mymask = wmask + warp * L;
+
+  auto contains = [&](int r, T px, T py) {
+    const Rect4<T> q = srect[r];
+    return (px >= q.minx) && (px <= q.maxx) && (py >= q.miny) && (py <= q.maxy);
+  };
+  // per warp membership counts of the tile
+  for (int k = 0; k < kExpPerLane; ++k) {
+    const int64_t i = wbase + k * 32 + lane;
+    const bool valid = i < n;
+    T px = 0, py = 0;
+    if (valid) { px = x[i]; py = y[i]; }
+    if (!__any_sync(kFullMask, valid)) break;
+    int beg, end;
+    cell_range<T>(g, cell_off, valid, px, py, beg, end);
+    for (int p = beg; p < end; ++p) {
+      const int r = cell_list[p];
+      if (contains(r, px, py)) atomicAdd(&mycnt[r], 1u);
+    }
+  }
+  __syncthreads();
+  if (!FILL) {
+    for (int r = threadIdx.x; r < L; r += blockDim.x) {
+      uint32_t s = 0;
+#pragma unroll
+      for (int w = 0; w < kExpWarps; ++w) s += wcnt[w * L + r];
+      tile_cnt[(size_t)r * n_tiles + tile] = s;
+    }
+    return;
+  }
+  for (int r = threadIdx.x; r < L; r += blockDim.x) {    // exclusive scan over the warps, per block
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < kExpWarps; ++w) {
+      const uint32_t c = wcnt[w * L + r];
+      wcnt[w * L + r] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  for (int k = 0; k < kExpPerLane; ++k) {
+    const int64_t i = wbase + k * 32 + lane;
+    const bool valid = i < n;
+    T px = 0, py = 0;
+    if (valid) { px = x[i]; py = y[i]; }
+    if (!__any_sync(kFullMask, valid)) break;
+    int beg, end;
+    cell_range<T>(g, cell_off, valid, px, py, beg, end);
+    for (int p = beg; p < end; ++p) {                    // a: who is in which rectangle
+      const int r = cell_list[p];
+      if (contains(r, px, py)) atomicOr(&mymask[r], 1u << lane);
+    }
+    __syncwarp();
+    for (int p = beg; p < end; ++p) {                    // b: emit at (tile base + warp base + rank)
+      const int r = cell_list[p];
+      if (contains(r, px, py)) {
+        const uint32_t m = mymask[r];
+        const int64_t pos = sbase[r] + mycnt[r] + __popc(m & lanemask_lt());
+        indices[pos] = (int32_t)i;
+      }
+    }
+    __syncwarp();
+    for (int p = beg; p < end; ++p) {                    // c: the lowest lane of each mask advances the counter
+      const int r = cell_list[p];
+      if (contains(r, px, py)) {
+        const uint32_t m = mymask[r];
+        if ((m & lanemask_lt()) == 0u) {                 // (a lane that reads an already cleared mask adds 0)
+          atomicAdd(&mycnt[r], (uint32_t)__popc(m));
+          mymask[r] = 0u;
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+template <typename T>
+static int expand_grid_impl(bool fill, const void* x, const void* y, int64_t n, const void* rects, int32_t L,
+                            const CellGrid& g, const int32_t* cell_off, const int32_t* cell_list,
+                            int64_t* counts, int64_t* offsets, int32_t* indices, void* ws, cudaStream_t st) {
+  ExpandWs e = carve_expand(ws, n, L);
+  const size_t smem = (size_t)L * (sizeof(Rect4<T>) + 8) + (size_t)L * kExpWarps * 4 * (fill ? 2 : 1);
+  if (!fill) {
+    PTGS_CUDA_TRY(cudaFuncSetAttribute(expand_grid_kernel<T, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    expand_grid_kernel<T, false><<<(unsigned)e.n_tiles, kExpWarps * 32, smem, st>>>(
+        (const T*)x, (const T*)y, n, (const Rect4<T>*)rects, L, g, cell_off, cell_list, e.n_tiles, e.tile_cnt,
+        nullptr, nullptr);
+    PTGS_LAUNCH_CHECK();
+    expand_scan_kernel<<<L, 1024, 0, st>>>(e.tile_cnt, e.n_tiles, e.tile_base, counts);
+    PTGS_LAUNCH_CHECK();
+    return PTGS_OK;
+  }
+  offsets_kernel<<<1, 1024, 0, st>>>(counts, L, offsets);
+  PTGS_LAUNCH_CHECK();
+  dim3 gb((unsigned)((e.n_tiles + 255) / 256 > 64 ? 64 : (e.n_tiles + 255) / 256), (unsigned)L);
+  add_base_kernel<<<gb, 256, 0, st>>>(e.tile_base, e.n_tiles, offsets);
+  PTGS_LAUNCH_CHECK();
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(expand_grid_kernel<T, true>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  expand_grid_kernel<T, true><<<(unsigned)e.n_tiles, kExpWarps * 32, smem, st>>>(
+      (const T*)x, (const T*)y, n, (const Rect4<T>*)rects, L, g, cell_off, cell_list, e.n_tiles, e.tile_cnt,
+      e.tile_base, indices);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+// ---------------------------------------------------------------------------
 // A5: camera centre strictly inside the expanded box (XY), float64.
 // One CTA per block; cameras scanned in order so the list is ascending.
 // ---------------------------------------------------------------------------
@@ -343,6 +501,53 @@ int ptgs_expand_fill(int dtype, const void* x, const void* y, int64_t n,
   if (dtype == PTGS_F32)
     return expand_fill_impl<float>(x, y, n, rects, n_blocks, offsets, indices, workspace, counts, (cudaStream_t)stream);
   return expand_fill_impl<double>(x, y, n, rects, n_blocks, offsets, indices, workspace, counts, (cudaStream_t)stream);
+}
+
+static int expand_grid_check(int dtype, int64_t n, const void* rects, int32_t n_blocks, const double* grid,
+                             const int32_t* cell_off, const int32_t* cell_list, size_t workspace_bytes,
+                             CellGrid* g) {
+  PTGS_REQUIRE(dtype == PTGS_F32 || dtype == PTGS_F64, "dtype");
+  PTGS_REQUIRE(n >= 0 && n < (1ll << 31), "n must fit int32 indices");
+  PTGS_REQUIRE(n_blocks >= 1 && n_blocks <= kExpMaxBlocks, "n_blocks must be in [1,1024]");
+  PTGS_REQUIRE(rects && grid && cell_off && cell_list, "arguments");
+  g->x0 = grid[0]; g->y0 = grid[1]; g->inv_x = grid[2]; g->inv_y = grid[3]; g->G = (int)grid[4];
+  PTGS_REQUIRE(g->G >= 1 && g->G <= 4096, "grid size must be in [1,4096]");
+  if (workspace_bytes < ptgs_expand_workspace_bytes(n, n_blocks)) {
+    set_error("expand_grid: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  return PTGS_OK;
+}
+
+int ptgs_expand_count_grid(int dtype, const void* x, const void* y, int64_t n, const void* rects,
+                           int32_t n_blocks, const double* grid, const int32_t* cell_off,
+                           const int32_t* cell_list, int64_t* counts, void* workspace,
+                           size_t workspace_bytes, ptgs_stream_t stream) {
+  CellGrid g;
+  int rc = expand_grid_check(dtype, n, rects, n_blocks, grid, cell_off, cell_list, workspace_bytes, &g);
+  if (rc) return rc;
+  PTGS_REQUIRE(counts, "arguments");
+  if (dtype == PTGS_F32)
+    return expand_grid_impl<float>(false, x, y, n, rects, n_blocks, g, cell_off, cell_list, counts, nullptr,
+                                   nullptr, workspace, (cudaStream_t)stream);
+  return expand_grid_impl<double>(false, x, y, n, rects, n_blocks, g, cell_off, cell_list, counts, nullptr,
+                                  nullptr, workspace, (cudaStream_t)stream);
+}
+
+int ptgs_expand_fill_grid(int dtype, const void* x, const void* y, int64_t n, const void* rects,
+                          int32_t n_blocks, const double* grid, const int32_t* cell_off,
+                          const int32_t* cell_list, const int64_t* counts, int64_t* offsets,
+                          int32_t* indices, int64_t indices_capacity, void* workspace,
+                          size_t workspace_bytes, ptgs_stream_t stream) {
+  CellGrid g;
+  int rc = expand_grid_check(dtype, n, rects, n_blocks, grid, cell_off, cell_list, workspace_bytes, &g);
+  if (rc) return rc;
+  PTGS_REQUIRE(counts && offsets && (indices || indices_capacity == 0), "arguments");
+  if (dtype == PTGS_F32)
+    return expand_grid_impl<float>(true, x, y, n, rects, n_blocks, g, cell_off, cell_list,
+                                   const_cast<int64_t*>(counts), offsets, indices, workspace, (cudaStream_t)stream);
+  return expand_grid_impl<double>(true, x, y, n, rects, n_blocks, g, cell_off, cell_list,
+                                  const_cast<int64_t*>(counts), offsets, indices, workspace, (cudaStream_t)stream);
 }
 
 int ptgs_assign_cameras(const double* centers, int32_t n_cameras,

@@ -96,8 +96,13 @@ template <typename T>
 __global__ void __launch_bounds__(1024) classify_kernel(SplitState<T> s, int cur,
                                                         double leaf_limit, int max_depth) {
   const int nn = s.n_nodes[cur];
+  __shared__ int s_active;
+  if (threadIdx.x == 0) s_active = 0;
+  __syncthreads();
+  int mine_active = 0;
   for (int j = threadIdx.x; j < nn; j += blockDim.x) {
     Node<T>& nd = s.nodes[cur][j];
+    if (!((double)nd.count <= leaf_limit || nd.depth >= max_depth)) ++mine_active;
     if ((double)nd.count <= leaf_limit || nd.depth >= max_depth) {
       int o = atomicAdd(s.lf_n, 1);
       s.lf_bounds[4 * o + 0] = (double)nd.minx; s.lf_bounds[4 * o + 1] = (double)nd.miny;
@@ -113,6 +118,9 @@ __global__ void __launch_bounds__(1024) classify_kernel(SplitState<T> s, int cur
       nd.active = 1;
     }
   }
+  if (mine_active) atomicAdd(&s_active, mine_active);
+  __syncthreads();
+  if (threadIdx.x == 0) s.n_nodes[2] = s_active;
 }
 
 template <typename T>
@@ -344,7 +352,7 @@ static SplitState<T> carve_state(void* workspace, int64_t capacity, int max_dept
   SplitState<T> s;
   s.nodes[0] = cv.take<Node<T>>(kMaxNodes);
   s.nodes[1] = cv.take<Node<T>>(kMaxNodes);
-  s.n_nodes = cv.take<int32_t>(2);
+  s.n_nodes = cv.take<int32_t>(4);          // [2] = nodes of the current level that still split
   s.level_total = cv.take<int64_t>(2);
   s.cursors = cv.take<unsigned long long>(2 * kMaxNodes);
   const int level_nodes = 1 << (max_depth > 0 ? max_depth - 1 : 0);
@@ -393,6 +401,12 @@ static int split_impl(const void* x, const void* y, const int64_t* n_dev, int64_
     classify_kernel<T><<<1, 1024, 0, st>>>(s, cur, leaf_limit, max_depth);
     PTGS_LAUNCH_CHECK();
     if (level == max_depth) break;
+    // every node of the level is a leaf: the remaining levels would only launch empty kernels
+    // (one 4-byte read-back per level; c2 stops after 4 of its 10 possible levels)
+    int32_t n_active = 0;
+    PTGS_CUDA_TRY(cudaMemcpyAsync(&n_active, s.n_nodes + 2, 4, cudaMemcpyDeviceToHost, st));
+    PTGS_CUDA_TRY(cudaStreamSynchronize(st));
+    if (n_active == 0) break;
     const int max_nodes_here = 1 << level;
     for (int pass = 0; pass < Digits<T>::passes; ++pass) {
       hist_kernel<T><<<tiles, 256, 0, st>>>(s, cur, pass, bufs[cur]);

@@ -193,10 +193,50 @@ def balanced_split(x, y, n_dev, root_bounds, threshold, max_depth=MAX_DEPTH, cap
                 ld[:L].cpu().numpy(), lc[:L].cpu().numpy())
 
 
-def expand_select(x, y, boxes: np.ndarray):
+GRID_MIN_BLOCKS = 33          # below this the lock-step kernel (every point x every rectangle) is as fast
+
+
+def _cell_grid(rects: np.ndarray):
+    """Uniform G x G cell grid over the rectangles {minx,maxx,miny,maxy} (float64 view of the values the
+    kernel compares with) -> (grid[5], cell_off int32[G*G+1], cell_list int32) or None when the rectangles
+    overlap so much that the grid would not prune.  The cell of a coordinate is floor((v - x0) * inv) in
+    float64, evaluated identically on the device, and rounding is monotone, so a point inside a rectangle
+    always falls into the rectangle's cell range; one extra cell on every side is kept anyway."""
+    L = len(rects)
+    r = rects.astype(np.float64)
+    if not np.isfinite(r).all():
+        return None
+    x0, x1, y0, y1 = r[:, 0].min(), r[:, 1].max(), r[:, 2].min(), r[:, 3].max()
+    if not (x1 > x0 and y1 > y0):
+        return None
+    G = int(min(256, max(16, 1 << int(np.ceil(np.log2(4.0 * np.sqrt(L)))))))
+    inv_x, inv_y = G / (x1 - x0), G / (y1 - y0)
+    cl = lambda v: np.clip(v, 0, G - 1).astype(np.int64)
+    ix0, ix1 = cl(np.floor((r[:, 0] - x0) * inv_x) - 1), cl(np.floor((r[:, 1] - x0) * inv_x) + 1)
+    iy0, iy1 = cl(np.floor((r[:, 2] - y0) * inv_y) - 1), cl(np.floor((r[:, 3] - y0) * inv_y) + 1)
+    n_cells = (ix1 - ix0 + 1) * (iy1 - iy0 + 1)
+    if int(n_cells.sum()) > 16 * G * G:
+        return None
+    # (cell, rectangle) pairs, vectorised: rectangle b covers w[b] x h[b] cells
+    w = ix1 - ix0 + 1
+    start = np.cumsum(n_cells) - n_cells
+    owners = np.repeat(np.arange(L, dtype=np.int32), n_cells)
+    local = np.arange(int(n_cells.sum()), dtype=np.int64) - np.repeat(start, n_cells)
+    ww = np.repeat(w, n_cells)
+    cells = (np.repeat(iy0, n_cells) + local // ww) * G + np.repeat(ix0, n_cells) + local % ww
+    order = np.argsort(cells, kind="stable")          # rectangles stay ascending inside a cell
+    cell_off = np.zeros(G * G + 1, np.int32)
+    np.cumsum(np.bincount(cells, minlength=G * G), out=cell_off[1:])
+    grid = np.array([x0, y0, inv_x, inv_y, float(G)], np.float64)
+    return grid, cell_off, np.ascontiguousarray(owners[order])
+
+
+def expand_select(x, y, boxes: np.ndarray, use_grid=None):
     """A4.  boxes (L,4) float64 {minx,miny,maxx,maxy}; the bounds are rounded
     to the cloud's dtype exactly as NumPy does for `f32_array >= python_float`
-    (shen_partation_densify.py:201-202)."""
+    (shen_partation_densify.py:201-202).  With many blocks the selection goes through a
+    cell grid (ptgs_expand_*_grid, identical results); use_grid forces one path."""
+    import ctypes as C
     lib = _lib.load()
     dev = x.device
     n, L = x.shape[0], len(boxes)
@@ -205,13 +245,29 @@ def expand_select(x, y, boxes: np.ndarray):
     rects_d = torch.from_numpy(np.ascontiguousarray(rects)).to(dev)
     counts = torch.empty(L, dtype=torch.int64, device=dev)
     ws = _ws(lib.ptgs_expand_workspace_bytes(n, L), dev)
-    check(lib.ptgs_expand_count(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
-                                _ptr(ws), ws.numel(), _stream()))
+    cg = None
+    if use_grid or (use_grid is None and L >= GRID_MIN_BLOCKS):
+        cg = _cell_grid(rects)
+    if cg is not None:
+        grid, cell_off, cell_list = cg
+        gp = grid.ctypes.data_as(C.POINTER(C.c_double))
+        off_d = torch.from_numpy(cell_off).to(dev)
+        lst_d = torch.from_numpy(cell_list if len(cell_list) else np.zeros(1, np.int32)).to(dev)
+        check(lib.ptgs_expand_count_grid(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, gp, _ptr(off_d), _ptr(lst_d),
+                                         _ptr(counts), _ptr(ws), ws.numel(), _stream()))
+    else:
+        check(lib.ptgs_expand_count(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
+                                    _ptr(ws), ws.numel(), _stream()))
     total = int(counts.sum().item())
     offsets = torch.empty(L + 1, dtype=torch.int64, device=dev)
     indices = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
-    check(lib.ptgs_expand_fill(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
-                               _ptr(offsets), _ptr(indices), total, _ptr(ws), ws.numel(), _stream()))
+    if cg is not None:
+        check(lib.ptgs_expand_fill_grid(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, gp, _ptr(off_d), _ptr(lst_d),
+                                        _ptr(counts), _ptr(offsets), _ptr(indices), total, _ptr(ws), ws.numel(),
+                                        _stream()))
+    else:
+        check(lib.ptgs_expand_fill(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
+                                   _ptr(offsets), _ptr(indices), total, _ptr(ws), ws.numel(), _stream()))
     return offsets, indices[:total]
 
 

@@ -130,6 +130,9 @@ int ptgs_bounds_xy(int dtype, const void* x, const void* y,
  *   buffers (sized by capacity_factor) overflowed (duplicate split-line
  *   points are copied into both children).
  *   max_leaves must be >= 2^max_depth.
+ *   The level loop reads back one int per level (number of nodes that still
+ *   split) and stops at the first level without any: the call synchronises
+ *   the stream once per executed level.
  * ------------------------------------------------------------------ */
 size_t ptgs_balanced_split_workspace_bytes(int dtype, int64_t n_capacity,
                                            double capacity_factor,
@@ -168,6 +171,28 @@ int ptgs_expand_fill(int dtype, const void* x, const void* y, int64_t n,
                      int32_t* indices, int64_t indices_capacity,
                      void* workspace, size_t workspace_bytes,
                      ptgs_stream_t stream);
+
+/* The same selection through a uniform cell grid, for many blocks (N * L
+ * closed-rectangle tests become N * ~2).  grid[5] (HOST doubles) = {x0, y0,
+ * cells per unit in x, in y, G}: a point's cell is
+ * (clamp(floor((x - x0) * grid[2]), 0, G-1), same in y), row-major y * G + x;
+ * cell_off[G*G + 1] / cell_list (device int32) give, per cell, the rectangles
+ * that may contain a point of that cell (any superset; the exact compares are
+ * those of ptgs_expand_count).  Results are identical to ptgs_expand_count /
+ * ptgs_expand_fill; workspace = ptgs_expand_workspace_bytes(n, n_blocks). */
+int ptgs_expand_count_grid(int dtype, const void* x, const void* y, int64_t n,
+                           const void* rects, int32_t n_blocks,
+                           const double* grid, const int32_t* cell_off,
+                           const int32_t* cell_list, int64_t* counts,
+                           void* workspace, size_t workspace_bytes,
+                           ptgs_stream_t stream);
+int ptgs_expand_fill_grid(int dtype, const void* x, const void* y, int64_t n,
+                          const void* rects, int32_t n_blocks,
+                          const double* grid, const int32_t* cell_off,
+                          const int32_t* cell_list, const int64_t* counts,
+                          int64_t* offsets, int32_t* indices,
+                          int64_t indices_capacity, void* workspace,
+                          size_t workspace_bytes, ptgs_stream_t stream);
 
 /* ------------------------------------------------------------------ *
  * A5 -- camera -> block assignment

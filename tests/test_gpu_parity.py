@@ -376,3 +376,32 @@ def test_full_partition_vs_oracle():
         res2 = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold)
         for g, w in zip(_csr_lists(res2.kept_offsets, res2.kept_index), want.kept_cameras):
             assert set(g.tolist()) == set(w.tolist())
+
+
+@pytest.mark.parametrize("f64", [False, True])
+def test_expand_grid_path_equals_lockstep(f64):
+    """ptgs_expand_*_grid (cell-grid candidates) == ptgs_expand_* (every point x every rectangle),
+    and both == the NumPy closed-box mask, for many overlapping rectangles."""
+    rng = np.random.default_rng(23)
+    n, L = 200003, 150
+    pts = rng.uniform(-100, 100, (n, 2))
+    pts[::97] = np.round(pts[::97])                      # points on rectangle edges
+    dt = np.float64 if f64 else np.float32
+    pts = pts.astype(dt)
+    pts[11] = [np.nan, 0.0]
+    pts[12] = [1e9, -1e9]                                # far outside every rectangle
+    lo = np.round(rng.uniform(-100, 80, (L, 2)))
+    hi = lo + np.round(rng.uniform(1, 40, (L, 2)))
+    boxes = np.stack([lo[:, 0], lo[:, 1], hi[:, 0], hi[:, 1]], 1).astype(np.float64)
+    x = torch.from_numpy(np.ascontiguousarray(pts[:, 0])).to(DEV)
+    y = torch.from_numpy(np.ascontiguousarray(pts[:, 1])).to(DEV)
+    o1, i1 = D.expand_select(x, y, boxes, use_grid=False)
+    o2, i2 = D.expand_select(x, y, boxes, use_grid=True)
+    assert D._cell_grid(np.stack([boxes[:, 0], boxes[:, 2], boxes[:, 1], boxes[:, 3]], 1)) is not None
+    assert torch.equal(o1, o2) and torch.equal(i1, i2)
+    off, idx = o2.cpu().numpy(), i2.cpu().numpy()
+    for b in range(L):
+        m = (pts[:, 0] >= dt(boxes[b, 0])) & (pts[:, 0] <= dt(boxes[b, 2])) & \
+            (pts[:, 1] >= dt(boxes[b, 1])) & (pts[:, 1] <= dt(boxes[b, 3]))
+        assert np.array_equal(idx[off[b]:off[b + 1]], np.nonzero(m)[0]), b
+    assert off[-1] > n // 2
