@@ -285,7 +285,7 @@ def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device):
     return offsets, index[:total].clone()
 
 
-def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None):
+def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None, sync=True):
     """A6 over every block at once.  Voxels of a block come out in ascending
     (vx,vy,vz) order; ds_first gives the reference's first-occurrence order."""
     lib = _lib.load()
@@ -302,6 +302,9 @@ def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None
                                     ne, L, float(voxel), _ptr(buf[0]), _ptr(buf[1]), _ptr(buf[2]),
                                     _ptr(ds_first), _ptr(ds_off), _ptr(status), _ptr(ws), ws.numel(),
                                     _stream()))
+    if not sync:
+        # no host round trip: full-capacity planes (ds_off bounds every later read), status unchecked
+        return ds_off, buf[0], buf[1], buf[2], ds_first
     m = int(ds_off[L].item())
     return ds_off, buf[0, :m], buf[1, :m], buf[2, :m], ds_first[:m]
 
@@ -342,7 +345,8 @@ def pick_cam_split(n_points_total: int, n_blocks: int) -> int:
 def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
                cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False,
-               cand_pool=None, interior=True, sample_stride=SAMPLE_STRIDE) -> VisibilityResult:
+               cand_pool=None, interior=True, sample_stride=SAMPLE_STRIDE,
+               defer_check=False) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair.
 
     sweep 1 (hit counts, pivot, 8 extremes) -> area bounds + early decision ->
@@ -451,7 +455,15 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         mark("vis_hull")
         # the one synchronisation: [overflowed pairs, hull budget exceeded, exact pairs]
         bad = need.bool() & ((flags & 4) != 0)
-        stat = torch.stack([bad.sum(), ((flags & 8) != 0).sum(), sub_off[L]]).cpu()
+        stat_d = torch.stack([bad.sum(), ((flags & 8) != 0).sum(), sub_off[L]])
+        if defer_check and rounds == 1:
+            # the caller reads `pending` later (one synchronisation for several calls) and
+            # re-runs this call without defer_check when pending[0] != 0
+            res = VisibilityResult(n_hit, area, ratio, keep, flags, cand_count, rounds)
+            res.ratio_lo, res.ratio_hi, res.n_exact, res.pending = ratio_lo, ratio_hi, None, stat_d
+            mark("vis_check")
+            return res
+        stat = stat_d.cpu()
         if n_exact is None:
             n_exact = int(stat[2])
         if int(stat[1]):
@@ -812,11 +824,22 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
         for t in (pts_d, off_d, coff_d, cidx_d, cams_d):
             t.record_stream(main)
         x, y, z = aos_to_soa(pts_d)
-        ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e)
-        vis = visibility_sharded(dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group,
-                                 threshold=threshold)
+        # no host synchronisation inside a group: the host queues group g+1 while group g runs
+        ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e, sync=False)
+        args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group)
+        vis = visibility_sharded(*args, threshold=threshold, defer_check=(world <= 1))
         k_off, k_idx = select_cameras(vis.keep, coff_d, cidx_d, sync=False)
-        parts.append((k_off, k_idx, vis, ds_off, nb))
+        parts.append([k_off, k_idx, vis, ds_off, nb, args, coff_d, cidx_d])
+    for part in parts:          # deferred candidate-capacity checks (rare: re-run that group)
+        pend = getattr(part[2], "pending", None)
+        if pend is not None:
+            st_h = pend.cpu()
+            if int(st_h[1]):
+                raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
+            if int(st_h[0]):
+                part[2] = visibility_sharded(*part[5], threshold=threshold)
+                part[0], part[1] = select_cameras(part[2].keep, part[6], part[7], sync=False)
+    parts = [tuple(p[:5]) for p in parts]
     # one round of D2H at the end
     k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1, np.int64)], [], [], [], [], []
     base = 0
