@@ -540,6 +540,23 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
     return (n_hit[:cam_count], seen[:n]) if want_seen else n_hit[:cam_count]
 
 
+def coverage_sweep_sharded(px, py, pz, cameras_d, rank: int, world: int, group=None, want_seen=False,
+                           ordered=None):
+    """Config c5 over several GPUs: the cloud is replicated, rank r sweeps the
+    cameras multigpu.camera_range(C, r, world); the per-camera counts are all-gathered (and the
+    per-point seen flags max-reduced).  Returns the full result on every rank."""
+    from . import multigpu as M
+    C = cameras_d.shape[0]
+    first, cnt = M.camera_range(C, rank, world)
+    out = coverage_sweep(px, py, pz, cameras_d, cam_first=first, cam_count=cnt, want_seen=want_seen,
+                         ordered=ordered)
+    n_hit, seen = out if want_seen else (out, None)
+    n_hit = M.gather_camera_counts(n_hit, C, world, group)
+    if want_seen:
+        return n_hit, M.merge_seen(seen, world, group)
+    return n_hit
+
+
 # ---------------------------------------------------------------- A14: the camera-grid (Vast) path
 VAST_CAMERA_DOUBLES = 20
 

@@ -122,3 +122,33 @@ def gather_records(local: torch.Tensor, cam_idx: torch.Tensor, world: int, group
     recv = torch.empty((world * max(P, 1), REC_COLS), dtype=torch.float64, device=local.device)
     dist.all_gather_into_tensor(recv, send, group=group)
     return recv.view(world, max(P, 1), REC_COLS).sum(dim=0)[:P]
+
+
+# ---- coverage sweep (config c5): points replicated, cameras sharded in contiguous ranges ----
+def camera_range(n_cameras: int, rank: int, world: int):
+    """(first, count) of rank's cameras: ceil(C / world) consecutive cameras per rank."""
+    per = (n_cameras + world - 1) // max(world, 1)
+    first = min(rank * per, n_cameras)
+    return first, max(0, min(per, n_cameras - first))
+
+
+def gather_camera_counts(local: torch.Tensor, n_cameras: int, world: int, group=None) -> torch.Tensor:
+    """All-gather of the per-camera hit counts of a camera-sharded coverage sweep (`local` = this
+    rank's camera_range, int32) -> counts of all cameras on every rank.  64 KB at c5."""
+    import torch.distributed as dist
+    if world <= 1:
+        return local
+    per = (n_cameras + world - 1) // world
+    send = torch.zeros(per, dtype=local.dtype, device=local.device)
+    send[: local.shape[0]] = local
+    recv = torch.empty(world * per, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    return recv[:n_cameras]
+
+
+def merge_seen(seen: torch.Tensor, world: int, group=None) -> torch.Tensor:
+    """Per-point "seen by any camera" flags of all ranks (uint8 max all-reduce, in place)."""
+    import torch.distributed as dist
+    if world > 1:
+        dist.all_reduce(seen, op=dist.ReduceOp.MAX, group=group)
+    return seen

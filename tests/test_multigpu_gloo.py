@@ -79,6 +79,14 @@ def _worker(rank, world, port, seed, out_dir):
         full3 = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world, pos=r_pos)
         for g, w in zip(M.unpack_records(full3), want):
             assert torch.equal(g, w), "rank %d: gathered table differs (ranges)" % rank
+        # coverage sweep exchange (c5): contiguous camera ranges, counts gathered, seen flags merged
+        C = 57
+        first, cnt = M.camera_range(C, rank, world)
+        counts = (torch.arange(first, first + cnt) * 7 + 3).to(torch.int32)
+        allc = M.gather_camera_counts(counts, C, world)
+        assert torch.equal(allc, (torch.arange(C) * 7 + 3).to(torch.int32))
+        seen = ((torch.arange(1000) % world) == rank).to(torch.uint8)
+        assert bool(M.merge_seen(seen, world).all())
         torch.save([g.clone() for g in got], os.path.join(out_dir, "r%d.pt" % rank))
     finally:
         dist.destroy_process_group()
@@ -92,6 +100,16 @@ def test_sharded_records_gloo(world, seed, tmp_path):
     for t in tabs[1:]:
         for a, b in zip(tabs[0], t):
             assert torch.equal(a, b)
+
+
+def test_camera_range_partitions_cameras():
+    for C in (0, 1, 7, 16000):
+        for world in (1, 2, 3, 8):
+            got = []
+            for r in range(world):
+                f, c = M.camera_range(C, r, world)
+                got.extend(range(f, f + c))
+            assert got == list(range(C))
 
 
 def test_shard_csr_single_process_identity():
