@@ -541,20 +541,31 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
 
 
 def coverage_sweep_sharded(px, py, pz, cameras_d, rank: int, world: int, group=None, want_seen=False,
-                           ordered=None):
-    """Config c5 over several GPUs: the cloud is replicated, rank r sweeps the
-    cameras multigpu.camera_range(C, r, world); the per-camera counts are all-gathered (and the
-    per-point seen flags max-reduced).  Returns the full result on every rank."""
+                           shard="points", ordered=None):
+    """Config c5 over several GPUs.  Every rank holds the whole cloud and all cameras.
+    shard="points" (default): rank r orders and sweeps only its slice of the cloud
+    (multigpu.point_range) against ALL cameras -- the Morton sort and the per-tile camera culls,
+    which dominate after the sort, both divide by the number of ranks; per-camera counts are one
+    int32 sum all-reduce, per-point seen flags an all-gather of the slices.
+    shard="cameras": rank r sweeps the whole cloud against its camera range (SURVEY's layout; the
+    sort is then repeated on every rank).  Returns the full result on every rank."""
     from . import multigpu as M
     C = cameras_d.shape[0]
-    first, cnt = M.camera_range(C, rank, world)
-    out = coverage_sweep(px, py, pz, cameras_d, cam_first=first, cam_count=cnt, want_seen=want_seen,
-                         ordered=ordered)
+    if shard == "cameras":
+        first, cnt = M.camera_range(C, rank, world)
+        out = coverage_sweep(px, py, pz, cameras_d, cam_first=first, cam_count=cnt, want_seen=want_seen,
+                             ordered=ordered)
+        n_hit, seen = out if want_seen else (out, None)
+        n_hit = M.gather_camera_counts(n_hit, C, world, group)
+        return (n_hit, M.merge_seen(seen, world, group)) if want_seen else n_hit
+    n = px.shape[0]
+    p0, p1 = M.point_range(n, rank, world)
+    out = coverage_sweep(px[p0:p1], py[p0:p1], pz[p0:p1], cameras_d, want_seen=want_seen)
     n_hit, seen = out if want_seen else (out, None)
-    n_hit = M.gather_camera_counts(n_hit, C, world, group)
-    if want_seen:
-        return n_hit, M.merge_seen(seen, world, group)
-    return n_hit
+    if p1 <= p0:
+        n_hit = torch.zeros(C, dtype=torch.int32, device=px.device)
+    n_hit = M.sum_camera_counts(n_hit.contiguous(), world, group)
+    return (n_hit, M.gather_seen(seen, n, world, group)) if want_seen else n_hit
 
 
 # ---------------------------------------------------------------- A14: the camera-grid (Vast) path

@@ -152,3 +152,33 @@ def merge_seen(seen: torch.Tensor, world: int, group=None) -> torch.Tensor:
     if world > 1:
         dist.all_reduce(seen, op=dist.ReduceOp.MAX, group=group)
     return seen
+
+
+def point_range(n_points: int, rank: int, world: int):
+    """[p0, p1) of rank's slice of the cloud: equal slices, starts on multiples of 4 points so that
+    the planar float32 slices stay 16-byte aligned."""
+    per = ((n_points + max(world, 1) - 1) // max(world, 1) + 3) // 4 * 4
+    p0 = min(rank * per, n_points)
+    return p0, min(p0 + per, n_points)
+
+
+def sum_camera_counts(n_hit: torch.Tensor, world: int, group=None) -> torch.Tensor:
+    """Point-sharded coverage sweep: every rank counted its slice of the cloud for ALL cameras;
+    the per-camera totals are one int32 sum all-reduce (64 KB at c5)."""
+    import torch.distributed as dist
+    if world > 1:
+        dist.all_reduce(n_hit, op=dist.ReduceOp.SUM, group=group)
+    return n_hit
+
+
+def gather_seen(seen_local: torch.Tensor, n_points: int, world: int, group=None) -> torch.Tensor:
+    """Per-point flags of the point-sharded sweep: slices (point_range) all-gathered in rank order."""
+    import torch.distributed as dist
+    if world <= 1:
+        return seen_local
+    per = ((n_points + world - 1) // world + 3) // 4 * 4
+    send = torch.zeros(per, dtype=seen_local.dtype, device=seen_local.device)
+    send[: seen_local.shape[0]] = seen_local
+    recv = torch.empty(world * per, dtype=seen_local.dtype, device=seen_local.device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    return recv[:n_points]

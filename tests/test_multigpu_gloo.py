@@ -87,6 +87,15 @@ def _worker(rank, world, port, seed, out_dir):
         assert torch.equal(allc, (torch.arange(C) * 7 + 3).to(torch.int32))
         seen = ((torch.arange(1000) % world) == rank).to(torch.uint8)
         assert bool(M.merge_seen(seen, world).all())
+        # point-sharded coverage exchange: counts summed, seen slices gathered
+        npts = 1003
+        p0, p1 = M.point_range(npts, rank, world)
+        assert p0 % 4 == 0
+        part = torch.zeros(C, dtype=torch.int32)
+        part[rank::world] = (torch.arange(C)[rank::world] + 1).to(torch.int32)
+        assert torch.equal(M.sum_camera_counts(part, world), (torch.arange(C) + 1).to(torch.int32))
+        flags = (torch.arange(p0, p1) % 3 == 0).to(torch.uint8)
+        assert torch.equal(M.gather_seen(flags, npts, world), (torch.arange(npts) % 3 == 0).to(torch.uint8))
         torch.save([g.clone() for g in got], os.path.join(out_dir, "r%d.pt" % rank))
     finally:
         dist.destroy_process_group()
@@ -110,6 +119,15 @@ def test_camera_range_partitions_cameras():
                 f, c = M.camera_range(C, r, world)
                 got.extend(range(f, f + c))
             assert got == list(range(C))
+
+
+def test_point_range_partitions_points():
+    for n in (0, 3, 1003, 100_000_000):
+        for world in (1, 2, 3, 8):
+            edges = [M.point_range(n, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == n
+            assert all(edges[i][1] == edges[i + 1][0] or edges[i + 1][0] == n for i in range(world - 1))
+            assert all(a % 4 == 0 or a == n for a, _ in edges)
 
 
 def test_shard_csr_single_process_identity():

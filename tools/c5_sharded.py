@@ -25,9 +25,14 @@ cams_d = torch.from_numpy(recs).to(dev)
 x, y, z = D.aos_to_soa(torch.from_numpy(w.xyz).to(dev))
 
 
+mode = sys.argv[2] if len(sys.argv) > 2 else "points"
+
+
 def run():
-    od = D.spatial_order(x, y, z)
-    return D.coverage_sweep_sharded(x, y, z, cams_d, rank, world, ordered=od)
+    if mode == "cameras":
+        od = D.spatial_order(x, y, z)
+        return D.coverage_sweep_sharded(x, y, z, cams_d, rank, world, shard="cameras", ordered=od)
+    return D.coverage_sweep_sharded(x, y, z, cams_d, rank, world)
 
 
 best = None
@@ -46,7 +51,7 @@ for it in range(4):
     if it > 0:
         best = float(ms) if best is None else min(best, float(ms))
 if rank == 0:
-    print(json.dumps({"config": W.describe("c5", scale, w), "n_gpus": world, "ms_max_over_ranks_best_of_3": round(best, 3),
+    print(json.dumps({"config": W.describe("c5", scale, w), "n_gpus": world, "shard": mode, "ms_max_over_ranks_best_of_3": round(best, 3),
                       "hits": int(n_hit.sum().item()), "checksum": int((n_hit.to(torch.int64) * torch.arange(1, n_hit.numel() + 1, device=dev)).sum().item())}))
 if world > 1:
     dist.destroy_process_group()
