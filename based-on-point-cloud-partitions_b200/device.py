@@ -805,7 +805,7 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
 def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
                            cam_records: torch.Tensor, cam_offsets: np.ndarray,
                            cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
-                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2):
+                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2, exchange=None):
     """visibility_based_camera_selection (shen_partation_densify.py:911-954)
     for HOST inputs: the expanded blocks' points back to back
     (`block_points` (sum N_b, 3) float32/float64, ideally pinned), the camera
@@ -813,22 +813,38 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
     visibility pass (A7-A9) and returns host arrays
     (kept_offsets, kept_index, n_hit, ratio, keep, flags).
 
-    The blocks are cut into `groups` runs of consecutive blocks of about equal
+    With world > 1, rank r owns a contiguous range of the (block, camera) pair list of
+    about 1/world of the cost (multigpu.range_bounds on the expanded point counts); it uploads,
+    down-samples and sweeps only the blocks that range touches, and the per-pair records are
+    exchanged once at the end (every rank returns the full result).
+
+    The (local) blocks are cut into `groups` runs of consecutive blocks of about equal
     size; all uploads are queued on a copy stream up front and group g is
     processed on the current stream as soon as its points have landed, so the
     PCIe transfer of group g+1 overlaps the kernels of group g."""
+    from . import multigpu as M
     L = len(block_offsets) - 1
     block_offsets = np.ascontiguousarray(block_offsets, dtype=np.int64)
     cam_offsets = np.ascontiguousarray(cam_offsets, dtype=np.int64)
     cam_index = np.ascontiguousarray(cam_index, dtype=np.int32)
-    n_total = int(block_offsets[L])
-    # group boundaries: consecutive blocks, ~equal point counts
-    G = max(1, min(int(groups), L))
-    cuts = [0]
+    P = int(cam_offsets[L])
+    # rank r owns the contiguous pair range [lo, hi) (cost of a pair = expanded points of its block,
+    # known on the host) and uploads / down-samples only the blocks that range touches
+    lo, hi = (0, P) if world <= 1 else M.range_bounds(cam_offsets, np.diff(block_offsets), rank, world)
+    if hi > lo:
+        bl0 = int(np.searchsorted(cam_offsets, lo, side="right")) - 1
+        bl1 = int(np.searchsorted(cam_offsets, hi, side="left"))
+    else:
+        bl0 = bl1 = 0
+    loc_off = np.clip(cam_offsets, lo, hi) - lo            # this rank's block -> camera CSR (global blocks)
+    n_local = int(block_offsets[bl1] - block_offsets[bl0])
+    # group boundaries: consecutive local blocks, ~equal point counts
+    G = max(1, min(int(groups), max(bl1 - bl0, 1)))
+    cuts = [bl0]
     for g in range(1, G):
-        b = int(np.searchsorted(block_offsets, n_total * g / G, side="left"))
-        cuts.append(min(max(b, cuts[-1]), L))
-    cuts.append(L)
+        b = int(np.searchsorted(block_offsets, block_offsets[bl0] + n_local * g / G, side="left"))
+        cuts.append(min(max(b, cuts[-1]), bl1))
+    cuts.append(bl1)
     spans = [(cuts[i], cuts[i + 1]) for i in range(G) if cuts[i + 1] > cuts[i]]
     main = torch.cuda.current_stream(device)
     copy = _copy_stream(device)
@@ -840,12 +856,17 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
             p0, p1 = int(block_offsets[b0]), int(block_offsets[b1])
             pts_d = block_points[p0:p1].to(device, non_blocking=True)
             off_d = torch.from_numpy(block_offsets[b0:b1 + 1] - p0).to(device, non_blocking=True)
-            c0, c1 = int(cam_offsets[b0]), int(cam_offsets[b1])
-            coff_d = torch.from_numpy(cam_offsets[b0:b1 + 1] - c0).to(device, non_blocking=True)
-            cidx_d = torch.from_numpy(cam_index[c0:c1]).to(device, non_blocking=True)
+            c0, c1 = int(loc_off[b0]), int(loc_off[b1])
+            coff_d = torch.from_numpy(loc_off[b0:b1 + 1] - c0).to(device, non_blocking=True)
+            cidx_d = torch.from_numpy(cam_index[lo + c0:lo + c1]).to(device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy)
             staged.append((pts_d, off_d, coff_d, cidx_d, ev, p1 - p0, b1 - b0))
+        if world > 1:
+            full_off_d = torch.from_numpy(cam_offsets).to(device, non_blocking=True)
+            full_idx_d = torch.from_numpy(cam_index).to(device, non_blocking=True)
+            ev_full = torch.cuda.Event()
+            ev_full.record(copy)
     parts, n_ds = [], 0
     for (pts_d, off_d, coff_d, cidx_d, ev, n_e, nb) in staged:
         main.wait_event(ev)
@@ -854,34 +875,53 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
         x, y, z = aos_to_soa(pts_d)
         # no host synchronisation inside a group: the host queues group g+1 while group g runs
         ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e, sync=False)
-        args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d, rank, world, group)
-        vis = visibility_sharded(*args, threshold=threshold, defer_check=(world <= 1))
-        k_off, k_idx = select_cameras(vis.keep, coff_d, cidx_d, sync=False)
-        parts.append([k_off, k_idx, vis, ds_off, nb, args, coff_d, cidx_d])
+        args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d)
+        vis = visibility(*args, threshold=threshold, defer_check=True)
+        parts.append([vis, ds_off, nb, args, coff_d, cidx_d])
     for part in parts:          # deferred candidate-capacity checks (rare: re-run that group)
-        pend = getattr(part[2], "pending", None)
+        pend = getattr(part[0], "pending", None)
         if pend is not None:
             st_h = pend.cpu()
             if int(st_h[1]):
                 raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
             if int(st_h[0]):
-                part[2] = visibility_sharded(*part[5], threshold=threshold)
-                part[0], part[1] = select_cameras(part[2].keep, part[6], part[7], sync=False)
-    parts = [tuple(p[:5]) for p in parts]
-    # one round of D2H at the end
-    k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1, np.int64)], [], [], [], [], []
-    base = 0
-    for (k_off, k_idx, vis, ds_off, nb) in parts:
-        ko = k_off.cpu().numpy()
-        k_offs.append(ko[1:] + base)
-        k_idxs.append(k_idx[: int(ko[nb])].cpu().numpy())
-        base += int(ko[nb])
-        nh.append(vis.n_hit.cpu().numpy()); rt.append(vis.ratio.cpu().numpy())
-        kp.append(vis.keep.cpu().numpy()); fl.append(vis.flags.cpu().numpy())
-        n_ds += int(ds_off[nb].item())
-    cat = lambda xs, dt: np.concatenate(xs) if xs else np.zeros(0, dt)
-    out = (np.concatenate(k_offs), cat(k_idxs, np.int32), cat(nh, np.int32), cat(rt, np.float64),
-           cat(kp, np.uint8), cat(fl, np.uint8))
+                part[0] = visibility(*part[3], threshold=threshold)
+    if world <= 1:
+        # kept-camera lists per group, one round of D2H at the end
+        k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1, np.int64)], [], [], [], [], []
+        sel = [select_cameras(p[0].keep, p[4], p[5], sync=False) for p in parts]
+        base = 0
+        for (vis, ds_off, nb, _a, _c, _i), (k_off, k_idx) in zip(parts, sel):
+            ko = k_off.cpu().numpy()
+            k_offs.append(ko[1:] + base)
+            k_idxs.append(k_idx[: int(ko[nb])].cpu().numpy())
+            base += int(ko[nb])
+            nh.append(vis.n_hit.cpu().numpy()); rt.append(vis.ratio.cpu().numpy())
+            kp.append(vis.keep.cpu().numpy()); fl.append(vis.flags.cpu().numpy())
+            n_ds += int(ds_off[nb].item())
+        cat = lambda xs, dt: np.concatenate(xs) if xs else np.zeros(0, dt)
+        out = (np.concatenate(k_offs), cat(k_idxs, np.int32), cat(nh, np.int32), cat(rt, np.float64),
+               cat(kp, np.uint8), cat(fl, np.uint8))
+        return out, n_ds
+    # world > 1: the groups' records are this rank's pairs lo..hi-1 in order; ONE exchange
+    recs = [M.pack_records(p[0].n_hit, p[0].ratio, p[0].area, p[0].keep, p[0].flags) for p in parts
+            if p[0].n_hit.shape[0] > 0 and p[5].shape[0] > 0]
+    local = torch.cat(recs) if recs else torch.zeros((0, M.REC_COLS), dtype=torch.float64, device=device)
+    local = local[: hi - lo]
+    main.wait_event(ev_full)
+    full_off_d.record_stream(main); full_idx_d.record_stream(main)
+    pos = torch.arange(lo, hi, device=device)
+    if exchange is not None:       # tests: stand-in for the collective
+        full = exchange(local, pos)
+    else:
+        full = M.gather_records(local, full_idx_d, world, group, pos=pos)
+    n_hit, ratio, area, keep, flags = M.unpack_records(full)
+    k_off, k_idx = select_cameras(keep, full_off_d, full_idx_d, sync=False)
+    ko = k_off.cpu().numpy()
+    for p in parts:
+        n_ds += int(p[1][p[2]].item())
+    out = (ko, k_idx[: int(ko[L])].cpu().numpy(), n_hit.cpu().numpy(), ratio.cpu().numpy(),
+           keep.cpu().numpy(), flags.cpu().numpy())
     return out, n_ds
 
 

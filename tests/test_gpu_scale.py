@@ -131,3 +131,34 @@ def test_camera_sharding_equals_single_gpu(world, mode):
     n_hit, ratio, area, keep, flags = M.unpack_records(table)
     assert torch.equal(n_hit, full.n_hit) and torch.equal(keep, full.keep) and torch.equal(flags, full.flags)
     assert torch.equal(ratio, full.ratio)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_host_entry_rank_local_blocks(world):
+    """visibility_select_host with world > 1: every rank uploads and sweeps only the blocks of its
+    pair range; the union of the ranks' records equals the single-process result (the collective
+    is replaced by a recording stand-in, ranks run one after the other on this GPU)."""
+    w, recs, res = _scene_state()
+    x, y, z = D.aos_to_soa(torch.from_numpy(w.xyz).to(DEV))
+    idx = res.pt_index.to(torch.int64)
+    blocks = torch.stack([x[idx], y[idx], z[idx]], 1).contiguous().cpu()
+    blk_off = res.pt_offsets.cpu().numpy()
+    cam_off, cam_idx = res.cam_offsets.cpu().numpy(), res.cam_index.cpu().numpy()
+    recs_t = torch.from_numpy(recs)
+    one, _ = D.visibility_select_host(blocks, blk_off, recs_t, cam_off, cam_idx, torch.device(DEV))
+    P = len(cam_idx)
+    table = torch.zeros((P, M.REC_COLS), dtype=torch.float64, device=DEV)
+    seen = torch.zeros(P, dtype=torch.int32, device=DEV)
+
+    def exchange(local, pos):
+        table[pos] = local
+        seen[pos] += 1
+        return table.clone()
+    out = None
+    for r in range(world):
+        out, _ = D.visibility_select_host(blocks, blk_off, recs_t, cam_off, cam_idx, torch.device(DEV),
+                                          rank=r, world=world, exchange=exchange)
+    assert bool((seen == 1).all())
+    # after the last rank the table is complete: that call's outputs are the full result
+    for a, b in zip(one, out):
+        assert np.array_equal(a, b)
