@@ -61,7 +61,7 @@ SIGNATURES = {
     "ptgs_visibility_candidates": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                              _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
-                                       _vp, _vp, _vp, _vp, _vp, _vp]),
+                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
     "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),
     "ptgs_spatial_order_workspace_bytes": (_sz, [_i64]),

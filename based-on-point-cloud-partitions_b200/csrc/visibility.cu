@@ -1268,7 +1268,8 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
     double thr, double near_eps, double* __restrict__ area_out, double* __restrict__ ratio_out,
     uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out,
-    const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev) {
+    const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev,
+    int32_t* __restrict__ status /* [0] capacity overflows, [1] vertex-budget overflows; may be null */) {
   __shared__ float2 buf[kHullBuf];
   __shared__ float2 lower[kHullChain];
   __shared__ float2 upper[kHullChain];
@@ -1286,6 +1287,7 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     // re-runs the pair with cand_count[pair] slots
     if (tid == 0) {
       area_out[pair] = 0.0; ratio_out[pair] = 0.0; keep_out[pair] = 0; flags_out[pair] = 4;
+      if (status) atomicAdd(status, 1);
     }
     return;
   }
@@ -1434,6 +1436,7 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     const int nhit = n_hit[pair];
     const bool enough = nhit > min_hits;                  // densify:898
     flags |= s_flags;
+    if ((s_flags & 8) && status) atomicAdd(status + 1, 1);
     if (s_col) flags |= 2;
     if (enough && fabs(ratio - thr) <= near_eps) flags |= 1;
     area_out[pair] = enough ? area : 0.0;
@@ -1750,14 +1753,15 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* pair_cam, const float* cameras, int32_t min_hits,
                          double ratio_threshold, double near_eps, double* area, double* ratio,
                          uint8_t* keep, uint8_t* flags, const int32_t* pair_map,
-                         const int64_t* n_sub_dev, ptgs_stream_t stream) {
+                         const int64_t* n_sub_dev, int32_t* status, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_pairs >= 0 && n_pairs < (1ll << 31), "n_pairs");
   if (n_pairs == 0) return PTGS_OK;
   PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
                "arguments");
+  if (status) PTGS_CUDA_TRY(cudaMemsetAsync(status, 0, 8, (cudaStream_t)stream));
   hull_kernel<<<(unsigned)n_pairs, kHullThreads, 0, (cudaStream_t)stream>>>(
       (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-      ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev);
+      ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

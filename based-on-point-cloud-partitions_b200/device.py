@@ -425,6 +425,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
     sub_idx = torch.empty(P, dtype=torch.int32, device=dev)
     sub_pos = torch.empty(P, dtype=torch.int32, device=dev)
     cand_off = torch.empty(P + 1, dtype=torch.int64, device=dev)
+    hull_status = torch.empty(2, dtype=torch.int32, device=dev)
     caps_in = None
     rounds = 0
     n_exact = None
@@ -451,11 +452,11 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         check(lib.ptgs_visibility_hull(_ptr(cand_uv), _ptr(cand_off), _ptr(cand_count), _ptr(n_hit), P,
                                        _ptr(cam_index), _ptr(cameras_d), int(min_hits),
                                        float(threshold), float(near_eps), _ptr(area), _ptr(ratio),
-                                       _ptr(keep), _ptr(flags), _ptr(sub_pos), _ptr(sub_off[L:]), st))
+                                       _ptr(keep), _ptr(flags), _ptr(sub_pos), _ptr(sub_off[L:]),
+                                       _ptr(hull_status), st))
         mark("vis_hull")
         # the one synchronisation: [overflowed pairs, hull budget exceeded, exact pairs]
-        bad = need.bool() & ((flags & 4) != 0)
-        stat_d = torch.stack([bad.sum(), ((flags & 8) != 0).sum(), sub_off[L]])
+        stat_d = torch.cat([hull_status.to(torch.int64), sub_off[L:L + 1]])
         if defer_check and rounds == 1:
             # the caller reads `pending` later (one synchronisation for several calls) and
             # re-runs this call without defer_check when pending[0] != 0
@@ -473,7 +474,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         if rounds > 3:
             raise RuntimeError("visibility: candidate capacity did not converge")
         # re-run only the overflowed pairs with their exact candidate counts
-        need = bad.to(torch.uint8)
+        need = (need.bool() & ((flags & 4) != 0)).to(torch.uint8)
         caps_in = cand_count.clone()
     mark("vis_check")
     res = VisibilityResult(n_hit, area, ratio, keep, flags, cand_count, rounds)

@@ -391,7 +391,10 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          double ratio_threshold, double near_eps, double* area,
                          double* ratio, uint8_t* keep, uint8_t* flags,
                          const int32_t* pair_map, const int64_t* n_sub_dev,
-                         ptgs_stream_t stream);
+                         int32_t* status, ptgs_stream_t stream);
+/* status (device int32[2], may be NULL; zeroed by the call): [0] pairs whose
+ * candidate list overflowed its capacity (flags bit2, re-run them with
+ * cand_count slots), [1] pairs whose hull exceeded the vertex budget (bit3). */
 
 /* A9 selection: per block compaction of the kept cameras (ascending order of
  * the block's camera list).  kept_offsets[L+1] int64, kept_index capacity =
