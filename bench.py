@@ -322,8 +322,21 @@ def measure_e2e(args, out, ctx):
         tot += time.perf_counter() - t0
     barrier(world)
     tot = max_over_ranks(tot, world, dev)
-    h2d = blocks.numel() * blocks.element_size() + recs_pinned.numel() * 4 + blk_off.nbytes + \
-        cam_off.nbytes + cam_idx.nbytes
+    if world > 1:
+        # every rank uploads only the blocks its pair range touches: job total = sum over ranks
+        from ptgs_b200 import multigpu as M
+        import torch.distributed as dist
+        lo, hi = M.range_bounds(cam_off, np.diff(blk_off), rank, world)
+        b0 = int(np.searchsorted(cam_off, lo, side="right")) - 1 if hi > lo else 0
+        b1 = int(np.searchsorted(cam_off, hi, side="left")) if hi > lo else 0
+        mine = int(blk_off[b1] - blk_off[b0]) * blocks.shape[1] * blocks.element_size() + \
+            recs_pinned.numel() * 4 + cam_off.nbytes + cam_idx.nbytes + (b1 - b0 + 1) * 16
+        t = torch.tensor([mine], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        h2d = int(t.item())
+    else:
+        h2d = blocks.numel() * blocks.element_size() + recs_pinned.numel() * 4 + blk_off.nbytes + \
+            cam_off.nbytes + cam_idx.nbytes
     d2h = sum(a.nbytes for a in outp)
     out["e2e"] = {"value": ctx["tests"] / (tot / steps), "unit": UNIT, "ms_per_step": tot / steps * 1e3,
                   "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
