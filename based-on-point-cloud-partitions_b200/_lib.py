@@ -75,6 +75,7 @@ SIGNATURES = {
     "ptgs_vast_mark_own": (C.c_int, [_vp, _i64, _i32, _vp, _vp]),
     "ptgs_vast_unique_workspace_bytes": (_sz, [_i64]),
     "ptgs_vast_unique": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "ptgs_coverage_workspace_bytes": (_sz, [_i64, _i32]),
     "ptgs_coverage_sweep": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
 }
 

@@ -17,12 +17,15 @@
 //   MODE 0  hit counts (+ optional per-point "seen" flag)      -- coverage sweep
 //   MODE 1  hit counts + Graham pivot + 8 directional extremes -- sweep 1
 //   MODE 2  hull candidates                                   -- sweep 2
+#include <cstddef>
+
 #include "common.cuh"
 
 namespace ptgs {
 
 constexpr int kSwThreads = 256;
-constexpr int kSwP = 8;                          // points per thread
+constexpr int kSwP = 4;                          // points per thread
+constexpr int kSwCtasPerSM = 3;
 constexpr int kSwTile = kSwThreads * kSwP;       // 2048 points per tile
 constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
 constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups)
@@ -430,7 +433,7 @@ struct SweepSmem {
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(kSwThreads, 2) sweep_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
@@ -1579,13 +1582,140 @@ __global__ void __launch_bounds__(128) krect_kernel(
   out[0] = (float)gu; out[1] = (float)gv; out[2] = (float)hu; out[3] = (float)hv;
 }
 
+// ---- coverage sweep with many cameras: camera lists per super-tile ---------------------
+// The cloud (in Morton order) is cut into <= 1024 super-tiles of S consecutive points; one
+// pass tests every camera against every super-tile box and builds, per super-tile, the
+// ascending list of cameras that may see it.  The sweep then treats a super-tile as a block
+// with that list (typically ~100 of 16 000 cameras), so its 1024-point tiles cull a short,
+// shared-memory resident list instead of every camera.
+__global__ void __launch_bounds__(256) cov_box_kernel(
+    const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz, int64_t n,
+    int64_t S, int64_t* __restrict__ pt_off, float* __restrict__ box /* [B][6] centre, half extent */) {
+  __shared__ float sm[8][6];
+  const int b = blockIdx.x;
+  const int64_t p0 = (int64_t)b * S, p1 = (p0 + S < n) ? p0 + S : n;
+  const float inf = __int_as_float(0x7f800000);
+  float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+  for (int64_t i = p0 + threadIdx.x; i < p1; i += 256) {
+    const float v[3] = {px[i], py[i], pz[i]};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], v[a]); hi[a] = fmaxf(hi[a], v[a]); }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(kFullMask, lo[a], d));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(kFullMask, hi[a], d));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { sm[threadIdx.x >> 5][a] = lo[a]; sm[threadIdx.x >> 5][3 + a] = hi[a]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float l = sm[0][threadIdx.x], h = sm[0][3 + threadIdx.x];
+    for (int w = 1; w < 8; ++w) { l = fminf(l, sm[w][threadIdx.x]); h = fmaxf(h, sm[w][3 + threadIdx.x]); }
+    const float pad = (fabsf(l) + fabsf(h)) * (1.0f / 1048576.0f);
+    box[b * 6 + threadIdx.x] = 0.5f * l + 0.5f * h;
+    box[b * 6 + 3 + threadIdx.x] = (0.5f * h - 0.5f * l) + pad;   // NaN (all-NaN super-tile) keeps every camera
+  }
+  if (threadIdx.x == 0) {
+    pt_off[b] = p0;
+    if (b == (int)gridDim.x - 1) pt_off[b + 1] = n;
+  }
+}
+
+// FILL = false: counts[b]; FILL = true: cam_idx[cam_off[b] ...] ascending.
+template <bool FILL>
+__global__ void __launch_bounds__(256) cov_cull_kernel(
+    const float* __restrict__ cameras, int32_t cam_first, int32_t cam_count, const float* __restrict__ box,
+    int64_t* __restrict__ counts, const int64_t* __restrict__ cam_off, int32_t* __restrict__ cam_idx) {
+  __shared__ int sm[33];
+  __shared__ float sbox[6];
+  const int b = blockIdx.x;
+  if (threadIdx.x < 6) sbox[threadIdx.x] = box[b * 6 + threadIdx.x];
+  __syncthreads();
+  int64_t out = FILL ? cam_off[b] : 0;
+  int total = 0;
+  for (int s0 = 0; s0 < cam_count; s0 += 256) {
+    const int j = s0 + threadIdx.x;
+    int f = 0;
+    if (j < cam_count) {
+      float rec[kCamFloats];
+#pragma unroll
+      for (int q = 0; q < kCamFloats / 4; ++q)
+        reinterpret_cast<float4*>(rec)[q] =
+            __ldg(reinterpret_cast<const float4*>(cameras + (int64_t)(cam_first + j) * kCamFloats) + q);
+      f = tile_may_hit(load_cam(rec), sbox) ? 1 : 0;
+    }
+    int tot;
+    const int ex = block_exclusive_sum<int, 256>(f, sm, &tot);
+    if (FILL && f) cam_idx[out + ex] = cam_first + j;
+    out += tot;
+    total += tot;
+    __syncthreads();
+  }
+  if (!FILL && threadIdx.x == 0) counts[b] = total;
+}
+
+__global__ void __launch_bounds__(1024) cov_offsets_kernel(const int64_t* __restrict__ counts, int B,
+                                                           int64_t* __restrict__ cam_off) {
+  __shared__ long long sm[33];
+  long long carry = 0;
+  for (int s = 0; s < B; s += 1024) {
+    const int i = s + threadIdx.x;
+    const long long v = i < B ? counts[i] : 0;
+    long long tot;
+    const long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
+    if (i < B) cam_off[i] = carry + ex;
+    carry += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) cam_off[B] = carry;
+}
+
+__global__ void __launch_bounds__(256) cov_scatter_kernel(
+    const int32_t* __restrict__ pair_hits, const int32_t* __restrict__ cam_idx,
+    const int64_t* __restrict__ cam_off, int B, int32_t cam_first, int32_t* __restrict__ n_hit) {
+  const int64_t P = cam_off[B];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += stride) {
+    const int32_t h = pair_hits[p];
+    if (h) atomicAdd(n_hit + (cam_idx[p] - cam_first), h);
+  }
+}
+
+struct CovPlan {
+  int64_t S;        // points per super-tile
+  int32_t B;        // super-tiles
+  size_t bytes;     // workspace of the super-tile path
+};
+static CovPlan coverage_plan(int64_t n, int32_t cam_count) {
+  CovPlan c;
+  int64_t S = (n + kSwMaxBlocks - 1) / kSwMaxBlocks;
+  if (S < 16384) S = 16384;
+  S = (S + kSwTile - 1) / kSwTile * kSwTile;
+  c.S = S;
+  c.B = (int32_t)((n + S - 1) / S);
+  if (c.B < 1) c.B = 1;
+  const size_t pairs = (size_t)c.B * (size_t)(cam_count > 0 ? cam_count : 1);
+  c.bytes = align_up((size_t)(c.B + 2) * 8, 256) * 4 + align_up((size_t)c.B * 24, 256) +
+            2 * align_up(pairs * 4, 256) + 1024;
+  return c;
+}
+
 // ---- host side -----------------------------------------------------------------
 template <int MODE>
 static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
   static_assert(sizeof(SweepSmem) < 112 * 1024, "two CTAs per SM");
   PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(SweepSmem)));
-  sweep_kernel<MODE><<<kNumSMs * 2, kSwThreads, sizeof(SweepSmem), st>>>(a);
+  // `prefix` is the last member: only the entries of this launch's blocks are allocated, which is
+  // what lets kSwCtasPerSM CTAs fit one SM for the usual block counts
+  const size_t smem = offsetof(SweepSmem, prefix) + (size_t)(a.n_blocks + 1) * sizeof(int64_t);
+  sweep_kernel<MODE><<<kNumSMs * kSwCtasPerSM, kSwThreads, smem, st>>>(a);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
@@ -1593,7 +1723,7 @@ static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
 static int schedule(const int64_t* pt_offsets, const int64_t* cam_offsets, int32_t L,
                     int32_t cam_split, int64_t* item_prefix, cudaStream_t st) {
   sweep_schedule_kernel<<<1, 1024, 0, st>>>(pt_offsets, cam_offsets, L, cam_split, item_prefix,
-                                            kNumSMs * 2);
+                                            kNumSMs * kSwCtasPerSM);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
@@ -1795,6 +1925,40 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64
     set_error("coverage_sweep: workspace too small");
     return PTGS_E_WORKSPACE;
   }
+  const CovPlan plan = coverage_plan(n, cam_count);
+  if (cam_count > 2 * kSwCamChunk && workspace_bytes >= plan.bytes) {
+    // many cameras: per super-tile camera lists first (see cov_*_kernel)
+    Carver cv(workspace);
+    const int B = plan.B;
+    int64_t* pt_off = cv.take<int64_t>(B + 2);
+    int64_t* counts = cv.take<int64_t>(B + 2);
+    int64_t* cam_off = cv.take<int64_t>(B + 2);
+    int64_t* item_prefix = cv.take<int64_t>(B + 2);
+    float* box = cv.take<float>((size_t)B * 6);
+    int32_t* cam_idx = cv.take<int32_t>((size_t)B * cam_count);
+    int32_t* pair_hits = cv.take<int32_t>((size_t)B * cam_count);
+    cov_box_kernel<<<B, 256, 0, st>>>(px, py, pz, n, plan.S, pt_off, box);
+    PTGS_LAUNCH_CHECK();
+    cov_cull_kernel<false><<<B, 256, 0, st>>>(cameras, cam_first, cam_count, box, counts, nullptr, nullptr);
+    PTGS_LAUNCH_CHECK();
+    cov_offsets_kernel<<<1, 1024, 0, st>>>(counts, B, cam_off);
+    PTGS_LAUNCH_CHECK();
+    cov_cull_kernel<true><<<B, 256, 0, st>>>(cameras, cam_first, cam_count, box, nullptr, cam_off, cam_idx);
+    PTGS_LAUNCH_CHECK();
+    PTGS_CUDA_TRY(cudaMemsetAsync(pair_hits, 0, (size_t)B * cam_count * 4, st));
+    int rc = schedule(pt_off, cam_off, B, 1, item_prefix, st);
+    if (rc) return rc;
+    SweepArgs a = {};
+    a.px = px; a.py = py; a.pz = pz; a.pt_offsets = pt_off; a.n_blocks = B;
+    a.cameras = cameras; a.cam_offsets = cam_off; a.cam_index = cam_idx; a.cam_first = 0;
+    a.cam_split = 1; a.item_prefix = item_prefix;
+    a.n_hit = pair_hits; a.seen = seen;
+    rc = launch_sweep<0>(a, st);
+    if (rc) return rc;
+    cov_scatter_kernel<<<kNumSMs * 4, 256, 0, st>>>(pair_hits, cam_idx, cam_off, B, cam_first, n_hit);
+    PTGS_LAUNCH_CHECK();
+    return PTGS_OK;
+  }
   int64_t* ws = (int64_t*)workspace;
   coverage_setup_kernel<<<1, 1, 0, st>>>(n, cam_count, ws, ws + 2);
   PTGS_LAUNCH_CHECK();
@@ -1811,6 +1975,13 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz, int64
   a.cam_split = (int32_t)split; a.item_prefix = ws + 4;
   a.n_hit = n_hit; a.seen = seen;
   return launch_sweep<0>(a, st);
+}
+
+size_t ptgs_coverage_workspace_bytes(int64_t n, int32_t cam_count) {
+  const size_t direct = ptgs_visibility_workspace_bytes(1);
+  if (n <= 0 || cam_count <= 2 * kSwCamChunk) return direct;
+  const size_t b = coverage_plan(n, cam_count).bytes;
+  return b > direct ? b : direct;
 }
 
 }  // extern "C"

@@ -498,6 +498,10 @@ def select_cameras(keep, cam_offsets, cam_index, want_pos=False, sync=True):
     return (kept_off, kept_idx[:n], kept_pos[:n]) if want_pos else (kept_off, kept_idx[:n])
 
 
+# per super-tile camera lists in ptgs_coverage_sweep (selected by the workspace size)
+COVERAGE_SUPERTILES = False
+
+
 def spatial_order(px, py, pz):
     """Morton-ordered copy of a planar float32 cloud + the permutation
     (sorted[i] = input[perm[i]]); ptgs_spatial_order."""
@@ -531,7 +535,8 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
         px, py, pz, perm = spatial_order(px, py, pz)
     n_hit = torch.empty(max(cam_count, 1), dtype=torch.int32, device=dev)
     seen = torch.empty(max(n, 1), dtype=torch.uint8, device=dev) if want_seen else None
-    ws = _ws(lib.ptgs_visibility_workspace_bytes(1), dev)
+    ws = _ws(lib.ptgs_coverage_workspace_bytes(n, int(cam_count)) if COVERAGE_SUPERTILES
+             else lib.ptgs_visibility_workspace_bytes(1), dev)
     check(lib.ptgs_coverage_sweep(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(cameras_d), int(cam_first),
                                   int(cam_count), _ptr(n_hit), _ptr(seen), _ptr(ws), ws.numel(), _stream()))
     if want_seen and perm is not None and n > 0:

@@ -411,8 +411,15 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
  * camera cam_first..cam_first+cam_count-1; n_hit[cam_count] int32 (must be
  * zeroed by the caller... it is zeroed by the call); optional seen[n] uint8
  * (may be NULL): 1 when any camera of the range sees the point.
- * workspace: ptgs_visibility_workspace_bytes(1) bytes.
+ * workspace: ptgs_coverage_workspace_bytes(n, cam_count) bytes.  With more
+ * than a few hundred cameras the call first builds, per super-tile of the
+ * cloud (<= 1024 runs of consecutive points), the list of cameras whose
+ * frustum can meet the run's bounding box, and sweeps each run against its
+ * list only -- effective when the cloud is in spatial order
+ * (ptgs_spatial_order); a workspace of only ptgs_visibility_workspace_bytes(1)
+ * bytes selects the direct every-tile-by-every-camera sweep.
  * ------------------------------------------------------------------ */
+size_t ptgs_coverage_workspace_bytes(int64_t n, int32_t cam_count);
 int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
                         int64_t n, const float* cameras, int32_t cam_first,
                         int32_t cam_count, int32_t* n_hit, uint8_t* seen,

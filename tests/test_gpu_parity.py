@@ -405,3 +405,22 @@ def test_expand_grid_path_equals_lockstep(f64):
             (pts[:, 1] >= dt(boxes[b, 1])) & (pts[:, 1] <= dt(boxes[b, 3]))
         assert np.array_equal(idx[off[b]:off[b + 1]], np.nonzero(m)[0]), b
     assert off[-1] > n // 2
+
+
+def test_coverage_sweep_many_cameras_supertile_lists():
+    """More than 320 cameras: ptgs_coverage_sweep builds per super-tile camera lists first.
+    Counts, seen flags and a camera sub-range against the oracle, in file and Morton order."""
+    sc = small_scene(n=90001, c=420, thr=50000, seed=53, oblique_fraction=0.3)
+    cams = scene_cameras(sc)
+    recs = D.camera_records(cams.R, cams.T, cams.FoVx, cams.FoVy, cams.width, cams.height)
+    recs[::2, 18] = 2.0
+    x, y, z = D.aos_to_soa(_dev_xyz(sc))
+    cams_d = torch.from_numpy(recs).to(DEV)
+    want, wseen = O.coverage_counts(sc.xyz, recs, want_seen=True)
+    for order in (True, False):
+        n_hit, seen = D.coverage_sweep(x, y, z, cams_d, want_seen=True, spatial_order_points=order)
+        assert np.array_equal(n_hit.cpu().numpy(), want)
+        assert np.array_equal(seen.cpu().numpy().astype(bool), wseen)
+    part = D.coverage_sweep(x, y, z, cams_d, cam_first=17, cam_count=380)
+    assert np.array_equal(part.cpu().numpy(), want[17:397])
+    assert want.sum() > 10000 and (want == 0).sum() < len(want)
