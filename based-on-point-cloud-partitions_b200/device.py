@@ -499,7 +499,7 @@ def select_cameras(keep, cam_offsets, cam_index, want_pos=False, sync=True):
 
 
 # per super-tile camera lists in ptgs_coverage_sweep (selected by the workspace size)
-COVERAGE_SUPERTILES = False
+COVERAGE_SUPERTILES = True
 
 
 def spatial_order(px, py, pz):
