@@ -4,8 +4,8 @@
 // scene/ptgs/data_partition.py:385-424, :505) gets its points in file order.
 // The sweep culls cameras per 2048-point tile and per 256-point warp run, which
 // only works when consecutive points are neighbours in space: this pass sorts
-// the cloud by the Morton code of a 2^16-cell-per-axis cubic grid over its
-// bounding box (one cell size for all axes) and returns the permutation, so
+// the cloud by a 32-bit Morton-type code of a cubic-cell grid over its bounding
+// box (2048 cells along the longest axis, one cell size for all axes) and returns the permutation, so
 // per-point outputs can be written back in the caller's order.  The order only
 // affects speed: hit counts and seen flags do not depend on it.
 #include <cub/device/device_radix_sort.cuh>
@@ -14,7 +14,7 @@
 
 namespace ptgs {
 
-constexpr int kOrderBits = 16;   // per axis -> 48-bit keys, 6 radix passes
+constexpr int kOrderKeyBits = 32;   // 4 radix passes on 32-bit keys
 
 __global__ void __launch_bounds__(256) order_minmax_kernel(
     const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z, int64_t n,
@@ -49,28 +49,34 @@ __global__ void __launch_bounds__(256) order_minmax_kernel(
   }
 }
 
-// bit i of v -> bit 3 i
-__device__ __forceinline__ uint64_t spread3(uint32_t v) {
-  uint64_t x = v & 0x1fffffu;
-  x = (x | (x << 32)) & 0x1f00000000ffffull;
-  x = (x | (x << 16)) & 0x1f0000ff0000ffull;
-  x = (x | (x << 8)) & 0x100f00f00f00f00full;
-  x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
-  x = (x | (x << 2)) & 0x1249249249249249ull;
+// bit i of v (10 bits) -> bit 3 i
+__device__ __forceinline__ uint32_t spread3_10(uint32_t v) {
+  uint32_t x = v & 0x3ffu;
+  x = (x | (x << 16)) & 0x030000ffu;
+  x = (x | (x << 8)) & 0x0300f00fu;
+  x = (x | (x << 4)) & 0x030c30c3u;
+  x = (x | (x << 2)) & 0x09249249u;
   return x;
 }
 
+// 32-bit key: cubic cells of (largest extent / 2048); 11 bits for the two longer axes, 10 for the
+// shortest (clamped).  Top two bits = the high bits of the two longer axes, then a 3-D Morton code.
 __global__ void __launch_bounds__(256) order_key_kernel(
     const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z, int64_t n,
-    const uint32_t* __restrict__ mm, uint64_t* __restrict__ keys, uint32_t* __restrict__ idx) {
-  float lo[3], ext = 0.0f;
+    const uint32_t* __restrict__ mm, uint32_t* __restrict__ keys, uint32_t* __restrict__ idx) {
+  float lo[3], e[3], ext = 0.0f;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     lo[a] = KeyOf<float>::decode(mm[a]);
-    const float e = KeyOf<float>::decode(mm[3 + a]) - lo[a];
-    ext = (e > ext) ? e : ext;               // empty axis: +inf - (-inf) is never > ext ... NaN compares false
+    e[a] = KeyOf<float>::decode(mm[3 + a]) - lo[a];
+    if (!(e[a] >= 0.0f)) e[a] = 0.0f;        // empty axis (no finite value)
+    ext = (e[a] > ext) ? e[a] : ext;
   }
-  const float cells = (float)(1u << kOrderBits);
+  int small = 0;                              // shortest axis
+  if (e[1] < e[small]) small = 1;
+  if (e[2] < e[small]) small = 2;
+  const int a0 = (small == 0) ? 1 : 0, a1 = (small == 2) ? 1 : 2;   // the two longer axes
+  const float cells = 2048.0f;
   const float inv = (ext > 0.0f && ext < __int_as_float(0x7f800000)) ? cells / ext : 0.0f;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -80,9 +86,11 @@ __global__ void __launch_bounds__(256) order_key_kernel(
     for (int a = 0; a < 3; ++a) {
       const float f = (v[a] - lo[a]) * inv;
       const float g = (f >= 0.0f) ? f : 0.0f;                     // NaN, -inf -> cell 0
-      c[a] = (g < cells) ? (uint32_t)g : ((1u << kOrderBits) - 1);
+      c[a] = (g < cells) ? (uint32_t)g : 2047u;
     }
-    keys[i] = spread3(c[0]) | (spread3(c[1]) << 1) | (spread3(c[2]) << 2);
+    const uint32_t cs = c[small] > 1023u ? 1023u : c[small];
+    keys[i] = ((c[a0] >> 10) << 31) | ((c[a1] >> 10) << 30) | spread3_10(c[a0] & 1023u) |
+              (spread3_10(c[a1] & 1023u) << 1) | (spread3_10(cs) << 2);
     idx[i] = (uint32_t)i;
   }
 }
@@ -108,9 +116,9 @@ __global__ void __launch_bounds__(256) unpermute_u8_kernel(
 
 static size_t order_sort_temp_bytes(int64_t n) {
   size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                   (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0,
-                                  3 * kOrderBits);
+                                  kOrderKeyBits);
   return bytes;
 }
 
@@ -130,7 +138,7 @@ extern "C" {
 size_t ptgs_spatial_order_workspace_bytes(int64_t n) {
   if (n < 1) n = 1;
   size_t b = 512;
-  b += 2 * align_up((size_t)n * 8, 256);      // keys in / out
+  b += 2 * align_up((size_t)n * 4, 256);      // keys in / out
   b += align_up((size_t)n * 4, 256);          // identity index
   b += align_up(order_sort_temp_bytes(n), 256) + 4096;
   return b;
@@ -149,8 +157,8 @@ int ptgs_spatial_order(const float* px, const float* py, const float* pz, int64_
   cudaStream_t st = (cudaStream_t)stream;
   Carver cv(workspace);
   uint32_t* mm = cv.take<uint32_t>(8);
-  uint64_t* keys_a = cv.take<uint64_t>(n);
-  uint64_t* keys_b = cv.take<uint64_t>(n);
+  uint32_t* keys_a = cv.take<uint32_t>(n);
+  uint32_t* keys_b = cv.take<uint32_t>(n);
   uint32_t* idx_a = cv.take<uint32_t>(n);
   size_t tb = order_sort_temp_bytes(n);
   void* sort_tmp = cv.take<char>(tb);
@@ -162,8 +170,8 @@ int ptgs_spatial_order(const float* px, const float* py, const float* pz, int64_
   order_key_kernel<<<g, 256, 0, st>>>(px, py, pz, n, mm, keys_a, idx_a);
   PTGS_LAUNCH_CHECK();
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, perm,
-                                                (int64_t)n, 0, 3 * kOrderBits, st));
-  count_launch(2 + (3 * kOrderBits + 7) / 8);
+                                                (int64_t)n, 0, kOrderKeyBits, st));
+  count_launch(2 + (kOrderKeyBits + 7) / 8);
   order_gather_kernel<<<g, 256, 0, st>>>(px, py, pz, perm, n, sx, sy, sz);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;

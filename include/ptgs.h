@@ -429,8 +429,9 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
 /* ------------------------------------------------------------------ *
  * Spatial order for the coverage sweep (the Vast path's cloud arrives in file
  * order; scene/ptgs/data_partition.py:505 projects all of it per camera).
- * Sorts the planar float32 cloud by the 3-D Morton code of a 2^16-cells-per-
- * axis cubic grid over its bounding box: sx/sy/sz[n] = the points in that
+ * Sorts the planar float32 cloud by a 32-bit Morton-type code of a cubic-cell
+ * grid over its bounding box (2048 cells along the longest axis; 4 radix
+ * passes): sx/sy/sz[n] = the points in that
  * order, perm[n] uint32 = their indices in the input (n < 2^32).  Only the
  * speed of ptgs_coverage_sweep depends on the order, never its results.
  * ptgs_unpermute_u8: dst[perm[i]] = src[i] (per-point flags back to the
