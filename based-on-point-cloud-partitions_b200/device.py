@@ -894,7 +894,9 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
                 part[0] = visibility(*part[3], threshold=threshold)
     if world <= 1:
         # kept-camera lists per group, one round of D2H at the end
-        k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1, np.int64)], [], [], [], [], []
+        # kept_offsets has L + 1 entries whatever blocks were skipped: blocks before bl0 / after bl1
+        # have no cameras (searchsorted above) and repeat the running total
+        k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1 + bl0, np.int64)], [], [], [], [], []
         sel = [select_cameras(p[0].keep, p[4], p[5], sync=False) for p in parts]
         base = 0
         for (vis, ds_off, nb, _a, _c, _i), (k_off, k_idx) in zip(parts, sel):
@@ -905,6 +907,7 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
             nh.append(vis.n_hit.cpu().numpy()); rt.append(vis.ratio.cpu().numpy())
             kp.append(vis.keep.cpu().numpy()); fl.append(vis.flags.cpu().numpy())
             n_ds += int(ds_off[nb].item())
+        k_offs.append(np.full(L - bl1, base, np.int64))
         cat = lambda xs, dt: np.concatenate(xs) if xs else np.zeros(0, dt)
         out = (np.concatenate(k_offs), cat(k_idxs, np.int32), cat(nh, np.int32), cat(rt, np.float64),
                cat(kp, np.uint8), cat(fl, np.uint8))

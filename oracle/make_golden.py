@@ -20,6 +20,7 @@ Reference entry points executed (file:line under /root/reference):
   project_points_to_camera       scene/ptgs/shen_partation_densify.py:410
   run_graham_scan                scene/ptgs/shen_partation_densify.py:481
   visibility_based_camera_selection  scene/ptgs/shen_partation_densify.py:911
+  fetchPly (Manhattan rotation)  scene/ptgs/shen_data_read.py:120-133
 """
 from __future__ import annotations
 
@@ -207,6 +208,124 @@ def selection_case(ref):
     return d
 
 
+class _FakePly:
+    """Stand-in for plyfile.PlyData in shen_data_read.fetchPly (the module is absent here): .read()
+    returns the vertex columns of an in-memory cloud, so the reference's own Manhattan formula
+    (shen_data_read.py:126-130) runs unchanged."""
+    cloud = None
+
+    @classmethod
+    def read(cls, path):
+        xyz, rgb = cls.cloud
+        z = np.zeros(len(xyz), np.float32)
+        return {"vertex": {"x": xyz[:, 0], "y": xyz[:, 1], "z": xyz[:, 2], "red": rgb[:, 0], "green": rgb[:, 1],
+                           "blue": rgb[:, 2], "nx": z, "ny": z, "nz": z}}
+
+
+def ref_fetch_ply(ref, xyz, rgb, man_trans):
+    """fetchPly (scene/ptgs/shen_data_read.py:120-133) on an in-memory cloud."""
+    import contextlib
+    import io
+    mod = ref.shen_data_read
+    orig = mod.PlyData
+    _FakePly.cloud = (xyz, rgb)
+    mod.PlyData = _FakePly
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            return mod.fetchPly("in-memory", man_trans=man_trans)
+    finally:
+        mod.PlyData = orig
+
+
+def _selection_run(ref, split_p64, pcd, rcams, sc):
+    """run_DataPartition's steps 2-5 (utils-shen:65-91) with the reference's functions: bounds and
+    split on `split_p64` (what open3d read from the PLY), expansion / assignment / selection on `pcd`
+    (self.pcd).  No radius filter (open3d is absent).  Returns plain arrays."""
+    b = O.bounds_xy(split_p64)
+    parts = ref.densify.quad_tree_partition(split_p64, _rect(b), THR_MAN)
+    leaf_bounds = np.array([p.origin_box.bounds for p in parts], np.float64)
+    leaf_num = np.array([p.point_num for p in parts], np.int64)
+    parts = ref.densify.expand_partitions(parts, pcd)
+    pts = pcd.points
+    idx_lists = []
+    for e in parts:
+        minx, miny, maxx, maxy = e.extend_box.bounds
+        m = (pts[:, 0] >= minx) & (pts[:, 0] <= maxx) & (pts[:, 1] >= miny) & (pts[:, 1] <= maxy)
+        assert np.array_equal(pts[m], e.point_cloud.points)
+        idx_lists.append(np.nonzero(m)[0])
+    parts = ref.densify.assign_cameras_to_partitions(parts, rcams)
+    assigned = [[cp.camera.uid for cp in p.camera] for p in parts]
+    n_hit, rate, ds_all = [], [], []
+    for p in parts:
+        ds = ref.densify.downsample_point_cloud(p.point_cloud, 0.1).points
+        ds_all.append(ds)
+        for cp in p.camera:
+            uv = ref.densify.project_points_to_camera(ds, cp.camera)
+            k = len(uv)
+            n_hit.append(k if not isinstance(uv, tuple) else 0)
+            if k <= 3 or isinstance(uv, tuple):
+                rate.append(0.0)
+            else:
+                rate.append(float(ref.densify.run_graham_scan(uv, cp.camera.image_width,
+                                                              cp.camera.image_height)["intersection_rate"]))
+    with tempfile.TemporaryDirectory() as tmp:
+        vis_dir = os.path.join(tmp, "model", "split_result", "visible")
+        os.makedirs(vis_dir)
+        os.makedirs(os.path.join(tmp, "images"))
+        from ptgs_b200 import colmap_io
+        colmap_io.write_synthetic_colmap(sc, tmp)
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            out = ref.densify.visibility_based_camera_selection(parts, vis_dir, pcd, max_workers=4)
+    p_off, p_idx = _ragged(idx_lists, np.int64)
+    a_off, a_idx = _ragged(assigned, np.int64)
+    k_off, k_idx = _ragged([sorted(cp.camera.uid for cp in p.camera) for p in out], np.int64)
+    d_off, d_pts = _ragged([d.reshape(-1) for d in ds_all], np.float32)
+    return dict(ids=_ids(out), root=np.asarray(b, np.float64), leaf_bounds=leaf_bounds, leaf_num=leaf_num,
+                extend_bounds=np.array([p.extend_box.bounds for p in out], np.float64),
+                point_num=np.array([p.point_num for p in out], np.int64), pt_offsets=p_off, pt_index=p_idx,
+                cam_offsets=a_off, cam_index=a_idx, kept_offsets=k_off, kept_index=k_idx,
+                ds_offsets=d_off // 3, ds_points=d_pts.reshape(-1, 3),
+                n_hit=np.array(n_hit, np.int64), rate=np.array(rate, np.float64))
+
+
+THR_MAN = 3000
+
+
+def manhattan_case(ref):
+    """A13: the cloud rotated by the reference's fetchPly (float64 from there on), then A3-A9 by the
+    reference's functions under both semantics of SURVEY.md row A13:
+      consistent_*  cameras W2C @ inv(man_trans) (scene/dataset_readers.py:96-104), split on the rotated cloud;
+      literal_*     the shen path as written: cameras un-rotated (shen_data_read.py:62-70 is commented
+                    out), split on the UN-rotated PLY that open3d re-reads (utils-shen:62), expansion
+                    and visibility on the rotated self.pcd (utils-shen:86, :91).
+    Also pins A6 on a float64 cloud (densify:572-605 with f64 arithmetic, f32 cast at :605)."""
+    from ptgs_b200 import scene_synth
+    orig = ref.densify.project_points_to_camera
+    ref.densify.project_points_to_camera = lambda points, camera, device="cpu": orig(points, camera, device="cpu")
+    try:
+        sc = scene_synth.make_scene(14000, 20, THR_MAN, seed=18, height_scale=10.0, oblique_fraction=0.3,
+                                    manhattan_deg=21.0)
+        man = sc.man_trans
+        pcd = ref_fetch_ply(ref, sc.xyz, sc.rgb, man)
+        assert pcd.points.dtype == np.float64
+        cams = scene_cameras(sc)
+        Rm, Tm = O.manhattan_cameras(cams.R, cams.T, man)
+        mk = lambda R, T: [H.make_simple_camera(ref, i, i + 1, R[i], T[i], float(cams.FoVx[i]), float(cams.FoVy[i]),
+                                                "img_%06d" % i, sc.width, sc.height) for i in range(len(R))]
+        d = dict(points=sc.xyz, rgb=sc.rgb, man_trans=man, threshold=np.int64(THR_MAN), rotated=pcd.points,
+                 R_rot=Rm, T_rot=Tm)
+        d.update(_cam_arrays(cams))
+        for k, v in _selection_run(ref, pcd.points.astype(np.float64), pcd, mk(Rm, Tm), sc).items():
+            d["consistent_" + k] = v
+        for k, v in _selection_run(ref, sc.xyz.astype(np.float64), pcd, mk(cams.R, cams.T), sc).items():
+            d["literal_" + k] = v
+    finally:
+        ref.densify.project_points_to_camera = orig
+    return d
+
+
 def vast_case(ref):
     """A14: the reference's camera-grid partitioner (scene/ptgs/data_partition.py), run unchanged."""
     from types import SimpleNamespace
@@ -248,6 +367,7 @@ def main():
     np.savez_compressed(os.path.join(GOLDEN, "graham.npz"), **graham_cases(ref))
     np.savez_compressed(os.path.join(GOLDEN, "selection.npz"), **selection_case(ref))
     np.savez_compressed(os.path.join(GOLDEN, "vast.npz"), **vast_case(ref))
+    np.savez_compressed(os.path.join(GOLDEN, "manhattan.npz"), **manhattan_case(ref))
     for f in sorted(os.listdir(GOLDEN)):
         print("%-28s %8d B" % (f, os.path.getsize(os.path.join(GOLDEN, f))))
 

@@ -440,12 +440,17 @@ class PartitionResult(NamedTuple):
 
 
 def run_partition(points, cams: CameraSet, threshold, centers=None,
-                  radius_filter=True, visibility=True, front_axis=1):
+                  radius_filter=True, visibility=True, front_axis=1, split_points=None):
     """utils-shen:57-93 (run_DataPartition) without plotting and file output.
     `points` is the scene cloud as fetchPly returns it (float32, or float64
-    under a Manhattan transform)."""
+    under a Manhattan transform) = self.pcd, which A4 (utils-shen:86) and A6-A9
+    (:91) read.  `split_points` (default: `points`) is what A1-A3 read: the
+    reference re-reads the PLY with open3d (utils-shen:62, self.ply), which is
+    the UN-rotated float32 cloud even when fetchPly rotated self.pcd
+    (shen_data_read.py:126-130) -- the literal shen-path behaviour under
+    man_trans."""
     points = np.asarray(points)
-    p64 = points.astype(np.float64)                  # o3d.io.read_point_cloud -> f64
+    p64 = np.asarray(points if split_points is None else split_points).astype(np.float64)   # o3d.io.read_point_cloud -> f64
     keep_mask = radius_outlier_mask(p64) if radius_filter else np.ones(len(p64), bool)
     filt = p64[keep_mask]
     root = bounds_xy(filt)

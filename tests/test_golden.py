@@ -117,6 +117,51 @@ def test_oracle_selection():
     assert 0 < kept < int(g["cam_offsets"][-1])
 
 
+def _man_cams(g, sem):
+    """Camera arrays of the fixture's semantic: consistent = W2C @ inv(man_trans), literal = as read."""
+    if sem == "consistent":
+        return O.CameraSet(g["R_rot"], g["T_rot"], g["FoVx"], g["FoVy"], g["width"], g["height"])
+    return _camset(g)
+
+
+def test_oracle_manhattan_rotation():
+    """oracle.manhattan_points / manhattan_cameras == the reference's fetchPly output
+    (shen_data_read.py:126-130, float64) and dataset_readers.py:96-104."""
+    g = _load("manhattan")
+    rot = O.manhattan_points(g["points"], g["man_trans"])
+    assert rot.dtype == np.float64 and np.array_equal(rot, g["rotated"])
+    Rm, Tm = O.manhattan_cameras(g["R"], g["T"], g["man_trans"])
+    assert np.array_equal(Rm, g["R_rot"]) and np.array_equal(Tm, g["T_rot"])
+
+
+@pytest.mark.parametrize("sem", ["consistent", "literal"])
+def test_oracle_manhattan_selection(sem):
+    """A3-A9 on a float64 (Manhattan-rotated) cloud against the reference's own run, under both
+    semantics of SURVEY.md A13 (literal: split on the un-rotated PLY, utils-shen:62 vs :86)."""
+    g = _load("manhattan")
+    k = lambda name: g[sem + "_" + name]
+    rot = g["rotated"]
+    split = rot if sem == "consistent" else g["points"]
+    res = O.run_partition(rot, _man_cams(g, sem), int(g["threshold"]), radius_filter=False, split_points=split)
+    assert res.root_bounds == tuple(k("root").tolist())
+    assert [l.partition_id for l in res.leaves] == k("ids").tolist()
+    assert np.array_equal(np.array([l.bounds for l in res.leaves]), k("leaf_bounds"))
+    assert [l.point_num for l in res.leaves] == k("leaf_num").tolist()
+    assert np.array_equal(np.array(res.boxes), k("extend_bounds"))
+    for got, w in zip(res.block_index, _lists(k("pt_offsets"), k("pt_index"))):
+        assert np.array_equal(got, w)
+    for got, w in zip(res.cam_index, _lists(k("cam_offsets"), k("cam_index"))):
+        assert np.array_equal(got, w)
+    # A6 on float64 input: float32 bit patterns, first-occurrence order (densify:572-605)
+    for got, w in zip(res.ds_points, _lists(k("ds_offsets"), k("ds_points"))):
+        assert got.dtype == np.float32 and np.array_equal(got.view(np.uint32), w.view(np.uint32))
+    assert np.array_equal(np.concatenate(res.n_hit), k("n_hit"))
+    np.testing.assert_allclose(np.concatenate(res.ratio), k("rate"), rtol=1e-12, atol=1e-15)
+    for got, w in zip(res.kept_cameras, _lists(k("kept_offsets"), k("kept_index"))):
+        assert sorted(got.tolist()) == w.tolist()
+    assert 0 < int(k("kept_offsets")[-1]) < int(k("cam_offsets")[-1])
+
+
 def test_golden_output_layout():
     """The reference's on-disk layout for the selection fixture (A10)."""
     g = _load("selection")
@@ -221,4 +266,54 @@ def test_cuda_selection():
         koff = res.kept_offsets.cpu().numpy()
         kidx = res.kept_index.cpu().numpy().astype(np.int64)
         for got, w in zip(_lists(koff, kidx), _lists(g["kept_offsets"], g["kept_index"])):
+            assert sorted(got.tolist()) == w.tolist()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sem", ["consistent", "literal"])
+def test_cuda_manhattan(sem):
+    """partition_device(man_trans=...) -- float64 cloud from A13 on: Manhattan kernel, f64 split /
+    expansion / voxel kernels, visibility -- against the reference's own run (tests/golden/manhattan.npz).
+    literal = split_xyz=<un-rotated cloud> and un-rotated cameras (the shen path as written)."""
+    import torch
+    from ptgs_b200 import device as D
+    g = _load("manhattan")
+    k = lambda name: g[sem + "_" + name]
+    cs = _man_cams(g, sem)
+    recs = D.camera_records(cs.R, cs.T, cs.FoVx, cs.FoVy, cs.width, cs.height)
+    centers = D.camera_centers(cs.R, cs.T)
+    xyz = torch.from_numpy(g["points"]).to(DEV)
+    x, y, z = D.manhattan_apply(*D.aos_to_soa(xyz), g["man_trans"])
+    got_rot = np.stack([x.cpu().numpy(), y.cpu().numpy(), z.cpu().numpy()], 1)
+    assert np.array_equal(got_rot, g["rotated"])
+    for exact in (True, False):
+        res = D.partition_device(xyz, recs, centers, int(g["threshold"]), man_trans=g["man_trans"],
+                                 radius_filter=False, exact_ratio=exact,
+                                 split_xyz=xyz if sem == "literal" else None)
+        assert res.root_bounds == tuple(k("root").tolist())
+        assert res.leaf_ids == k("ids").tolist()
+        assert np.array_equal(res.leaf_bounds, k("leaf_bounds"))
+        assert [int(c) for c in res.leaf_count] == k("leaf_num").tolist()
+        assert np.array_equal(res.boxes, k("extend_bounds"))
+        assert np.array_equal(res.pt_offsets.cpu().numpy(), k("pt_offsets"))
+        assert np.array_equal(res.pt_index.cpu().numpy().astype(np.int64), k("pt_index"))
+        assert np.array_equal(res.cam_offsets.cpu().numpy(), k("cam_offsets"))
+        assert np.array_equal(res.cam_index.cpu().numpy().astype(np.int64), k("cam_index"))
+        # A6 <double>: float32 bit patterns in the reference's first-occurrence order
+        ds_off = res.ds_offsets.cpu().numpy()
+        assert np.array_equal(ds_off, k("ds_offsets"))
+        ds = np.stack([res.ds_x.cpu().numpy(), res.ds_y.cpu().numpy(), res.ds_z.cpu().numpy()], 1)
+        first = res.ds_first.cpu().numpy()
+        for b in range(len(ds_off) - 1):
+            order = np.argsort(first[ds_off[b]:ds_off[b + 1]], kind="stable")
+            assert np.array_equal(ds[ds_off[b]:ds_off[b + 1]][order].view(np.uint32),
+                                  k("ds_points")[ds_off[b]:ds_off[b + 1]].view(np.uint32)), b
+        assert np.array_equal(res.vis.n_hit.cpu().numpy().astype(np.int64), k("n_hit"))
+        flags = res.vis.flags.cpu().numpy()
+        assert not (flags & 3).any()
+        if exact:
+            np.testing.assert_allclose(res.vis.ratio.cpu().numpy(), k("rate"), rtol=1e-12, atol=1e-15)
+        koff = res.kept_offsets.cpu().numpy()
+        kidx = res.kept_index.cpu().numpy().astype(np.int64)
+        for got, w in zip(_lists(koff, kidx), _lists(k("kept_offsets"), k("kept_index"))):
             assert sorted(got.tolist()) == w.tolist()

@@ -378,6 +378,103 @@ def test_full_partition_vs_oracle():
             assert set(g.tolist()) == set(w.tolist())
 
 
+def test_voxel_downsample_float64():
+    """vox_*_kernel<double>: the instantiation every Manhattan configuration (bench c2) runs.
+    Reference: densify:572-605 on a float64 cloud (shen_data_read.py:126-130)."""
+    sc = small_scene(n=50000, c=8, thr=9000, seed=32)
+    sc.xyz[:, 2] = np.round(sc.xyz[:, 2] * 2) / 2
+    sc.xyz[:, :2] = np.round(sc.xyz[:, :2] * 8) / 8
+    man = np.eye(4)
+    a = np.deg2rad(21.0)
+    man[:2, :2] = [[np.cos(a), -np.sin(a)], [np.sin(a), np.cos(a)]]
+    man[:3, 3] = [3.0, -1.5, 0.25]
+    x, y, z = D.manhattan_apply(*D.aos_to_soa(_dev_xyz(sc)), man)
+    pts = O.manhattan_points(sc.xyz, man)
+    assert x.dtype == torch.float64
+    assert np.array_equal(np.stack([x.cpu().numpy(), y.cpu().numpy(), z.cpu().numpy()], 1), pts)
+    boxes = np.array([[-30, -30, 5, 5], [0, 0, 40, 40], [100, 100, 101, 101], [-5, -5, 5, 5.0]])
+    off, idx = D.expand_select(x, y, boxes)
+    ds_off, dx, dy, dz, dfirst = D.voxel_downsample(x, y, z, off, idx)
+    assert dx.dtype == torch.float32
+    ds_off = ds_off.cpu().numpy()
+    got = np.stack([dx.cpu().numpy(), dy.cpu().numpy(), dz.cpu().numpy()], 1)
+    first = dfirst.cpu().numpy()
+    lists = _csr_lists(off, idx)
+    for b in range(len(boxes)):
+        want, wfirst = O.voxel_downsample(pts[lists[b]], return_first=True)
+        g = got[ds_off[b]:ds_off[b + 1]]
+        f = first[ds_off[b]:ds_off[b + 1]]
+        order = np.argsort(f, kind="stable")
+        assert len(g) == len(want)
+        assert np.array_equal(f[order], wfirst)
+        assert np.array_equal(g[order].view(np.uint32), want.view(np.uint32))
+    assert any(len(l) > 0 and ds_off[b + 1] - ds_off[b] < len(l) for b, l in enumerate(lists))
+
+
+def _assert_partition_equals_oracle(res, want, exact=True):
+    assert np.array_equal(res.keep_mask.cpu().numpy().astype(bool), want.keep_mask)
+    assert res.root_bounds == want.root_bounds
+    assert res.leaf_ids == [l.partition_id for l in want.leaves]
+    assert [tuple(b) for b in res.leaf_bounds.tolist()] == [l.bounds for l in want.leaves]
+    assert [int(c) for c in res.leaf_count] == [l.point_num for l in want.leaves]
+    assert [tuple(b) for b in res.boxes.tolist()] == list(want.boxes)
+    for g, w in zip(_csr_lists(res.pt_offsets, res.pt_index), want.block_index):
+        assert np.array_equal(g, w)
+    for g, w in zip(_csr_lists(res.cam_offsets, res.cam_index), want.cam_index):
+        assert np.array_equal(g, w)
+    # A6: float32 bit patterns per block in first-occurrence order
+    ds_off = res.ds_offsets.cpu().numpy()
+    ds = np.stack([res.ds_x.cpu().numpy(), res.ds_y.cpu().numpy(), res.ds_z.cpu().numpy()], 1)
+    first = res.ds_first.cpu().numpy()
+    for b, wd in enumerate(want.ds_points):
+        order = np.argsort(first[ds_off[b]:ds_off[b + 1]], kind="stable")
+        assert np.array_equal(ds[ds_off[b]:ds_off[b + 1]][order].view(np.uint32), wd.view(np.uint32)), b
+    assert np.array_equal(res.vis.n_hit.cpu().numpy(), np.concatenate(want.n_hit))
+    flags = res.vis.flags.cpu().numpy()
+    ok = (flags & 3) == 0
+    assert np.array_equal(res.vis.keep.cpu().numpy().astype(bool)[ok], np.concatenate(want.keep)[ok])
+    if exact:
+        np.testing.assert_allclose(res.vis.ratio.cpu().numpy()[ok], np.concatenate(want.ratio)[ok],
+                                   rtol=1e-12, atol=1e-15)
+    if ok.all():
+        for g, w in zip(_csr_lists(res.kept_offsets, res.kept_index), want.kept_cameras):
+            assert set(g.tolist()) == set(w.tolist())
+    return int(ok.sum())
+
+
+@pytest.mark.parametrize("semantic", ["consistent", "literal"])
+def test_full_partition_manhattan_vs_oracle(semantic):
+    """run_DataPartition under a Manhattan transform, A1-A9 end to end on a float64 cloud
+    (what bench config c2 times), against the oracle:
+      consistent  cloud and cameras rotated before A1 (SURVEY.md A13, the declared c2 semantic);
+      literal     the shen path as written -- A1-A3 on the un-rotated PLY (utils-shen:62),
+                  A4 / A6-A9 on the rotated self.pcd (:86, :91), cameras as read."""
+    sc = small_scene(n=160000, c=80, thr=25000, seed=62, manhattan_deg=21.0, height_scale=6.0)
+    man = sc.man_trans
+    cams = scene_cameras(sc)
+    rot = O.manhattan_points(sc.xyz, man)
+    if semantic == "consistent":
+        Rm, Tm = O.manhattan_cameras(cams.R, cams.T, man)
+        cams = O.CameraSet(Rm, Tm, cams.FoVx, cams.FoVy, cams.width, cams.height)
+        split_np, split_dev = rot, None
+    else:
+        split_np, split_dev = sc.xyz, _dev_xyz(sc)
+    recs = D.camera_records(cams.R, cams.T, cams.FoVx, cams.FoVy, cams.width, cams.height)
+    centers = D.camera_centers(cams.R, cams.T)
+    want = O.run_partition(rot, cams, sc.threshold, centers=centers, split_points=split_np)
+    assert len(want.leaves) >= 4 and sum(len(c) for c in want.cam_index) > 40
+    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, man_trans=man, split_xyz=split_dev,
+                             exact_ratio=True)
+    assert res.ds_x.dtype == torch.float32 and res.leaf_bounds.dtype == np.float64
+    n_ok = _assert_partition_equals_oracle(res, want)
+    assert n_ok > 40
+    kept = np.concatenate(want.keep)
+    assert 0 < kept.sum() < len(kept)
+    # default (bound-decided) mode: same cameras
+    res2 = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, man_trans=man, split_xyz=split_dev)
+    _assert_partition_equals_oracle(res2, want, exact=False)
+
+
 @pytest.mark.parametrize("f64", [False, True])
 def test_expand_grid_path_equals_lockstep(f64):
     """ptgs_expand_*_grid (cell-grid candidates) == ptgs_expand_* (every point x every rectangle),

@@ -162,3 +162,45 @@ def test_host_entry_rank_local_blocks(world):
     # after the last rank the table is complete: that call's outputs are the full result
     for a, b in zip(one, out):
         assert np.array_equal(a, b)
+
+
+def test_host_entry_offsets_cover_camera_less_blocks():
+    """Blocks without cameras at either end of the block list are skipped by the host entry
+    (nothing to upload), but kept_offsets still has one entry per block + 1 and lines up with the
+    global block index, for world 1 and world > 1 (device.py visibility_select_host)."""
+    w, recs, res = _scene_state()
+    x, y, z = D.aos_to_soa(torch.from_numpy(w.xyz).to(DEV))
+    idx = res.pt_index.to(torch.int64)
+    blocks = torch.stack([x[idx], y[idx], z[idx]], 1).contiguous().cpu()
+    blk_off = res.pt_offsets.cpu().numpy()
+    cam_off, cam_idx = res.cam_offsets.cpu().numpy().copy(), res.cam_index.cpu().numpy()
+    L = len(cam_off) - 1
+    cnt = np.diff(cam_off)
+    keep_pairs = np.ones(len(cam_idx), bool)
+    for b in (0, 1, L - 1):                                   # two leading and one trailing empty list
+        keep_pairs[cam_off[b]:cam_off[b + 1]] = False
+        cnt[b] = 0
+    cam_idx = np.ascontiguousarray(cam_idx[keep_pairs])
+    cam_off = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int64)
+    recs_t = torch.from_numpy(recs)
+    one, _ = D.visibility_select_host(blocks, blk_off, recs_t, cam_off, cam_idx, torch.device(DEV))
+    k_off, k_idx, n_hit, ratio, keep, flags = one
+    assert len(k_off) == L + 1 and k_off[0] == 0 and k_off[1] == 0 and k_off[2] == 0
+    assert k_off[L] == k_off[L - 1] == len(k_idx) == int(keep.sum())
+    # per block: the kept list is the block's camera list filtered by keep
+    for b in range(L):
+        sl = slice(cam_off[b], cam_off[b + 1])
+        assert np.array_equal(k_idx[k_off[b]:k_off[b + 1]], cam_idx[sl][keep[sl].astype(bool)]), b
+    P = len(cam_idx)
+    table = torch.zeros((P, M.REC_COLS), dtype=torch.float64, device=DEV)
+
+    def exchange(local, pos):
+        table[pos] = local
+        return table.clone()
+    out = None
+    for r in range(3):
+        out, _ = D.visibility_select_host(blocks, blk_off, recs_t, cam_off, cam_idx, torch.device(DEV),
+                                          rank=r, world=3, exchange=exchange)
+    assert len(out[0]) == L + 1
+    for a, b in zip(one, out):
+        assert np.array_equal(a, b)

@@ -102,6 +102,36 @@ def test_voxel_downsample(ref):
     assert np.array_equal(O.voxel_downsample_literal(pts).view(np.uint32), want.view(np.uint32))
 
 
+def test_voxel_downsample_float64(ref):
+    """Under man_trans self.pcd is float64 (shen_data_read.py:126-130): densify:572 divides and floors
+    in float64, :588-591 averages in float64, :605 casts the means to float32."""
+    rng = np.random.default_rng(6)
+    p32 = rng.uniform(-3, 9, (6000, 3)).astype(np.float32)
+    p32[:, :2] = np.round(p32[:, :2] * 8) / 8
+    a = np.deg2rad(21.0)
+    Rz = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1.0]])
+    pts = (Rz @ p32.T).T.copy()
+    assert pts.dtype == np.float64
+    pc = ref.BasicPointCloud(points=pts, colors=np.zeros_like(pts), normals=np.zeros_like(pts))
+    want = ref.densify.downsample_point_cloud(pc, 0.1).points
+    got = O.voxel_downsample(pts)
+    assert want.dtype == np.float32 and got.dtype == np.float32 and len(got) < len(pts)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_manhattan_fetchply(ref):
+    """oracle.manhattan_points == the reference's fetchPly (shen_data_read.py:120-133) on the same cloud."""
+    import make_golden as G
+    from ptgs_b200 import scene_synth
+    sc = small_scene(n=5000, c=4, thr=5000, seed=19)
+    man = scene_synth.manhattan_z(21.0)
+    man[:3, 3] = [0.5, -2.0, 3.25]
+    pcd = G.ref_fetch_ply(ref, sc.xyz, sc.rgb, man)
+    got = O.manhattan_points(sc.xyz, man)
+    assert pcd.points.dtype == np.float64 and np.array_equal(got, pcd.points)
+    assert np.array_equal(pcd.colors, sc.rgb / 255.0)
+
+
 def test_projection(ref):
     sc = small_scene(n=30000, c=12, thr=30000, seed=14, oblique_fraction=0.5)
     cams, rcams = _ref_cameras(ref, sc)
