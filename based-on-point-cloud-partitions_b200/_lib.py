@@ -14,6 +14,7 @@ PTGS_E_CAPACITY = -3
 PTGS_E_RANGE = -4
 CAMERA_FLOATS = 20
 POLY_FLOATS = 28
+PAIR_RECORD_BYTES = 24
 
 _vp, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t
 
@@ -63,6 +64,8 @@ SIGNATURES = {
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
                                        _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "ptgs_pack_records": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "ptgs_unpack_records": (C.c_int, [_vp, _i32, _i64, C.POINTER(_i64), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),
     "ptgs_spatial_order_workspace_bytes": (_sz, [_i64]),
     "ptgs_spatial_order": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libptgs.so")
-SOURCES = ["prep.cu", "radius.cu", "split.cu", "expand.cu", "voxel.cu", "visibility.cu", "order.cu", "vast.cu"]
+SOURCES = ["prep.cu", "radius.cu", "split.cu", "expand.cu", "voxel.cu", "visibility.cu", "order.cu", "vast.cu", "exchange.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-fmad=false", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -781,28 +781,77 @@ def camera_centers(R, T) -> np.ndarray:
 StageTimer = _Timer
 
 
+def pack_records_dev(local, slot: int) -> torch.Tensor:
+    """ptgs_pack_records: (n_hit, ratio, area, keep, flags) of this rank's range -> a (slot, 24) byte
+    tensor whose first rows are the records (the padding rows are never read)."""
+    lib = _lib.load()
+    n_hit, ratio, area, keep, flags = local
+    n = int(n_hit.shape[0])
+    send = torch.empty((max(int(slot), 1), _lib.PAIR_RECORD_BYTES), dtype=torch.uint8, device=n_hit.device)
+    check(lib.ptgs_pack_records(_ptr(n_hit), _ptr(ratio), _ptr(area), _ptr(keep), _ptr(flags), n, _ptr(send),
+                                _stream()))
+    return send
+
+
+def unpack_records_dev(recv: torch.Tensor, plan):
+    """ptgs_unpack_records: the gathered slots -> full-length (n_hit, ratio, area, keep, flags)."""
+    lib = _lib.load()
+    dev, P = recv.device, plan.P
+    Pa = max(P, 1)
+    n_hit = torch.empty(Pa, dtype=torch.int32, device=dev)
+    ratio = torch.empty(Pa, dtype=torch.float64, device=dev)
+    area = torch.empty(Pa, dtype=torch.float64, device=dev)
+    keep = torch.empty(Pa, dtype=torch.uint8, device=dev)
+    flags = torch.empty(Pa, dtype=torch.uint8, device=dev)
+    b = np.ascontiguousarray(plan.bounds, dtype=np.int64)
+    check(lib.ptgs_unpack_records(_ptr(recv), plan.world, max(plan.slot, 1), b.ctypes.data_as(C.POINTER(C.c_int64)),
+                                  P, _ptr(n_hit), _ptr(ratio), _ptr(area), _ptr(keep), _ptr(flags), _stream()))
+    return n_hit[:P], ratio[:P], area[:P], keep[:P], flags[:P]
+
+
+def range_plan(ds_offsets, cam_offsets, cam_index, rank: int, world: int, cam_off_h=None, block_cost_h=None):
+    """multigpu.RangePlan of a device CSR.  The L-sized host tables are taken from the caller when it
+    has them (partition_device keeps them), otherwise copied from the device once."""
+    from . import multigpu as M
+    if cam_off_h is None:
+        cam_off_h = cam_offsets.cpu().numpy()
+    if block_cost_h is None:
+        block_cost_h = (ds_offsets[1:] - ds_offsets[:-1]).cpu().numpy()
+    return M.RangePlan(cam_offsets, cam_index, cam_off_h, block_cost_h, rank, world)
+
+
 def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
-                       rank: int, world: int, group=None, timer=None, shard="ranges", **kw) -> VisibilityResult:
+                       rank: int, world: int, group=None, timer=None, shard="ranges", plan=None,
+                       **kw) -> VisibilityResult:
     """A7-A9 with the (block, camera) pairs sharded over the ranks (north star: only the
     visibility pass is partitioned; the per-pair result vectors are all-gathered).
-    shard="ranges": contiguous equal-cost ranges of the pair list (multigpu.shard_csr_ranges);
-    shard="modulo": cameras c % world == rank of every block (multigpu.shard_csr).
+    shard="ranges": contiguous equal-cost ranges of the pair list (multigpu.RangePlan; pass a
+    `plan` built once per partition result to keep its host arithmetic out of the step), records
+    exchanged as one padded all-gather of the ranks' contiguous slices between a pack and an
+    unpack kernel;
+    shard="modulo": cameras c % world == rank of every block (multigpu.shard_csr + gather_records).
     Returns the FULL per-pair result on every rank."""
     from . import multigpu as M
     if world <= 1:
         return visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                           timer=timer, **kw)
     if shard == "ranges":
-        my_off, my_idx, my_pos = M.shard_csr_ranges(cam_offsets, cam_index, rank, world,
-                                                    ds_offsets[1:] - ds_offsets[:-1])
+        if plan is None:
+            plan = range_plan(ds_offsets, cam_offsets, cam_index, rank, world)
+        if timer is not None:
+            timer.mark("vis_shard")
+        v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, plan.my_off, plan.my_idx, timer=timer, **kw)
+        n = plan.hi - plan.lo
+        local = (v.n_hit[:n], v.ratio[:n], v.area[:n], v.keep[:n], v.flags[:n])
+        n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev, group)
     else:
         my_off, my_idx, my_pos = M.shard_csr(cam_offsets, cam_index, rank, world)
-    if timer is not None:
-        timer.mark("vis_shard")
-    v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, my_off, my_idx, timer=timer, **kw)
-    rec = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
-    full = M.gather_records(rec, cam_index, world, group, pos=my_pos)
-    n_hit, ratio, area, keep, flags = M.unpack_records(full)
+        if timer is not None:
+            timer.mark("vis_shard")
+        v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, my_off, my_idx, timer=timer, **kw)
+        rec = M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags)
+        full = M.gather_records(rec, cam_index, world, group, pos=my_pos)
+        n_hit, ratio, area, keep, flags = M.unpack_records(full)
     if timer is not None:
         timer.mark("vis_allgather")
     return VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
@@ -913,18 +962,20 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
                cat(kp, np.uint8), cat(fl, np.uint8))
         return out, n_ds
     # world > 1: the groups' records are this rank's pairs lo..hi-1 in order; ONE exchange
-    recs = [M.pack_records(p[0].n_hit, p[0].ratio, p[0].area, p[0].keep, p[0].flags) for p in parts
-            if p[0].n_hit.shape[0] > 0 and p[5].shape[0] > 0]
-    local = torch.cat(recs) if recs else torch.zeros((0, M.REC_COLS), dtype=torch.float64, device=device)
-    local = local[: hi - lo]
+    live = [p[0] for p in parts if p[0].n_hit.shape[0] > 0 and p[5].shape[0] > 0]
     main.wait_event(ev_full)
     full_off_d.record_stream(main); full_idx_d.record_stream(main)
-    pos = torch.arange(lo, hi, device=device)
     if exchange is not None:       # tests: stand-in for the collective
-        full = exchange(local, pos)
+        recs = [M.pack_records(v.n_hit, v.ratio, v.area, v.keep, v.flags) for v in live]
+        local = torch.cat(recs) if recs else torch.zeros((0, M.REC_COLS), dtype=torch.float64, device=device)
+        n_hit, ratio, area, keep, flags = M.unpack_records(exchange(local[: hi - lo], torch.arange(lo, hi, device=device)))
     else:
-        full = M.gather_records(local, full_idx_d, world, group, pos=pos)
-    n_hit, ratio, area, keep, flags = M.unpack_records(full)
+        cat = lambda f, dt: (torch.cat([getattr(v, f) for v in live]) if live
+                             else torch.zeros(0, dtype=dt, device=device))[: hi - lo]
+        local = (cat("n_hit", torch.int32), cat("ratio", torch.float64), cat("area", torch.float64),
+                 cat("keep", torch.uint8), cat("flags", torch.uint8))
+        plan = M.RangePlan(None, None, cam_offsets, np.diff(block_offsets), rank, world)
+        n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev, group)
     k_off, k_idx = select_cameras(keep, full_off_d, full_idx_d, sync=False)
     ko = k_off.cpu().numpy()
     for p in parts:

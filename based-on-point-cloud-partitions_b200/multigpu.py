@@ -1,15 +1,19 @@
-"""Camera-sharded visibility pass (one process per GPU, torch.distributed).
+"""Sharded visibility pass (one process per GPU, torch.distributed).
 
 The reference is single process; the north star shards
-only the visibility pass: every rank holds the same down-sampled blocks, rank r
-evaluates the cameras  c % world == r  of every block's list
-(shen_partation_densify.py:932-936 is the loop being split) and the small
-per-pair result vectors are all-gathered (NCCL over NVLink on the GPU box,
-gloo in the CPU tests).  Everything here is device agnostic torch; the
-compute callback is the CUDA visibility pass.
+only the visibility pass (shen_partation_densify.py:932-936 is the loop being
+split).  Default sharding: the (block, camera) pair list, in CSR order, is cut
+into `world` CONTIGUOUS ranges of about equal cost (RangePlan / range_bounds);
+rank r sweeps its range and the per-pair records are exchanged with ONE padded
+all-gather of every rank's contiguous slice (exchange_ranges: NCCL over NVLink
+on the GPU box, gloo in the CPU tests).  The older modulo sharding
+(c % world == rank, shard_csr + gather_records) is kept for comparison.
+Everything here is device agnostic torch; the compute callback is the CUDA
+visibility pass and the pack / unpack kernels come from device.py.
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 # columns of the packed per-pair record (float64: every field is exact)
@@ -81,6 +85,94 @@ def range_bounds(cam_off_h, block_cost_h, rank: int, world: int):
     lo = first_at_least(total * rank)
     hi = first_at_least(total * (rank + 1)) if rank + 1 < world else int(cam_off_h[L])
     return lo, hi
+
+
+def all_range_bounds(cam_off_h, block_cost_h, world: int) -> np.ndarray:
+    """bounds[world + 1] with rank r owning pairs [bounds[r], bounds[r + 1]) -- the same ranges as
+    range_bounds(), computed for every rank at once with exact int64 arithmetic on the L-sized host
+    tables (vectorised: pair k of block b has exclusive cost E_b + k * M_b, and the first pair at or
+    above a threshold lies in the first non-empty block whose LAST pair reaches it)."""
+    co = np.asarray(cam_off_h, dtype=np.int64)
+    L = len(co) - 1
+    cnt = np.diff(co)
+    M = np.asarray(block_cost_h, dtype=np.int64)[:L]
+    P = int(co[L])
+    world = max(int(world), 1)
+    out = np.empty(world + 1, np.int64)
+    out[0], out[world] = 0, P
+    if world == 1:
+        return out
+    w = cnt * M
+    E = np.cumsum(w) - w                                   # exclusive cost prefix per block
+    total = int(w.sum())
+    nz = np.nonzero(cnt > 0)[0]
+    key = (E[nz] + (cnt[nz] - 1) * M[nz]) * world          # non-decreasing over the non-empty blocks
+    for r in range(1, world):
+        t = total * r
+        j = int(np.searchsorted(key, t, side="left"))
+        if j >= len(nz):
+            out[r] = P
+            continue
+        b = int(nz[j])
+        k = 0
+        if M[b] > 0:
+            need = t - int(E[b]) * world
+            k = max(0, -(-need // (int(M[b]) * world)))
+        out[r] = int(co[b]) + k
+    return out
+
+
+class RangePlan:
+    """Static part of the range-sharded visibility pass for one block -> camera CSR: every rank's
+    pair range, this rank's clamped offset table and camera-list view.  Built once per partition
+    result (the tables are L-sized and host resident); the per-step work is then the sweep itself
+    and one exchange."""
+
+    def __init__(self, cam_off: torch.Tensor, cam_idx: torch.Tensor, cam_off_h, block_cost_h, rank: int,
+                 world: int):
+        self.rank, self.world = int(rank), int(world)
+        self.bounds = all_range_bounds(cam_off_h, block_cost_h, world)
+        self.P = int(self.bounds[-1])
+        self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
+        self.slot = int(np.diff(self.bounds).max()) if world > 0 else self.P
+        # a host-only plan (cam_off None) carries the bounds and the block span, no device tables
+        self.my_off = (cam_off.clamp(self.lo, self.hi) - self.lo).to(torch.int64).contiguous() \
+            if cam_off is not None else None
+        self.my_idx = cam_idx[self.lo:self.hi] if cam_idx is not None else None
+        co = np.asarray(cam_off_h, dtype=np.int64)
+        if self.hi > self.lo:     # blocks the range touches: [bl0, bl1)
+            self.bl0 = int(np.searchsorted(co, self.lo, side="right")) - 1
+            self.bl1 = int(np.searchsorted(co, self.hi, side="left"))
+        else:
+            self.bl0 = self.bl1 = 0
+
+
+def exchange_ranges(local, plan: "RangePlan", pack, unpack, group=None):
+    """All-gather of the per-pair result vectors of a range-sharded pass.  `local` = this rank's
+    (n_hit, ratio, area, keep, flags) over its range (in range order); pack(local, slot) -> a
+    contiguous (slot, k) send tensor whose first hi - lo rows are the rank's records;
+    unpack(recv, plan) -> the full-length vectors from the (world * slot, k) gathered tensor
+    (slot r holds rank r's range).  One collective, no zero fill, no reduction."""
+    import torch.distributed as dist
+    slot = max(plan.slot, 1)
+    send = pack(local, slot)
+    recv = torch.empty((plan.world * slot,) + tuple(send.shape[1:]), dtype=send.dtype, device=send.device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    return unpack(recv, plan)
+
+
+def pack_slot_torch(local, slot: int) -> torch.Tensor:
+    """Device-agnostic pack for exchange_ranges (CPU tests; the CUDA path uses ptgs_pack_records)."""
+    rec = pack_records(*local)
+    send = torch.zeros((slot, REC_COLS), dtype=torch.float64, device=rec.device)
+    send[: rec.shape[0]] = rec
+    return send
+
+
+def unpack_slot_torch(recv: torch.Tensor, plan: "RangePlan"):
+    slot = max(plan.slot, 1)
+    parts = [recv[r * slot: r * slot + int(plan.bounds[r + 1] - plan.bounds[r])] for r in range(plan.world)]
+    return unpack_records(torch.cat(parts) if parts else recv[:0])
 
 
 def pack_records(n_hit, ratio, area, keep, flags) -> torch.Tensor:

@@ -406,6 +406,31 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
                         int32_t* kept_pos, ptgs_stream_t stream);
 
 /* ------------------------------------------------------------------ *
+ * Multi-GPU exchange of the per-pair records (the reference is
+ * single process -- the loop that is split across GPUs is
+ * scene/ptgs/shen_partation_densify.py:932-944).  With range sharding rank r
+ * owns the contiguous pair range [rank_lo[r], rank_lo[r+1]).
+ * ptgs_pack_records: the rank's result vectors -> n_pairs records of
+ *   PTGS_PAIR_RECORD_BYTES bytes {f64 ratio, f64 area, i32 n_hit, u8 keep,
+ *   u8 flags, u16 0} (8-byte aligned buffer).  The caller all-gathers the
+ *   (padded to `slot_pairs` records) buffers of all ranks, e.g. NCCL
+ *   all_gather on the same stream.
+ * ptgs_unpack_records: gathered = world slots of slot_pairs records in rank
+ *   order; rank_lo is a HOST array of world + 1 bounds (rank_lo[0] = 0,
+ *   rank_lo[world] = n_pairs); writes the full per-pair vectors.
+ * ------------------------------------------------------------------ */
+#define PTGS_PAIR_RECORD_BYTES 24
+int ptgs_pack_records(const int32_t* n_hit, const double* ratio,
+                      const double* area, const uint8_t* keep,
+                      const uint8_t* flags, int64_t n_pairs, void* records,
+                      ptgs_stream_t stream);
+int ptgs_unpack_records(const void* gathered, int32_t world,
+                        int64_t slot_pairs, const int64_t* rank_lo_host,
+                        int64_t n_pairs, int32_t* n_hit, double* ratio,
+                        double* area, uint8_t* keep, uint8_t* flags,
+                        ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
  * Coverage sweep (config 5; the camera x all-points pass of the Vast path,
  * scene/ptgs/data_partition.py:385-424, :505): every point against every
  * camera cam_first..cam_first+cam_count-1; n_hit[cam_count] int32 (must be

@@ -79,6 +79,18 @@ def _worker(rank, world, port, seed, out_dir):
         full3 = M.gather_records(M.pack_records(nh, rt, ar, kp, fl), idx, world, pos=r_pos)
         for g, w in zip(M.unpack_records(full3), want):
             assert torch.equal(g, w), "rank %d: gathered table differs (ranges)" % rank
+        # the same ranges through the plan + ONE padded all-gather of the contiguous slices (the product path)
+        cost = _block_cost(off.shape[0] - 1, seed)
+        plan = M.RangePlan(off, idx, off.numpy(), cost.numpy(), rank, world)
+        assert torch.equal(plan.my_off, r_off) and torch.equal(plan.my_idx, r_idx)
+        assert (plan.lo, plan.hi) == M.range_bounds(off.numpy(), cost.numpy(), rank, world)
+        assert plan.slot == int(np.diff(plan.bounds).max()) and plan.bounds[0] == 0 and plan.bounds[-1] == idx.shape[0]
+        got4 = M.exchange_ranges(_fake_records(plan.my_off, plan.my_idx), plan, M.pack_slot_torch, M.unpack_slot_torch)
+        for g, w in zip(got4, want):
+            assert torch.equal(g, w), "rank %d: gathered table differs (slot exchange)" % rank
+        if plan.hi > plan.lo:   # the block span covers exactly the blocks with a pair in the range
+            blk = torch.repeat_interleave(torch.arange(off.shape[0] - 1), off[1:] - off[:-1])[plan.lo:plan.hi]
+            assert int(blk.min()) == plan.bl0 and int(blk.max()) == plan.bl1 - 1
         # coverage sweep exchange (c5): contiguous camera ranges, counts gathered, seen flags merged
         C = 57
         first, cnt = M.camera_range(C, rank, world)
@@ -109,6 +121,23 @@ def test_sharded_records_gloo(world, seed, tmp_path):
     for t in tabs[1:]:
         for a, b in zip(tabs[0], t):
             assert torch.equal(a, b)
+
+
+def test_all_range_bounds_equals_per_rank_loop():
+    rng = np.random.default_rng(0)
+    for trial in range(200):
+        L, world = int(rng.integers(1, 40)), int(rng.integers(1, 9))
+        cnt = rng.integers(0, 9, L)
+        cost = rng.integers(0, 5000, L).astype(np.int64)
+        if trial % 5 == 0:
+            cnt[rng.integers(0, L)] = 0
+        if trial % 7 == 0:
+            cost[rng.integers(0, L)] = 0
+        co = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int64)
+        b = M.all_range_bounds(co, cost, world)
+        assert b[0] == 0 and b[-1] == co[-1] and bool((np.diff(b) >= 0).all())
+        for r in range(world):
+            assert (int(b[r]), int(b[r + 1])) == M.range_bounds(co, cost, r, world)
 
 
 def test_camera_range_partitions_cameras():
