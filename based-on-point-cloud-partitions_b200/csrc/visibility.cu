@@ -400,9 +400,11 @@ __device__ __forceinline__ Item decode_item(const SweepArgs& a, const int64_t* s
 }
 
 // diagnostics (ptgs_debug_sweep_stats): point-camera tests before / after the
-// tile cull, summed over every sweep launch since the last reset
+// tile cull etc., summed over every sweep launch since the last reset.  The
+// counters are device-global state on the hot path, so they exist only in
+// diagnostics builds (-DPTGS_SWEEP_STATS_FINE); the release library has none.
+#ifdef PTGS_SWEEP_STATS_FINE
 __device__ unsigned long long g_sweep_stats[8];
-#ifdef PTGS_SWEEP_STATS_FINE   // counters [2..7] sit on the hot path: diagnostics builds only
 #define PTGS_FINE_STAT(i, v) atomicAdd(&g_sweep_stats[i], (unsigned long long)(v))
 #else
 #define PTGS_FINE_STAT(i, v) ((void)0)
@@ -662,8 +664,8 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
       __syncthreads();
       const int nact_all = S.nact;
       if (tid == 0) {
-        atomicAdd(&g_sweep_stats[0], (unsigned long long)nr * (unsigned)cur.cnt);
-        atomicAdd(&g_sweep_stats[1], (unsigned long long)nact_all * (unsigned)cur.cnt);
+        PTGS_FINE_STAT(0, (unsigned long long)nr * (unsigned)cur.cnt);
+        PTGS_FINE_STAT(1, (unsigned long long)nact_all * (unsigned)cur.cnt);
       }
     for (int c0 = 0; c0 < nact_all; c0 += kSwCamChunk) {
       const int nc = (nact_all - c0) < kSwCamChunk ? (nact_all - c0) : kSwCamChunk;
@@ -1897,6 +1899,7 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
 }
 
 int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset) {
+#ifdef PTGS_SWEEP_STATS_FINE
   unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   PTGS_CUDA_TRY(cudaDeviceSynchronize());
   if (out4) {
@@ -1907,6 +1910,39 @@ int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset) {
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     PTGS_CUDA_TRY(cudaMemcpyToSymbol(g_sweep_stats, z, sizeof(z)));
   }
+  return PTGS_OK;
+#else
+  (void)reset;
+  if (out4)
+    for (int i = 0; i < 8; ++i) out4[i] = 0;
+  set_error("sweep statistics are compiled out (build with -DPTGS_SWEEP_STATS_FINE)");
+  return PTGS_E_INVALID;
+#endif
+}
+
+// FP32 FMA issue-rate probe: 8 independent chains per thread, no memory traffic
+// inside the loop.  Diagnostics for the roofline report (bench.py).
+namespace ptgs {
+__global__ void __launch_bounds__(256) fma_probe_kernel(float* out, int iters) {
+  float a[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = 1.0f + 1e-3f * (float)(threadIdx.x + k);
+  const float m = 1.0f - 1e-7f * (float)(blockIdx.x & 3), c = 1e-6f;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = __fmaf_rn(a[k], m, c);
+  }
+  float s = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += a[k];
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace ptgs
+
+int ptgs_debug_fma_probe(float* out, int32_t iters, ptgs_stream_t stream) {
+  PTGS_REQUIRE(out && iters > 0, "arguments");
+  fma_probe_kernel<<<kNumSMs * 8, 256, 0, (cudaStream_t)stream>>>(out, iters);
+  PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
 

@@ -82,6 +82,9 @@ class PartitionDeviceResult:
     kept_offsets: torch.Tensor = None  # A9 CSR
     kept_index: torch.Tensor = None
     timings_ms: dict = field(default_factory=dict)
+    pt_counts_h: np.ndarray = None     # host copies of the L-sized tables (no extra synchronisation)
+    cam_offsets_h: np.ndarray = None
+    ds_block0: int = 0                 # first block of ds_* (range-sharded runs keep only their own blocks)
 
 
 def leaf_id(path: int, depth: int) -> str:
@@ -231,7 +234,7 @@ def _cell_grid(rects: np.ndarray):
     return grid, cell_off, np.ascontiguousarray(owners[order])
 
 
-def expand_select(x, y, boxes: np.ndarray, use_grid=None):
+def expand_select(x, y, boxes: np.ndarray, use_grid=None, want_counts=False):
     """A4.  boxes (L,4) float64 {minx,miny,maxx,maxy}; the bounds are rounded
     to the cloud's dtype exactly as NumPy does for `f32_array >= python_float`
     (shen_partation_densify.py:201-202).  With many blocks the selection goes through a
@@ -258,7 +261,8 @@ def expand_select(x, y, boxes: np.ndarray, use_grid=None):
     else:
         check(lib.ptgs_expand_count(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
                                     _ptr(ws), ws.numel(), _stream()))
-    total = int(counts.sum().item())
+    counts_h = counts.cpu().numpy()               # the one host read of the stage (L values)
+    total = int(counts_h.sum())
     offsets = torch.empty(L + 1, dtype=torch.int64, device=dev)
     indices = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
     if cg is not None:
@@ -268,10 +272,12 @@ def expand_select(x, y, boxes: np.ndarray, use_grid=None):
     else:
         check(lib.ptgs_expand_fill(_dt(x), _ptr(x), _ptr(y), n, _ptr(rects_d), L, _ptr(counts),
                                    _ptr(offsets), _ptr(indices), total, _ptr(ws), ws.numel(), _stream()))
+    if want_counts:
+        return offsets, indices[:total], counts_h
     return offsets, indices[:total]
 
 
-def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device):
+def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device, want_host=False):
     """A5.  centers (C,3) (float32 values widened to float64), boxes (L,4) f64."""
     lib = _lib.load()
     Cn, L = len(centers), len(boxes)
@@ -281,7 +287,10 @@ def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device):
     cap = max(Cn * L, 1)
     index = torch.empty(cap, dtype=torch.int32, device=device)
     check(lib.ptgs_assign_cameras(_ptr(cen), Cn, _ptr(bx), L, _ptr(offsets), _ptr(index), cap, _stream()))
-    total = int(offsets[L].item())
+    off_h = offsets.cpu().numpy()                 # the one host read of the stage (L + 1 values)
+    total = int(off_h[L])
+    if want_host:
+        return offsets, index[:total].clone(), off_h
     return offsets, index[:total].clone()
 
 
@@ -683,7 +692,7 @@ class _Timer:
 def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np.ndarray,
                      threshold: int, man_trans: np.ndarray | None = None, radius_filter: bool = True,
                      do_visibility: bool = True, time_stages: bool = False,
-                     cam_shard: tuple | None = None, split_xyz: torch.Tensor | None = None,
+                     shard: tuple | None = None, split_xyz: torch.Tensor | None = None,
                      exact_ratio: bool = False) -> PartitionDeviceResult:
     """run_DataPartition (shen_partition_utils.py:57-93) on the device.
 
@@ -695,8 +704,13 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     split_xyz   optional (N,3) float32 tensor used for A1-A3 instead of `xyz`
                 (the reference's literal shen-path behaviour under man_trans:
                 the split reads the un-rotated PLY, shen_partition_utils.py:62).
-    cam_shard   (rank, world): this process evaluates only cameras
-                c % world == rank in the visibility pass (multi-GPU).
+    shard       (rank, world[, group]): multi-GPU.  A1-A5 are computed by every rank
+                (deterministic, no communication); the visibility stage is range-sharded: rank r
+                owns a contiguous range of the (block, camera) pair list of about 1 / world of the
+                cost (multigpu.RangePlan on the expanded point counts), down-samples (A6) and
+                sweeps (A7-A8) only the blocks that range touches, and the per-pair records are
+                exchanged once (one padded all-gather).  Every rank returns the FULL per-pair
+                result and kept-camera CSR; ds_* hold the rank's own blocks (ds_block0 = first).
     exact_ratio every pair's exact hull ratio (default: pairs decided by the
                 area bounds skip the exact hull, see visibility()).
     """
@@ -726,23 +740,48 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     tm.mark("A3_split")
     del fx, fy
     boxes = expanded_boxes(lb)
-    pt_off, pt_idx = expand_select(x, y, boxes)
+    pt_off, pt_idx, pt_cnt_h = expand_select(x, y, boxes, want_counts=True)
     tm.mark("A4_expand")
-    cam_off, cam_idx = assign_cameras(cam_centers, boxes, dev)
-    if cam_shard is not None:
-        cam_off, cam_idx = shard_cameras(cam_off, cam_idx, *cam_shard)
+    cam_off, cam_idx, cam_off_h = assign_cameras(cam_centers, boxes, dev, want_host=True)
     tm.mark("A5_assign")
     res = PartitionDeviceResult(
         keep_mask=keep_mask, n_filtered=int(n_f.item()), root_bounds=tuple(root.cpu().tolist()),
         leaf_bounds=lb, leaf_path=lp, leaf_depth=ld, leaf_count=lc,
         leaf_ids=[leaf_id(p, d) for p, d in zip(lp.tolist(), ld.tolist())], boxes=boxes,
         pt_offsets=pt_off, pt_index=pt_idx, cam_offsets=cam_off, cam_index=cam_idx)
+    res.pt_counts_h, res.cam_offsets_h = pt_cnt_h, cam_off_h
     if do_visibility:
-        ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx)
-        tm.mark("A6_voxel")
         cams_d = torch.from_numpy(np.ascontiguousarray(cam_records, dtype=np.float32)).to(dev)
-        vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx, exact_ratio=exact_ratio)
-        tm.mark("A7_A8_visibility")
+        if shard is not None and int(shard[1]) > 1:
+            from . import multigpu as M
+            rank, world = int(shard[0]), int(shard[1])
+            group = shard[2] if len(shard) > 2 else None
+            plan = M.RangePlan(None, None, cam_off_h, pt_cnt_h, rank, world)
+            b0, b1 = plan.bl0, plan.bl1
+            pt_off_h = np.concatenate([[0], np.cumsum(pt_cnt_h)]).astype(np.int64)
+            e0, e1 = int(pt_off_h[b0]), int(pt_off_h[b1])
+            sub_off = torch.from_numpy(pt_off_h[b0:b1 + 1] - e0).to(dev)
+            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, sub_off, pt_idx[e0:e1]) if b1 > b0 else \
+                voxel_downsample(x, y, z, torch.zeros(2, dtype=torch.int64, device=dev), pt_idx[:0])
+            tm.mark("A6_voxel")
+            loc = np.clip(cam_off_h[b0:b1 + 1], plan.lo, plan.hi) - plan.lo if b1 > b0 else np.zeros(2, np.int64)
+            loc_off = torch.from_numpy(np.ascontiguousarray(loc, dtype=np.int64)).to(dev)
+            v = visibility(dx, dy, dz, ds_off, cams_d, loc_off, cam_idx[plan.lo:plan.hi], exact_ratio=exact_ratio)
+            tm.mark("A7_A8_visibility")
+            nl = plan.hi - plan.lo
+            local = (v.n_hit[:nl], v.ratio[:nl], v.area[:nl], v.keep[:nl], v.flags[:nl])
+            n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev,
+                                                                group)
+            vis = VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
+            vis.n_exact = v.n_exact
+            tm.mark("exchange")
+            res.ds_block0 = b0
+        else:
+            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx)
+            tm.mark("A6_voxel")
+            vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx, exact_ratio=exact_ratio)
+            tm.mark("A7_A8_visibility")
+            res.ds_block0 = 0
         k_off, k_idx = select_cameras(vis.keep, cam_off, cam_idx)
         tm.mark("A9_select")
         res.ds_offsets, res.ds_x, res.ds_y, res.ds_z, res.ds_first = ds_off, dx, dy, dz, dfirst
@@ -751,20 +790,45 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     return res
 
 
-def shard_cameras(cam_off: torch.Tensor, cam_idx: torch.Tensor, rank: int, world: int):
-    """Keeps the cameras c % world == rank of every block's list (order kept)."""
-    if world <= 1:
-        return cam_off, cam_idx
-    L = cam_off.shape[0] - 1
-    mine = (cam_idx % world) == rank
-    seg = torch.repeat_interleave(torch.arange(L, device=cam_off.device),
-                                  (cam_off[1:] - cam_off[:-1]))
-    counts = torch.zeros(L, dtype=torch.int64, device=cam_off.device)
-    counts.index_add_(0, seg[mine], torch.ones(int(mine.sum().item()), dtype=torch.int64,
-                                               device=cam_off.device))
-    new_off = torch.zeros(L + 1, dtype=torch.int64, device=cam_off.device)
-    torch.cumsum(counts, 0, out=new_off[1:])
-    return new_off, cam_idx[mine].contiguous()
+def partition_results_to_host(res: PartitionDeviceResult) -> dict:
+    """The result set SURVEY.md 8(d)(ii) ends the end-to-end partition on, as host arrays: leaf
+    rectangles / ids / counts (already host side), the expanded index CSR, the block -> camera CSR,
+    per-pair n_hit / ratio / keep / flags and the kept-camera CSR.  The index list is the large one
+    (4 bytes per expanded point); it lands in pinned memory so the copy runs at PCIe speed."""
+    out = {"leaf_bounds": res.leaf_bounds, "leaf_ids": res.leaf_ids, "leaf_count": res.leaf_count,
+           "boxes": res.boxes}
+    n = int(res.pt_index.shape[0])
+    idx_h = torch.empty(n, dtype=torch.int32, pin_memory=True)
+    idx_h.copy_(res.pt_index, non_blocking=True)
+    out["pt_index"] = idx_h.numpy()
+    small = {"pt_offsets": res.pt_offsets, "cam_offsets": res.cam_offsets, "cam_index": res.cam_index}
+    if res.vis is not None:
+        small.update({"n_hit": res.vis.n_hit, "ratio": res.vis.ratio, "keep": res.vis.keep, "flags": res.vis.flags,
+                      "kept_offsets": res.kept_offsets, "kept_index": res.kept_index})
+    for k, t in small.items():
+        out[k] = t.cpu().numpy()
+    torch.cuda.current_stream().synchronize()
+    return out
+
+
+def fma_probe(device, iters: int = 4096) -> float:
+    """Measured FP32 FMA issue peak of the device in lane-ops/s (ptgs_debug_fma_probe: 8 independent
+    FMA chains per thread, 148 x 8 CTAs of 256 threads).  Diagnostics for the roofline report."""
+    lib = _lib.load()
+    out = torch.empty(148 * 8 * 256, dtype=torch.float32, device=device)
+    st = _stream()
+    check(lib.ptgs_debug_fma_probe(_ptr(out), int(iters), st))
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(lib.ptgs_debug_fma_probe(_ptr(out), int(iters), st))
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+    return float(148 * 8 * 256) * iters * 8 / (best * 1e-3)
 
 
 def camera_centers(R, T) -> np.ndarray:

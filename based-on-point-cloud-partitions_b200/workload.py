@@ -84,10 +84,10 @@ def make(name: str, scale: float = 1.0, **kw) -> HostWorkload:
     return from_scene(scene_synth.make_config(name, scale, **kw), name)
 
 
-def describe(name: str, scale: float, w: HostWorkload) -> str:
+def describe(name: str, scale: float, w: HostWorkload, n_points: int | None = None) -> str:
     N, C, thr, seed, obl, man = scene_synth.CONFIGS[name]
     s = "%s: synthetic COLMAP scene %d points / %d cameras, threshold_value=%d, seed %d" % (
-        name, w.n_points, w.n_cameras, w.threshold, seed)
+        name, w.n_points if n_points is None else n_points, w.n_cameras, w.threshold, seed)
     if man is not None:
         s += ", Manhattan rotation %g deg about Z (consistent: points and cameras)" % man
     if obl:

@@ -6,14 +6,20 @@ Metric (BASELINE.json): point-camera visibility tests/s (one test = one
 scene/ptgs/shen_partation_densify.py:429-471), plus the end-to-end partition
 wall time of the same scene (`partition` object of the JSON line).
 
-A "step" is one visibility pass (A7-A9: sweep 1, inner polygons, sweep 2, exact
-hulls, camera selection, and for N > 1 the all-gather of the per-pair records)
-over every (block, camera) pair of the workload, with the down-sampled blocks
-resident in HBM.  `e2e` is the same metric through the host-buffer entry
-(`visibility_select_host`: H2D of the expanded blocks' points and the camera
-records, A6 voxel down-sampling, A7-A9, D2H of the kept-camera lists).
+Default workload: **c4** (50 M points / 8 000 cameras / threshold 500 000), the
+largest block-partition configuration of BASELINE.json -- it fits one B200.
+A "step" is one visibility pass (A7-A9: sample pass, sweep 1, area bounds,
+sweep 2, exact hulls, camera selection, and for N > 1 the exchange of the
+per-pair records) over every (block, camera) pair of the workload, with the
+down-sampled blocks resident in HBM.  `e2e` is the same metric through the
+host-buffer entry (`visibility_select_host`: H2D of the expanded blocks' points
+and the camera records, A6 voxel down-sampling, A7-A9, D2H of the kept-camera
+lists).  The same line carries `sweep_c5` (config c5: 100 M points x 16 000
+cameras, Morton order + coverage sweep, point-sharded at N > 1), `partition`
+(A1-A9 wall time, to host-resident results), `parity` (the CPU arm's per-pair
+results compared with the GPU's for the same pairs) and `cpu_baseline`.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2] [--scale s]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4] [--scale s]
   python bench.py --impl reference ...     (CPU arm: the oracle port, rank 0 only)
 """
 from __future__ import annotations
@@ -44,9 +50,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4"])
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-c5", action="store_true", help="skip the sweep_c5 object")
+    ap.add_argument("--c5-scale", type=float, default=1.0)
+    ap.add_argument("--secondary", default="c2", help="second workload reported at N=1 ('' to skip)")
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
     ap.add_argument("--sample-file", default=None, help="internal: cpu_baseline leg input")
     return ap.parse_args()
@@ -142,15 +151,42 @@ def max_over_ranks(v, world, dev):
     return float(t.item())
 
 
-def sweep_traffic_bytes():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one sweep_kernel<1> launch on
-    the bench workload, from the committed ncu capture (profiles/r01_sweep_traffic.json)."""
-    p = os.path.join(ROOT, "profiles", "r01_sweep_traffic.json")
+def committed_profile(name):
+    """A JSON summary of a committed ncu capture under profiles/ (None when absent)."""
     try:
-        with open(p) as f:
-            return float(json.load(f)["dram_bytes_per_launch"])
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            return json.load(f)
     except Exception:
         return None
+
+
+def load_workload(name, scale, rank, world, dev):
+    """Rank 0 generates the synthetic scene (6 s at c4, 13 s at c5, several GB of host memory) and
+    the other ranks receive the cloud over NCCL and the (small) camera arrays as an object, instead
+    of every rank running the generator.  Returns (HostWorkload [xyz None on ranks > 0], xyz device)."""
+    import ptgs_b200  # noqa: F401
+    from ptgs_b200 import workload as W
+    if world <= 1:
+        w = W.make(name, scale)
+        return w, torch.from_numpy(w.xyz).pin_memory().to(dev)
+    import copy
+    import torch.distributed as dist
+    box = [None]
+    w = None
+    if rank == 0:
+        w = W.make(name, scale)
+        light = copy.copy(w)
+        light.xyz = None
+        box = [(light, len(w.xyz))]
+    dist.broadcast_object_list(box, src=0)
+    light, n = box[0]
+    if rank == 0:
+        xyz = torch.from_numpy(w.xyz).pin_memory().to(dev)
+    else:
+        w = light
+        xyz = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    dist.broadcast(xyz, src=0)
+    return w, xyz
 
 
 def run_ours(args):
@@ -164,11 +200,10 @@ def run_ours(args):
     lib = _lib.load(build_if_missing=False)
     hbm_peak, sm_max, peak_kind = peaks()
 
-    w = W.make(args.workload, args.scale)
+    w, xyz = load_workload(args.workload, args.scale, rank, world, dev)
+    n_points = int(xyz.shape[0])
     recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
     centers = D.camera_centers(w.R, w.T)
-    xyz_pinned = torch.from_numpy(w.xyz).pin_memory()
-    xyz = xyz_pinned.to(dev)
 
     # ---- full partition once (also the warm-up of every kernel) -------------
     res = D.partition_device(xyz, recs, centers, w.threshold, man_trans=w.man_trans)
@@ -182,11 +217,15 @@ def run_ours(args):
     pairs = int(C_b.sum())
     cams_d = torch.from_numpy(recs).to(dev)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    # static part of the sharded pass (every rank's pair range; L-sized host arithmetic), built once
+    # per partition result
+    plan = D.range_plan(res.ds_offsets, res.cam_offsets, res.cam_index, rank, world,
+                        cam_off_h=cam_off_h, block_cost_h=M_b) if world > 1 else None
 
     def vis_step(timer=None):
         v = D.visibility_sharded(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d,
-                                 res.cam_offsets, res.cam_index, rank, world, timer=timer)
-        k_off, k_idx = D.select_cameras(v.keep, res.cam_offsets, res.cam_index)
+                                 res.cam_offsets, res.cam_index, rank, world, timer=timer, plan=plan)
+        k_off, k_idx = D.select_cameras(v.keep, res.cam_offsets, res.cam_index, sync=False)
         return v, k_off, k_idx
 
     for _ in range(max(args.warmup, 3)):
@@ -226,58 +265,96 @@ def run_ours(args):
         for k, t in tm.result().items():
             stage[k] = stage.get(k, 0.0) + t / args.steps
     n_kept = int(k_off[-1].item())
+    flags_h = v.flags.cpu().numpy()
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {
-            "workload": W.describe(args.workload, args.scale, w),
+            "workload": W.describe(args.workload, args.scale, w, n_points),
             "leaves": L, "pairs": pairs, "tests_per_step": tests,
             "downsampled_points": int(M_b.sum()), "kept_cameras": n_kept,
             "kept_fraction": n_kept / max(pairs, 1),
-            "parallelism": "(block, camera) pairs sharded in %d contiguous equal-cost ranges, per-pair records all-gathered" % world if world > 1 else "single GPU",
+            "parallelism": ("(block, camera) pairs sharded in %d contiguous equal-cost ranges, per-pair records "
+                            "exchanged with one padded all-gather" % world) if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MB write)",
         },
         "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall,
         "stage_ms": {k: round(t, 4) for k, t in stage.items()},
     }
-    # ---- roofline of the dominant kernel (sweep 1: sweep_kernel<1>) -----------
+    # ---- roofline of the dominant kernel (sweep 1: sweep_kernel<1>), this rank's launch ---------
     k_ms = stage.get("vis_sweep1_count", float("nan"))
-    shard_tests = tests / world
-    alg_bytes = float(M_b.sum()) * 12 + float(C_b.sum()) / world * 80 + pairs / world * 16
+    if world > 1:
+        my_pts = float(ds_off_h[plan.bl1] - ds_off_h[plan.bl0])
+        my_pairs = float(plan.hi - plan.lo)
+        my_tests = float(sum(int(M_b[b]) * (min(int(cam_off_h[b + 1]), plan.hi) - max(int(cam_off_h[b]), plan.lo))
+                             for b in range(plan.bl0, plan.bl1)))
+    else:
+        my_pts, my_pairs, my_tests = float(M_b.sum()), float(pairs), float(tests)
+    alg_bytes = my_pts * 12 + my_pairs * 80 + my_pairs * 16
     lane_peak = 148 * 128 * sm_max * 1e6
+    ncu = committed_profile("r02_sweep1_ncu.json") or {}
     out["roofline"] = {
-        "kernel": "sweep_kernel<1> (ptgs_visibility_count)", "bound": "hbm",
+        "kernel": "sweep_kernel<1> (ptgs_visibility_count), rank 0's launch", "bound": "hbm",
         "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": sweep_traffic_bytes(),
+        "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": ncu.get("dram_bytes_per_launch"),
         "peak_kind": peak_kind,
         "algorithmic_bytes": alg_bytes, "kernel_ms": k_ms,
         "note": "the sweep re-uses every staged point tile for all cameras of the block, so its HBM traffic "
                 "is 12 B/point by construction and the binding roof is FP32 issue (see fp32; DESIGN.md 4.1); "
                 "`traffic` = dram read+write bytes of one launch from the ncu --set full capture in profiles/",
-        "fp32": {"slots_per_test": SLOTS_PER_TEST,
+        "fp32": {"issue_active_pct": ncu.get("issue_active_pct"), "fma_pipe_pct": ncu.get("fma_pipe_pct"),
+                 "alu_pipe_pct": ncu.get("alu_pipe_pct"),
+                 "lane_ops_per_test": ncu.get("lane_ops_per_test"),
+                 "source": ncu.get("source", "no committed capture"),
+                 "slots_per_test_bruteforce": SLOTS_PER_TEST,
                  "bruteforce_roof_tests_per_s": lane_peak / SLOTS_PER_TEST,
-                 "achieved_tests_per_s": shard_tests / (k_ms * 1e-3),
-                 "ratio": shard_tests / (k_ms * 1e-3) / (lane_peak / SLOTS_PER_TEST),
-                 "peak_kind": "148 SMs x 128 lanes x sm_max_mhz / 34 issue slots per test",
-                 "note": "roof of a kernel that evaluates EVERY (point, camera) test at full FP32 issue rate; the "
-                         "sweep decides most tests per box (tile / warp run) without touching the points, so the "
-                         "ratio can exceed 1 -- it is an algorithmic speed, not an issue-slot utilisation "
-                         "(that is in profiles/: smsp__issue_active, inst_executed)"},
+                 "achieved_tests_per_s": my_tests / (k_ms * 1e-3),
+                 "note": "issue_active / fma_pipe / lane_ops_per_test come from the committed ncu capture of this "
+                         "kernel; bruteforce_roof = 148 SMs x 128 lanes x sm_max / 34 slots is the rate of a kernel "
+                         "that evaluates EVERY test -- the sweep decides most tests per box, so achieved can exceed "
+                         "it (algorithmic speed, not utilisation)"},
     }
-    ctx = dict(w=w, res=res, recs=recs, centers=centers, xyz_pinned=xyz_pinned, xyz=xyz, dev=dev,
-               tests=tests, world=world, rank=rank, flush=flush, lib=lib, D=D)
+    fp = measure_fp32_peak(D, dev)
+    if fp:
+        out["roofline"]["fp32"]["measured_fma_lane_ops_per_s"] = fp
+    ctx = dict(w=w, res=res, recs=recs, centers=centers, xyz=xyz, dev=dev, tests=tests, world=world,
+               rank=rank, flush=flush, lib=lib, D=D, vis=v, cam_off_h=cam_off_h, flags_h=flags_h, args=args)
     measure_e2e(args, out, ctx)
     measure_partition(args, out, ctx)
+    out["parity"] = {"near_threshold_pairs_all": int(((flags_h & 1) != 0).sum()),
+                     "first_ray_collinear_pairs_all": int(((flags_h & 2) != 0).sum()),
+                     "pairs_all": int(len(flags_h))}
+    c5 = None
+    if not args.no_c5:
+        c5 = prepare_c5(args, ctx)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        measure_cpu_baseline(args, out, ctx)
+        measure_cpu_baseline(args, out, ctx, c5)
+    # release the c4 state before the 100 M-point sweep
+    for k in ("res", "vis", "xyz", "blocks"):
+        ctx.pop(k, None)
+    del res, v, xyz
+    torch.cuda.empty_cache()
+    if c5 is not None:
+        measure_c5(args, out, ctx, c5)
+    if rank == 0 and world == 1 and args.secondary and args.secondary != args.workload:
+        measure_secondary(args, out, ctx)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(out), flush=True)
+
+
+def measure_fp32_peak(D, dev):
+    """FP32 FMA issue peak measured live (ptgs_debug_fma_probe: dependent-chain-free FMA loop on
+    every SM) -> lane-ops/s.  BASELINE.md section 3 asks for the measured figure."""
+    try:
+        return D.fma_probe(dev)
+    except Exception:
+        return None
 
 
 def _host_blocks(ctx):
@@ -289,9 +366,11 @@ def _host_blocks(ctx):
     if w.man_trans is not None:
         x, y, z = D.manhattan_apply(x, y, z, w.man_trans)
     idx = res.pt_index.to(torch.int64)
-    pts = torch.stack([x[idx], y[idx], z[idx]], dim=1).contiguous()
-    host = torch.empty(pts.shape, dtype=pts.dtype, pin_memory=True)
-    host.copy_(pts)
+    host = torch.empty((idx.shape[0], 3), dtype=x.dtype, pin_memory=True)
+    step = 8 << 20                                   # bounded device staging
+    for s in range(0, idx.shape[0], step):
+        i = idx[s:s + step]
+        host[s:s + step].copy_(torch.stack([x[i], y[i], z[i]], dim=1))
     torch.cuda.synchronize()
     return host, res.pt_offsets.cpu().numpy()
 
@@ -303,15 +382,15 @@ def measure_e2e(args, out, ctx):
     recs_pinned = torch.from_numpy(ctx["recs"]).pin_memory()
     cam_off = res.cam_offsets.cpu().numpy()
     cam_idx = res.cam_index.cpu().numpy()
-    steps = max(2, min(args.steps, 10))
+    steps = max(2, min(args.steps, 6))
+    groups = 4 if blocks.numel() * blocks.element_size() > (256 << 20) else 2
 
     def one():
         return D.visibility_select_host(blocks, blk_off, recs_pinned, cam_off, cam_idx, dev,
-                                        rank=rank, world=world)
+                                        rank=rank, world=world, groups=groups)
     for _ in range(2):
         outp, m = one()
     barrier(world)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     tot = 0.0
     for i in range(steps):
         ctx["flush"].fill_(i & 0xff)
@@ -338,36 +417,49 @@ def measure_e2e(args, out, ctx):
         h2d = blocks.numel() * blocks.element_size() + recs_pinned.numel() * 4 + blk_off.nbytes + \
             cam_off.nbytes + cam_idx.nbytes
     d2h = sum(a.nbytes for a in outp)
+    # the host entry must agree with the device-resident pass (same pairs, same decisions)
+    same = bool(np.array_equal(outp[2], ctx["vis"].n_hit.cpu().numpy()) and
+                np.array_equal(outp[4], ctx["vis"].keep.cpu().numpy()))
     out["e2e"] = {"value": ctx["tests"] / (tot / steps), "unit": UNIT, "ms_per_step": tot / steps * 1e3,
                   "steps": steps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                  "upload_groups": groups, "equals_device_pass": same,
                   "api": "ptgs_b200.device.visibility_select_host (host blocks -> A6 -> A7-A9 -> host kept lists)",
                   "timing": "host wall clock around the call, synchronised both sides, max over ranks"}
 
 
 def measure_partition(args, out, ctx):
-    """End-to-end partition wall time (second half of BASELINE.json's metric):
-    device-resident cloud + host camera records -> every per-leaf / per-pair
-    result (A1-A9).  Rank r evaluates its camera shard; A1-A6 are replicated."""
+    """End-to-end partition wall time (second half of BASELINE.json's metric, SURVEY.md 8(d)(ii)):
+    device-resident cloud + host camera records -> every per-leaf / per-pair result (A1-A9) ON THE
+    HOST (leaf rectangles / ids / counts, expanded index CSR, per-pair n_hit / ratio / keep, kept
+    CSR).  With N > 1 the visibility pass (A6-A9) is range-sharded and the records exchanged;
+    A1-A5 are replicated."""
     D, w, dev, world, rank = ctx["D"], ctx["w"], ctx["dev"], ctx["world"], ctx["rank"]
-    runs = []
+    runs, runs_dev = [], []
     stages = None
     for i in range(4):
         ctx["flush"].fill_(i)
-        torch.cuda.synchronize()
+        barrier(world)
         t0 = time.perf_counter()
         r = D.partition_device(ctx["xyz"], ctx["recs"], ctx["centers"], w.threshold, man_trans=w.man_trans,
-                               time_stages=True, cam_shard=(rank, world) if world > 1 else None)
+                               time_stages=True, shard=(rank, world) if world > 1 else None)
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
+        t1 = time.perf_counter()
+        host = D.partition_results_to_host(r)
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
         if i > 0:
-            runs.append(dt)
+            runs.append(t2 - t0)
+            runs_dev.append(t1 - t0)
             stages = r.timings_ms
+        d2h = sum(a.nbytes for a in host.values() if hasattr(a, "nbytes"))
+        del r, host
     best = max_over_ranks(min(runs), world, dev)
+    best_dev = max_over_ranks(min(runs_dev), world, dev)
     # HBM fractions of the streaming stages (algorithmic bytes of DESIGN.md section 4 / stage time)
     res = ctx["res"]
     es = 8 if w.man_trans is not None else 4            # coordinate bytes (float64 under a Manhattan transform)
-    N = float(w.xyz.shape[0])
-    Nf = float(res.keep_mask.sum().item())
+    N = float(ctx["xyz"].shape[0])
+    Nf = float(res.n_filtered)
     Nb = float(res.pt_index.shape[0])
     levels = max(1, max(len(i) for i in res.leaf_ids))
     passes = 6 if es == 8 else 3
@@ -384,28 +476,196 @@ def measure_partition(args, out, ctx):
         if t:
             stage_roof[k] = {"algorithmic_bytes": b, "GBps": b / (t * 1e-3) / 1e9,
                              "hbm_frac": b / (t * 1e-3) / 1e9 / hbm_peak}
-    out["partition_stage_rooflines"] = stage_roof
+    if world == 1:
+        out["partition_stage_rooflines"] = stage_roof
     out["partition"] = {"wall_ms_best": best * 1e3, "wall_ms_mean": float(np.mean(runs)) * 1e3, "runs": len(runs),
+                        "device_resident_ms_best": best_dev * 1e3, "d2h_bytes": int(d2h),
                         "stage_ms": {k: round(v, 3) for k, v in (stages or {}).items()},
-                        "scope": "A1-A9 from the device-resident cloud to device-resident results (+ host scalars)"}
+                        "scope": "A1-A9 from the device-resident cloud to HOST-resident results (leaf tables, "
+                                 "expanded index CSR, per-pair n_hit / ratio / keep, kept CSR); "
+                                 "device_resident_ms_best stops before the device->host copies"}
 
 
-def measure_cpu_baseline(args, out, ctx):
-    """Oracle port of A6-A9 on a bounded sample, in a subprocess (fork pool
-    without a CUDA context)."""
+def prepare_c5(args, ctx):
+    """Config c5 inputs: the 100 M-point cloud and 16 000 camera records (Z-front test of the Vast
+    path, data_partition.py:412)."""
+    D, dev, rank, world = ctx["D"], ctx["dev"], ctx["rank"], ctx["world"]
+    from ptgs_b200 import workload as W
+    t0 = time.perf_counter()
+    w5, xyz5 = load_workload("c5", args.c5_scale, rank, world, dev)
+    recs5 = D.camera_records(w5.R, w5.T, w5.FoVx, w5.FoVy, w5.width, w5.height)
+    recs5[:, 18] = 2.0
+    x, y, z = D.aos_to_soa(xyz5)
+    n = int(xyz5.shape[0])
+    desc = W.describe("c5", args.c5_scale, w5, n)
+    # parity sample: a 1 M-point slice x 16 random cameras, counted by the CPU oracle in the
+    # cpu_baseline leg and by the GPU sweep here
+    sample = None
+    if rank == 0:
+        rng = np.random.default_rng(5)
+        s0 = int(rng.integers(0, max(n - 1_000_000, 1)))
+        s1 = min(n, s0 + 1_000_000)
+        # cameras near the slice would need the geometry; random cameras mostly see nothing of a
+        # random file-order slice -- which is exactly the all-pairs workload (file order = random space)
+        cams = np.sort(rng.choice(len(recs5), size=min(16, len(recs5)), replace=False))
+        sample = dict(points=xyz5[s0:s1].cpu().numpy(), recs=recs5[cams], s0=s0, s1=s1, cams=cams)
+    del xyz5
+    return dict(x=x, y=y, z=z, recs=recs5, n=n, desc=desc, sample=sample, gen_s=time.perf_counter() - t0)
+
+
+def measure_c5(args, out, ctx, c5):
+    """sweep_c5: every point x every camera.  One step = Morton order of the (rank's slice of the)
+    cloud + coverage sweep; N > 1 shards the POINTS (counts summed with one all-reduce)."""
+    D, dev, rank, world = ctx["D"], ctx["dev"], ctx["rank"], ctx["world"]
+    x, y, z, n = c5["x"], c5["y"], c5["z"], c5["n"]
+    cams_d = torch.from_numpy(c5["recs"]).to(dev)
+    C = int(cams_d.shape[0])
+    from ptgs_b200 import multigpu as M
+    p0, p1 = M.point_range(n, rank, world)
+    xs, ys, zs = x[p0:p1], y[p0:p1], z[p0:p1]
+
+    def step(timer=None):
+        mark = timer.mark if timer is not None else (lambda name: None)
+        od = D.spatial_order(xs, ys, zs)
+        mark("c5_order")
+        nh = D.coverage_sweep(xs, ys, zs, cams_d, ordered=od)
+        mark("c5_sweep")
+        if world > 1:
+            nh = M.sum_camera_counts(nh.contiguous(), world)
+            mark("c5_allreduce")
+        return nh
+    step()
+    barrier(world)
+    reps = 3
+    tot, stage = 0.0, {}
+    for i in range(reps):
+        ctx["flush"].fill_(i)
+        tm = D.StageTimer(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(world)
+        e0.record()
+        tm.mark("start")
+        n_hit = step(tm)
+        e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+        for k, t in tm.result().items():
+            stage[k] = stage.get(k, 0.0) + t / reps
+    ms = max_over_ranks(tot / reps, world, dev)
+    tests = float(n) * C
+    hbm_peak = peaks()[0]
+    nh64 = n_hit.to(torch.int64)
+    obj = {"workload": c5["desc"], "ms_per_step": ms, "tests_per_step": tests, "tests_per_s": tests / (ms * 1e-3),
+           "order_ms": round(stage.get("c5_order", 0.0), 3), "sweep_ms": round(stage.get("c5_sweep", 0.0), 3),
+           "hits": int(nh64.sum().item()),
+           "hits_checksum": int((nh64 * torch.arange(1, C + 1, device=dev)).sum().item()),
+           "cameras_with_hits": int((n_hit > 0).sum().item()),
+           "sharding": "points (every rank orders and sweeps n/N points against all cameras; int32 sum all-reduce)"
+           if world > 1 else "single GPU",
+           "scene_generation_s": round(c5["gen_s"], 1),
+           "hbm": {"algorithmic_bytes_survey_Bc64": float(np.ceil(C / 64.0) * n * 12 + C * 84),
+                   "frac_of_peak_at_that_figure": (np.ceil(C / 64.0) * n * 12 + C * 84) / world / (ms * 1e-3) / 1e9 / hbm_peak,
+                   "note": "SURVEY.md 8(d)'s byte figure (camera batches of 64 re-reading the cloud); the sweep reads "
+                           "the cloud once (n x 12 B) after the Morton sort and culls per tile, so this fraction is "
+                           "an algorithmic speed relative to that schedule, not a DRAM utilisation"}}
+    # parity: the GPU's counts of the sample slice x cameras (compared with the oracle's in `parity`)
+    if rank == 0 and c5.get("sample") is not None and c5["sample"].get("want") is not None:
+        s = c5["sample"]
+        px, py, pz = D.aos_to_soa(torch.from_numpy(s["points"]).to(dev))
+        got = D.coverage_sweep(px, py, pz, torch.from_numpy(s["recs"]).to(dev)).cpu().numpy()
+        want = np.asarray(s["want"], dtype=np.int64)
+        out["parity"]["c5_slice"] = {"points": int(len(s["points"])), "cameras": int(len(s["recs"])),
+                                     "count_mismatch": int((got.astype(np.int64) != want).sum()),
+                                     "hits": int(want.sum())}
+    out["sweep_c5"] = obj
+
+
+def measure_secondary(args, out, ctx):
+    """A second BASELINE.json configuration at N = 1 (default c2: Manhattan rotation, float64 cloud):
+    one partition + the visibility step, so the line also carries the round-1 headline workload."""
+    D, dev = ctx["D"], ctx["dev"]
+    from ptgs_b200 import workload as W
+    name = args.secondary
+    w = W.make(name, 1.0)
+    recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+    centers = D.camera_centers(w.R, w.T)
+    xyz = torch.from_numpy(w.xyz).to(dev)
+    best = None
+    for i in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = D.partition_device(xyz, recs, centers, w.threshold, man_trans=w.man_trans, time_stages=(i == 2))
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        best = dt if best is None or (i > 0 and dt < best) else best
+    M_b = np.diff(res.ds_offsets.cpu().numpy())
+    C_b = np.diff(res.cam_offsets.cpu().numpy())
+    tests = int((M_b * C_b).sum())
+    cams_d = torch.from_numpy(recs).to(dev)
+    ms = []
+    for i in range(5):
+        ctx["flush"].fill_(i)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        v = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets, res.cam_index)
+        D.select_cameras(v.keep, res.cam_offsets, res.cam_index, sync=False)
+        e1.record()
+        torch.cuda.synchronize()
+        if i > 0:
+            ms.append(e0.elapsed_time(e1))
+    out["secondary"] = {"workload": W.describe(name, 1.0, w), "leaves": len(res.leaf_ids), "pairs": int(C_b.sum()),
+                        "tests_per_step": tests, "visibility_ms_per_step": float(np.mean(ms)),
+                        "tests_per_s": tests / (float(np.mean(ms)) * 1e-3), "partition_device_ms_best": best * 1e3,
+                        "partition_stage_ms": {k: round(t, 3) for k, t in res.timings_ms.items()},
+                        "kept_cameras": int(v.keep.sum().item())}
+
+
+def measure_cpu_baseline(args, out, ctx, c5):
+    """Oracle port of A6-A9 on a bounded sample, in a subprocess (fork pool without a CUDA
+    context).  The same leg is the CHECKER of the at-size parity report: the per-camera
+    (n_hit, ratio, keep) it computes for its block x cameras are compared with the GPU's results
+    for the same pairs, and the c5 slice is counted by the oracle's coverage_counts."""
     res, blocks, blk_off = ctx["res"], ctx["blocks"], ctx["blk_off"]
-    cam_off = res.cam_offsets.cpu().numpy()
+    cam_off = ctx["cam_off_h"]
     cam_idx = res.cam_index.cpu().numpy()
     b = int(np.argmax(np.diff(cam_off) > 0))
     path = "/tmp/ptgs_cpu_sample_%d.npz" % os.getpid()
-    np.savez(path, points=blocks[blk_off[b]:blk_off[b + 1]].numpy(),
-             recs=ctx["recs"][cam_idx[cam_off[b]:cam_off[b + 1]]])
+    arrays = dict(points=blocks[blk_off[b]:blk_off[b + 1]].numpy(),
+                  recs=ctx["recs"][cam_idx[cam_off[b]:cam_off[b + 1]]])
+    if c5 is not None and c5.get("sample") is not None:
+        arrays["c5_points"], arrays["c5_recs"] = c5["sample"]["points"], c5["sample"]["recs"]
+    np.savez(path, **arrays)
     try:
         r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--sample-file", path,
                             "--steps", "2", "--warmup", "0", "--cpu-seconds", str(args.cpu_seconds)],
-                           capture_output=True, text=True, timeout=600)
+                           capture_output=True, text=True, timeout=900)
         line = [l for l in r.stdout.splitlines() if l.startswith("{")]
-        out["cpu_baseline"] = json.loads(line[-1])["cpu_baseline"] if line else {"error": r.stderr[-400:]}
+        if not line:
+            out["cpu_baseline"] = {"error": r.stderr[-400:]}
+            return
+        d = json.loads(line[-1])
+        out["cpu_baseline"] = d["cpu_baseline"]
+        chk = d.get("check") or {}
+        if "n_hit" in chk:
+            k = len(chk["n_hit"])
+            p0 = int(cam_off[b])
+            g_hit = ctx["vis"].n_hit[p0:p0 + k].cpu().numpy()
+            g_keep = ctx["vis"].keep[p0:p0 + k].cpu().numpy().astype(bool)
+            fl = ctx["flags_h"][p0:p0 + k]
+            ok = (fl & 3) == 0                      # near-threshold / first-ray-collinear pairs are reported apart
+            c_hit, c_keep = np.asarray(chk["n_hit"]), np.asarray(chk["keep"], dtype=bool)
+            c_ratio = np.asarray(chk["ratio"])
+            out["parity"].update({
+                "pairs_checked": int(k), "n_hit_mismatch": int((g_hit != c_hit).sum()),
+                "keep_mismatch": int((g_keep[ok] != c_keep[ok]).sum()),
+                "near_threshold": int((np.abs(c_ratio - 0.45) <= 1e-6).sum()),
+                "edge_flips": int(chk.get("edge_sensitive", 0)),
+                "checker": "oracle port (cpu_baseline leg) on block %d x its first %d cameras; edge_flips = hits of "
+                           "those pairs whose projection lies within 1e-5 (relative to W / H) of an image edge, i.e. "
+                           "that a different BLAS rounding could flip; near_threshold = pairs with |ratio - 0.45| <= 1e-6"
+                           % (b, k)})
+        if "c5_counts" in chk and c5 is not None:
+            c5["sample"]["want"] = chk["c5_counts"]
     except Exception as e:  # the baseline is informative; never fail the bench on it
         out["cpu_baseline"] = {"error": repr(e)}
     finally:
@@ -414,32 +674,37 @@ def measure_cpu_baseline(args, out, ctx):
 
 
 def _reference_prep(args):
-    """CPU-only preparation of the reference arm: scene -> (first non-empty
-    block's expanded points, its cameras' records) with the oracle (A1-A5).
-    Cached in /tmp because the exact radius filter costs about a minute."""
+    """CPU-only preparation of the reference arm: a bounded sample of the workload -- one
+    leaf-sized block and its cameras.  The exact leaf rectangles need the radius filter and the
+    median split over the whole cloud (minutes of CPU at c4), so the sample block is DECLARED as:
+    the scene rectangle cut into the expected leaf grid (gx x gy cells, gx * gy = expected leaves),
+    the cell nearest the scene centre expanded by 5 % per side (densify:222-232), all cloud points
+    inside it, and the cameras whose centre lies strictly inside it (densify:388)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ptgs_oracle as O
     import ptgs_b200  # noqa: F401
     from ptgs_b200 import workload as W
-    cache = "/tmp/ptgs_refprep_%s_%g.npz" % (args.workload, args.scale)
+    cache = "/tmp/ptgs_refprep2_%s_%g.npz" % (args.workload, args.scale)
     if os.path.exists(cache):
         z = np.load(cache, allow_pickle=False)
-        return z["points"], z["recs"], str(z["desc"]), int(z["cores"])
+        return z["points"], z["recs"], str(z["desc"])
     w = W.make(args.workload, args.scale)
     pts = w.xyz if w.man_trans is None else O.manhattan_points(w.xyz, w.man_trans)
-    keep = O.radius_outlier_mask(pts.astype(np.float64))
-    filt = pts.astype(np.float64)[keep]
-    leaves = O.quad_tree_partition(filt, O.bounds_xy(filt), w.threshold)
+    Lx, Ly = float(w.meta["Lx"]), float(w.meta["Ly"])
+    leaves = max(1, int(2 ** np.ceil(np.log2(max(1.0, 0.88 * len(pts) / (1.2 * w.threshold))))))
+    gx = int(2 ** np.ceil(np.log2(leaves) / 2))
+    gy = max(1, leaves // gx)
+    cw, ch = Lx / gx, Ly / gy
+    x0, y0 = -Lx / 2 + (gx // 2) * cw, -Ly / 2 + (gy // 2) * ch
+    box = (x0 - 0.05 * cw, y0 - 0.05 * ch, x0 + 1.05 * cw, y0 + 1.05 * ch)
+    block = pts[O.expand_mask(pts, box)]
     centers = O.camera_centers(w.R, w.T)
-    boxes = [O.expanded_box(l.bounds) for l in leaves]
-    cams = O.assign_cameras(boxes, centers)
-    b = next(i for i, c in enumerate(cams) if len(c) > 0)
-    block = pts[O.expand_mask(pts, boxes[b])]
+    cams = O.assign_cameras([box], centers)[0]
     recs = np.stack([O.camera_record(w.R[c], w.T[c], w.FoVx[c], w.FoVy[c], int(w.width[c]), int(w.height[c]))
-                     for c in cams[b]])
+                     for c in cams])
     desc = W.describe(args.workload, args.scale, w)
-    np.savez(cache, points=block, recs=recs, desc=desc, cores=os.cpu_count() or 1)
-    return block, recs, desc, os.cpu_count() or 1
+    np.savez(cache, points=block, recs=recs, desc=desc)
+    return block, recs, desc
 
 
 def run_reference(args):
@@ -449,24 +714,31 @@ def run_reference(args):
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cpu_arm
+    check = None
     if args.sample_file:
         z = np.load(args.sample_file)
         block, recs, desc = z["points"], z["recs"], "sample file"
         budget = args.cpu_seconds
+        r = cpu_arm.run(block, recs, args.steps, args.warmup, budget, want_results=True)
+        check = r.pop("results")
+        if "c5_points" in z.files:
+            import ptgs_oracle as O
+            check["c5_counts"] = [int(v) for v in O.coverage_counts(z["c5_points"], z["c5_recs"])]
     else:
-        block, recs, desc, _ = _reference_prep(args)
-        budget = 90.0
-    r = cpu_arm.run(block, recs, args.steps, args.warmup, budget)
+        block, recs, desc = _reference_prep(args)
+        r = cpu_arm.run(block, recs, args.steps, args.warmup, 90.0)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "sample": r["sample"]},
-        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "literal") if k in r},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if check is not None:
+        line["check"] = check
     print(json.dumps(line), flush=True)
 
 

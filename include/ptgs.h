@@ -19,7 +19,9 @@
  *   - variable-length outputs: caller allocates capacity, the library writes a
  *     device-side count; PTGS_E_CAPACITY is reported through the device-side
  *     status word (see each call) because the overflow is detected on device.
- *   - no global mutable state: re-entrant across streams, devices and threads.
+ *   - no global mutable state on the device; the only host state is thread
+ *     local (the last error string and the launch counter of the calling
+ *     thread): re-entrant across streams, devices and threads.
  *   - arithmetic: every kernel is compiled with -fmad=false and IEEE division;
  *     fused multiply-adds appear only where this header says "fma".
  */
@@ -531,13 +533,21 @@ int ptgs_vast_unique(int dtype, const void* x, const void* y, const void* z,
                      int64_t capacity, int64_t* n_unique_dev, void* workspace,
                      size_t workspace_bytes, ptgs_stream_t stream);
 
-/* Diagnostics (synchronising; HOST pointer to 8 counters since the last
- * reset): [0] point-camera tests presented to the sweeps, [1] left after the
+/* Diagnostics of a -DPTGS_SWEEP_STATS_FINE build only (the release library
+ * keeps no device-global counters: the call then zeroes out4 and returns
+ * PTGS_E_INVALID).  Synchronising; HOST pointer to 8 counters since the last
+ * reset: [0] point-camera tests presented to the sweeps, [1] left after the
  * CTA-level tile cull, [2] swept per point (sweep 1 / coverage), [3] swept per
  * point (sweep 2), [4] accepted per warp box, [5] accepted per tile box,
  * [6] (warp, camera) passes that entered the exact path, [7] 32-point groups
  * on the exact path.  reset != 0 zeroes the counters. */
 int ptgs_debug_sweep_stats(uint64_t* out4, int32_t reset);
+
+/* Diagnostics for the roofline report: an FP32 FMA loop without memory traffic
+ * (148 x 8 CTAs x 256 threads x 8 independent chains x `iters` FMAs each);
+ * out[148 * 8 * 256] float.  The caller times it: lane-ops/s = threads * 8 *
+ * iters / seconds. */
+int ptgs_debug_fma_probe(float* out, int32_t iters, ptgs_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -28,10 +28,21 @@ def _one_camera(c):
     return O.camera_visibility(_G["ds"], _G["recs"][c])
 
 
-def visibility_step(block_points, recs, workers):
+def _edge_sensitive(c):
+    """Hits of camera c whose projection lies within 1e-5 (relative to the image size) of an image
+    edge: the hits a different SGEMM rounding could flip (north star: reported separately)."""
+    rec = _G["recs"][c]
+    hit, u, v = O.project_port(_G["ds"], rec)
+    W, H = float(rec[16]), float(rec[17])
+    u, v = u[hit].astype(np.float64), v[hit].astype(np.float64)
+    e = (np.minimum(u, W - u) <= 1e-5 * W) | (np.minimum(v, H - v) <= 1e-5 * H)
+    return int(e.sum())
+
+
+def visibility_step(block_points, recs, workers, want_results=False):
     """One block: A6 once, then every camera of `recs` (A7-A9) over a fork
     pool of `workers` processes (the reference uses a 48-thread pool under the
-    GIL, densify:932).  Returns (tests, n_kept, ds_count)."""
+    GIL, densify:932).  Returns (tests, n_kept, ds_count[, per-camera results])."""
     ds = O.voxel_downsample(block_points)
     _G["ds"], _G["recs"] = ds, recs
     n = len(recs)
@@ -40,10 +51,45 @@ def visibility_step(block_points, recs, workers):
             out = pool.map(_one_camera, range(n), chunksize=max(1, n // (4 * workers)))
     else:
         out = [_one_camera(c) for c in range(n)]
+    if want_results:
+        return len(ds) * n, sum(1 for r in out if r[2]), len(ds), out
     return len(ds) * n, sum(1 for r in out if r[2]), len(ds)
 
 
-def run(block_points, recs, steps, warmup, budget_s, workers=None):
+def literal_rate(block_points, recs, budget_s=12.0):
+    """The reference's own formulation restated call for call -- the per-point dict loop of
+    downsample_point_cloud (densify:566-605), project_points_to_camera with torch on the CPU and its
+    .tolist() (densify:410-477), run_graham_scan (densify:481-539) -- on a sub-block small enough
+    for `budget_s` seconds, single thread like the reference's GIL-bound pool.  tests/s."""
+    n = min(len(block_points), 40000)
+    sub = np.ascontiguousarray(block_points[:n])
+    t0 = time.perf_counter()
+    ds = O.voxel_downsample_literal(sub)
+    t_a6 = time.perf_counter() - t0
+    n_cam, t_cam = 0, 0.0
+    for c in range(len(recs)):
+        if t_a6 + t_cam > budget_s and n_cam >= 1:
+            break
+        rec = recs[c]
+        R = np.asarray(rec[0:9], dtype=np.float64).reshape(3, 3)
+        T = np.asarray(rec[9:12], dtype=np.float64)
+        W, H = int(rec[16]), int(rec[17])
+        import math
+        fovx, fovy = 2 * math.atan(W / (2 * float(rec[12]))), 2 * math.atan(H / (2 * float(rec[13])))
+        t0 = time.perf_counter()
+        uv = O.project_points_to_camera_ref(ds, R, T, fovx, fovy, W, H).tolist()
+        if len(uv) > 3:
+            O.run_graham_scan(uv, W, H)
+        t_cam += time.perf_counter() - t0
+        n_cam += 1
+    t = t_a6 + t_cam
+    return {"value": len(ds) * n_cam / t if t > 0 else None, "unit": "tests/s", "cores": 1,
+            "sample": "first %d points of the block -> %d voxels (dict loop %.2f s) x %d cameras (%.2f s)"
+                      % (n, len(ds), t_a6, n_cam, t_cam),
+            "kind": "port, literal formulation of the reference's loops (densify:541-614, :410-539)"}
+
+
+def run(block_points, recs, steps, warmup, budget_s, workers=None, want_results=False):
     """Times `steps` visibility steps on a bounded sample: the given block and
     as many of its cameras as fit `budget_s` seconds in total (calibrated on
     the first cameras).  Returns a dict for the JSON line."""
@@ -64,15 +110,25 @@ def run(block_points, recs, steps, warmup, budget_s, workers=None):
     use = recs[:n_cam]
     for _ in range(warmup):
         visibility_step(block_points, use, workers)
-    times, tests = [], 0
+    times, tests, results = [], 0, None
     for _ in range(steps):
         t0 = time.perf_counter()
-        tests, kept, m = visibility_step(block_points, use, workers)
+        tests, kept, m, results = visibility_step(block_points, use, workers, want_results=True)
         times.append(time.perf_counter() - t0)
     t = float(np.mean(times)) if times else float("nan")
-    return {
+    out = {
         "value": tests / t if times else None, "unit": "tests/s", "cores": int(min(workers, max(n_cam, 1))),
         "kind": "port", "seconds_per_step": t, "tests_per_step": int(tests),
-        "sample": "first block (%d expanded points -> %d voxels) x its first %d cameras, A6-A9 per step" % (
+        "sample": "one block (%d expanded points -> %d voxels) x its first %d cameras, A6-A9 per step" % (
             len(block_points), len(ds), n_cam),
     }
+    try:
+        out["literal"] = literal_rate(block_points, recs)
+    except Exception as e:   # informative
+        out["literal"] = {"error": repr(e)}
+    if want_results and results is not None:
+        _G["ds"], _G["recs"] = ds, use
+        out["results"] = {"n_hit": [int(r[0]) for r in results], "ratio": [float(r[1]) for r in results],
+                          "keep": [bool(r[2]) for r in results],
+                          "edge_sensitive": int(sum(_edge_sensitive(c) for c in range(len(use))))}
+    return out
