@@ -27,6 +27,7 @@ SIGNATURES = {
     "ptgs_aos_to_soa_f32": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     "ptgs_aos_to_soa_f64": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     "ptgs_manhattan_apply": (C.c_int, [_vp, _vp, _vp, _i64, C.POINTER(_f64), _vp, _vp, _vp, _vp]),
+    "ptgs_aos_to_soa_manhattan": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp, _vp, _vp, _vp]),
     "ptgs_radius_outlier_workspace_bytes": (_sz, [_i64]),
     "ptgs_radius_outlier_mask": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _f64, C.c_int, _vp, _vp,
                                            _vp, _sz, _vp]),

@@ -99,6 +99,53 @@ __global__ void __launch_bounds__(256) manhattan_kernel(
   }
 }
 
+// AoS float32 -> planar float64 with the Manhattan transform applied on the way
+// (layout + A13 in ONE pass: 12 B read + 24 B written per point instead of the
+// 24 + 36 B of aos_to_soa followed by manhattan_kernel).  Same arithmetic as
+// manhattan_kernel.  4 points per thread: 3 float4 loads, 6 double2 stores.
+__device__ __forceinline__ void man_point(const Man& m, float fx, float fy, float fz, double& ox,
+                                          double& oy, double& oz) {
+  const double px = fx, py = fy, pz = fz;
+  double a = __dmul_rn(m.r[0], px);
+  a = fma(m.r[1], py, a);
+  a = fma(m.r[2], pz, a);
+  double b = __dmul_rn(m.r[3], px);
+  b = fma(m.r[4], py, b);
+  b = fma(m.r[5], pz, b);
+  double c = __dmul_rn(m.r[6], px);
+  c = fma(m.r[7], py, c);
+  c = fma(m.r[8], pz, c);
+  ox = __dadd_rn(a, m.t[0]);
+  oy = __dadd_rn(b, m.t[1]);
+  oz = __dadd_rn(c, m.t[2]);
+}
+
+__global__ void __launch_bounds__(256) aos_manhattan_kernel(
+    const float* __restrict__ xyz, int64_t n, Man m, double* __restrict__ ox,
+    double* __restrict__ oy, double* __restrict__ oz) {
+  const int64_t n4 = n / 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const float4* in = reinterpret_cast<const float4*>(xyz);
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += stride) {
+    const float4 a = __ldg(in + 3 * g), b = __ldg(in + 3 * g + 1), c = __ldg(in + 3 * g + 2);
+    double x0, y0, z0, x1, y1, z1, x2, y2, z2, x3, y3, z3;
+    man_point(m, a.x, a.y, a.z, x0, y0, z0);
+    man_point(m, a.w, b.x, b.y, x1, y1, z1);
+    man_point(m, b.z, b.w, c.x, x2, y2, z2);
+    man_point(m, c.y, c.z, c.w, x3, y3, z3);
+    double2* px = reinterpret_cast<double2*>(ox) + 2 * g;
+    double2* py = reinterpret_cast<double2*>(oy) + 2 * g;
+    double2* pz = reinterpret_cast<double2*>(oz) + 2 * g;
+    px[0] = make_double2(x0, x1); px[1] = make_double2(x2, x3);
+    py[0] = make_double2(y0, y1); py[1] = make_double2(y2, y3);
+    pz[0] = make_double2(z0, z1); pz[1] = make_double2(z2, z3);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const int64_t i = n4 * 4 + threadIdx.x;
+    man_point(m, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], ox[i], oy[i], oz[i]);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // XY bounds: block reduce in registers/shuffles, one atomic per block on
 // order-preserving keys.
@@ -294,6 +341,24 @@ int ptgs_manhattan_apply(const float* x, const float* y, const float* z,
   }
   int grid = grid_for(n, 256, kNumSMs * 8);
   manhattan_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, y, z, n, m, ox, oy, oz);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_aos_to_soa_manhattan(const float* xyz, int64_t n, const double* man_trans_host,
+                              double* ox, double* oy, double* oz, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && man_trans_host, "n / man_trans");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(((uintptr_t)xyz % 16 == 0) && ((uintptr_t)ox % 16 == 0) &&
+                   ((uintptr_t)oy % 16 == 0) && ((uintptr_t)oz % 16 == 0),
+               "pointers must be 16-byte aligned");
+  Man m;
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) m.r[r * 3 + c] = man_trans_host[r * 4 + c];
+    m.t[r] = man_trans_host[r * 4 + 3];
+  }
+  int grid = grid_for(n / 4 + 1, 256, kNumSMs * 8);
+  aos_manhattan_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz, n, m, ox, oy, oz);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

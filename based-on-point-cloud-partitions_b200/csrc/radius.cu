@@ -15,32 +15,41 @@ namespace ptgs {
 struct GridSpec {
   double xmin, ymin, inv_cell;
   long long nx, ny;
+  // narrow (32-bit) keys: column << zbits | z bucket, bucket = floor((z - zmin) * inv_cell) >> zshift
+  double zmin;
+  long long nzf;        // fine z cells (cell = the XY cell size)
+  int zbits, zshift;
 };
 
 template <typename T>
 __global__ void __launch_bounds__(256) minmax_xy_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, int64_t n,
-    unsigned long long* __restrict__ keys /*xmin,ymin,xmax,ymax as u64 keys of double*/) {
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, int64_t n,
+    unsigned long long* __restrict__ keys /*xmin,ymin,xmax,ymax,zmin,zmax as u64 keys of double*/) {
   using KD = KeyOf<double>;
-  uint64_t xmin = ~0ull, ymin = ~0ull, xmax = 0, ymax = 0;
+  uint64_t xmin = ~0ull, ymin = ~0ull, zmin = ~0ull, xmax = 0, ymax = 0, zmax = 0;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint64_t kx = KD::encode((double)x[i]), ky = KD::encode((double)y[i]);
+    uint64_t kx = KD::encode((double)x[i]), ky = KD::encode((double)y[i]), kz = KD::encode((double)z[i]);
     xmin = min(xmin, kx); xmax = max(xmax, kx);
     ymin = min(ymin, ky); ymax = max(ymax, ky);
+    zmin = min(zmin, kz); zmax = max(zmax, kz);
   }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {
     xmin = min(xmin, __shfl_xor_sync(kFullMask, xmin, d));
     ymin = min(ymin, __shfl_xor_sync(kFullMask, ymin, d));
+    zmin = min(zmin, __shfl_xor_sync(kFullMask, zmin, d));
     xmax = max(xmax, __shfl_xor_sync(kFullMask, xmax, d));
     ymax = max(ymax, __shfl_xor_sync(kFullMask, ymax, d));
+    zmax = max(zmax, __shfl_xor_sync(kFullMask, zmax, d));
   }
   if (lane_id() == 0) {
     atomicMin(keys + 0, (unsigned long long)xmin);
     atomicMin(keys + 1, (unsigned long long)ymin);
     atomicMax(keys + 2, (unsigned long long)xmax);
     atomicMax(keys + 3, (unsigned long long)ymax);
+    atomicMin(keys + 4, (unsigned long long)zmin);
+    atomicMax(keys + 5, (unsigned long long)zmax);
   }
 }
 
@@ -56,15 +65,30 @@ __device__ __forceinline__ uint32_t zkey_of(float f) {
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
 
-template <typename T>
+// z bucket of the narrow key: monotone in z (every operation is a correctly rounded,
+// monotone float64 function), clamped to the bucket range
+__device__ __forceinline__ uint32_t zbucket_of(double z, const GridSpec& g) {
+  const double f = floor((z - g.zmin) * g.inv_cell);
+  const long long c = (f >= 0.0) ? ((f < (double)g.nzf) ? (long long)f : g.nzf - 1) : 0;   // NaN -> 0
+  return (uint32_t)(c >> g.zshift);
+}
+
+// Key layout: column << ZB | z part.  WIDE: 64-bit keys, ZB = 32, z part = the order-preserving
+// image of float(z) (exact height order inside a column).  Narrow: 32-bit keys, ZB = g.zbits, z
+// part = the z bucket -- half the sort traffic and 4 instead of 7 radix passes at 50 M points.
+template <typename T, typename K>
 __global__ void __launch_bounds__(256) column_key_kernel(
     const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, int64_t n, GridSpec g,
-    uint64_t* __restrict__ keys, uint32_t* __restrict__ idx) {
+    K* __restrict__ keys, uint32_t* __restrict__ idx) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     long long ix = cell_of((double)x[i], g.xmin, g.inv_cell, g.nx);
     long long iy = cell_of((double)y[i], g.ymin, g.inv_cell, g.ny);
-    keys[i] = ((uint64_t)(ix * g.ny + iy) << 32) | zkey_of((float)z[i]);   // float(z): monotone in z
+    const uint64_t col = (uint64_t)(ix * g.ny + iy);
+    if (sizeof(K) == 8)
+      keys[i] = (K)((col << 32) | zkey_of((float)z[i]));   // float(z): monotone in z
+    else
+      keys[i] = (K)(((uint32_t)col << g.zbits) | zbucket_of((double)z[i], g));
     idx[i] = (uint32_t)i;
   }
 }
@@ -132,15 +156,16 @@ __global__ void __launch_bounds__(256) radius_count_kernel(
 // cell_start[k] = first sorted position whose key is >= k (k in [0, ncell]); one
 // thread per sorted point fills the gap of (possibly empty) cells that ends at
 // its own key.
-__global__ void __launch_bounds__(256) cell_start_kernel(const uint64_t* __restrict__ keys, int64_t n,
+template <typename K>
+__global__ void __launch_bounds__(256) cell_start_kernel(const K* __restrict__ keys, int64_t n, int zb,
                                                          uint64_t ncell, uint32_t* __restrict__ cs) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const uint64_t k = keys[i] >> 32;
+  const uint64_t k = (uint64_t)(keys[i] >> zb);
   if (i == 0) {
     for (uint64_t c = 0; c <= k; ++c) cs[c] = 0u;
   } else {
-    const uint64_t kp = keys[i - 1] >> 32;
+    const uint64_t kp = (uint64_t)(keys[i - 1] >> zb);
     for (uint64_t c = kp + 1; c <= k; ++c) cs[c] = (uint32_t)i;
   }
   if (i == n - 1)
@@ -150,23 +175,35 @@ __global__ void __launch_bounds__(256) cell_start_kernel(const uint64_t* __restr
 // Neighbour count with the cell table: the point's own cell first (most likely
 // to hold close neighbours, so the `> nb_points` early exit comes soonest), then
 // the 8 surrounding cells.
-template <typename T>
+template <typename T, typename K>
 __global__ void __launch_bounds__(256) radius_count_cells_kernel(
     const T* __restrict__ sx, const T* __restrict__ sy, const T* __restrict__ sz,
-    const uint64_t* __restrict__ keys, const uint32_t* __restrict__ idx,
+    const K* __restrict__ keys, const uint32_t* __restrict__ idx,
     const uint32_t* __restrict__ cs, int64_t n, GridSpec g, double r2, int nb,
     uint8_t* __restrict__ keep, unsigned long long* __restrict__ n_keep) {
+  constexpr bool kWide = sizeof(K) == 8;
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int kept = 0;
   if (p < n) {
     const double xi = (double)sx[p], yi = (double)sy[p], zi = (double)sz[p];
-    const uint64_t key = keys[p] >> 32;
+    const int zb = kWide ? 32 : g.zbits;
+    const uint32_t zmask = kWide ? 0xffffffffu : ((1u << g.zbits) - 1u);
+    const uint64_t key = (uint64_t)(keys[p] >> zb);
     const long long ix = (long long)(key / (uint64_t)g.ny);
     const long long iy = (long long)(key % (uint64_t)g.ny);
-    // height slab in the (rounded-to-float) sort order: conservative by one float step
+    // height slab in the sort order of the column.  Wide keys: the (rounded-to-float) height
+    // itself, conservative by one float step.  Narrow keys: the buckets of zi -+ r with the
+    // difference rounded away from zi, so every z within r of zi falls into [zlo, zhi] (the
+    // bucket function is monotone).
     const double rr = sqrt(r2);
-    const uint32_t zlo = zkey_of(__double2float_rd(zi - rr)) - 1u;
-    const uint32_t zhi = zkey_of(__double2float_ru(zi + rr)) + 1u;
+    uint32_t zlo, zhi;
+    if (kWide) {
+      zlo = zkey_of(__double2float_rd(zi - rr)) - 1u;
+      zhi = zkey_of(__double2float_ru(zi + rr)) + 1u;
+    } else {
+      zlo = zbucket_of(__dadd_rd(zi, -rr), g);
+      zhi = zbucket_of(__dadd_ru(zi, rr), g);
+    }
     int cnt = 0;
     // visiting order: (0,0), then the 4 edge neighbours, then the 4 corners
     const int ox[9] = {0, 0, 0, -1, 1, -1, -1, 1, 1};
@@ -180,10 +217,10 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
       uint32_t lo = __ldg(cs + k), hi = j1;
       while (lo < hi) {                      // first point of the column inside the slab
         const uint32_t mid = (lo + hi) >> 1;
-        if ((uint32_t)__ldg(keys + mid) < zlo) lo = mid + 1; else hi = mid;
+        if (((uint32_t)__ldg(keys + mid) & zmask) < zlo) lo = mid + 1; else hi = mid;
       }
       for (uint32_t j = lo; j < j1 && cnt <= nb; ++j) {
-        if ((uint32_t)__ldg(keys + j) > zhi) break;
+        if (((uint32_t)__ldg(keys + j) & zmask) > zhi) break;
         double ddx = __dsub_rn((double)sx[j], xi);
         double ddy = __dsub_rn((double)sy[j], yi);
         double ddz = __dsub_rn((double)sz[j], zi);
@@ -209,10 +246,12 @@ static inline int grid_for(int64_t n, int per_block, int max_blocks) {
 }
 
 static size_t sort_temp_bytes(int64_t n) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+  size_t b64 = 0, b32 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, b64, (const uint64_t*)nullptr, (uint64_t*)nullptr,
                                   (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0, 64);
-  return bytes;
+  cub::DeviceRadixSort::SortPairs(nullptr, b32, (const uint32_t*)nullptr, (uint32_t*)nullptr,
+                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0, 32);
+  return b64 > b32 ? b64 : b32;
 }
 
 template <typename T>
@@ -221,7 +260,7 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
                        void* workspace, cudaStream_t st) {
   const T* x = (const T*)vx; const T* y = (const T*)vy; const T* z = (const T*)vz;
   Carver cv(workspace);
-  unsigned long long* mm = cv.take<unsigned long long>(4);
+  unsigned long long* mm = cv.take<unsigned long long>(6);
   uint64_t* keys_a = cv.take<uint64_t>(n);
   uint64_t* keys_b = cv.take<uint64_t>(n);
   uint32_t* idx_a = cv.take<uint32_t>(n);
@@ -231,19 +270,22 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
   void* sort_tmp = cv.take<char>(tb);
   uint32_t* cell_start = cv.take<uint32_t>(cell_table_capacity(n) + 2);
 
-  const unsigned long long init[4] = {~0ull, ~0ull, 0ull, 0ull};
+  const unsigned long long init[6] = {~0ull, ~0ull, 0ull, 0ull, ~0ull, 0ull};
   PTGS_CUDA_TRY(cudaMemcpyAsync(mm, init, sizeof(init), cudaMemcpyHostToDevice, st));
   PTGS_CUDA_TRY(cudaMemsetAsync(n_keep, 0, 8, st));
   int g1 = grid_for(n, 2048, kNumSMs * 8);
-  minmax_xy_kernel<T><<<g1, 256, 0, st>>>(x, y, n, mm);
+  minmax_xy_kernel<T><<<g1, 256, 0, st>>>(x, y, z, n, mm);
   PTGS_LAUNCH_CHECK();
-  unsigned long long h[4];
+  unsigned long long h[6];
+  // synchronises: the grid dimensions size the sort and the cell table
   PTGS_CUDA_TRY(cudaMemcpyAsync(h, mm, sizeof(h), cudaMemcpyDeviceToHost, st));
   PTGS_CUDA_TRY(cudaStreamSynchronize(st));
   GridSpec g;
   g.xmin = KeyOf<double>::decode(h[0]);
   g.ymin = KeyOf<double>::decode(h[1]);
   const double xmax = KeyOf<double>::decode(h[2]), ymax = KeyOf<double>::decode(h[3]);
+  g.zmin = KeyOf<double>::decode(h[4]);
+  const double zmax = KeyOf<double>::decode(h[5]);
   const double cell = radius * (1.0 + 1.0 / 8192.0);
   g.inv_cell = 1.0 / cell;
   g.nx = (long long)floor((xmax - g.xmin) * g.inv_cell) + 1;
@@ -256,25 +298,59 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
     set_error("radius_outlier: grid %lld x %lld has more than 2^31 columns", g.nx, g.ny);
     return PTGS_E_RANGE;
   }
-  int bits = 1;
-  while (bits < 32 && ((unsigned long long)(g.nx * g.ny - 1) >> bits)) ++bits;
-  bits += 32;                                // column | height key
-  column_key_kernel<T><<<g1, 256, 0, st>>>(x, y, z, n, g, keys_a, idx_a);
+  int colbits = 1;
+  while (colbits < 32 && ((unsigned long long)(g.nx * g.ny - 1) >> colbits)) ++colbits;
+  const uint64_t ncell = (uint64_t)g.nx * (uint64_t)g.ny;
+  const bool table = ncell <= cell_table_capacity(n);
+  // narrow keys: column | z bucket in 32 bits.  Buckets are 2^zshift cells tall; the coarser they
+  // are the more candidates a query walks, so at most 4 cells (the slab then spans <= 12 of them)
+  g.nzf = 1; g.zbits = 1; g.zshift = 0;
+  bool narrow = false;
+  {
+    const double nz = floor((zmax - g.zmin) * g.inv_cell) + 1.0;
+    if (table && nz >= 1.0 && nz < 1.0e9) {
+      g.nzf = (long long)nz;
+      for (int sh = 0; sh <= 2 && !narrow; ++sh) {
+        int zb = 1;
+        while (zb < 31 && (((unsigned long long)(g.nzf - 1) >> sh) >> zb)) ++zb;
+        if (colbits + zb <= 32) { narrow = true; g.zshift = sh; g.zbits = zb; }
+      }
+    }
+  }
+  const int nthreads_blocks = (int)((n + 255) / 256);
+  if (narrow) {
+    uint32_t* k32a = reinterpret_cast<uint32_t*>(keys_a);
+    uint32_t* k32b = reinterpret_cast<uint32_t*>(keys_b);
+    const int bits = colbits + g.zbits;
+    column_key_kernel<T, uint32_t><<<g1, 256, 0, st>>>(x, y, z, n, g, k32a, idx_a);
+    PTGS_LAUNCH_CHECK();
+    PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, k32a, k32b, idx_a, idx_b, (int64_t)n, 0, bits, st));
+    count_launch(2 + (bits + 7) / 8);
+    gather_sorted_kernel<T><<<g1, 256, 0, st>>>(x, y, z, idx_b, n, sx, sy, sz);
+    PTGS_LAUNCH_CHECK();
+    cell_start_kernel<uint32_t><<<nthreads_blocks, 256, 0, st>>>(k32b, n, g.zbits, ncell, cell_start);
+    PTGS_LAUNCH_CHECK();
+    radius_count_cells_kernel<T, uint32_t><<<nthreads_blocks, 256, 0, st>>>(
+        sx, sy, sz, k32b, idx_b, cell_start, n, g, radius * radius, nb, keep, (unsigned long long*)n_keep);
+    PTGS_LAUNCH_CHECK();
+    return PTGS_OK;
+  }
+  const int bits = colbits + 32;             // column | height key
+  column_key_kernel<T, uint64_t><<<g1, 256, 0, st>>>(x, y, z, n, g, keys_a, idx_a);
   PTGS_LAUNCH_CHECK();
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, idx_b,
                                                 (int64_t)n, 0, bits, st));
   count_launch(2 + (bits + 7) / 8);
   gather_sorted_kernel<T><<<g1, 256, 0, st>>>(x, y, z, idx_b, n, sx, sy, sz);
   PTGS_LAUNCH_CHECK();
-  const uint64_t ncell = (uint64_t)g.nx * (uint64_t)g.ny;
-  if (ncell <= cell_table_capacity(n)) {
-    cell_start_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(keys_b, n, ncell, cell_start);
+  if (table) {
+    cell_start_kernel<uint64_t><<<nthreads_blocks, 256, 0, st>>>(keys_b, n, 32, ncell, cell_start);
     PTGS_LAUNCH_CHECK();
-    radius_count_cells_kernel<T><<<(int)((n + 255) / 256), 256, 0, st>>>(
+    radius_count_cells_kernel<T, uint64_t><<<nthreads_blocks, 256, 0, st>>>(
         sx, sy, sz, keys_b, idx_b, cell_start, n, g, radius * radius, nb, keep,
         (unsigned long long*)n_keep);
   } else {   // very sparse grid (far outliers): binary search per column
-    radius_count_kernel<T><<<(int)((n + 255) / 256), 256, 0, st>>>(
+    radius_count_kernel<T><<<nthreads_blocks, 256, 0, st>>>(
         sx, sy, sz, keys_b, idx_b, n, g, radius * radius, nb, keep,
         (unsigned long long*)n_keep);
   }

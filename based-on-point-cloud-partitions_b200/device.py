@@ -135,6 +135,21 @@ def manhattan_apply(x, y, z, man_trans: np.ndarray):
     return ox, oy, oz
 
 
+def aos_to_soa_manhattan(xyz: torch.Tensor, man_trans: np.ndarray):
+    """(N,3) float32 device tensor -> planar float64 x, y, z in the Manhattan frame, one pass
+    (ptgs_aos_to_soa_manhattan == manhattan_apply(*aos_to_soa(xyz), man_trans))."""
+    lib = _lib.load()
+    assert xyz.is_cuda and xyz.dtype == torch.float32 and xyz.is_contiguous()
+    n = xyz.shape[0]
+    m = np.ascontiguousarray(man_trans, dtype=np.float64)
+    pitch = (n + 8 + 1) // 2 * 2
+    buf = torch.zeros((3, pitch), dtype=torch.float64, device=xyz.device)
+    ox, oy, oz = buf[0, :n], buf[1, :n], buf[2, :n]
+    check(lib.ptgs_aos_to_soa_manhattan(_ptr(xyz), n, m.ctypes.data_as(C.POINTER(C.c_double)), _ptr(ox), _ptr(oy),
+                                        _ptr(oz), _stream()))
+    return ox, oy, oz
+
+
 def radius_outlier_mask(x, y, z, radius=RADIUS, nb_points=NB_POINTS):
     lib = _lib.load()
     n = x.shape[0]
@@ -718,9 +733,10 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     dev = xyz.device
     tm = _Timer(time_stages)
     tm.mark("start")
-    x, y, z = aos_to_soa(xyz)
     if man_trans is not None:
-        x, y, z = manhattan_apply(x, y, z, man_trans)
+        x, y, z = aos_to_soa_manhattan(xyz, man_trans)
+    else:
+        x, y, z = aos_to_soa(xyz)
     tm.mark("layout")
     if split_xyz is not None:
         sx, sy, sz = aos_to_soa(split_xyz)

@@ -83,6 +83,14 @@ int ptgs_manhattan_apply(const float* x, const float* y, const float* z,
                          int64_t n, const double* man_trans_host, double* ox,
                          double* oy, double* oz, ptgs_stream_t stream);
 
+/* Layout + A13 in one pass: (N,3) row-major float32 -> planar float64 with the
+ * Manhattan transform of ptgs_manhattan_apply applied on the way (identical
+ * arithmetic, 36 instead of 60 bytes of traffic per point).  16-byte aligned
+ * pointers; `man_trans` is a HOST pointer to the row-major 4x4 matrix. */
+int ptgs_aos_to_soa_manhattan(const float* xyz, int64_t n,
+                              const double* man_trans_host, double* ox,
+                              double* oy, double* oz, ptgs_stream_t stream);
+
 /* ------------------------------------------------------------------ *
  * A1 -- radius outlier removal
  *   replaces o3d PointCloud.remove_radius_outlier(nb_points, radius) as

@@ -24,13 +24,19 @@ def _csr_lists(off, idx):
     return [idx[off[i]:off[i + 1]] for i in range(len(off) - 1)]
 
 
-@pytest.mark.parametrize("n,seed", [(0, 1), (1, 2), (37, 3), (5000, 4), (60000, 5)])
-def test_radius_mask(n, seed):
+@pytest.mark.parametrize("n,seed,zfar", [(0, 1, None), (1, 2, None), (37, 3, None), (5000, 4, None),
+                                         (60000, 5, None), (5000, 6, 1.2e8), (5000, 7, 3.0e9)])
+def test_radius_mask(n, seed, zfar):
+    """zfar: one point far above the cloud -- 1.2e8 needs coarse (4-cell) height buckets in the
+    32-bit sort keys, 3e9 does not fit them at all (64-bit keys with the exact height order)."""
     rng = np.random.default_rng(seed)
     pts = (rng.uniform(0, max(1.0, (n / 48.0) ** 0.5), (n, 3)) * [1, 1, 0.2]).astype(np.float32)
     if n > 100:
         pts[:50] += 500.0   # isolated points
         pts[50:60] = pts[60]  # exact duplicates
+        pts[100:160, 2] += rng.uniform(0, 40, 60).astype(np.float32)   # tall columns
+    if zfar is not None:
+        pts[200, 2] = zfar
     x, y, z = D.aos_to_soa(torch.from_numpy(pts).to(DEV)) if n else (torch.empty(0, device=DEV),) * 3
     keep, n_keep = D.radius_outlier_mask(x, y, z)
     want = O.radius_outlier_mask(pts.astype(np.float64))
@@ -62,6 +68,11 @@ def test_split_expand_assign(f64):
         pts = O.manhattan_points(sc.xyz, man)
         got = np.stack([x.cpu().numpy(), y.cpu().numpy(), z.cpu().numpy()], 1)
         assert np.array_equal(got, pts), "manhattan rotation must be bit-identical to NumPy"
+        # the fused layout + rotation pass (what partition_device runs), incl. a ragged tail
+        for n in (len(sc.xyz), 4099, 3, 0):
+            fx_, fy_, fz_ = D.aos_to_soa_manhattan(_dev_xyz(sc)[:n].contiguous(), man)
+            got = np.stack([fx_.cpu().numpy(), fy_.cpu().numpy(), fz_.cpu().numpy()], 1)
+            assert np.array_equal(got, pts[:n]), n
     keep, _ = D.radius_outlier_mask(x, y, z)
     want_keep = O.radius_outlier_mask(pts.astype(np.float64))
     assert np.array_equal(keep.cpu().numpy().astype(bool), want_keep)
