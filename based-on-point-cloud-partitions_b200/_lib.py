@@ -65,6 +65,8 @@ SIGNATURES = {
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
                                        _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "ptgs_points3d_index": (_i64, [_vp, _i64, _vp, _i64]),
+    "ptgs_points3d_decode": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_pack_records": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
     "ptgs_unpack_records": (C.c_int, [_vp, _i32, _i64, C.POINTER(_i64), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),

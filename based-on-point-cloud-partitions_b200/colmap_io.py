@@ -37,6 +37,7 @@ class ColmapImages(NamedTuple):
     tvecs: np.ndarray      # (C,3) float64
     camera_ids: np.ndarray  # (C,) int32
     names: list            # str
+    point3D_ids: list = None   # per image int64 array (colmap_loader.py:276-277), when requested
 
 
 def read_cameras_binary(path) -> dict:
@@ -56,9 +57,10 @@ def read_cameras_binary(path) -> dict:
     return cams
 
 
-def read_images_binary(path) -> ColmapImages:
+def read_images_binary(path, with_point3D_ids: bool = False) -> ColmapImages:
     """colmap_loader.read_extrinsics_binary (:250-282) without materialising
-    the per-image 2D point lists."""
+    the per-image 2D point lists; with_point3D_ids keeps the point3D id column of
+    the 2D observations (one strided view per image, :276-277)."""
     with open(path, "rb") as f:
         buf = f.read()
     n = struct.unpack_from("<Q", buf, 0)[0]
@@ -67,6 +69,7 @@ def read_images_binary(path) -> ColmapImages:
     t = np.empty((n, 3), np.float64)
     cid = np.empty(n, np.int32)
     names = []
+    p3d = [] if with_point3D_ids else None
     off = 8
     for i in range(n):
         rec = struct.unpack_from("<idddddddi", buf, off)
@@ -79,38 +82,106 @@ def read_images_binary(path) -> ColmapImages:
         names.append(buf[off:end].decode("utf-8"))
         off = end + 1
         n2d = struct.unpack_from("<Q", buf, off)[0]
+        if p3d is not None:
+            p3d.append(np.frombuffer(buf, dtype=_P2D, count=n2d, offset=off + 8)["id"].copy())
         off += 8 + 24 * n2d
-    return ColmapImages(ids, q, t, cid, names)
+    return ColmapImages(ids, q, t, cid, names, p3d)
 
 
+_P2D = np.dtype([("xy", "<f8", 2), ("id", "<i8")])
 _P3D_HEAD = np.dtype([("id", "<u8"), ("xyz", "<f8", 3), ("rgb", "u1", 3), ("error", "<f8"), ("track", "<u8")])
+
+
+def _record_offsets(buf, n):
+    """Byte offset of every points3D record: libptgs' host walk (ptgs_points3d_index)."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    off = np.empty(n, dtype=np.int64)
+    src = np.frombuffer(buf, dtype=np.uint8)
+    got = lib.ptgs_points3d_index(C.c_void_p(src.ctypes.data), len(buf), C.c_void_p(off.ctypes.data), n)
+    if got != n:
+        raise ValueError("points3D.bin: %s" % lib.ptgs_last_error().decode("utf-8", "replace"))
+    return off
 
 
 def read_points3D_binary(path):
     """colmap_loader.read_points3D_binary (:195-224): (xyz f64 (N,3), rgb u8
-    (N,3), error f64 (N,)).  Fixed 43-byte head + 8 bytes per track element;
-    when every track has the same length (the files this package writes have
-    none) the whole file is one structured frombuffer."""
+    (N,3), error f64 (N,)).  Fixed 51-byte head + 8 bytes per track element.  Without tracks
+    the whole file is one structured frombuffer; with tracks the record offsets come from one
+    native walk over the file image and the heads are gathered with one fancy index -- no
+    per-point Python loop either way (the reference unpacks record by record)."""
     with open(path, "rb") as f:
         buf = f.read()
     n = struct.unpack_from("<Q", buf, 0)[0]
-    head = _P3D_HEAD.itemsize  # 43
+    head = _P3D_HEAD.itemsize  # 51
     if n == 0:
         return np.zeros((0, 3)), np.zeros((0, 3), np.uint8), np.zeros(0)
     if len(buf) == 8 + n * head:  # no tracks at all
         a = np.frombuffer(buf, dtype=_P3D_HEAD, count=n, offset=8)
         return a["xyz"].copy(), a["rgb"].copy(), a["error"].copy()
-    xyz = np.empty((n, 3), np.float64)
-    rgb = np.empty((n, 3), np.uint8)
-    err = np.empty(n, np.float64)
-    off = 8
-    for i in range(n):
-        _, x, y, z, r, g, b, e, tl = struct.unpack_from("<QdddBBBdQ", buf, off)
-        xyz[i] = (x, y, z)
-        rgb[i] = (r, g, b)
-        err[i] = e
-        off += head + 8 * tl
-    return xyz, rgb, err
+    off = _record_offsets(buf, n)
+    raw = np.frombuffer(buf, dtype=np.uint8)
+    heads = raw[off[:, None] + np.arange(head, dtype=np.int64)[None, :]]        # (n, 43) gather
+    a = heads.reshape(-1).view(_P3D_HEAD)
+    return a["xyz"].copy(), a["rgb"].copy(), a["error"].copy()
+
+
+def read_points3D_to_device(path, device, want_rgb: bool = True):
+    """points3D.bin -> planar float32 device tensors without the PLY round trip
+    (shen_data_read.py:185-193 converts to points3D.ply and reads it back): the file image goes
+    to the device through pinned memory and ptgs_points3d_decode extracts xyz (with storePly's
+    float32 cast), rgb and the error there.  Returns (x, y, z, rgb (N,3) u8 or None)."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    lib = _lib.load()
+    size = os.path.getsize(path)
+    host = torch.empty(size, dtype=torch.uint8, pin_memory=True)
+    with open(path, "rb") as f:
+        f.readinto(memoryview(host.numpy()))
+    buf = host.numpy()
+    n = int(struct.unpack_from("<Q", buf, 0)[0])
+    off = torch.empty(max(n, 1), dtype=torch.int64, pin_memory=True)
+    got = lib.ptgs_points3d_index(C.c_void_p(buf.ctypes.data), size, C.c_void_p(off.numpy().ctypes.data), n)
+    if got != n:
+        raise ValueError("points3D.bin: %s" % lib.ptgs_last_error().decode("utf-8", "replace"))
+    dev = torch.device(device)
+    file_d = host.to(dev, non_blocking=True)
+    off_d = off.to(dev, non_blocking=True)
+    pitch = (n + 8 + 3) // 4 * 4
+    planes = torch.zeros((3, pitch), dtype=torch.float32, device=dev)
+    rgb = torch.empty((max(n, 1), 3), dtype=torch.uint8, device=dev) if want_rgb else None
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(lib.ptgs_points3d_decode(C.c_void_p(file_d.data_ptr()), C.c_void_p(off_d.data_ptr()), n,
+                                        C.c_void_p(planes[0].data_ptr()), C.c_void_p(planes[1].data_ptr()),
+                                        C.c_void_p(planes[2].data_ptr()),
+                                        C.c_void_p(rgb.data_ptr()) if rgb is not None else C.c_void_p(0),
+                                        C.c_void_p(0), st))
+    return planes[0, :n], planes[1, :n], planes[2, :n], (rgb[:n] if rgb is not None else None)
+
+
+def write_points3D_binary_with_tracks(xyz, rgb_u8, track_lengths, path, seed=0):
+    """A points3D.bin WITH tracks (synthetic image ids / 2D indices), the shape real COLMAP
+    reconstructions have: test and benchmark input for the readers above."""
+    n = len(xyz)
+    tl = np.asarray(track_lengths, dtype=np.int64)
+    rec = 51 + 8 * tl
+    off = np.concatenate([[0], np.cumsum(rec)])
+    out = np.zeros(int(off[-1]), dtype=np.uint8)
+    a = np.zeros(n, dtype=_P3D_HEAD)
+    a["id"] = np.arange(1, n + 1, dtype=np.uint64)
+    a["xyz"] = np.asarray(xyz, dtype=np.float64)
+    a["rgb"] = rgb_u8
+    a["error"] = np.random.default_rng(seed).uniform(0, 2, n)
+    a["track"] = tl.astype(np.uint64)
+    out[off[:-1, None] + np.arange(51)[None, :]] = a.view(np.uint8).reshape(n, 51)
+    tracks = np.random.default_rng(seed + 1).integers(0, 1000, int(tl.sum()) * 2).astype("<i4")
+    pos = np.repeat(off[:-1] + 51, tl) + 8 * (np.arange(int(tl.sum())) - np.repeat(np.cumsum(tl) - tl, tl))
+    out[pos[:, None] + np.arange(8)[None, :]] = tracks.view(np.uint8).reshape(-1, 8)
+    with open(path, "wb") as f:
+        f.write(struct.pack("<Q", n))
+        out.tofile(f)
 
 
 # ---------------------------------------------------------------------------

@@ -268,6 +268,35 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(
   }
 }
 
+// ---------------------------------------------------------------------------
+// N3: COLMAP points3D.bin on the fast path (reference: the per-record struct
+// loop of scene/colmap_loader.py:195-224).  Records are 51 bytes + 8 bytes per
+// track element; the host walks the record offsets once (ptgs_points3d_index),
+// the device decodes xyz / rgb / error straight from the uploaded file image.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double load_f64_unaligned(const uint8_t* p) {
+  unsigned long long v = 0;
+#pragma unroll
+  for (int b = 0; b < 8; ++b) v |= (unsigned long long)p[b] << (8 * b);
+  return __longlong_as_double((long long)v);
+}
+
+__global__ void __launch_bounds__(256) points3d_decode_kernel(
+    const uint8_t* __restrict__ buf, const int64_t* __restrict__ offsets, int64_t n,
+    float* __restrict__ x, float* __restrict__ y, float* __restrict__ z,
+    uint8_t* __restrict__ rgb, double* __restrict__ error) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint8_t* r = buf + offsets[i];
+    // id u64 | xyz 3 x f64 | rgb 3 x u8 | error f64 | track length u64
+    x[i] = (float)load_f64_unaligned(r + 8);      // storePly's float32 cast (shen_data_read.py:135-148)
+    y[i] = (float)load_f64_unaligned(r + 16);
+    z[i] = (float)load_f64_unaligned(r + 24);
+    if (rgb) { rgb[3 * i] = r[32]; rgb[3 * i + 1] = r[33]; rgb[3 * i + 2] = r[34]; }
+    if (error) error[i] = load_f64_unaligned(r + 35);
+  }
+}
+
 static inline int grid_for(int64_t n, int per_block, int max_blocks) {
   int64_t b = (n + per_block - 1) / per_block;
   if (b < 1) b = 1;
@@ -359,6 +388,39 @@ int ptgs_aos_to_soa_manhattan(const float* xyz, int64_t n, const double* man_tra
   }
   int grid = grid_for(n / 4 + 1, 256, kNumSMs * 8);
   aos_manhattan_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(xyz, n, m, ox, oy, oz);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int64_t ptgs_points3d_index(const uint8_t* file_host, int64_t n_bytes, int64_t* offsets_host,
+                            int64_t capacity) {
+  // HOST function: walks the variable-length records; returns the record count or a negative status
+  if (!file_host || n_bytes < 8) { set_error("points3d_index: truncated file"); return PTGS_E_INVALID; }
+  uint64_t n;
+  memcpy(&n, file_host, 8);
+  if ((int64_t)n < 0 || (offsets_host && (int64_t)n > capacity)) {
+    set_error("points3d_index: %llu records exceed the capacity", (unsigned long long)n);
+    return PTGS_E_CAPACITY;
+  }
+  int64_t off = 8;
+  for (uint64_t i = 0; i < n; ++i) {
+    if (off + 51 > n_bytes) { set_error("points3d_index: truncated record %llu", (unsigned long long)i); return PTGS_E_INVALID; }
+    if (offsets_host) offsets_host[i] = off;
+    uint64_t tl;
+    memcpy(&tl, file_host + off + 43, 8);
+    if (tl > (uint64_t)(n_bytes - off - 51) / 8) { set_error("points3d_index: truncated track %llu", (unsigned long long)i); return PTGS_E_INVALID; }
+    off += 51 + 8 * (int64_t)tl;
+  }
+  return (int64_t)n;
+}
+
+int ptgs_points3d_decode(const uint8_t* file_dev, const int64_t* offsets_dev, int64_t n, float* x,
+                         float* y, float* z, uint8_t* rgb, double* error, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0, "n");
+  if (n == 0) return PTGS_OK;
+  PTGS_REQUIRE(file_dev && offsets_dev && x && y && z, "arguments");
+  int grid = grid_for(n, 256, kNumSMs * 8);
+  points3d_decode_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(file_dev, offsets_dev, n, x, y, z, rgb, error);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

@@ -12,7 +12,8 @@ import ptgs_b200  # noqa: E402,F401
 from ptgs_b200.partition import (  # noqa: E402,F401
     BasicPointCloud, Partition, CameraPose, SimpleCamera, Rect, Point, box,
     quad_tree_partition, expand_partitions, assign_cameras_to_partitions, downsample_point_cloud,
-    visibility_based_camera_selection, save_partition_as_pkl, save_partition_data)
+    visibility_based_camera_selection, save_partition_as_pkl, save_partition_data,
+    plot_quad_tree, plot_quad_tree_extend, plot_subregions)
 
 for _t in (BasicPointCloud, Partition, CameraPose):
     _t.__module__ = __name__

@@ -416,6 +416,24 @@ int ptgs_select_cameras(const uint8_t* keep, const int64_t* cam_offsets,
                         int32_t* kept_pos, ptgs_stream_t stream);
 
 /* ------------------------------------------------------------------ *
+ * N3 -- COLMAP points3D.bin ingest (reference: the per-record struct loop of
+ * scene/colmap_loader.py:195-224 and the points3D.bin -> points3D.ply ->
+ * fetchPly round trip of scene/ptgs/shen_data_read.py:185-193).
+ * ptgs_points3d_index: HOST function on a HOST image of the file; writes the
+ *   byte offset of every record (51 bytes + 8 per track element) to
+ *   offsets_host[capacity] (may be NULL to count only) and returns the record
+ *   count, or a negative ptgs_status (truncated file / capacity).
+ * ptgs_points3d_decode: device image of the same file + device offsets ->
+ *   planar float32 xyz (the float32 cast storePly applies), optional rgb
+ *   (n x 3 uint8, may be NULL) and reprojection error (float64, may be NULL).
+ * ------------------------------------------------------------------ */
+int64_t ptgs_points3d_index(const uint8_t* file_host, int64_t n_bytes,
+                            int64_t* offsets_host, int64_t capacity);
+int ptgs_points3d_decode(const uint8_t* file_dev, const int64_t* offsets_dev,
+                         int64_t n, float* x, float* y, float* z, uint8_t* rgb,
+                         double* error, ptgs_stream_t stream);
+
+/* ------------------------------------------------------------------ *
  * Multi-GPU exchange of the per-pair records (the reference is
  * single process -- the loop that is split across GPUs is
  * scene/ptgs/shen_partation_densify.py:932-944).  With range sharding rank r

@@ -113,6 +113,17 @@ def _box(minx, miny, maxx, maxy, ccw=True):
     return _Polygon([(maxx, miny), (maxx, maxy), (minx, maxy), (minx, miny)])
 
 
+def _from_wkb(data):
+    """shapely.from_wkb for the single-ring polygons the partitioner pickles (shapely 2 reduces a
+    geometry to from_wkb(bytes)); third-party restatement, shapely is absent here."""
+    import struct
+    order = "<" if data[0] == 1 else ">"
+    gtype, nrings, npts = struct.unpack_from(order + "III", data, 1)
+    assert gtype == 3 and nrings == 1
+    xy = struct.unpack_from(order + "%dd" % (2 * npts), data, 13)
+    return _Polygon([(xy[2 * i], xy[2 * i + 1]) for i in range(npts - 1)])
+
+
 class _Anything:
     """Attribute sink for plotting / unused third-party APIs."""
 
@@ -154,7 +165,7 @@ def load():
     import torch  # noqa: F401  (real torch must be imported before the stubs exist)
     import scipy.spatial.transform  # noqa: F401
 
-    shp = _mod("shapely")
+    shp = _mod("shapely", from_wkb=_from_wkb)
     geo = _mod("shapely.geometry", Polygon=_Polygon, Point=_Point, box=_box,
                LineString=_Anything, MultiPolygon=_Anything)
     _mod("shapely.geometry.geo", box=_box)

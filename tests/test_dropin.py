@@ -146,7 +146,7 @@ def test_function_level_pipeline_vs_reference_golden(tmp_path):
     assert sorted(imgs.ids.tolist()) == sorted(cp.camera.uid for cp in out[0].camera)
     assert all(n.endswith(".jpg") for n in imgs.names)
     with open(vis_dir / pid / ("partition_%s.pkl" % pid), "rb") as f:
-        q = pickle.load(f)
+        q = P.load_compat(f)          # the file carries the reference's class paths (test_io_pickle.py)
     assert q.partition_id == pid and q.point_num == out[0].point_num
     assert np.array_equal(q.point_cloud.points, out[0].point_cloud.points)
 
@@ -157,6 +157,34 @@ def test_downsample_point_cloud_vs_reference_golden():
     pc = P.BasicPointCloud(g["points"], np.zeros_like(g["points"]), np.zeros_like(g["points"]))
     got = P.downsample_point_cloud(pc, float(g["voxel"])).points
     assert got.dtype == np.float32 and np.array_equal(got.view(np.uint32), g["out"].view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_downsample_point_cloud_attribute_means():
+    """Colours / normals of the down-sampled cloud are the per-voxel means (normals re-normalised),
+    densify:593-603, restated literally here on a cloud with many multi-member voxels."""
+    rng = np.random.default_rng(12)
+    n = 4000
+    pts = (np.round(rng.uniform(0, 3, (n, 3)) * 16) / 16).astype(np.float32)
+    cols = rng.uniform(0, 1, (n, 3))
+    nrm = rng.normal(size=(n, 3)).astype(np.float32)
+    nrm[::50] = 0.0
+    got = P.downsample_point_cloud(P.BasicPointCloud(pts, cols, nrm), 0.1)
+    vid = np.floor((pts - pts.min(0)) / 0.1).astype(np.int32)
+    groups = {}
+    for i, v in enumerate(vid):
+        groups.setdefault((v[0], v[1], v[2]), []).append(i)
+    wp, wc, wn = [], [], []
+    for idx in groups.values():
+        wp.append(np.mean(pts[idx], axis=0))
+        wc.append(np.mean(cols[idx], axis=0))
+        m = np.mean(nrm[idx], axis=0)
+        ln = np.linalg.norm(m)
+        wn.append(m / ln if ln > 1e-12 else m)
+    assert len(groups) < n // 2
+    assert np.array_equal(got.points.view(np.uint32), np.array(wp, dtype=np.float32).view(np.uint32))
+    assert got.colors.dtype == np.float32 and np.array_equal(got.colors, np.array(wc, dtype=np.float32))
+    np.testing.assert_allclose(got.normals, np.array(wn, dtype=np.float32), rtol=2e-7, atol=1e-12)
 
 
 @pytest.mark.gpu
