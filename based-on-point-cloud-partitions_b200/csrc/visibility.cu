@@ -18,6 +18,7 @@
 //   MODE 1  hit counts + Graham pivot + 8 directional extremes -- sweep 1
 //   MODE 2  hull candidates                                   -- sweep 2
 #include <cstddef>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -134,6 +135,9 @@ __device__ __forceinline__ bool project_exact(const Cam& c, const Proj& p, float
 __device__ __forceinline__ uint32_t order_key(float f) {
   const uint32_t b = __float_as_uint(f);
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key_to_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
 // ---- conservative tile cull ----------------------------------------------------
@@ -429,12 +433,22 @@ struct SweepSmem {
   int tile_seen;                                          // MODE 0: a camera contains the whole tile
   alignas(16) float der[kSwCamChunk][8];                  // MODE 0/1: fast-in / not-miss rectangles
   float wbox[kSwThreads / 32][6];                         // per warp tile AABB
+  // exact path of MODE 0 / 1 (COMPACT): the pass's band points as a dense list of slots
+  // (k * 32 + lane) and the pair's current extreme thresholds, per warp
+  unsigned char slist[kSwThreads / 32][32 * kSwP];
+  float thr[kSwThreads / 32][8];
+  unsigned long long pvthr[kSwThreads / 32];
   float box[6];                                           // centre xyz, half extent xyz (padded)
   alignas(8) uint64_t bar[2];
   int64_t prefix[kSwMaxBlocks + 1];
 };
 
-template <int MODE>
+// COMPACT (MODE 0 / 1): the exact path runs on the band points of a pass compacted into dense
+// 32-lane groups (re-read from the staged tile) and tracks pivot / extremes only for hits that
+// can improve the pair's current global values; false = every lane handles its own 4 points and
+// the pass always ends with the 18 warp reductions (the round-1 formulation, kept for A/B runs:
+// PTGS_SWEEP_EXACT=legacy).
+template <int MODE, bool COMPACT>
 __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
@@ -804,73 +818,173 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
           const int64_t pair = S.pair[j];
           if (__any_sync(kFullMask, slow != 0)) {
             if (lane == 0) PTGS_FINE_STAT(6, 1);
-            unsigned long long t_pv = ~0ull;
-            float t_best[8];
-            unsigned t_k = 0;                 // 4 bits per direction: the slot k that holds t_best[d]
-            if (MODE == 1) {
+            if (COMPACT) {
+              const int wp = tid >> 5;
+              unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+              unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
+              if (MODE == 1) {
+                // the pair's extremes as of now: a stale value is only less extreme, so the
+                // filter below lets through a superset of the hits that can improve them
+                if (lane < 8) {
+                  const unsigned long long g = *reinterpret_cast<volatile unsigned long long*>(gex + lane);
+                  S.thr[wp][lane] = g ? key_to_float((uint32_t)(g >> 32)) : -__int_as_float(0x7f800000);
+                } else if (lane == 8) {
+                  S.pvthr[wp] = *reinterpret_cast<volatile unsigned long long*>(gpv);
+                }
+              }
+              int total = 0;
 #pragma unroll
-              for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
-            }
+              for (int k = 0; k < kSwP; ++k) {
+                const bool mine = (slow >> k) & 1u;
+                const unsigned mk = __ballot_sync(kFullMask, mine);
+                if (mine) S.slist[wp][total + __popc(mk & lanemask_lt())] = (unsigned char)(k * 32 + lane);
+                total += __popc(mk);
+              }
+              __syncwarp();
+              unsigned long long t_pv = ~0ull;
+              float t_best[8];
+              unsigned t_s0 = 0, t_s1 = 0;        // 8 bits per direction: the slot that holds t_best[d]
+              if (MODE == 1) {
 #pragma unroll
-            for (int k = 0; k < kSwP; ++k) {
-              const bool mine = (slow >> k) & 1u;
-              if (!__any_sync(kFullMask, mine)) continue;
-              if (lane == 0) PTGS_FINE_STAT(7, 1);
-              bool hit = false;
-              if (mine) {
-                const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
-                const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
-                Proj p;
-                p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, x[k], y[k], z[k]);
-                p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
-                p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
-                float u, v;
-                if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
-                  hit = true;
-                  if (MODE == 0 && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
-                  if (MODE == 1) {
-                    u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
-                    v = __fadd_rn(v, 0.0f);
-                    const unsigned long long pk =
-                        ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                    t_pv = pk < t_pv ? pk : t_pv;
-                    const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
-                    const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
+                for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
+              }
+              const int shift0 = (int)(cur.start & 3);
+              for (int base = 0; base < total; base += 32) {
+                if (lane == 0) PTGS_FINE_STAT(7, 1);
+                bool hit = false;
+                if (base + lane < total) {
+                  const int sl = S.slist[wp][base + lane];
+                  const int i = run * (32 * kSwP) + sl;
+                  const float qx = S.tile[stage][0][shift0 + i], qy = S.tile[stage][1][shift0 + i],
+                              qz = S.tile[stage][2][shift0 + i];
+                  const float X = cam_row(c.r00, c.r01, c.r02, c.tx, qx, qy, qz);
+                  const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, qx, qy, qz);
+                  Proj p;
+                  p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, qx, qy, qz);
+                  p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
+                  p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
+                  float u, v;
+                  if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
+                    hit = true;
+                    if (MODE == 0 && a.seen) a.seen[cur.start + i] = 1;
+                    if (MODE == 1) {
+                      u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                      v = __fadd_rn(v, 0.0f);
+                      const unsigned long long pk =
+                          ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                      const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
+                      const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
+                      bool imp = pk < S.pvthr[wp];
 #pragma unroll
-                    for (int d = 0; d < 8; ++d) {
-                      // >=: among equal values the larger point index (= later k) wins
-                      if (dir[d] >= t_best[d]) {
-                        t_best[d] = dir[d];
-                        t_k = (t_k & ~(0xfu << (4 * d))) | ((unsigned)k << (4 * d));
+                      for (int d = 0; d < 8; ++d) imp = imp || (dir[d] >= S.thr[wp][d]);
+                      if (imp) {
+                        t_pv = pk < t_pv ? pk : t_pv;
+#pragma unroll
+                        for (int d = 0; d < 8; ++d) {
+                          // >=: among equal values the larger point index (= later slot) wins
+                          if (dir[d] >= t_best[d]) {
+                            t_best[d] = dir[d];
+                            if (d < 4) t_s0 = (t_s0 & ~(0xffu << (8 * d))) | ((unsigned)sl << (8 * d));
+                            else t_s1 = (t_s1 & ~(0xffu << (8 * (d - 4)))) | ((unsigned)sl << (8 * (d - 4)));
+                          }
+                        }
                       }
                     }
                   }
                 }
+                cnt += __popc(__ballot_sync(kFullMask, hit));
               }
-              cnt += __popc(__ballot_sync(kFullMask, hit));
-            }
-            if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
-              unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-              unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
-              const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + lane);
-              const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
-              const uint32_t mh = __reduce_min_sync(kFullMask, ph);
-              const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
-              unsigned long long mine_val = 0;
+              if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
+                const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP));
+                const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
+                const uint32_t mh = __reduce_min_sync(kFullMask, ph);
+                const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
+                unsigned long long mine_val = 0;
 #pragma unroll
-              for (int d = 0; d < 8; ++d) {
-                const uint32_t key = order_key(t_best[d]);          // -inf (no hit in this lane) is below every hit
-                const uint32_t kmax = __reduce_max_sync(kFullMask, key);
-                const uint32_t idx = base_idx + ((t_k >> (4 * d)) & 0xfu) * 32u;
-                const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? idx : 0u);
-                if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
+                for (int d = 0; d < 8; ++d) {
+                  const uint32_t key = order_key(t_best[d]);          // -inf (no improving hit in this lane) is below every hit
+                  const uint32_t kmax = __reduce_max_sync(kFullMask, key);
+                  const uint32_t sd = d < 4 ? ((t_s0 >> (8 * d)) & 0xffu) : ((t_s1 >> (8 * (d - 4))) & 0xffu);
+                  const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? base_idx + sd : 0u);
+                  if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
+                }
+                if (lane < 8) {
+                  if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
+                    atomicMax(gex + lane, mine_val);
+                } else if (lane == 8) {
+                  const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
+                  if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
+                }
               }
-              if (lane < 8) {
-                if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
-                  atomicMax(gex + lane, mine_val);
-              } else if (lane == 8) {
-                const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
-                if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
+            } else {
+              unsigned long long t_pv = ~0ull;
+              float t_best[8];
+              unsigned t_k = 0;                 // 4 bits per direction: the slot k that holds t_best[d]
+              if (MODE == 1) {
+#pragma unroll
+                for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
+              }
+#pragma unroll
+              for (int k = 0; k < kSwP; ++k) {
+                const bool mine = (slow >> k) & 1u;
+                if (!__any_sync(kFullMask, mine)) continue;
+                if (lane == 0) PTGS_FINE_STAT(7, 1);
+                bool hit = false;
+                if (mine) {
+                  const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
+                  const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
+                  Proj p;
+                  p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, x[k], y[k], z[k]);
+                  p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
+                  p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
+                  float u, v;
+                  if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
+                    hit = true;
+                    if (MODE == 0 && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
+                    if (MODE == 1) {
+                      u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                      v = __fadd_rn(v, 0.0f);
+                      const unsigned long long pk =
+                          ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                      t_pv = pk < t_pv ? pk : t_pv;
+                      const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
+                      const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
+#pragma unroll
+                      for (int d = 0; d < 8; ++d) {
+                        // >=: among equal values the larger point index (= later k) wins
+                        if (dir[d] >= t_best[d]) {
+                          t_best[d] = dir[d];
+                          t_k = (t_k & ~(0xfu << (4 * d))) | ((unsigned)k << (4 * d));
+                        }
+                      }
+                    }
+                  }
+                }
+                cnt += __popc(__ballot_sync(kFullMask, hit));
+              }
+              if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
+                unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+                unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
+                const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + lane);
+                const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
+                const uint32_t mh = __reduce_min_sync(kFullMask, ph);
+                const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
+                unsigned long long mine_val = 0;
+#pragma unroll
+                for (int d = 0; d < 8; ++d) {
+                  const uint32_t key = order_key(t_best[d]);          // -inf (no hit in this lane) is below every hit
+                  const uint32_t kmax = __reduce_max_sync(kFullMask, key);
+                  const uint32_t idx = base_idx + ((t_k >> (4 * d)) & 0xfu) * 32u;
+                  const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? idx : 0u);
+                  if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
+                }
+                if (lane < 8) {
+                  if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
+                    atomicMax(gex + lane, mine_val);
+                } else if (lane == 8) {
+                  const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
+                  if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
+                }
               }
             }
           }
@@ -983,9 +1097,6 @@ __device__ double shoelace(const double* px, const double* py, int n) {
     acc += px[i] * py[k] - px[k] * py[i];
   }
   return 0.5 * fabs(acc);
-}
-__device__ __forceinline__ float key_to_float(uint32_t k) {
-  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
 // Per pair: the inner polygon (extreme hits that belong to the point set the
@@ -1709,17 +1820,29 @@ static CovPlan coverage_plan(int64_t n, int32_t cam_count) {
 }
 
 // ---- host side -----------------------------------------------------------------
-template <int MODE>
-static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
+template <int MODE, bool COMPACT>
+static int launch_sweep_variant(const SweepArgs& a, cudaStream_t st) {
   static_assert(sizeof(SweepSmem) < 112 * 1024, "two CTAs per SM");
-  PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE, COMPACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(SweepSmem)));
   // `prefix` is the last member: only the entries of this launch's blocks are allocated, which is
   // what lets kSwCtasPerSM CTAs fit one SM for the usual block counts
   const size_t smem = offsetof(SweepSmem, prefix) + (size_t)(a.n_blocks + 1) * sizeof(int64_t);
-  sweep_kernel<MODE><<<kNumSMs * kSwCtasPerSM, kSwThreads, smem, st>>>(a);
+  sweep_kernel<MODE, COMPACT><<<kNumSMs * kSwCtasPerSM, kSwThreads, smem, st>>>(a);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
+}
+
+// PTGS_SWEEP_EXACT=legacy selects the round-1 exact path (A/B measurements; results are identical)
+static bool sweep_legacy_exact() {
+  const char* e = getenv("PTGS_SWEEP_EXACT");
+  return e && e[0] == 'l';
+}
+
+template <int MODE>
+static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
+  if (MODE == 2 || sweep_legacy_exact()) return launch_sweep_variant<MODE, false>(a, st);
+  return launch_sweep_variant<MODE, true>(a, st);
 }
 
 static int schedule(const int64_t* pt_offsets, const int64_t* cam_offsets, int32_t L,
