@@ -29,7 +29,7 @@ SIGNATURES = {
     "ptgs_manhattan_apply": (C.c_int, [_vp, _vp, _vp, _i64, C.POINTER(_f64), _vp, _vp, _vp, _vp]),
     "ptgs_aos_to_soa_manhattan": (C.c_int, [_vp, _i64, C.POINTER(_f64), _vp, _vp, _vp, _vp]),
     "ptgs_radius_outlier_workspace_bytes": (_sz, [_i64]),
-    "ptgs_radius_outlier_mask": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _f64, C.c_int, _vp, _vp,
+    "ptgs_radius_outlier_mask": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _i64, _f64, C.c_int, _vp, _vp,
                                            _vp, _sz, _vp]),
     "ptgs_compact_xy_workspace_bytes": (_sz, [_i64]),
     "ptgs_compact_xy": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -47,7 +47,7 @@ SIGNATURES = {
                                         _vp, _vp, _i64, _vp, _sz, _vp]),
     "ptgs_assign_cameras": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _i64, _vp]),
     "ptgs_voxel_downsample_workspace_bytes": (_sz, [_i64, _i32]),
-    "ptgs_voxel_downsample": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f64, _vp,
+    "ptgs_voxel_downsample": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f64, _vp,
                                         _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_visibility_workspace_bytes": (_sz, [_i32]),
     "ptgs_visibility_init": (C.c_int, [_i64, _vp, _vp, _vp, _vp, _vp]),

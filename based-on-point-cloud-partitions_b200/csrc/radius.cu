@@ -93,15 +93,35 @@ __global__ void __launch_bounds__(256) column_key_kernel(
   }
 }
 
-template <typename T>
+// Sorted points as packed (x, y, z, w) records, w = the bit pattern of the key's z part: the
+// neighbour walk reads ONE record per candidate (a full 16 / 32-byte sector piece) instead of
+// three plane values and the key.  `aos` (may be null): the cloud as (N,3) rows -- the gather
+// from file order then touches one or two sectors per point instead of three.
+template <typename T> struct V4Of;
+template <> struct V4Of<float> {
+  using type = float4;
+  __device__ static __forceinline__ float pack(uint32_t z) { return __uint_as_float(z); }
+  __device__ static __forceinline__ uint32_t unpack(float w) { return __float_as_uint(w); }
+};
+template <> struct V4Of<double> {
+  using type = double4;
+  __device__ static __forceinline__ double pack(uint32_t z) { return __longlong_as_double((long long)z); }
+  __device__ static __forceinline__ uint32_t unpack(double w) { return (uint32_t)__double_as_longlong(w); }
+};
+
+template <typename T, typename K>
 __global__ void __launch_bounds__(256) gather_sorted_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
-    const uint32_t* __restrict__ idx, int64_t n, T* __restrict__ sx,
-    T* __restrict__ sy, T* __restrict__ sz) {
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, const T* __restrict__ aos,
+    const uint32_t* __restrict__ idx, const K* __restrict__ keys, uint32_t zmask, int64_t n,
+    typename V4Of<T>::type* __restrict__ sp) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint32_t j = idx[i];
-    sx[i] = x[j]; sy[i] = y[j]; sz[i] = z[j];
+    const int64_t j = idx[i];
+    typename V4Of<T>::type v;
+    if (aos) { v.x = aos[3 * j]; v.y = aos[3 * j + 1]; v.z = aos[3 * j + 2]; }
+    else { v.x = x[j]; v.y = y[j]; v.z = z[j]; }
+    v.w = V4Of<T>::pack((uint32_t)keys[i] & zmask);
+    sp[i] = v;
   }
 }
 
@@ -116,14 +136,15 @@ __device__ __forceinline__ int64_t lower_bound_u64(const uint64_t* __restrict__ 
 
 template <typename T>
 __global__ void __launch_bounds__(256) radius_count_kernel(
-    const T* __restrict__ sx, const T* __restrict__ sy, const T* __restrict__ sz,
+    const typename V4Of<T>::type* __restrict__ sp,
     const uint64_t* __restrict__ keys, const uint32_t* __restrict__ idx,
     int64_t n, GridSpec g, double r2, int nb, uint8_t* __restrict__ keep,
     unsigned long long* __restrict__ n_keep) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int kept = 0;
   if (p < n) {
-    const double xi = (double)sx[p], yi = (double)sy[p], zi = (double)sz[p];
+    const typename V4Of<T>::type me = sp[p];
+    const double xi = (double)me.x, yi = (double)me.y, zi = (double)me.z;
     const uint64_t key = keys[p] >> 32;
     const long long ix = (long long)(key / (uint64_t)g.ny);
     const long long iy = (long long)(key % (uint64_t)g.ny);
@@ -137,9 +158,10 @@ __global__ void __launch_bounds__(256) radius_count_kernel(
       int64_t j = lower_bound_u64(keys, n, klo << 32);
       for (; j < n && cnt <= nb; ++j) {
         if ((__ldg(keys + j) >> 32) > khi) break;
-        double ddx = __dsub_rn((double)sx[j], xi);
-        double ddy = __dsub_rn((double)sy[j], yi);
-        double ddz = __dsub_rn((double)sz[j], zi);
+        const typename V4Of<T>::type q = sp[j];
+        double ddx = __dsub_rn((double)q.x, xi);
+        double ddy = __dsub_rn((double)q.y, yi);
+        double ddz = __dsub_rn((double)q.z, zi);
         double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)),
                               __dmul_rn(ddz, ddz));
         cnt += (d2 < r2) ? 1 : 0;
@@ -177,7 +199,7 @@ __global__ void __launch_bounds__(256) cell_start_kernel(const K* __restrict__ k
 // the 8 surrounding cells.
 template <typename T, typename K>
 __global__ void __launch_bounds__(256) radius_count_cells_kernel(
-    const T* __restrict__ sx, const T* __restrict__ sy, const T* __restrict__ sz,
+    const typename V4Of<T>::type* __restrict__ sp,
     const K* __restrict__ keys, const uint32_t* __restrict__ idx,
     const uint32_t* __restrict__ cs, int64_t n, GridSpec g, double r2, int nb,
     uint8_t* __restrict__ keep, unsigned long long* __restrict__ n_keep) {
@@ -185,7 +207,8 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int kept = 0;
   if (p < n) {
-    const double xi = (double)sx[p], yi = (double)sy[p], zi = (double)sz[p];
+    const typename V4Of<T>::type me = sp[p];
+    const double xi = (double)me.x, yi = (double)me.y, zi = (double)me.z;
     const int zb = kWide ? 32 : g.zbits;
     const uint32_t zmask = kWide ? 0xffffffffu : ((1u << g.zbits) - 1u);
     const uint64_t key = (uint64_t)(keys[p] >> zb);
@@ -220,10 +243,11 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
         if (((uint32_t)__ldg(keys + mid) & zmask) < zlo) lo = mid + 1; else hi = mid;
       }
       for (uint32_t j = lo; j < j1 && cnt <= nb; ++j) {
-        if (((uint32_t)__ldg(keys + j) & zmask) > zhi) break;
-        double ddx = __dsub_rn((double)sx[j], xi);
-        double ddy = __dsub_rn((double)sy[j], yi);
-        double ddz = __dsub_rn((double)sz[j], zi);
+        const typename V4Of<T>::type q = sp[j];
+        if (V4Of<T>::unpack(q.w) > zhi) break;
+        double ddx = __dsub_rn((double)q.x, xi);
+        double ddy = __dsub_rn((double)q.y, yi);
+        double ddz = __dsub_rn((double)q.z, zi);
         double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)),
                               __dmul_rn(ddz, ddz));
         cnt += (d2 < r2) ? 1 : 0;
@@ -255,17 +279,19 @@ static size_t sort_temp_bytes(int64_t n) {
 }
 
 template <typename T>
-static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n,
+static int radius_impl(const void* vx, const void* vy, const void* vz, const void* vaos, int64_t n,
                        double radius, int nb, uint8_t* keep, int64_t* n_keep,
                        void* workspace, cudaStream_t st) {
+  using V4 = typename V4Of<T>::type;
   const T* x = (const T*)vx; const T* y = (const T*)vy; const T* z = (const T*)vz;
+  const T* aos = (const T*)vaos;
   Carver cv(workspace);
   unsigned long long* mm = cv.take<unsigned long long>(6);
   uint64_t* keys_a = cv.take<uint64_t>(n);
   uint64_t* keys_b = cv.take<uint64_t>(n);
   uint32_t* idx_a = cv.take<uint32_t>(n);
   uint32_t* idx_b = cv.take<uint32_t>(n);
-  T* sx = cv.take<T>(n); T* sy = cv.take<T>(n); T* sz = cv.take<T>(n);
+  V4* sp = cv.take<V4>(n);
   size_t tb = sort_temp_bytes(n);
   void* sort_tmp = cv.take<char>(tb);
   uint32_t* cell_start = cv.take<uint32_t>(cell_table_capacity(n) + 2);
@@ -326,12 +352,12 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
     PTGS_LAUNCH_CHECK();
     PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, k32a, k32b, idx_a, idx_b, (int64_t)n, 0, bits, st));
     count_launch(2 + (bits + 7) / 8);
-    gather_sorted_kernel<T><<<g1, 256, 0, st>>>(x, y, z, idx_b, n, sx, sy, sz);
+    gather_sorted_kernel<T, uint32_t><<<g1, 256, 0, st>>>(x, y, z, aos, idx_b, k32b, (1u << g.zbits) - 1u, n, sp);
     PTGS_LAUNCH_CHECK();
     cell_start_kernel<uint32_t><<<nthreads_blocks, 256, 0, st>>>(k32b, n, g.zbits, ncell, cell_start);
     PTGS_LAUNCH_CHECK();
     radius_count_cells_kernel<T, uint32_t><<<nthreads_blocks, 256, 0, st>>>(
-        sx, sy, sz, k32b, idx_b, cell_start, n, g, radius * radius, nb, keep, (unsigned long long*)n_keep);
+        sp, k32b, idx_b, cell_start, n, g, radius * radius, nb, keep, (unsigned long long*)n_keep);
     PTGS_LAUNCH_CHECK();
     return PTGS_OK;
   }
@@ -341,17 +367,17 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, int64_t n
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, idx_b,
                                                 (int64_t)n, 0, bits, st));
   count_launch(2 + (bits + 7) / 8);
-  gather_sorted_kernel<T><<<g1, 256, 0, st>>>(x, y, z, idx_b, n, sx, sy, sz);
+  gather_sorted_kernel<T, uint64_t><<<g1, 256, 0, st>>>(x, y, z, aos, idx_b, keys_b, 0xffffffffu, n, sp);
   PTGS_LAUNCH_CHECK();
   if (table) {
     cell_start_kernel<uint64_t><<<nthreads_blocks, 256, 0, st>>>(keys_b, n, 32, ncell, cell_start);
     PTGS_LAUNCH_CHECK();
     radius_count_cells_kernel<T, uint64_t><<<nthreads_blocks, 256, 0, st>>>(
-        sx, sy, sz, keys_b, idx_b, cell_start, n, g, radius * radius, nb, keep,
+        sp, keys_b, idx_b, cell_start, n, g, radius * radius, nb, keep,
         (unsigned long long*)n_keep);
   } else {   // very sparse grid (far outliers): binary search per column
     radius_count_kernel<T><<<nthreads_blocks, 256, 0, st>>>(
-        sx, sy, sz, keys_b, idx_b, n, g, radius * radius, nb, keep,
+        sp, keys_b, idx_b, n, g, radius * radius, nb, keep,
         (unsigned long long*)n_keep);
   }
   PTGS_LAUNCH_CHECK();
@@ -369,14 +395,14 @@ size_t ptgs_radius_outlier_workspace_bytes(int64_t n) {
   size_t b = 256;
   b += 2 * align_up((size_t)n * 8, 256);      // keys
   b += 2 * align_up((size_t)n * 4, 256);      // idx
-  b += 3 * align_up((size_t)n * 8, 256);      // sorted coords (f64 worst case)
+  b += align_up((size_t)n * 32, 256);         // sorted packed points (double4 worst case)
   b += align_up(sort_temp_bytes(n), 256) + 4096;
   b += align_up((size_t)(cell_table_capacity(n) + 2) * 4, 256);   // cell table
   return b;
 }
 
 int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
-                             const void* z, int64_t n, double radius,
+                             const void* z, const void* xyz_aos, int64_t n, double radius,
                              int nb_points, uint8_t* keep, int64_t* n_keep,
                              void* workspace, size_t workspace_bytes,
                              ptgs_stream_t stream) {
@@ -392,9 +418,9 @@ int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
     return PTGS_E_WORKSPACE;
   }
   if (dtype == PTGS_F32)
-    return radius_impl<float>(x, y, z, n, radius, nb_points, keep, n_keep, workspace, (cudaStream_t)stream);
+    return radius_impl<float>(x, y, z, xyz_aos, n, radius, nb_points, keep, n_keep, workspace, (cudaStream_t)stream);
   if (dtype == PTGS_F64)
-    return radius_impl<double>(x, y, z, n, radius, nb_points, keep, n_keep, workspace, (cudaStream_t)stream);
+    return radius_impl<double>(x, y, z, xyz_aos, n, radius, nb_points, keep, n_keep, workspace, (cudaStream_t)stream);
   PTGS_REQUIRE(false, "dtype");
 }
 

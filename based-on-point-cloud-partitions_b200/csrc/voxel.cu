@@ -43,6 +43,49 @@ template <> struct VoxArith<double> {
   }
 };
 
+// Where an entry's coordinates come from.  With an index list the points of a block are scattered
+// over a file-ordered cloud: reading three planes at a random position costs three 32-byte
+// sectors per value, and the three passes that need coordinates (min / max, keys, means) would
+// each pay that.  vox_gather_kernel therefore packs the entries ONCE into (x, y, z, -) records
+// (`ent`, 16 / 32 bytes: one sector per random read, fully used by sequential ones); without an
+// index list (entries = the points themselves) the planes are read directly.
+template <typename T> struct Vec4Of;
+template <> struct Vec4Of<float> { using type = float4; };
+template <> struct Vec4Of<double> { using type = double4; };
+
+template <typename T>
+struct PointSrc {
+  const T* x; const T* y; const T* z;
+  const int32_t* indices;                       // may be null
+  const typename Vec4Of<T>::type* ent;          // may be null
+  __device__ __forceinline__ void load(int64_t e, T& px, T& py, T& pz) const {
+    if (ent) {
+      const typename Vec4Of<T>::type v = ent[e];
+      px = v.x; py = v.y; pz = v.z;
+    } else {
+      const int64_t i = indices ? (int64_t)indices[e] : e;
+      px = x[i]; py = y[i]; pz = z[i];
+    }
+  }
+};
+
+// ent[e] = point indices[e].  `aos` (may be null): the same cloud as (N,3) rows -- one or two
+// sectors per point instead of three.
+template <typename T>
+__global__ void __launch_bounds__(256) vox_gather_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, const T* __restrict__ aos,
+    const int32_t* __restrict__ indices, int64_t n_entries, typename Vec4Of<T>::type* __restrict__ ent) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
+    const int64_t i = indices[e];
+    typename Vec4Of<T>::type v;
+    if (aos) { v.x = aos[3 * i]; v.y = aos[3 * i + 1]; v.z = aos[3 * i + 2]; }
+    else { v.x = x[i]; v.y = y[i]; v.z = z[i]; }
+    v.w = T(0);
+    ent[e] = v;
+  }
+}
+
 __device__ __forceinline__ int find_block(const int64_t* s_off, int L, int64_t e) {
   int lo = 0, hi = L - 1;  // last b with off[b] <= e
   while (lo < hi) {
@@ -66,8 +109,7 @@ __global__ void vox_init_kernel(K* mm, int L) {
 // per block min (slots 0..2) and max (3..5) as ordered keys.
 template <typename T>
 __global__ void __launch_bounds__(256) vox_minmax_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
-    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    PointSrc<T> src, const int64_t* __restrict__ offsets,
     int64_t n_entries, int L, typename KeyOf<T>::type* __restrict__ mm) {
   using K = typename KeyOf<T>::type;
   __shared__ int64_t s_off[kVoxMaxBlocks + 1];
@@ -107,8 +149,9 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
     K k[3] = {~K(0), ~K(0), ~K(0)};
     if (valid) {
       b = find_block(s_off, L, e);
-      const int32_t i = indices ? indices[e] : (int32_t)e;
-      k[0] = KeyOf<T>::encode(x[i]); k[1] = KeyOf<T>::encode(y[i]); k[2] = KeyOf<T>::encode(z[i]);
+      T px, py, pz;
+      src.load(e, px, py, pz);
+      k[0] = KeyOf<T>::encode(px); k[1] = KeyOf<T>::encode(py); k[2] = KeyOf<T>::encode(pz);
     }
     const int b0 = __shfl_sync(kFullMask, b, 0);
     const bool uniform = __all_sync(kFullMask, b == b0 || !valid) && b0 >= 0;
@@ -182,8 +225,7 @@ __global__ void __launch_bounds__(1024) vox_layout_kernel(
 
 template <typename T>
 __global__ void __launch_bounds__(256) vox_key_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
-    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    PointSrc<T> src, const int64_t* __restrict__ offsets,
     int64_t n_entries, int L, const T* __restrict__ bmin, double voxel,
     const VoxLayout* __restrict__ lay, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   __shared__ int64_t s_off[kVoxMaxBlocks + 1];
@@ -194,10 +236,11 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
     const int b = find_block(s_off, L, e);
-    const int32_t i = indices ? indices[e] : (int32_t)e;
-    const uint64_t vx = (uint64_t)VoxArith<T>::vid(x[i], bmin[3 * b], vs);
-    const uint64_t vy = (uint64_t)VoxArith<T>::vid(y[i], bmin[3 * b + 1], vs);
-    const uint64_t vz = (uint64_t)VoxArith<T>::vid(z[i], bmin[3 * b + 2], vs);
+    T px, py, pz;
+    src.load(e, px, py, pz);
+    const uint64_t vx = (uint64_t)VoxArith<T>::vid(px, bmin[3 * b], vs);
+    const uint64_t vy = (uint64_t)VoxArith<T>::vid(py, bmin[3 * b + 1], vs);
+    const uint64_t vz = (uint64_t)VoxArith<T>::vid(pz, bmin[3 * b + 2], vs);
     // block | coarse layer (vz >> s) | coarse cell (vx >> s, vy >> s, Morton
     // interleaved) | fine (vx, vy, vz): an injective re-arrangement of the bits
     // of (vx, vy, vz), so the voxel groups are unchanged and only their order
@@ -269,8 +312,7 @@ __global__ void __launch_bounds__(1024) vox_scan_tiles_kernel(
 // one thread per sorted entry; heads walk their run and emit the mean.
 template <typename T>
 __global__ void __launch_bounds__(256) vox_mean_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z,
-    const int64_t* __restrict__ offsets, const int32_t* __restrict__ indices,
+    PointSrc<T> src, const int64_t* __restrict__ offsets,
     const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
     int L, const VoxLayout* __restrict__ lay, const int64_t* __restrict__ tile_base,
     float* __restrict__ ds_x, float* __restrict__ ds_y, float* __restrict__ ds_z,
@@ -305,14 +347,16 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
       // whose members are all -0.0 averages to +0.0
       T sx, sy, sz;
       {
-        const int32_t p = indices ? indices[e0] : (int32_t)e0;
-        sx = T(0) + x[p]; sy = T(0) + y[p]; sz = T(0) + z[p];
+        T px, py, pz;
+        src.load((int64_t)e0, px, py, pz);
+        sx = T(0) + px; sy = T(0) + py; sz = T(0) + pz;
       }
       int64_t j = i + 1;
       long long cnt = 1;
       for (; j < n && keys[j] == key; ++j) {
-        const int32_t p = indices ? indices[vals[j]] : (int32_t)vals[j];
-        sx = sx + x[p]; sy = sy + y[p]; sz = sz + z[p];   // sequential, entry order
+        T px, py, pz;
+        src.load((int64_t)vals[j], px, py, pz);
+        sx = sx + px; sy = sy + py; sz = sz + pz;   // sequential, entry order
         ++cnt;
       }
       const T c = (T)cnt;
@@ -348,6 +392,7 @@ static size_t vox_sort_temp_bytes(int64_t n) {
 }
 
 struct VoxWs {
+  void* ent;
   void* mm; void* bmin; VoxLayout* lay; uint64_t* keys_a; uint64_t* keys_b;
   uint32_t* vals_a; uint32_t* vals_b; int32_t* tile_count; int64_t* tile_base; int64_t* total;
   void* sort_tmp; size_t sort_bytes; int64_t n_tiles; size_t bytes;
@@ -369,12 +414,13 @@ static VoxWs carve_vox(void* ws, int64_t n, int32_t L) {
   v.total = cv.take<int64_t>(1);
   v.sort_bytes = vox_sort_temp_bytes(n);
   v.sort_tmp = cv.take<char>(v.sort_bytes);
+  v.ent = cv.take<double4>(n);                 // packed entries (float4 or double4), index-list calls only
   v.bytes = cv.used() + 256;
   return v;
 }
 
 template <typename T>
-static int voxel_impl(const void* vx, const void* vy, const void* vz, const int64_t* offsets,
+static int voxel_impl(const void* vx, const void* vy, const void* vz, const void* vaos, const int64_t* offsets,
                       const int32_t* indices, int64_t n, int32_t L, double voxel,
                       float* ds_x, float* ds_y, float* ds_z, int32_t* ds_first,
                       int64_t* ds_offsets, int32_t* status_dev, void* ws, cudaStream_t st) {
@@ -387,7 +433,14 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const int6
   PTGS_LAUNCH_CHECK();
   int64_t g64 = (n + 2047) / 2048;
   int grid = (int)(g64 < 1 ? 1 : (g64 > kNumSMs * 8 ? kNumSMs * 8 : g64));
-  vox_minmax_kernel<T><<<grid, 256, 0, st>>>(x, y, z, offsets, indices, n, L, mm);
+  PointSrc<T> src = {x, y, z, indices, nullptr};
+  if (indices) {
+    using V4 = typename Vec4Of<T>::type;
+    vox_gather_kernel<T><<<grid, 256, 0, st>>>(x, y, z, (const T*)vaos, indices, n, (V4*)w.ent);
+    PTGS_LAUNCH_CHECK();
+    src.ent = (const V4*)w.ent;
+  }
+  vox_minmax_kernel<T><<<grid, 256, 0, st>>>(src, offsets, n, L, mm);
   PTGS_LAUNCH_CHECK();
   vox_layout_kernel<T><<<1, 1024, 0, st>>>(mm, offsets, L, voxel, bmin, w.lay, status_dev);
   PTGS_LAUNCH_CHECK();
@@ -401,8 +454,7 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const int6
               lay.bits_b, lay.bits_x, lay.bits_y, lay.bits_z);
     return PTGS_E_RANGE;
   }
-  vox_key_kernel<T><<<grid, 256, 0, st>>>(x, y, z, offsets, indices, n, L, bmin, voxel, w.lay,
-                                         w.keys_a, w.vals_a);
+  vox_key_kernel<T><<<grid, 256, 0, st>>>(src, offsets, n, L, bmin, voxel, w.lay, w.keys_a, w.vals_a);
   PTGS_LAUNCH_CHECK();
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_bytes, w.keys_a, w.keys_b,
                                                 w.vals_a, w.vals_b, (int64_t)n, 0, lay.total_bits, st));
@@ -411,7 +463,7 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const int6
   PTGS_LAUNCH_CHECK();
   vox_scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_count, w.n_tiles, w.tile_base, w.total);
   PTGS_LAUNCH_CHECK();
-  vox_mean_kernel<T><<<(unsigned)w.n_tiles, 256, 0, st>>>(x, y, z, offsets, indices, w.keys_b, w.vals_b,
+  vox_mean_kernel<T><<<(unsigned)w.n_tiles, 256, 0, st>>>(src, offsets, w.keys_b, w.vals_b,
                                                          n, L, w.lay, w.tile_base, ds_x, ds_y, ds_z,
                                                          ds_first, ds_offsets);
   PTGS_LAUNCH_CHECK();
@@ -437,7 +489,7 @@ size_t ptgs_voxel_downsample_workspace_bytes(int64_t n_entries, int32_t n_blocks
 }
 
 int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
-                          const void* z, const int64_t* offsets,
+                          const void* z, const void* xyz_aos, const int64_t* offsets,
                           const int32_t* indices, int64_t n_entries,
                           int32_t n_blocks, double voxel_size, float* ds_x,
                           float* ds_y, float* ds_z, int32_t* ds_first,
@@ -460,9 +512,9 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
     return PTGS_OK;
   }
   if (dtype == PTGS_F32)
-    return voxel_impl<float>(x, y, z, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
+    return voxel_impl<float>(x, y, z, xyz_aos, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
                              ds_z, ds_first, ds_offsets, status_dev, workspace, st);
-  return voxel_impl<double>(x, y, z, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
+  return voxel_impl<double>(x, y, z, xyz_aos, offsets, indices, n_entries, n_blocks, voxel_size, ds_x, ds_y,
                             ds_z, ds_first, ds_offsets, status_dev, workspace, st);
 }
 

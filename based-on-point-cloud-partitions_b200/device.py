@@ -150,13 +150,16 @@ def aos_to_soa_manhattan(xyz: torch.Tensor, man_trans: np.ndarray):
     return ox, oy, oz
 
 
-def radius_outlier_mask(x, y, z, radius=RADIUS, nb_points=NB_POINTS):
+def radius_outlier_mask(x, y, z, radius=RADIUS, nb_points=NB_POINTS, xyz_aos=None):
+    """A1.  xyz_aos: the cloud as (N,3) rows of the planes' dtype (optional, cheaper gather)."""
     lib = _lib.load()
     n = x.shape[0]
+    if xyz_aos is not None:
+        assert xyz_aos.dtype == x.dtype and xyz_aos.is_contiguous() and xyz_aos.shape[0] == n
     keep = torch.empty(n, dtype=torch.uint8, device=x.device)
     n_keep = torch.zeros(1, dtype=torch.int64, device=x.device)
     ws = _ws(lib.ptgs_radius_outlier_workspace_bytes(n), x.device)
-    check(lib.ptgs_radius_outlier_mask(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, float(radius),
+    check(lib.ptgs_radius_outlier_mask(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(xyz_aos), n, float(radius),
                                        int(nb_points), _ptr(keep), _ptr(n_keep), _ptr(ws),
                                        ws.numel(), _stream()))
     return keep, n_keep
@@ -309,9 +312,10 @@ def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device, want_host=Fal
     return offsets, index[:total].clone()
 
 
-def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None, sync=True):
+def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None, sync=True, xyz_aos=None):
     """A6 over every block at once.  Voxels of a block come out in ascending
-    (vx,vy,vz) order; ds_first gives the reference's first-occurrence order."""
+    key order; ds_first gives the reference's first-occurrence order.  xyz_aos: the cloud as (N,3)
+    rows of the planes' dtype (optional; makes the entry gather of an index-list call cheaper)."""
     lib = _lib.load()
     dev = x.device
     L = offsets.shape[0] - 1
@@ -322,7 +326,9 @@ def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None
     ds_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     ws = _ws(lib.ptgs_voxel_downsample_workspace_bytes(ne, L), dev)
-    check(lib.ptgs_voxel_downsample(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(offsets), _ptr(indices),
+    if xyz_aos is not None:
+        assert xyz_aos.dtype == x.dtype and xyz_aos.is_contiguous() and xyz_aos.shape[0] == x.shape[0]
+    check(lib.ptgs_voxel_downsample(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(xyz_aos), _ptr(offsets), _ptr(indices),
                                     ne, L, float(voxel), _ptr(buf[0]), _ptr(buf[1]), _ptr(buf[2]),
                                     _ptr(ds_first), _ptr(ds_off), _ptr(status), _ptr(ws), ws.numel(),
                                     _stream()))
@@ -740,11 +746,13 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     tm.mark("layout")
     if split_xyz is not None:
         sx, sy, sz = aos_to_soa(split_xyz)
+        s_aos = split_xyz if split_xyz.is_contiguous() else None
     else:
         sx, sy, sz = x, y, z
+        s_aos = xyz if (man_trans is None and xyz.is_contiguous()) else None
     n = sx.shape[0]
     if radius_filter:
-        keep_mask, n_keep = radius_outlier_mask(sx, sy, sz)
+        keep_mask, n_keep = radius_outlier_mask(sx, sy, sz, xyz_aos=s_aos)
     else:
         keep_mask = torch.ones(n, dtype=torch.uint8, device=dev)
         n_keep = torch.full((1,), n, dtype=torch.int64, device=dev)
@@ -768,6 +776,8 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     res.pt_counts_h, res.cam_offsets_h = pt_cnt_h, cam_off_h
     if do_visibility:
         cams_d = torch.from_numpy(np.ascontiguousarray(cam_records, dtype=np.float32)).to(dev)
+        # the input rows double as the gather source of A6 when the planes carry the same values
+        aos = xyz if (man_trans is None and xyz.dtype == x.dtype and xyz.is_contiguous()) else None
         if shard is not None and int(shard[1]) > 1:
             from . import multigpu as M
             rank, world = int(shard[0]), int(shard[1])
@@ -777,7 +787,7 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
             pt_off_h = np.concatenate([[0], np.cumsum(pt_cnt_h)]).astype(np.int64)
             e0, e1 = int(pt_off_h[b0]), int(pt_off_h[b1])
             sub_off = torch.from_numpy(pt_off_h[b0:b1 + 1] - e0).to(dev)
-            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, sub_off, pt_idx[e0:e1]) if b1 > b0 else \
+            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, sub_off, pt_idx[e0:e1], xyz_aos=aos) if b1 > b0 else \
                 voxel_downsample(x, y, z, torch.zeros(2, dtype=torch.int64, device=dev), pt_idx[:0])
             tm.mark("A6_voxel")
             loc = np.clip(cam_off_h[b0:b1 + 1], plan.lo, plan.hi) - plan.lo if b1 > b0 else np.zeros(2, np.int64)
@@ -793,7 +803,7 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
             tm.mark("exchange")
             res.ds_block0 = b0
         else:
-            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx)
+            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, pt_off, pt_idx, xyz_aos=aos)
             tm.mark("A6_voxel")
             vis = visibility(dx, dy, dz, ds_off, cams_d, cam_off, cam_idx, exact_ratio=exact_ratio)
             tm.mark("A7_A8_visibility")

@@ -98,10 +98,15 @@ int ptgs_aos_to_soa_manhattan(const float* xyz, int64_t n,
  *   un-pinned): keep point i iff #{j : |pi-pj|^2 < radius^2, j incl. i}
  *   > nb_points, distances in float64.
  *   out keep[n] (uint8) and *n_keep (device int64).
+ *   xyz_aos (may be NULL): the same cloud as (N,3) rows of the same dtype;
+ *   the gather of the points into grid order then reads one or two sectors
+ *   per point instead of three.  Synchronises once (the grid dimensions size
+ *   the sort and the cell table).
  * ------------------------------------------------------------------ */
 size_t ptgs_radius_outlier_workspace_bytes(int64_t n);
 int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
-                             const void* z, int64_t n, double radius,
+                             const void* z, const void* xyz_aos, int64_t n,
+                             double radius,
                              int nb_points, uint8_t* keep, int64_t* n_keep,
                              void* workspace, size_t workspace_bytes,
                              ptgs_stream_t stream);
@@ -229,6 +234,11 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
  *   count (:588-591), cast to float32 (:605).
  *   Inputs: planar coordinates, block CSR (offsets[L+1], indices; indices may
  *   be NULL = identity, i.e. the blocks' points are stored back to back).
+ *   xyz_aos (may be NULL; only read when `indices` is given): the same cloud
+ *   as (N,3) rows of the same dtype.  With an index list the call first packs
+ *   the entries' coordinates into one 16 / 32-byte record each (workspace) so
+ *   that the three passes that need them read whole sectors; reading the rows
+ *   instead of three planes makes that one gather 2-3x cheaper.
  *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
  *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
  *   index list of the first point of the voxel.  Voxels of a block are
@@ -240,7 +250,8 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
 size_t ptgs_voxel_downsample_workspace_bytes(int64_t n_entries,
                                              int32_t n_blocks);
 int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
-                          const void* z, const int64_t* offsets,
+                          const void* z, const void* xyz_aos,
+                          const int64_t* offsets,
                           const int32_t* indices, int64_t n_entries,
                           int32_t n_blocks, double voxel_size, float* ds_x,
                           float* ds_y, float* ds_z, int32_t* ds_first,
