@@ -31,6 +31,9 @@ SIGNATURES = {
     "ptgs_radius_outlier_workspace_bytes": (_sz, [_i64]),
     "ptgs_radius_outlier_mask": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _i64, _f64, C.c_int, _vp, _vp,
                                            _vp, _sz, _vp]),
+    "ptgs_slab_select_workspace_bytes": (_sz, [_i64]),
+    "ptgs_slab_select": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _f64, _f64, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ptgs_slab_keep": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _f64, _f64, _vp, _vp]),
     "ptgs_compact_xy_workspace_bytes": (_sz, [_i64]),
     "ptgs_compact_xy": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_bounds_xy": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp]),

@@ -260,6 +260,81 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
   if (lane_id() == 0 && s) atomicAdd(n_keep, (unsigned long long)s);
 }
 
+// ---------------------------------------------------------------------------
+// Multi-GPU A1: rank r filters the points of the X slab [lo, hi) and needs, besides them, the
+// points within one cell of the slab (halo) as neighbours.  slab_select compacts the planes of
+// { p : lo - halo <= x < hi + halo } (index order kept) together with their cloud indices;
+// slab_scatter writes the slab's own keep flags back to the cloud-sized mask (zero elsewhere, so
+// the ranks' masks combine with one MAX all-reduce).
+// ---------------------------------------------------------------------------
+constexpr int kSlabTile = 2048;
+
+template <typename T>
+__global__ void __launch_bounds__(256) slab_count_kernel(const T* __restrict__ x, int64_t n, double lo, double hi,
+                                                         int32_t* __restrict__ tile_count) {
+  __shared__ int s[33];
+  const int64_t base = (int64_t)blockIdx.x * kSlabTile;
+  int c = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    if (i < n) { const double v = (double)x[i]; c += (v >= lo && v < hi) ? 1 : 0; }
+  }
+  int tot;
+  block_exclusive_sum<int, 256>(c, s, &tot);
+  if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) slab_scan_kernel(const int32_t* __restrict__ tile_count, int64_t n_tiles,
+                                                         int64_t* __restrict__ tile_base, int64_t* __restrict__ total) {
+  __shared__ long long s[33];
+  long long carry = 0;
+  for (int64_t start = 0; start < n_tiles; start += 1024) {
+    const int64_t i = start + threadIdx.x;
+    long long v = (i < n_tiles) ? tile_count[i] : 0;
+    long long tot;
+    long long ex = block_exclusive_sum<long long, 1024>(v, s, &tot);
+    if (i < n_tiles) tile_base[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) slab_scatter_kernel(
+    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, int64_t n, double lo, double hi,
+    const int64_t* __restrict__ tile_base, T* __restrict__ ox, T* __restrict__ oy, T* __restrict__ oz,
+    int32_t* __restrict__ oidx) {
+  __shared__ int s[33];
+  const int64_t base = (int64_t)blockIdx.x * kSlabTile;
+  int64_t out = tile_base[blockIdx.x];
+#pragma unroll 1
+  for (int k = 0; k < 8; ++k) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    T vx = 0;
+    int f = 0;
+    if (i < n) { vx = x[i]; const double v = (double)vx; f = (v >= lo && v < hi) ? 1 : 0; }
+    int tot;
+    const int ex = block_exclusive_sum<int, 256>(f, s, &tot);
+    if (f) {
+      ox[out + ex] = vx; oy[out + ex] = y[i]; oz[out + ex] = z[i];
+      oidx[out + ex] = (int32_t)i;
+    }
+    out += tot;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) slab_keep_kernel(const T* __restrict__ sx, const int32_t* __restrict__ sidx,
+                                                        const uint8_t* __restrict__ skeep, int64_t m, double lo,
+                                                        double hi, uint8_t* __restrict__ keep) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+    const double v = (double)sx[i];
+    if (v >= lo && v < hi) keep[sidx[i]] = skeep[i];
+  }
+}
+
 static inline uint64_t cell_table_capacity(int64_t n) { return (uint64_t)4 * (uint64_t)n + (1ull << 20); }
 
 static inline int grid_for(int64_t n, int per_block, int max_blocks) {
@@ -389,6 +464,59 @@ static int radius_impl(const void* vx, const void* vy, const void* vz, const voi
 using namespace ptgs;
 
 extern "C" {
+
+size_t ptgs_slab_select_workspace_bytes(int64_t n) {
+  int64_t tiles = (n + kSlabTile - 1) / kSlabTile + 1;
+  return align_up(tiles * 4, 256) + align_up(tiles * 8, 256) + 256;
+}
+
+int ptgs_slab_select(int dtype, const void* x, const void* y, const void* z, int64_t n, double lo,
+                     double hi, void* out_x, void* out_y, void* out_z, int32_t* out_index,
+                     int64_t* n_out, void* workspace, size_t workspace_bytes, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && n < (1ll << 31) && n_out, "arguments");
+  PTGS_REQUIRE(dtype == PTGS_F32 || dtype == PTGS_F64, "dtype");
+  if (workspace_bytes < ptgs_slab_select_workspace_bytes(n)) {
+    set_error("slab_select: workspace too small");
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t tiles = (n + kSlabTile - 1) / kSlabTile;
+  if (tiles == 0) {
+    PTGS_CUDA_TRY(cudaMemsetAsync(n_out, 0, 8, st));
+    return PTGS_OK;
+  }
+  Carver cv(workspace);
+  int32_t* tile_count = cv.take<int32_t>(tiles);
+  int64_t* tile_base = cv.take<int64_t>(tiles);
+  if (dtype == PTGS_F32) slab_count_kernel<float><<<(int)tiles, 256, 0, st>>>((const float*)x, n, lo, hi, tile_count);
+  else slab_count_kernel<double><<<(int)tiles, 256, 0, st>>>((const double*)x, n, lo, hi, tile_count);
+  PTGS_LAUNCH_CHECK();
+  slab_scan_kernel<<<1, 1024, 0, st>>>(tile_count, tiles, tile_base, n_out);
+  PTGS_LAUNCH_CHECK();
+  if (dtype == PTGS_F32)
+    slab_scatter_kernel<float><<<(int)tiles, 256, 0, st>>>((const float*)x, (const float*)y, (const float*)z, n, lo, hi,
+                                                          tile_base, (float*)out_x, (float*)out_y, (float*)out_z, out_index);
+  else
+    slab_scatter_kernel<double><<<(int)tiles, 256, 0, st>>>((const double*)x, (const double*)y, (const double*)z, n, lo,
+                                                           hi, tile_base, (double*)out_x, (double*)out_y, (double*)out_z,
+                                                           out_index);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_slab_keep(int dtype, const void* slab_x, const int32_t* slab_index, const uint8_t* slab_keep,
+                   int64_t m, double lo, double hi, uint8_t* keep, ptgs_stream_t stream) {
+  PTGS_REQUIRE(m >= 0 && (dtype == PTGS_F32 || dtype == PTGS_F64), "arguments");
+  if (m == 0) return PTGS_OK;
+  PTGS_REQUIRE(slab_x && slab_index && slab_keep && keep, "arguments");
+  const int grid = grid_for(m, 256, kNumSMs * 8);
+  if (dtype == PTGS_F32)
+    slab_keep_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)slab_x, slab_index, slab_keep, m, lo, hi, keep);
+  else
+    slab_keep_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>((const double*)slab_x, slab_index, slab_keep, m, lo, hi, keep);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
 
 size_t ptgs_radius_outlier_workspace_bytes(int64_t n) {
   if (n < 1) n = 1;

@@ -165,6 +165,60 @@ def radius_outlier_mask(x, y, z, radius=RADIUS, nb_points=NB_POINTS, xyz_aos=Non
     return keep, n_keep
 
 
+def slab_bounds(x, world: int, sample: int = 65536) -> np.ndarray:
+    """X boundaries of `world` slabs with about equal point counts: quantiles of an every-k-th
+    sample of x (deterministic, identical on every rank; any boundaries give the same mask, only
+    the balance depends on them).  bounds[0] = -inf, bounds[world] = +inf."""
+    n = int(x.shape[0])
+    b = np.full(world + 1, np.inf, dtype=np.float64)
+    b[0] = -np.inf
+    if n == 0 or world <= 1:
+        return b
+    step = max(1, n // sample)
+    xs = torch.sort(x[::step].to(torch.float64)).values
+    xs = xs[torch.isfinite(xs)]
+    m = int(xs.shape[0])
+    if m == 0:
+        return b
+    q = xs[[min(m - 1, (m * r) // world) for r in range(1, world)]].cpu().numpy()
+    b[1:world] = np.maximum.accumulate(q)
+    return b
+
+
+def radius_outlier_mask_sharded(x, y, z, rank: int, world: int, group=None, radius=RADIUS, nb_points=NB_POINTS,
+                                bounds=None, reduce=True):
+    """A1 over several GPUs: rank r filters the points of its X slab, with the points within one grid
+    cell of the slab as halo (every neighbour within `radius` is inside it); the cloud-sized masks
+    (zero outside the own slab) are combined with one MAX all-reduce.  Bit-identical to
+    radius_outlier_mask.  reduce=False returns the rank's partial mask (tests)."""
+    lib = _lib.load()
+    if world <= 1:
+        return radius_outlier_mask(x, y, z, radius, nb_points)
+    dev = x.device
+    n = int(x.shape[0])
+    if bounds is None:
+        bounds = slab_bounds(x, world)
+    lo, hi = float(bounds[rank]), float(bounds[rank + 1])
+    halo = float(radius) * (1.0 + 1.0 / 1024.0)
+    keep = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+    sub = torch.empty((3, max(n, 1)), dtype=x.dtype, device=dev)
+    sidx = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    m_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+    ws = _ws(lib.ptgs_slab_select_workspace_bytes(n), dev)
+    check(lib.ptgs_slab_select(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, lo - halo, hi + halo, _ptr(sub[0]),
+                               _ptr(sub[1]), _ptr(sub[2]), _ptr(sidx), _ptr(m_dev), _ptr(ws), ws.numel(), _stream()))
+    m = int(m_dev.item())
+    if m > 0:
+        skeep, _ = radius_outlier_mask(sub[0, :m], sub[1, :m], sub[2, :m], radius, nb_points)
+        check(lib.ptgs_slab_keep(_dt(x), _ptr(sub[0]), _ptr(sidx), _ptr(skeep), m, lo, hi, _ptr(keep), _stream()))
+    keep = keep[:n]
+    if reduce:
+        import torch.distributed as dist
+        dist.all_reduce(keep, op=dist.ReduceOp.MAX, group=group)
+    n_keep = keep.sum(dtype=torch.int64).reshape(1)
+    return keep, n_keep
+
+
 def compact_xy(x, y, keep):
     lib = _lib.load()
     n = x.shape[0]
@@ -725,7 +779,8 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
     split_xyz   optional (N,3) float32 tensor used for A1-A3 instead of `xyz`
                 (the reference's literal shen-path behaviour under man_trans:
                 the split reads the un-rotated PLY, shen_partition_utils.py:62).
-    shard       (rank, world[, group]): multi-GPU.  A1-A5 are computed by every rank
+    shard       (rank, world[, group]): multi-GPU.  A1 is sharded by X slabs with a one-cell halo
+                (one MAX all-reduce of the keep mask), A2-A5 are computed by every rank
                 (deterministic, no communication); the visibility stage is range-sharded: rank r
                 owns a contiguous range of the (block, camera) pair list of about 1 / world of the
                 cost (multigpu.RangePlan on the expanded point counts), down-samples (A6) and
@@ -751,7 +806,10 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
         sx, sy, sz = x, y, z
         s_aos = xyz if (man_trans is None and xyz.is_contiguous()) else None
     n = sx.shape[0]
-    if radius_filter:
+    if radius_filter and shard is not None and int(shard[1]) > 1:
+        keep_mask, n_keep = radius_outlier_mask_sharded(sx, sy, sz, int(shard[0]), int(shard[1]),
+                                                        shard[2] if len(shard) > 2 else None)
+    elif radius_filter:
         keep_mask, n_keep = radius_outlier_mask(sx, sy, sz, xyz_aos=s_aos)
     else:
         keep_mask = torch.ones(n, dtype=torch.uint8, device=dev)

@@ -111,6 +111,27 @@ int ptgs_radius_outlier_mask(int dtype, const void* x, const void* y,
                              void* workspace, size_t workspace_bytes,
                              ptgs_stream_t stream);
 
+/* Multi-GPU A1 (SURVEY.md 8e names only the visibility pass for sharding; the
+ * radius filter is the largest replicated stage, and it shards exactly: a
+ * point's neighbours lie within `radius` of it).  Rank r owns the X slab
+ * [lo, hi):
+ * ptgs_slab_select: compacts the planes and cloud indices of the points with
+ *   lo_halo <= x < hi_halo (caller passes lo - halo, hi + halo; index order
+ *   kept); out_* have capacity n, *n_out (device int64) receives the count.
+ * ptgs_slab_keep: keep[slab_index[i]] = slab_keep[i] for the slab points
+ *   whose own x lies in [lo, hi) (the halo points belong to the neighbours);
+ *   `keep` (cloud sized) must be zeroed by the caller, the ranks' masks are
+ *   then combined with one MAX all-reduce. */
+size_t ptgs_slab_select_workspace_bytes(int64_t n);
+int ptgs_slab_select(int dtype, const void* x, const void* y, const void* z,
+                     int64_t n, double lo, double hi, void* out_x, void* out_y,
+                     void* out_z, int32_t* out_index, int64_t* n_out,
+                     void* workspace, size_t workspace_bytes,
+                     ptgs_stream_t stream);
+int ptgs_slab_keep(int dtype, const void* slab_x, const int32_t* slab_index,
+                   const uint8_t* slab_keep, int64_t m, double lo, double hi,
+                   uint8_t* keep, ptgs_stream_t stream);
+
 /* Stream compaction of the kept points (index order preserved), i.e.
  * `pcd.select_by_index(ind)`; only x and y are needed by the split.
  * out_x/out_y have capacity n; *n_out receives the count. */

@@ -225,3 +225,32 @@ def test_slot_exchange_kernels_equal_single_gpu(world):
     n_hit, ratio, area, keep, flags = D.unpack_records_dev(torch.cat(slots), plan)
     assert torch.equal(n_hit, full.n_hit) and torch.equal(keep, full.keep) and torch.equal(flags, full.flags)
     assert torch.equal(ratio, full.ratio) and torch.equal(area, full.area)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("f64", [False, True])
+def test_slab_sharded_radius_filter_equals_single_gpu(world, f64):
+    """Multi-GPU A1: every rank filters its X slab (+ one-cell halo); the union of the ranks' partial
+    masks (what the MAX all-reduce produces) is the unsharded mask, bit for bit.  Ranks run one
+    after the other on this GPU."""
+    w = W.make("c3", 0.05)
+    x, y, z = D.aos_to_soa(torch.from_numpy(w.xyz).to(DEV))
+    if f64:
+        man = np.eye(4)
+        a = np.deg2rad(33.0)
+        man[:2, :2] = [[np.cos(a), -np.sin(a)], [np.sin(a), np.cos(a)]]
+        x, y, z = D.manhattan_apply(x, y, z, man)
+    full, n_full = D.radius_outlier_mask(x, y, z)
+    bounds = D.slab_bounds(x, world)
+    assert bounds[0] == -np.inf and bounds[-1] == np.inf and bool((np.diff(bounds) >= 0).all())
+    acc = torch.zeros_like(full)
+    owned = torch.zeros(full.shape[0], dtype=torch.int32, device=DEV)
+    for r in range(world):
+        part, _ = D.radius_outlier_mask_sharded(x, y, z, r, world, bounds=bounds, reduce=False)
+        acc = torch.maximum(acc, part)
+        xs = x.to(torch.float64)
+        owned += ((xs >= bounds[r]) & (xs < bounds[r + 1])).to(torch.int32)
+        assert int(part[~((xs >= bounds[r]) & (xs < bounds[r + 1]))].sum()) == 0    # zero outside the own slab
+    assert bool((owned == 1).all())
+    assert torch.equal(acc, full) and int(acc.sum()) == int(n_full.item())
+    assert 0 < int(full.sum()) < full.numel()
