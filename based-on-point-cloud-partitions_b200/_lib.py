@@ -75,7 +75,7 @@ SIGNATURES = {
     "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),
     "ptgs_debug_fma_probe": (C.c_int, [_vp, _i32, _vp]),
     "ptgs_spatial_order_workspace_bytes": (_sz, [_i64]),
-    "ptgs_spatial_order": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ptgs_spatial_order": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_unpermute_u8": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "ptgs_vast_point_range": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _sz, _vp]),
     "ptgs_vast_airspace": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp]),

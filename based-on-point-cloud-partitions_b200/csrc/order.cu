@@ -95,14 +95,17 @@ __global__ void __launch_bounds__(256) order_key_kernel(
   }
 }
 
+// `aos` (may be null): the same cloud as (N,3) rows -- the random read of a point then touches one
+// or two 32-byte sectors instead of one per plane.
 __global__ void __launch_bounds__(256) order_gather_kernel(
     const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ z,
-    const uint32_t* __restrict__ perm, int64_t n, float* __restrict__ sx, float* __restrict__ sy,
-    float* __restrict__ sz) {
+    const float* __restrict__ aos, const uint32_t* __restrict__ perm, int64_t n, float* __restrict__ sx,
+    float* __restrict__ sy, float* __restrict__ sz) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint32_t j = perm[i];
-    sx[i] = x[j]; sy[i] = y[j]; sz[i] = z[j];
+    const int64_t j = perm[i];
+    if (aos) { sx[i] = aos[3 * j]; sy[i] = aos[3 * j + 1]; sz[i] = aos[3 * j + 2]; }
+    else { sx[i] = x[j]; sy[i] = y[j]; sz[i] = z[j]; }
   }
 }
 
@@ -144,7 +147,7 @@ size_t ptgs_spatial_order_workspace_bytes(int64_t n) {
   return b;
 }
 
-int ptgs_spatial_order(const float* px, const float* py, const float* pz, int64_t n, float* sx,
+int ptgs_spatial_order(const float* px, const float* py, const float* pz, const float* xyz_aos, int64_t n, float* sx,
                        float* sy, float* sz, uint32_t* perm, void* workspace,
                        size_t workspace_bytes, ptgs_stream_t stream) {
   PTGS_REQUIRE(n >= 0 && n < 4294967296ll, "spatial_order: n must be in [0, 2^32)");
@@ -172,7 +175,7 @@ int ptgs_spatial_order(const float* px, const float* py, const float* pz, int64_
   PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort_tmp, tb, keys_a, keys_b, idx_a, perm,
                                                 (int64_t)n, 0, kOrderKeyBits, st));
   count_launch(2 + (kOrderKeyBits + 7) / 8);
-  order_gather_kernel<<<g, 256, 0, st>>>(px, py, pz, perm, n, sx, sy, sz);
+  order_gather_kernel<<<g, 256, 0, st>>>(px, py, pz, xyz_aos, perm, n, sx, sy, sz);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

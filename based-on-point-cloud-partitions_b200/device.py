@@ -586,16 +586,22 @@ def select_cameras(keep, cam_offsets, cam_index, want_pos=False, sync=True):
 COVERAGE_SUPERTILES = True
 
 
-def spatial_order(px, py, pz):
+def spatial_order(px, py, pz, xyz_aos=None):
     """Morton-ordered copy of a planar float32 cloud + the permutation
-    (sorted[i] = input[perm[i]]); ptgs_spatial_order."""
+    (sorted[i] = input[perm[i]]); ptgs_spatial_order.  xyz_aos: the same cloud as (N,3) float32
+    rows (optional, cheaper gather).  The sorted planes carry 16 bytes of tail padding: the sweep's
+    bulk copies round the last tile's window up to 16 bytes."""
     lib = _lib.load()
     dev = px.device
     n = px.shape[0]
-    sx, sy, sz = (torch.empty(max(n, 1), dtype=torch.float32, device=dev) for _ in range(3))
+    if xyz_aos is not None:
+        assert xyz_aos.dtype == torch.float32 and xyz_aos.is_contiguous() and xyz_aos.shape[0] == n
+    pitch = (n + 8 + 3) // 4 * 4
+    planes = torch.zeros((3, pitch), dtype=torch.float32, device=dev)
+    sx, sy, sz = planes[0], planes[1], planes[2]
     perm = torch.empty(max(n, 1), dtype=torch.int32, device=dev)       # uint32 payload
     ws = _ws(lib.ptgs_spatial_order_workspace_bytes(n), dev)
-    check(lib.ptgs_spatial_order(_ptr(px), _ptr(py), _ptr(pz), n, _ptr(sx), _ptr(sy), _ptr(sz), _ptr(perm),
+    check(lib.ptgs_spatial_order(_ptr(px), _ptr(py), _ptr(pz), _ptr(xyz_aos), n, _ptr(sx), _ptr(sy), _ptr(sz), _ptr(perm),
                                  _ptr(ws), ws.numel(), _stream()))
     return sx[:n], sy[:n], sz[:n], perm[:n]
 

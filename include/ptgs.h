@@ -503,6 +503,8 @@ int ptgs_unpack_records(const void* gathered, int32_t world,
  * list only -- effective when the cloud is in spatial order
  * (ptgs_spatial_order); a workspace of only ptgs_visibility_workspace_bytes(1)
  * bytes selects the direct every-tile-by-every-camera sweep.
+ * px / py / pz must be 16-byte aligned and readable up to 16 bytes past their
+ * last element (the tiles are staged with 16-byte granular bulk copies).
  * ------------------------------------------------------------------ */
 size_t ptgs_coverage_workspace_bytes(int64_t n, int32_t cam_count);
 int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
@@ -524,6 +526,7 @@ int ptgs_coverage_sweep(const float* px, const float* py, const float* pz,
  * ------------------------------------------------------------------ */
 size_t ptgs_spatial_order_workspace_bytes(int64_t n);
 int ptgs_spatial_order(const float* px, const float* py, const float* pz,
+                       const float* xyz_aos /* may be NULL: same cloud as (N,3) rows, cheaper gather */,
                        int64_t n, float* sx, float* sy, float* sz,
                        uint32_t* perm, void* workspace, size_t workspace_bytes,
                        ptgs_stream_t stream);

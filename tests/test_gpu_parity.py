@@ -331,6 +331,8 @@ def test_coverage_sweep():
     od = D.spatial_order(x, y, z)
     n3, s3 = D.coverage_sweep(x, y, z, cams_d, want_seen=True, ordered=od)
     assert torch.equal(n3, n_hit) and torch.equal(s3, seen)
+    od2 = D.spatial_order(x, y, z, xyz_aos=_dev_xyz(sc))       # gather from the (N,3) rows: same order
+    assert all(torch.equal(a, b) for a, b in zip(od, od2))
 
 
 def test_spatial_order_is_a_permutation_and_local():
