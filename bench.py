@@ -666,11 +666,49 @@ def measure_cpu_baseline(args, out, ctx, c5):
                            % (b, k)})
         if "c5_counts" in chk and c5 is not None:
             c5["sample"]["want"] = chk["c5_counts"]
+        out["cpu_baseline"]["reference_cuda"] = measure_reference_cuda(ctx, b, cam_idx[cam_off[b]:cam_off[b + 1]])
     except Exception as e:  # the baseline is informative; never fail the bench on it
         out["cpu_baseline"] = {"error": repr(e)}
     finally:
         if os.path.exists(path):
             os.remove(path)
+
+
+def measure_reference_cuda(ctx, b, cams, max_cams=16):
+    """The reference's OWN GPU path for A7 (project_points_to_camera(device='cuda'), densify:410,
+    :431-475), restated call for call by the oracle: per camera one torch.tensor(points, device)
+    upload of the block's down-sampled points, two K = 4 matmuls, the divide / mask, and the
+    .tolist() of the in-image points; A8 (the Python Graham scan) is NOT included, so this is an
+    upper bound of the reference's GPU-assisted rate.  Same block as the CPU arm, its first cameras."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import math
+        import ptgs_oracle as O
+        res, recs = ctx["res"], ctx["recs"]
+        ds_off = res.ds_offsets.cpu().numpy()
+        lo, hi = int(ds_off[b]), int(ds_off[b + 1])
+        pts = torch.stack([res.ds_x[lo:hi], res.ds_y[lo:hi], res.ds_z[lo:hi]], 1).cpu().numpy()
+        cams = list(cams[:max_cams])
+
+        def one(c):
+            r = recs[c]
+            W_, H_ = int(r[16]), int(r[17])
+            fovx, fovy = 2 * math.atan(W_ / (2 * float(r[12]))), 2 * math.atan(H_ / (2 * float(r[13])))
+            return O.project_points_to_camera_ref(pts, np.asarray(r[0:9], np.float64).reshape(3, 3),
+                                                  np.asarray(r[9:12], np.float64), fovx, fovy, W_, H_,
+                                                  device="cuda").tolist()
+        one(cams[0])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for c in cams:
+            one(c)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        return {"value": len(pts) * len(cams) / dt, "unit": UNIT, "kind": "port of the reference's device='cuda' "
+                "projection (A7 only, no Graham scan)", "seconds_per_camera": dt / len(cams),
+                "sample": "block %d (%d voxels) x %d cameras" % (b, len(pts), len(cams))}
+    except Exception as e:   # informative
+        return {"error": repr(e)}
 
 
 def _reference_prep(args):

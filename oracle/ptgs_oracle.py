@@ -316,13 +316,13 @@ def project_port(points, rec):
     return hit, u, v
 
 
-def project_points_to_camera_ref(points, R, T, FoVx, FoVy, width, height):
-    """densify:410-477 restated call for call with torch on the CPU
-    (device='cpu').  Returns the (M,2) float32 array of in-image points (the
+def project_points_to_camera_ref(points, R, T, FoVx, FoVy, width, height, device="cpu"):
+    """densify:410-477 restated call for call with torch (device='cpu' by default; 'cuda' is the
+    reference's own default, densify:410: one host->device copy of the points per camera, two
+    K = 4 matmuls, a device->host copy).  Returns the (M,2) float32 array of in-image points (the
     reference returns its .tolist())."""
     import torch
     points = np.asarray(points, dtype=np.float32)
-    device = "cpu"
     points_t = torch.tensor(points, device=device)
     R_wc = torch.tensor(np.asarray(R), dtype=torch.float32, device=device)
     T_wc = torch.tensor(np.asarray(T), dtype=torch.float32, device=device)
@@ -346,7 +346,7 @@ def project_points_to_camera_ref(points, R, T, FoVx, FoVy, width, height):
     ih = (K @ pcf.transpose(0, 1)).transpose(0, 1)
     img = ih[:, :2] / ih[:, 2, None]
     ok = (img[:, 0] >= 0) & (img[:, 0] < width) & (img[:, 1] >= 0) & (img[:, 1] < height)
-    return img[ok].numpy()
+    return img[ok].cpu().numpy()
 
 
 # --------------------------------------------------------------------------
