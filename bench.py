@@ -667,11 +667,34 @@ def measure_cpu_baseline(args, out, ctx, c5):
         if "c5_counts" in chk and c5 is not None:
             c5["sample"]["want"] = chk["c5_counts"]
         out["cpu_baseline"]["reference_cuda"] = measure_reference_cuda(ctx, b, cam_idx[cam_off[b]:cam_off[b + 1]])
+        out["cpu_baseline"]["reference_code"] = reference_code_timing(args.workload)
     except Exception as e:  # the baseline is informative; never fail the bench on it
         out["cpu_baseline"] = {"error": repr(e)}
     finally:
         if os.path.exists(path):
             os.remove(path)
+
+
+def reference_code_timing(workload):
+    """The REFERENCE's own code timed in the build container (tools/time_reference.py, committed under
+    profiles/): the full run at c1, the declared sub-sample extrapolation at c2-c4.  Not measured on
+    this box (/root/reference does not travel); quoted beside the port for scale."""
+    for name in ("r02_reference_cpu_c1.jsonl", "r02_reference_cpu_c2_c4.jsonl"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                for line in f:
+                    d = json.loads(line)
+                    if d.get("config") == workload:
+                        v = d.get("visibility_tests_per_s") or d.get("visibility_tests_per_s_extrapolated")
+                        return {"tests_per_s": v, "host_cores": d.get("host_cores"),
+                                "how": "full reference run (A6-A10)" if "visibility_tests_per_s" in d else
+                                       "sub-sample (4 leaves x 16 cameras) extrapolated linearly, single thread",
+                                "A3_s": d["stage_s"].get("A3_quad_tree_partition"),
+                                "A4_s": d["stage_s"].get("A4_expand_partitions"),
+                                "where": "build container, profiles/" + name}
+        except Exception:
+            pass
+    return None
 
 
 def measure_reference_cuda(ctx, b, cams, max_cams=16):
@@ -771,7 +794,8 @@ def run_reference(args):
         "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "sample": r["sample"]},
-        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "literal") if k in r},
+        "cpu_baseline": dict({k: r[k] for k in ("value", "unit", "cores", "kind", "sample") if k in r},
+                             reference_code=reference_code_timing(args.workload)),
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

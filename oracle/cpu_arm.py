@@ -56,39 +56,6 @@ def visibility_step(block_points, recs, workers, want_results=False):
     return len(ds) * n, sum(1 for r in out if r[2]), len(ds)
 
 
-def literal_rate(block_points, recs, budget_s=12.0):
-    """The reference's own formulation restated call for call -- the per-point dict loop of
-    downsample_point_cloud (densify:566-605), project_points_to_camera with torch on the CPU and its
-    .tolist() (densify:410-477), run_graham_scan (densify:481-539) -- on a sub-block small enough
-    for `budget_s` seconds, single thread like the reference's GIL-bound pool.  tests/s."""
-    n = min(len(block_points), 40000)
-    sub = np.ascontiguousarray(block_points[:n])
-    t0 = time.perf_counter()
-    ds = O.voxel_downsample_literal(sub)
-    t_a6 = time.perf_counter() - t0
-    n_cam, t_cam = 0, 0.0
-    for c in range(len(recs)):
-        if t_a6 + t_cam > budget_s and n_cam >= 1:
-            break
-        rec = recs[c]
-        R = np.asarray(rec[0:9], dtype=np.float64).reshape(3, 3)
-        T = np.asarray(rec[9:12], dtype=np.float64)
-        W, H = int(rec[16]), int(rec[17])
-        import math
-        fovx, fovy = 2 * math.atan(W / (2 * float(rec[12]))), 2 * math.atan(H / (2 * float(rec[13])))
-        t0 = time.perf_counter()
-        uv = O.project_points_to_camera_ref(ds, R, T, fovx, fovy, W, H).tolist()
-        if len(uv) > 3:
-            O.run_graham_scan(uv, W, H)
-        t_cam += time.perf_counter() - t0
-        n_cam += 1
-    t = t_a6 + t_cam
-    return {"value": len(ds) * n_cam / t if t > 0 else None, "unit": "tests/s", "cores": 1,
-            "sample": "first %d points of the block -> %d voxels (dict loop %.2f s) x %d cameras (%.2f s)"
-                      % (n, len(ds), t_a6, n_cam, t_cam),
-            "kind": "port, literal formulation of the reference's loops (densify:541-614, :410-539)"}
-
-
 def run(block_points, recs, steps, warmup, budget_s, workers=None, want_results=False):
     """Times `steps` visibility steps on a bounded sample: the given block and
     as many of its cameras as fit `budget_s` seconds in total (calibrated on
@@ -122,10 +89,6 @@ def run(block_points, recs, steps, warmup, budget_s, workers=None, want_results=
         "sample": "one block (%d expanded points -> %d voxels) x its first %d cameras, A6-A9 per step" % (
             len(block_points), len(ds), n_cam),
     }
-    try:
-        out["literal"] = literal_rate(block_points, recs)
-    except Exception as e:   # informative
-        out["literal"] = {"error": repr(e)}
     if want_results and results is not None:
         _G["ds"], _G["recs"] = ds, use
         out["results"] = {"n_hit": [int(r[0]) for r in results], "ratio": [float(r[1]) for r in results],
