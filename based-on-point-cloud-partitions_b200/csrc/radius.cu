@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
     // itself, conservative by one float step.  Narrow keys: the buckets of zi -+ r with the
     // difference rounded away from zi, so every z within r of zi falls into [zlo, zhi] (the
     // bucket function is monotone).
-    const double rr = sqrt(r2);
+    const double rr = sqrt(r2) * (1.0 + 1e-12);    // never below the true root: |dz| < sqrt(r2) stays inside
     uint32_t zlo, zhi;
     if (kWide) {
       zlo = zkey_of(__double2float_rd(zi - rr)) - 1u;
