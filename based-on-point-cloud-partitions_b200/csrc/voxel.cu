@@ -46,7 +46,7 @@ template <> struct VoxArith<double> {
 // Where an entry's coordinates come from.  With an index list the points of a block are scattered
 // over a file-ordered cloud: reading three planes at a random position costs three 32-byte
 // sectors per value, and the three passes that need coordinates (min / max, keys, means) would
-// each pay that.  vox_gather_kernel therefore packs the entries ONCE into (x, y, z, -) records
+// each pay that.  The first pass (min / max) therefore packs the entries ONCE into (x, y, z, -) records
 // (`ent`, 16 / 32 bytes: one sector per random read, fully used by sequential ones); without an
 // index list (entries = the points themselves) the planes are read directly.
 template <typename T> struct Vec4Of;
@@ -58,6 +58,18 @@ struct PointSrc {
   const T* x; const T* y; const T* z;
   const int32_t* indices;                       // may be null
   const typename Vec4Of<T>::type* ent;          // may be null
+  const T* aos;                                 // may be null: the cloud as (N,3) rows
+  // first touch of an index-list call (the min / max pass): read the point through the index list
+  // and leave its packed record behind for the later passes
+  __device__ __forceinline__ void load_and_pack(int64_t e, typename Vec4Of<T>::type* out, T& px, T& py,
+                                                T& pz) const {
+    const int64_t i = indices[e];
+    if (aos) { px = aos[3 * i]; py = aos[3 * i + 1]; pz = aos[3 * i + 2]; }
+    else { px = x[i]; py = y[i]; pz = z[i]; }
+    typename Vec4Of<T>::type v;
+    v.x = px; v.y = py; v.z = pz; v.w = T(0);
+    out[e] = v;
+  }
   __device__ __forceinline__ void load(int64_t e, T& px, T& py, T& pz) const {
     if (ent) {
       const typename Vec4Of<T>::type v = ent[e];
@@ -68,23 +80,6 @@ struct PointSrc {
     }
   }
 };
-
-// ent[e] = point indices[e].  `aos` (may be null): the same cloud as (N,3) rows -- one or two
-// sectors per point instead of three.
-template <typename T>
-__global__ void __launch_bounds__(256) vox_gather_kernel(
-    const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ z, const T* __restrict__ aos,
-    const int32_t* __restrict__ indices, int64_t n_entries, typename Vec4Of<T>::type* __restrict__ ent) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
-    const int64_t i = indices[e];
-    typename Vec4Of<T>::type v;
-    if (aos) { v.x = aos[3 * i]; v.y = aos[3 * i + 1]; v.z = aos[3 * i + 2]; }
-    else { v.x = x[i]; v.y = y[i]; v.z = z[i]; }
-    v.w = T(0);
-    ent[e] = v;
-  }
-}
 
 __device__ __forceinline__ int find_block(const int64_t* s_off, int L, int64_t e) {
   int lo = 0, hi = L - 1;  // last b with off[b] <= e
@@ -109,7 +104,8 @@ __global__ void vox_init_kernel(K* mm, int L) {
 // per block min (slots 0..2) and max (3..5) as ordered keys.
 template <typename T>
 __global__ void __launch_bounds__(256) vox_minmax_kernel(
-    PointSrc<T> src, const int64_t* __restrict__ offsets,
+    PointSrc<T> src, typename Vec4Of<T>::type* __restrict__ pack_out /* may be null */,
+    const int64_t* __restrict__ offsets,
     int64_t n_entries, int L, typename KeyOf<T>::type* __restrict__ mm) {
   using K = typename KeyOf<T>::type;
   __shared__ int64_t s_off[kVoxMaxBlocks + 1];
@@ -150,7 +146,8 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
     if (valid) {
       b = find_block(s_off, L, e);
       T px, py, pz;
-      src.load(e, px, py, pz);
+      if (pack_out) src.load_and_pack(e, pack_out, px, py, pz);
+      else src.load(e, px, py, pz);
       k[0] = KeyOf<T>::encode(px); k[1] = KeyOf<T>::encode(py); k[2] = KeyOf<T>::encode(pz);
     }
     const int b0 = __shfl_sync(kFullMask, b, 0);
@@ -433,14 +430,11 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const void
   PTGS_LAUNCH_CHECK();
   int64_t g64 = (n + 2047) / 2048;
   int grid = (int)(g64 < 1 ? 1 : (g64 > kNumSMs * 8 ? kNumSMs * 8 : g64));
-  PointSrc<T> src = {x, y, z, indices, nullptr};
-  if (indices) {
-    using V4 = typename Vec4Of<T>::type;
-    vox_gather_kernel<T><<<grid, 256, 0, st>>>(x, y, z, (const T*)vaos, indices, n, (V4*)w.ent);
-    PTGS_LAUNCH_CHECK();
-    src.ent = (const V4*)w.ent;
-  }
-  vox_minmax_kernel<T><<<grid, 256, 0, st>>>(src, offsets, n, L, mm);
+  using V4 = typename Vec4Of<T>::type;
+  PointSrc<T> src = {x, y, z, indices, nullptr, (const T*)vaos};
+  // with an index list the min / max pass packs the entries' coordinates on the way (w.ent)
+  vox_minmax_kernel<T><<<grid, 256, 0, st>>>(src, indices ? (V4*)w.ent : nullptr, offsets, n, L, mm);
+  if (indices) src.ent = (const V4*)w.ent;
   PTGS_LAUNCH_CHECK();
   vox_layout_kernel<T><<<1, 1024, 0, st>>>(mm, offsets, L, voxel, bmin, w.lay, status_dev);
   PTGS_LAUNCH_CHECK();
