@@ -18,5 +18,8 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:swee
 timeout 300 python tools/partition_once.py c4 > $out/${tag}_partition_once.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
     --log-file $out/${tag}_launches_partition_c4.csv python tools/partition_once.py c4 > $out/${tag}_ncu_launches.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
+    -k regex:'vox_|radius_count|gather_sorted|hist_kernel|partition_kernel|expand_|aos_' -c 60 -f \
+    -o $out/${tag}_partition python tools/partition_once.py c4 > $out/${tag}_ncu_partition.log 2>&1
 tail -5 $out/${tag}_tests.log
 head -c 1500 $out/${tag}_bench.json
