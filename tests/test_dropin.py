@@ -165,7 +165,7 @@ def test_downsample_point_cloud_attribute_means():
     densify:593-603, restated literally here on a cloud with many multi-member voxels."""
     rng = np.random.default_rng(12)
     n = 4000
-    pts = (np.round(rng.uniform(0, 3, (n, 3)) * 16) / 16).astype(np.float32)
+    pts = (np.round(rng.uniform(0, 3, (n, 3)) * 4) / 4).astype(np.float32)
     cols = rng.uniform(0, 1, (n, 3))
     nrm = rng.normal(size=(n, 3)).astype(np.float32)
     nrm[::50] = 0.0
