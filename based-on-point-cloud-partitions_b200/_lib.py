@@ -13,7 +13,8 @@ PTGS_OK = 0
 PTGS_E_CAPACITY = -3
 PTGS_E_RANGE = -4
 CAMERA_FLOATS = 20
-POLY_FLOATS = 28
+POLY_FLOATS = 52
+EXTREME_DIRS = 16
 PAIR_RECORD_BYTES = 24
 
 _vp, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t

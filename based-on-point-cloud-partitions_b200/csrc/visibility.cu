@@ -29,7 +29,8 @@ constexpr int kSwP = 4;                          // points per thread
 constexpr int kSwCtasPerSM = 3;
 constexpr int kSwTile = kSwThreads * kSwP;       // 2048 points per tile
 constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
-constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups)
+constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups); MODE 2: half (wider polygon rows)
+constexpr int kDirs = PTGS_EXTREME_DIRS;         // 16 directional extremes per pair
 constexpr int kSwMaxBlocks = 1024;
 constexpr int kCamFloats = PTGS_CAMERA_FLOATS;   // 20
 constexpr int kPolyFloats = PTGS_POLY_FLOATS;    // 28
@@ -138,6 +139,25 @@ __device__ __forceinline__ uint32_t order_key(float f) {
 }
 __device__ __forceinline__ float key_to_float(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// The 16 directions (a, b) along which a pair's extreme hits are tracked, counter-clockwise from
+// +u: (1,0) (2,1) (1,1) (1,2) (0,1) (-1,2) (-1,1) (-2,1) and their negatives.  value = a*u + b*v with
+// ONE float32 rounding (2u / 2v are exact); the even directions are round 1's eight.
+__constant__ float kDirA[16] = {1, 2, 1, 1, 0, -1, -1, -2, -1, -2, -1, -1, 0, 1, 1, 2};
+__constant__ float kDirB[16] = {0, 1, 1, 2, 1, 2, 1, 1, 0, -1, -1, -2, -1, -2, -1, -1};
+__device__ __forceinline__ void dir_values(float u, float v, float* dv) {
+  const float u2 = __fadd_rn(u, u), v2 = __fadd_rn(v, v);
+  dv[0] = u;
+  dv[1] = __fadd_rn(u2, v);
+  dv[2] = __fadd_rn(u, v);
+  dv[3] = __fadd_rn(u, v2);
+  dv[4] = v;
+  dv[5] = __fsub_rn(v2, u);
+  dv[6] = __fsub_rn(v, u);
+  dv[7] = __fsub_rn(v, u2);
+#pragma unroll
+  for (int d = 0; d < 8; ++d) dv[8 + d] = -dv[d];
 }
 
 // ---- conservative tile cull ----------------------------------------------------
@@ -418,7 +438,9 @@ __device__ unsigned long long g_sweep_stats[8];
 struct SweepSmem {
   alignas(128) float tile[2][3][kSwStageFloats];
   alignas(16) float cam[kSwCamChunk][kCamFloats];
-  alignas(16) float poly[kSwCamChunk][kKrectFloats];      // MODE 2: inner polygon; MODE 1: krect record
+  // MODE 1: kSwCamChunk krect records (kKrectFloats each); MODE 2: kSwCamChunk / 2 inner polygons
+  // (rows of 2 * kKrectFloats >= kPolyFloats floats) -- the same bytes
+  alignas(16) float poly[kSwCamChunk * kKrectFloats];
   long long cand_off[kSwCamChunk];                        // MODE 2
   int cand_cap[kSwCamChunk];                              // MODE 2
   int pair_of[kSwCamChunk];                               // MODE 2
@@ -436,20 +458,21 @@ struct SweepSmem {
   // exact path of MODE 0 / 1 (COMPACT): the pass's band points as a dense list of slots
   // (k * 32 + lane) and the pair's current extreme thresholds, per warp
   unsigned char slist[kSwThreads / 32][32 * kSwP];
-  float thr[kSwThreads / 32][8];
+  float thr[kSwThreads / 32][kDirs];
   unsigned long long pvthr[kSwThreads / 32];
   float box[6];                                           // centre xyz, half extent xyz (padded)
   alignas(8) uint64_t bar[2];
   int64_t prefix[kSwMaxBlocks + 1];
 };
 
-// COMPACT (MODE 0 / 1): the exact path runs on the band points of a pass compacted into dense
-// 32-lane groups (re-read from the staged tile) and tracks pivot / extremes only for hits that
-// can improve the pair's current global values; false = every lane handles its own 4 points and
-// the pass always ends with the 18 warp reductions (the round-1 formulation, kept for A/B runs:
-// PTGS_SWEEP_EXACT=legacy).
-template <int MODE, bool COMPACT>
+// Exact path (MODE 0 / 1): the band points of a pass are compacted into dense 32-lane groups
+// (re-read from the staged tile); pivot / directional extremes are updated only by hits that can
+// still improve the pair's current global values (thresholds read once per pass).
+template <int MODE>
 __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepArgs a) {
+  constexpr int kChunk = (MODE == 2) ? kSwCamChunk / 2 : kSwCamChunk;          // cameras staged per chunk
+  constexpr int kPolyStride = (MODE == 2) ? 2 * kKrectFloats : kKrectFloats;   // floats per staged polygon row
+  static_assert(kPolyFloats <= 2 * kKrectFloats, "inner polygon row");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
@@ -565,7 +588,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
     if (MODE == 0 && tid == 0) S.tile_seen = 0;   // ordered by the chunk loop's barriers
     // The item's cameras are culled against the tile box by all threads at once
     // (rounds of kSwThreads cameras), the survivors are compacted into S.act and
-    // swept in chunks of kSwCamChunk; tiles that lie wholly inside a camera's "in"
+    // swept in chunks of kChunk; tiles that lie wholly inside a camera's "in"
     // rectangle are counted right here.
     // Stages cameras [first, first + count) of the item's list (positions S.act[c0 + j] - or
     // cur.cam_lo + j when `direct`) with everything the sweep needs per camera.
@@ -582,7 +605,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
           const int j = i / (kPolyFloats / 4), q = i % (kPolyFloats / 4);
           const int64_t slot = cam_base + cur.cam_lo + (direct ? j : S.act[c0 + j]);
           const int64_t pair = a.pair_map ? (int64_t)a.pair_map[slot] : slot;
-          reinterpret_cast<float4*>(S.poly[j])[q] =
+          reinterpret_cast<float4*>(S.poly + j * kPolyStride)[q] =
               __ldg(reinterpret_cast<const float4*>(a.poly + pair * kPolyFloats) + q);
         }
       }
@@ -590,7 +613,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
         for (int i = tid; i < nc * (kKrectFloats / 4); i += kSwThreads) {
           const int j = i / (kKrectFloats / 4), q = i % (kKrectFloats / 4);
           const int64_t slot = cam_base + cur.cam_lo + (direct ? j : S.act[c0 + j]);
-          reinterpret_cast<float4*>(S.poly[j])[q] =
+          reinterpret_cast<float4*>(S.poly + j * kPolyStride)[q] =
               a.krect ? __ldg(reinterpret_cast<const float4*>(a.krect + slot * kKrectFloats) + q)
                       : make_float4(0.0f, 0.0f, -1.0f, -1.0f);
         }
@@ -624,7 +647,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
     // the CTA stays on the same (block, range): consecutive items are mostly tiles of the same
     // block, so the camera / interior-region records are read from global memory once per block
     // and not three dependent L2 round trips per tile.
-    const bool cached = (cur.cam_hi - cur.cam_lo) <= kSwCamChunk;
+    const bool cached = (cur.cam_hi - cur.cam_lo) <= kChunk;
     if (cached) {
       const bool fresh = (S.tag_b == cur.b) && (S.tag_lo == cur.cam_lo);   // ordered by the barrier above
       if (!fresh) stage_cameras(0, (int)(cur.cam_hi - cur.cam_lo), true);
@@ -655,7 +678,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
         if (MODE != 2 && live) {
           bool all_in;
           if (cached) {
-            all_in = (MODE == 1 && a.krect) ? tile_all_in_poly(cj, S.poly[tid], S.box)
+            all_in = (MODE == 1 && a.krect) ? tile_all_in_poly(cj, S.poly + tid * kPolyStride, S.box)
                                             : tile_all_in(cj, S.der[tid], S.box);
           } else {
             float der[8];
@@ -681,8 +704,8 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
         PTGS_FINE_STAT(0, (unsigned long long)nr * (unsigned)cur.cnt);
         PTGS_FINE_STAT(1, (unsigned long long)nact_all * (unsigned)cur.cnt);
       }
-    for (int c0 = 0; c0 < nact_all; c0 += kSwCamChunk) {
-      const int nc = (nact_all - c0) < kSwCamChunk ? (nact_all - c0) : kSwCamChunk;
+    for (int c0 = 0; c0 < nact_all; c0 += kChunk) {
+      const int nc = (nact_all - c0) < kChunk ? (nact_all - c0) : kChunk;
       // ---- stage the chunk of surviving cameras (already resident when `cached`)
       if (!cached) stage_cameras(c0, nc, false);
       if (tid == 0) { S.qn = 0; S.qhead = 0; }
@@ -704,11 +727,11 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
           may = tile_may_hit(cj, wb);
           if (MODE == 1 && may) {
             bool fz;
-            und = poly_undecided(cj, S.poly[sl], wb, fz);
+            und = poly_undecided(cj, S.poly + sl * kPolyStride, wb, fz);
             allin = und == 0u && fz;
           }
           if (MODE == 0 && may) allin = tile_all_in(cj, S.der[sl], wb);
-          if (MODE == 2 && may) allin = inner_all_in(cj, S.poly[sl], wb);   // nothing to emit
+          if (MODE == 2 && may) allin = inner_all_in(cj, S.poly + sl * kPolyStride, wb);   // nothing to emit
           if (MODE != 2 && allin) atomicAdd(a.n_hit + S.pair[sl], wcnt);
         }
         pm = __ballot_sync(kFullMask, may && !allin);
@@ -777,8 +800,9 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
             if (uj != 0xffffffffu && uj != 0u && __popc(uj) <= 2) {
               use_edges = true;
               const int ea = __ffs(uj) - 1, eb = 31 - __clz(uj);
-              e1a = S.poly[j][8 + 3 * ea]; e1b = S.poly[j][9 + 3 * ea]; e1c = S.poly[j][10 + 3 * ea];
-              e2a = S.poly[j][8 + 3 * eb]; e2b = S.poly[j][9 + 3 * eb]; e2c = S.poly[j][10 + 3 * eb];
+              const float* pr = S.poly + j * kPolyStride;
+              e1a = pr[8 + 3 * ea]; e1b = pr[9 + 3 * ea]; e1c = pr[10 + 3 * ea];
+              e2a = pr[8 + 3 * eb]; e2b = pr[9 + 3 * eb]; e2c = pr[10 + 3 * eb];
             }
           }
 #pragma unroll
@@ -818,174 +842,70 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
           const int64_t pair = S.pair[j];
           if (__any_sync(kFullMask, slow != 0)) {
             if (lane == 0) PTGS_FINE_STAT(6, 1);
-            if (COMPACT) {
-              const int wp = tid >> 5;
-              unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-              unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
-              if (MODE == 1) {
-                // the pair's extremes as of now: a stale value is only less extreme, so the
-                // filter below lets through a superset of the hits that can improve them
-                if (lane < 8) {
-                  const unsigned long long g = *reinterpret_cast<volatile unsigned long long*>(gex + lane);
-                  S.thr[wp][lane] = g ? key_to_float((uint32_t)(g >> 32)) : -__int_as_float(0x7f800000);
-                } else if (lane == 8) {
-                  S.pvthr[wp] = *reinterpret_cast<volatile unsigned long long*>(gpv);
-                }
+            const int wp = tid >> 5;
+            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * kDirs;
+            if (MODE == 1) {
+              // the pair's extremes as of now: a stale value is only less extreme, so the
+              // filter below lets through a superset of the hits that can improve them
+              if (lane < kDirs) {
+                const unsigned long long g = *reinterpret_cast<volatile unsigned long long*>(gex + lane);
+                S.thr[wp][lane] = g ? key_to_float((uint32_t)(g >> 32)) : -__int_as_float(0x7f800000);
+              } else if (lane == kDirs) {
+                S.pvthr[wp] = *reinterpret_cast<volatile unsigned long long*>(gpv);
               }
-              int total = 0;
+            }
+            int total = 0;
 #pragma unroll
-              for (int k = 0; k < kSwP; ++k) {
-                const bool mine = (slow >> k) & 1u;
-                const unsigned mk = __ballot_sync(kFullMask, mine);
-                if (mine) S.slist[wp][total + __popc(mk & lanemask_lt())] = (unsigned char)(k * 32 + lane);
-                total += __popc(mk);
-              }
-              __syncwarp();
-              unsigned long long t_pv = ~0ull;
-              float t_best[8];
-              unsigned t_s0 = 0, t_s1 = 0;        // 8 bits per direction: the slot that holds t_best[d]
-              if (MODE == 1) {
+            for (int k = 0; k < kSwP; ++k) {
+              const bool mine = (slow >> k) & 1u;
+              const unsigned mk = __ballot_sync(kFullMask, mine);
+              if (mine) S.slist[wp][total + __popc(mk & lanemask_lt())] = (unsigned char)(k * 32 + lane);
+              total += __popc(mk);
+            }
+            __syncwarp();
+            const int shift0 = (int)(cur.start & 3);
+            const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP));
+            for (int base = 0; base < total; base += 32) {
+              if (lane == 0) PTGS_FINE_STAT(7, 1);
+              bool hit = false;
+              if (base + lane < total) {
+                const int sl = S.slist[wp][base + lane];
+                const int i = run * (32 * kSwP) + sl;
+                const float qx = S.tile[stage][0][shift0 + i], qy = S.tile[stage][1][shift0 + i],
+                            qz = S.tile[stage][2][shift0 + i];
+                const float X = cam_row(c.r00, c.r01, c.r02, c.tx, qx, qy, qz);
+                const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, qx, qy, qz);
+                Proj p;
+                p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, qx, qy, qz);
+                p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
+                p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
+                float u, v;
+                if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
+                  hit = true;
+                  if (MODE == 0 && a.seen) a.seen[cur.start + i] = 1;
+                  if (MODE == 1) {
+                    u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                    v = __fadd_rn(v, 0.0f);
+                    const unsigned long long pk =
+                        ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                    if (pk < S.pvthr[wp] && pk < *reinterpret_cast<volatile unsigned long long*>(gpv))
+                      atomicMin(gpv, pk);
+                    float dv[kDirs];
+                    dir_values(u, v, dv);
+                    const uint32_t idx = base_idx + (uint32_t)sl;
 #pragma unroll
-                for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
-              }
-              const int shift0 = (int)(cur.start & 3);
-              for (int base = 0; base < total; base += 32) {
-                if (lane == 0) PTGS_FINE_STAT(7, 1);
-                bool hit = false;
-                if (base + lane < total) {
-                  const int sl = S.slist[wp][base + lane];
-                  const int i = run * (32 * kSwP) + sl;
-                  const float qx = S.tile[stage][0][shift0 + i], qy = S.tile[stage][1][shift0 + i],
-                              qz = S.tile[stage][2][shift0 + i];
-                  const float X = cam_row(c.r00, c.r01, c.r02, c.tx, qx, qy, qz);
-                  const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, qx, qy, qz);
-                  Proj p;
-                  p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, qx, qy, qz);
-                  p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
-                  p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
-                  float u, v;
-                  if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
-                    hit = true;
-                    if (MODE == 0 && a.seen) a.seen[cur.start + i] = 1;
-                    if (MODE == 1) {
-                      u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
-                      v = __fadd_rn(v, 0.0f);
-                      const unsigned long long pk =
-                          ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                      const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
-                      const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
-                      bool imp = pk < S.pvthr[wp];
-#pragma unroll
-                      for (int d = 0; d < 8; ++d) imp = imp || (dir[d] >= S.thr[wp][d]);
-                      if (imp) {
-                        t_pv = pk < t_pv ? pk : t_pv;
-#pragma unroll
-                        for (int d = 0; d < 8; ++d) {
-                          // >=: among equal values the larger point index (= later slot) wins
-                          if (dir[d] >= t_best[d]) {
-                            t_best[d] = dir[d];
-                            if (d < 4) t_s0 = (t_s0 & ~(0xffu << (8 * d))) | ((unsigned)sl << (8 * d));
-                            else t_s1 = (t_s1 & ~(0xffu << (8 * (d - 4)))) | ((unsigned)sl << (8 * (d - 4)));
-                          }
-                        }
+                    for (int d = 0; d < kDirs; ++d) {
+                      // >=: among equal values the larger point index wins (max of (key, index))
+                      if (dv[d] >= S.thr[wp][d]) {
+                        const unsigned long long val = ((unsigned long long)order_key(dv[d]) << 32) | idx;
+                        if (val > *reinterpret_cast<volatile unsigned long long*>(gex + d)) atomicMax(gex + d, val);
                       }
                     }
                   }
                 }
-                cnt += __popc(__ballot_sync(kFullMask, hit));
               }
-              if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
-                const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP));
-                const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
-                const uint32_t mh = __reduce_min_sync(kFullMask, ph);
-                const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
-                unsigned long long mine_val = 0;
-#pragma unroll
-                for (int d = 0; d < 8; ++d) {
-                  const uint32_t key = order_key(t_best[d]);          // -inf (no improving hit in this lane) is below every hit
-                  const uint32_t kmax = __reduce_max_sync(kFullMask, key);
-                  const uint32_t sd = d < 4 ? ((t_s0 >> (8 * d)) & 0xffu) : ((t_s1 >> (8 * (d - 4))) & 0xffu);
-                  const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? base_idx + sd : 0u);
-                  if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
-                }
-                if (lane < 8) {
-                  if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
-                    atomicMax(gex + lane, mine_val);
-                } else if (lane == 8) {
-                  const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
-                  if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
-                }
-              }
-            } else {
-              unsigned long long t_pv = ~0ull;
-              float t_best[8];
-              unsigned t_k = 0;                 // 4 bits per direction: the slot k that holds t_best[d]
-              if (MODE == 1) {
-#pragma unroll
-                for (int d = 0; d < 8; ++d) t_best[d] = -__int_as_float(0x7f800000);
-              }
-#pragma unroll
-              for (int k = 0; k < kSwP; ++k) {
-                const bool mine = (slow >> k) & 1u;
-                if (!__any_sync(kFullMask, mine)) continue;
-                if (lane == 0) PTGS_FINE_STAT(7, 1);
-                bool hit = false;
-                if (mine) {
-                  const float X = cam_row(c.r00, c.r01, c.r02, c.tx, x[k], y[k], z[k]);
-                  const float Y = cam_row(c.r10, c.r11, c.r12, c.ty, x[k], y[k], z[k]);
-                  Proj p;
-                  p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, x[k], y[k], z[k]);
-                  p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
-                  p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
-                  float u, v;
-                  if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
-                    hit = true;
-                    if (MODE == 0 && a.seen) a.seen[cur.start + run * (32 * kSwP) + k * 32 + lane] = 1;
-                    if (MODE == 1) {
-                      u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
-                      v = __fadd_rn(v, 0.0f);
-                      const unsigned long long pk =
-                          ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                      t_pv = pk < t_pv ? pk : t_pv;
-                      const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
-                      const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
-#pragma unroll
-                      for (int d = 0; d < 8; ++d) {
-                        // >=: among equal values the larger point index (= later k) wins
-                        if (dir[d] >= t_best[d]) {
-                          t_best[d] = dir[d];
-                          t_k = (t_k & ~(0xfu << (4 * d))) | ((unsigned)k << (4 * d));
-                        }
-                      }
-                    }
-                  }
-                }
-                cnt += __popc(__ballot_sync(kFullMask, hit));
-              }
-              if (MODE == 1 && __any_sync(kFullMask, t_pv != ~0ull)) {
-                unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-                unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * 8;
-                const uint32_t base_idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + lane);
-                const uint32_t ph = (uint32_t)(t_pv >> 32), pl = (uint32_t)t_pv;
-                const uint32_t mh = __reduce_min_sync(kFullMask, ph);
-                const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
-                unsigned long long mine_val = 0;
-#pragma unroll
-                for (int d = 0; d < 8; ++d) {
-                  const uint32_t key = order_key(t_best[d]);          // -inf (no hit in this lane) is below every hit
-                  const uint32_t kmax = __reduce_max_sync(kFullMask, key);
-                  const uint32_t idx = base_idx + ((t_k >> (4 * d)) & 0xfu) * 32u;
-                  const uint32_t imax = __reduce_max_sync(kFullMask, key == kmax ? idx : 0u);
-                  if (lane == d) mine_val = ((unsigned long long)kmax << 32) | imax;
-                }
-                if (lane < 8) {
-                  if (mine_val > *reinterpret_cast<volatile unsigned long long*>(gex + lane))
-                    atomicMax(gex + lane, mine_val);
-                } else if (lane == 8) {
-                  const unsigned long long pk = ((unsigned long long)mh << 32) | ml;
-                  if (pk < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, pk);
-                }
-              }
+              cnt += __popc(__ballot_sync(kFullMask, hit));
             }
           }
           if (lane == 0 && cnt) atomicAdd(a.n_hit + pair, cnt);
@@ -994,41 +914,16 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
       {
         const Cam c = load_cam(S.cam[j]);
         const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
-        int cnt = 0;
-        // MODE 1: per thread running pivot / directional extremes (registers)
-        unsigned long long t_pv = ~0ull;
-        float t_best[8];
-        uint32_t t_idx[8];
-        if (MODE == 1) {
-#pragma unroll
-          for (int d = 0; d < 8; ++d) { t_best[d] = -__int_as_float(0x7f800000); t_idx[d] = 0; }
-        }
 #pragma unroll
         for (int k = 0; k < kSwP; ++k) {
           const Proj p = project_pre(c, w1, h1, x[k], y[k], z[k]);
           if (p.maybe) {
             float u, v;
             if (project_exact(c, p, u, v)) {
-              if (MODE != 2) ++cnt;
-              if (MODE == 0) seen_mask |= 1u << k;
-              if (MODE == 1) {
-                u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
-                v = __fadd_rn(v, 0.0f);
-                const unsigned long long pk =
-                    ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                t_pv = pk < t_pv ? pk : t_pv;
-                const uint32_t idx = (uint32_t)(cur.tile * kSwTile + run * (32 * kSwP) + k * 32 + lane);
-                const float upv = __fadd_rn(u, v), umv = __fsub_rn(u, v);
-                const float dir[8] = {u, upv, v, -umv, -u, -upv, -v, umv};
-#pragma unroll
-                for (int d = 0; d < 8; ++d) {
-                  if (dir[d] > t_best[d]) { t_best[d] = dir[d]; t_idx[d] = idx; }
-                }
-              }
               if (MODE == 2) {
                 u = __fadd_rn(u, 0.0f);
                 v = __fadd_rn(v, 0.0f);
-                const float* pl = S.poly[j];
+                const float* pl = S.poly + j * kPolyStride;
                 // the pivot's row: only the pivot itself takes part (see ptgs.h)
                 const bool excluded = (v == pl[1]) && (u != pl[2]);
                 if (!excluded) {
@@ -1054,8 +949,8 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
       }
       }   // queue
 
-      // staging arrays are rewritten by the next chunk (rare: > kSwCamChunk surviving cameras)
-      if (c0 + kSwCamChunk < nact_all) __syncthreads();
+      // staging arrays are rewritten by the next chunk (rare: > kChunk surviving cameras)
+      if (c0 + kChunk < nact_all) __syncthreads();
     }
     }
     if (MODE == 0 && a.seen) {
@@ -1139,14 +1034,14 @@ __global__ void __launch_bounds__(128) bounds_kernel(
   out[1] = vp; out[2] = up;
   const float Dm = fmaxf(c.w, c.h);
   out[3] = 4e-6f * Dm * Dm;           // > the float32 evaluation error of the half planes
-  double vx[8], vy[8], sup[8];
+  double vx[kDirs], vy[kDirs], sup[kDirs];
   int m = 0;
-  for (int d = 0; d < 8; ++d) {
-    const uint64_t e = extreme[pair * 8 + d];
+  for (int d = 0; d < kDirs; ++d) {
+    const uint64_t e = extreme[pair * kDirs + d];
     sup[d] = 0.0;
     if (!e) continue;
     const double hval = (double)key_to_float((uint32_t)(e >> 32));
-    sup[d] = hval + fabs(hval) * (1.0 / 4194304.0) + 1e-30;   // outward, covers fl(u+v)
+    sup[d] = hval + fabs(hval) * (1.0 / 4194304.0) + 1e-30;   // outward, covers the one float32 rounding of a*u + b*v
     const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
     const Proj p = project_pre(c, w1, h1, px[gi], py[gi], pz[gi]);
     float u, v;
@@ -1169,17 +1064,26 @@ __global__ void __launch_bounds__(128) bounds_kernel(
     out[0] = (float)m;
     a_in = shoelace(vx, vy, m);
   }
-  // outer octagon: u <= s0, u+v <= s1, v <= s2, v-u <= s3, -u <= s4, -(u+v) <= s5, -v <= s6, u-v <= s7
+  // outer polygon: the 16 supporting half planes a_d*u + b_d*v <= sup_d.  Start from the rectangle of
+  // the four axis directions, clip by the other twelve (each clip adds at most one vertex: <= 16).
   double ax[16], ay[16], bx[16], by[16];
-  ax[0] = -sup[4]; ay[0] = -sup[6];
-  ax[1] = sup[0];  ay[1] = -sup[6];
-  ax[2] = sup[0];  ay[2] = sup[2];
-  ax[3] = -sup[4]; ay[3] = sup[2];
+  ax[0] = -sup[8]; ay[0] = -sup[12];
+  ax[1] = sup[0];  ay[1] = -sup[12];
+  ax[2] = sup[0];  ay[2] = sup[4];
+  ax[3] = -sup[8]; ay[3] = sup[4];
   int n = 4;
-  n = clip_halfplane(ax, ay, n, 1.0, 1.0, sup[1], bx, by);
-  n = clip_halfplane(bx, by, n, -1.0, 1.0, sup[3], ax, ay);
-  n = clip_halfplane(ax, ay, n, -1.0, -1.0, sup[5], bx, by);
-  n = clip_halfplane(bx, by, n, 1.0, -1.0, sup[7], ax, ay);
+  {
+    double* sx_ = ax; double* sy_ = ay; double* tx_ = bx; double* ty_ = by;
+    for (int d = 1; d < kDirs; ++d) {
+      if ((d & 3) == 0) continue;
+      n = clip_halfplane(sx_, sy_, n, (double)kDirA[d], (double)kDirB[d], sup[d], tx_, ty_);
+      double* t = sx_; sx_ = tx_; tx_ = t;
+      t = sy_; sy_ = ty_; ty_ = t;
+    }
+    if (sx_ != ax) {
+      for (int i = 0; i < n; ++i) { ax[i] = sx_[i]; ay[i] = sy_[i]; }
+    }
+  }
   const double a_out = shoelace(ax, ay, n) * (1.0 + 1e-12);
   const double wh = (double)c.w * (double)c.h;
   const double rlo = a_in / wh, rhi = a_out / wh;
@@ -1566,7 +1470,7 @@ __global__ void __launch_bounds__(256) vis_init_kernel(int64_t n_pairs, int32_t*
                                                        uint64_t* pivot, uint64_t* extreme,
                                                        int32_t* cand_count) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs * 8; i += stride) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs * kDirs; i += stride) {
     if (extreme) extreme[i] = 0ull;
     if (i < n_pairs) {
       if (n_hit) n_hit[i] = 0;
@@ -1650,7 +1554,7 @@ __global__ void __launch_bounds__(128) krect_kernel(
   double vx[8], vy[8];
   int m = 0;
   for (int d = 0; d < 8; ++d) {
-    const uint64_t e = extreme_s[pair * 8 + d];
+    const uint64_t e = extreme_s[pair * kDirs + 2 * d];      // the eight even (axis / diagonal) directions
     if (!e) continue;
     const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
     const Proj p = project_pre(c, 0.0f, 0.0f, sx[gi], sy[gi], sz[gi]);
@@ -1820,29 +1724,17 @@ static CovPlan coverage_plan(int64_t n, int32_t cam_count) {
 }
 
 // ---- host side -----------------------------------------------------------------
-template <int MODE, bool COMPACT>
-static int launch_sweep_variant(const SweepArgs& a, cudaStream_t st) {
+template <int MODE>
+static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
   static_assert(sizeof(SweepSmem) < 112 * 1024, "two CTAs per SM");
-  PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE, COMPACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(SweepSmem)));
   // `prefix` is the last member: only the entries of this launch's blocks are allocated, which is
   // what lets kSwCtasPerSM CTAs fit one SM for the usual block counts
   const size_t smem = offsetof(SweepSmem, prefix) + (size_t)(a.n_blocks + 1) * sizeof(int64_t);
-  sweep_kernel<MODE, COMPACT><<<kNumSMs * kSwCtasPerSM, kSwThreads, smem, st>>>(a);
+  sweep_kernel<MODE><<<kNumSMs * kSwCtasPerSM, kSwThreads, smem, st>>>(a);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
-}
-
-// PTGS_SWEEP_EXACT=legacy selects the round-1 exact path (A/B measurements; results are identical)
-static bool sweep_legacy_exact() {
-  const char* e = getenv("PTGS_SWEEP_EXACT");
-  return e && e[0] == 'l';
-}
-
-template <int MODE>
-static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
-  if (MODE == 2 || sweep_legacy_exact()) return launch_sweep_variant<MODE, false>(a, st);
-  return launch_sweep_variant<MODE, true>(a, st);
 }
 
 static int schedule(const int64_t* pt_offsets, const int64_t* cam_offsets, int32_t L,
@@ -1870,7 +1762,7 @@ int ptgs_visibility_init(int64_t n_pairs, int32_t* n_hit, uint64_t* pivot, uint6
                          int32_t* cand_count, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_pairs >= 0, "n_pairs");
   if (n_pairs == 0) return PTGS_OK;
-  int64_t g = (n_pairs * 8 + 255) / 256;
+  int64_t g = (n_pairs * kDirs + 255) / 256;
   if (g > kNumSMs * 8) g = kNumSMs * 8;
   vis_init_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(n_pairs, n_hit, pivot, extreme, cand_count);
   PTGS_LAUNCH_CHECK();
