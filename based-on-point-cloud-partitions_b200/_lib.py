@@ -63,7 +63,7 @@ SIGNATURES = {
     "ptgs_visibility_bounds": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
                                          _i64, _i32, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
                                          _vp, _vp, _vp]),
-    "ptgs_visibility_plan": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _i64, _vp, _vp]),
+    "ptgs_visibility_plan": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i64, _vp, _vp]),
     "ptgs_visibility_candidates": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                              _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,

@@ -228,6 +228,15 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
       zhi = zbucket_of(__dadd_ru(zi, rr), g);
     }
     int cnt = 0;
+    // float32 screening of the float64 test d2 < r2 (the FP64 pipe issues at half rate and the walk
+    // is issue bound).  With af = fl32(a): |fl32(bf - af) - (b - a)| <= 2^-24 (|a| + |b| + |b - a|) per
+    // axis; candidates of the walk are within 2 cells in x / y and r + 4 cells in z (D <= 6), so
+    // |sum df^2 - d2| <= 2 D sum_axes(err) <= 2^-24 (24 S + 432) with S = |x| + |y| + |z| of the query,
+    // plus 3 roundings of the sum (<= 2^-22 d2).  M and the relative term carry a 4x / 8x margin;
+    // whatever falls inside the band is decided by the exact float64 expression.
+    const float xf = (float)me.x, yf = (float)me.y, zf = (float)me.z;
+    const float Mtol = 2.384185791015625e-07f * (24.0f * (fabsf(xf) + fabsf(yf) + fabsf(zf)) + 432.0f);
+    const float r2f = (float)r2;
     // visiting order: (0,0), then the 4 edge neighbours, then the 4 corners
     const int ox[9] = {0, 0, 0, -1, 1, -1, -1, 1, 1};
     const int oy[9] = {0, -1, 1, 0, 0, -1, 1, -1, 1};
@@ -245,12 +254,19 @@ __global__ void __launch_bounds__(256) radius_count_cells_kernel(
       for (uint32_t j = lo; j < j1 && cnt <= nb; ++j) {
         const typename V4Of<T>::type q = sp[j];
         if (V4Of<T>::unpack(q.w) > zhi) break;
-        double ddx = __dsub_rn((double)q.x, xi);
-        double ddy = __dsub_rn((double)q.y, yi);
-        double ddz = __dsub_rn((double)q.z, zi);
-        double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)),
-                              __dmul_rn(ddz, ddz));
-        cnt += (d2 < r2) ? 1 : 0;
+        const float dxf = __fsub_rn((float)q.x, xf), dyf = __fsub_rn((float)q.y, yf), dzf = __fsub_rn((float)q.z, zf);
+        const float d2f = __fmaf_rn(dzf, dzf, __fmaf_rn(dyf, dyf, __fmul_rn(dxf, dxf)));
+        const float tol = __fmaf_rn(1.9073486328125e-06f, d2f, Mtol);
+        if (d2f < __fsub_rn(r2f, tol)) {
+          ++cnt;
+        } else if (d2f <= __fadd_rn(r2f, tol)) {
+          double ddx = __dsub_rn((double)q.x, xi);
+          double ddy = __dsub_rn((double)q.y, yi);
+          double ddz = __dsub_rn((double)q.z, zi);
+          double d2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)),
+                                __dmul_rn(ddz, ddz));
+          cnt += (d2 < r2) ? 1 : 0;
+        }
       }
     }
     kept = cnt > nb;

@@ -787,6 +787,16 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
       if (MODE != 2) {
         {
           const Cam c = load_cam(S.cam[j]);
+          const int64_t pair = S.pair[j];
+          // MODE 1: the pair's extremes / pivot as of now, requested before the classification
+          // loop so that their L2 latency is hidden (only used when the pass has band points)
+          unsigned long long gcur = 0;
+          unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
+          unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * kDirs;
+          if (MODE == 1) {
+            if (lane < kDirs) gcur = *reinterpret_cast<volatile unsigned long long*>(gex + lane);
+            else if (lane == kDirs) gcur = *reinterpret_cast<volatile unsigned long long*>(gpv);
+          }
           const float4 din = *reinterpret_cast<const float4*>(&S.der[j][0]);
           const float4 dout = *reinterpret_cast<const float4*>(&S.der[j][4]);
           const bool front_y = c.front_axis == 1.0f;
@@ -839,21 +849,16 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
           // its best pivot / directional extremes of the pass in registers; one warp
           // reduction per pass then sends at most 9 atomics (lane d owns direction d)
           // to the pair's global slots, and only for values that improve them.
-          const int64_t pair = S.pair[j];
           if (__any_sync(kFullMask, slow != 0)) {
             if (lane == 0) PTGS_FINE_STAT(6, 1);
             const int wp = tid >> 5;
-            unsigned long long* gpv = reinterpret_cast<unsigned long long*>(a.pivot) + pair;
-            unsigned long long* gex = reinterpret_cast<unsigned long long*>(a.extreme) + pair * kDirs;
             if (MODE == 1) {
-              // the pair's extremes as of now: a stale value is only less extreme, so the
-              // filter below lets through a superset of the hits that can improve them
-              if (lane < kDirs) {
-                const unsigned long long g = *reinterpret_cast<volatile unsigned long long*>(gex + lane);
-                S.thr[wp][lane] = g ? key_to_float((uint32_t)(g >> 32)) : -__int_as_float(0x7f800000);
-              } else if (lane == kDirs) {
-                S.pvthr[wp] = *reinterpret_cast<volatile unsigned long long*>(gpv);
-              }
+              // a stale value is only less extreme, so the filter below lets through a superset of
+              // the hits that can improve the pair's extremes
+              if (lane < kDirs)
+                S.thr[wp][lane] = gcur ? key_to_float((uint32_t)(gcur >> 32)) : -__int_as_float(0x7f800000);
+              else if (lane == kDirs)
+                S.pvthr[wp] = gcur;
             }
             int total = 0;
 #pragma unroll
@@ -1102,7 +1107,8 @@ __global__ void __launch_bounds__(128) bounds_kernel(
 // cand_offsets = exclusive scan (single CTA).
 __global__ void __launch_bounds__(1024) cand_plan_kernel(
     const int32_t* __restrict__ n_hit, const uint8_t* __restrict__ need,
-    const int32_t* __restrict__ caps_in, const float* __restrict__ poly, int64_t n_pairs,
+    const int32_t* __restrict__ caps_in, const float* __restrict__ poly,
+    const double* __restrict__ ratio_lo, const double* __restrict__ ratio_hi, int64_t n_pairs,
     int cap_max, int64_t pool, int64_t* __restrict__ cand_offsets) {
   __shared__ long long sm[33];
   long long carry = 0;
@@ -1113,10 +1119,17 @@ __global__ void __launch_bounds__(1024) cand_plan_kernel(
       if (caps_in) {
         v = caps_in[i];
       } else {
-        // candidates are a fraction of the hits (a third for the worst shapes
-        // measured): half of them, at least cap_max, never more than the hits
+        // candidates = the hits outside the inner polygon.  With the area bounds of the pair at
+        // hand their share is about 1 - (inner area / hull area) <= 1 - ratio_lo / ratio_hi: twice
+        // that share of the hits plus cap_max, never more than the hits (without the bounds: half
+        // of the hits).  Overflowing pairs are re-run by the caller with their exact counts.
         const int h = n_hit[i];
-        const int want = (h >> 1) > cap_max ? (h >> 1) : cap_max;
+        long long want = (h >> 1) > cap_max ? (h >> 1) : cap_max;
+        if (ratio_lo && ratio_hi) {
+          const double hi_ = ratio_hi[i], lo_ = ratio_lo[i];
+          const double share = (hi_ > 0.0 && lo_ >= 0.0 && lo_ <= hi_) ? (1.0 - lo_ / hi_) : 1.0;
+          want = (long long)(2.0 * share * (double)h) + cap_max;
+        }
         v = h < want ? h : want;
         // no inner polygon (degenerate extremes): every hit is a candidate
         if (poly && poly[i * kPolyFloats] == 0.0f) v = h;
@@ -1855,13 +1868,14 @@ int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
 }
 
 int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need, const int32_t* caps_in,
-                         const float* poly, int64_t n_pairs, int32_t cap_max,
+                         const float* poly, const double* ratio_lo, const double* ratio_hi,
+                         int64_t n_pairs, int32_t cap_max,
                          int64_t pool_capacity,
                          int64_t* cand_offsets, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_pairs >= 0 && n_hit && need && cand_offsets && cap_max >= 1 && pool_capacity >= 0,
                "arguments");
-  cand_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_hit, need, caps_in, poly, n_pairs,
-                                                       cap_max, pool_capacity, cand_offsets);
+  cand_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n_hit, need, caps_in, poly, ratio_lo, ratio_hi,
+                                                       n_pairs, cap_max, pool_capacity, cand_offsets);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

@@ -520,11 +520,11 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                                       _ptr(sub_idx), _ptr(sub_pos), st))
         if caps_in is None:
             # fixed pool (no sync): pairs that do not fit overflow and are re-run
-            total = max(P * 256, 32 << 20) if cand_pool is None else int(cand_pool)
+            total = max(P * 256, 64 << 20) if cand_pool is None else int(cand_pool)
         else:
             total = int(caps_in[need.bool()].sum().item())
-        check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), _ptr(poly), P, int(cand_capacity),
-                                       total, _ptr(cand_off), st))
+        check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), _ptr(poly), _ptr(ratio_lo),
+                                       _ptr(ratio_hi), P, int(cand_capacity), total, _ptr(cand_off), st))
         cand_uv = torch.empty((max(total, 1), 2), dtype=torch.float32, device=dev)
         check(lib.ptgs_visibility_init(P, None, None, None, _ptr(cand_count), st))
         mark("vis_plan")

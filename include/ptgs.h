@@ -414,8 +414,12 @@ int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
                            double* ratio_hi, uint8_t* need, double* area,
                            double* ratio, uint8_t* keep, uint8_t* flags,
                            ptgs_stream_t stream);
+/* ratio_lo / ratio_hi (may be NULL): the pair's area bounds of
+ * ptgs_visibility_bounds; the candidate capacity of an undecided pair is then
+ * sized from 1 - ratio_lo / ratio_hi instead of half of its hits. */
 int ptgs_visibility_plan(const int32_t* n_hit, const uint8_t* need,
                          const int32_t* caps_in, const float* poly,
+                         const double* ratio_lo, const double* ratio_hi,
                          int64_t n_pairs, int32_t cap_max,
                          int64_t pool_capacity,
                          int64_t* cand_offsets, ptgs_stream_t stream);

@@ -25,10 +25,10 @@ ncu_sweep)
   if [ -f /tmp/${tag}_sweep.ncu-rep ]; then
     tests=$(python -c "import json;print(json.load(open('$out/${tag}_vis_once.log'))['tests'])" 2>/dev/null || echo 0)
     python tools/ncu_summary.py /tmp/${tag}_sweep.ncu-rep > $out/${tag}_ncu_sweep_summary.txt 2>&1
-    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep 'sweep_kernel<\(int\)1' > $out/${tag}_ncu_sweep1_lines.txt 2>&1
-    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep 'sweep_kernel<\(int\)2' > $out/${tag}_ncu_sweep2_lines.txt 2>&1
-    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep 'hull_kernel' > $out/${tag}_ncu_hull_lines.txt 2>&1
-    python tools/ncu_json.py /tmp/${tag}_sweep.ncu-rep 'sweep_kernel<\(int\)1' $tests c4 $out/${tag}_sweep1_ncu.json > /dev/null 2>> $out/${tag}_ncu_sweep.log
+    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep sweep_kernel '<(int)1' > $out/${tag}_ncu_sweep1_lines.txt 2>&1
+    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep sweep_kernel '<(int)2' > $out/${tag}_ncu_sweep2_lines.txt 2>&1
+    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep hull_kernel > $out/${tag}_ncu_hull_lines.txt 2>&1
+    python tools/ncu_json.py /tmp/${tag}_sweep.ncu-rep 'sweep_kernel<1' $tests c4 $out/${tag}_sweep1_ncu.json > /dev/null 2>> $out/${tag}_ncu_sweep.log
   fi ;;
 launches)
   timeout 300 python tools/partition_once.py c4 > $out/${tag}_partition_once.log 2>&1 && \

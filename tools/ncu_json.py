@@ -1,8 +1,9 @@
 """One kernel launch of an .ncu-rep (ncu --set full) -> the JSON summary bench.py reads for its
 `roofline` object (profiles/r02_sweep1_ncu.json): DRAM bytes of the launch, issue-slot and pipe
 utilisation, executed lane operations per nominal point-camera test.
-usage: python tools/ncu_json.py rep.ncu-rep kernel-regex n_tests workload-label out.json
-       (the LONGEST matching launch is taken: the full-size sweep, not the sample pass)"""
+usage: python tools/ncu_json.py rep.ncu-rep kernel-name-substring n_tests workload-label out.json
+       (the LONGEST launch whose demangled name contains the substring is taken: the full-size sweep,
+       not the sample pass)"""
 import csv
 import io
 import json
@@ -10,11 +11,13 @@ import subprocess
 import sys
 
 rep, kre, n_tests, label, out = sys.argv[1], sys.argv[2], float(sys.argv[3]), sys.argv[4], sys.argv[5]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--kernel-name", "regex:" + kre],
-                     capture_output=True, text=True).stdout
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
 idx = {h: i for i, h in enumerate(hdr)}
+rows = rows[:2] + [r for r in rows[2:] if kre in r[idx["Kernel Name"]]]
+if len(rows) < 3:
+    sys.exit("no launch whose name contains %r" % kre)
 
 
 def val(r, name):

@@ -1,7 +1,9 @@
 """Per-source-line totals (instructions executed, stall samples) of one kernel launch in an .ncu-rep.
-usage: python tools/ncu_lines.py rep.ncu-rep kernel-regex [launch-ordinal among matches, default: the longest]"""
+usage: python tools/ncu_lines.py rep.ncu-rep kernel-base-name-regex [substring of the demangled name, e.g. "<(int)1"]
+(ncu's --kernel-name matches the base name without template arguments; the longest matching launch is reported)"""
 import csv, io, subprocess, sys, collections
 rep, kre = sys.argv[1], sys.argv[2]
+sub = sys.argv[3] if len(sys.argv) > 3 else None
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass",
                       "--kernel-name", "regex:" + kre], capture_output=True, text=True).stdout
 sections, cur, cols, fpath = [], None, None, ""
@@ -30,6 +32,8 @@ for row in csv.reader(io.StringIO(out)):
         continue
     e = cur["lines"].setdefault((fpath, ln), [0, 0, 0, row[first_src].strip()])
     e[0] += ins; e[1] += smp; e[2] += thr
+if sub:
+    sections = [x for x in sections if sub in x["name"]]
 if not sections:
     sys.exit("no sections parsed")
 sel = max(sections, key=lambda s: sum(v[0] for v in s["lines"].values()))
