@@ -319,14 +319,25 @@ __global__ void __launch_bounds__(kExpWarps * 32) expand_grid_kernel(
     if (!__any_sync(kFullMask, valid)) break;
     int beg, end;
     cell_range<T>(g, cell_off, valid, px, py, beg, end);
+    // which of the cell's candidate rectangles contain the point: evaluated once, as a bit mask
+    // over the candidate list (cells with more than 32 candidates re-test in every step)
+    const bool wide = (end - beg) > 32;
+    unsigned cm = 0;
+    if (!wide) {
+      for (int p = beg; p < end; ++p)
+        if (contains(cell_list[p], px, py)) cm |= 1u << (p - beg);
+    }
+    auto in_rect = [&](int p, int r) { return wide ? contains(r, px, py) : ((cm >> (p - beg)) & 1u) != 0u; };
     for (int p = beg; p < end; ++p) {                    // a: who is in which rectangle
+      if (!wide && !((cm >> (p - beg)) & 1u)) continue;
       const int r = cell_list[p];
-      if (contains(r, px, py)) atomicOr(&mymask[r], 1u << lane);
+      if (in_rect(p, r)) atomicOr(&mymask[r], 1u << lane);
     }
     __syncwarp();
     for (int p = beg; p < end; ++p) {                    // b: emit at (tile base + warp base + rank)
+      if (!wide && !((cm >> (p - beg)) & 1u)) continue;
       const int r = cell_list[p];
-      if (contains(r, px, py)) {
+      if (in_rect(p, r)) {
         const uint32_t m = mymask[r];
         const int64_t pos = sbase[r] + mycnt[r] + __popc(m & lanemask_lt());
         indices[pos] = (int32_t)i;
@@ -334,8 +345,9 @@ __global__ void __launch_bounds__(kExpWarps * 32) expand_grid_kernel(
     }
     __syncwarp();
     for (int p = beg; p < end; ++p) {                    // c: the lowest lane of each mask advances the counter
+      if (!wide && !((cm >> (p - beg)) & 1u)) continue;
       const int r = cell_list[p];
-      if (contains(r, px, py)) {
+      if (in_rect(p, r)) {
         const uint32_t m = mymask[r];
         if ((m & lanemask_lt()) == 0u) {                 // (a lane that reads an already cleared mask adds 0)
           atomicAdd(&mycnt[r], (uint32_t)__popc(m));
