@@ -1147,8 +1147,10 @@ __global__ void __launch_bounds__(1024) cand_plan_kernel(
 }
 
 // ---- exact hull + area per pair ----------------------------------------------
-constexpr int kHullThreads = 512;   // a pair's chain of passes is latency bound: 4 warps per scheduler
-constexpr int kHullParts = kHullThreads / 128;   // point partitions of the directional scan
+// Threads per pair (template NT): 512 when there are few undecided pairs (a pair's chain of passes is
+// latency bound: 4 warps per scheduler, one CTA per SM at 128 registers), 256 when there are many
+// (two CTAs per SM overlap one pair's serial phases with the other's parallel ones).
+constexpr int kHullMaxParts = 4;    // NT / 128 point partitions of the directional scan
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
 constexpr int kHullFilterMin = 128; // candidates above which the directional pre-filter runs
@@ -1181,11 +1183,13 @@ struct FilterSmem {
   int m;
   int out;
   int scan[33];
-  uint32_t pkey[kHullParts][kFiltDirs];
-  int pidx[kHullParts][kFiltDirs];
+  uint32_t pkey[kHullMaxParts][kFiltDirs];
+  int pidx[kHullMaxParts][kFiltDirs];
 };
 
+template <int NT>
 __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
+  constexpr int kHullThreads = NT, kHullParts = NT / 128;
   const int tid = threadIdx.x, lane = tid & 31, w = (tid >> 5) & 3, part = tid >> 7;
   // 1. extremes: warp (w, part) scans every kHullParts-th 128-point slice for the 16 directions of group w
   float best[16];
@@ -1295,7 +1299,8 @@ __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
   return F.out;
 }
 
-__global__ void __launch_bounds__(kHullThreads) hull_kernel(
+template <int NT>
+__global__ void __launch_bounds__(NT) hull_kernel(
     float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
     const int32_t* __restrict__ cand_count, const int32_t* __restrict__ n_hit, int64_t n_pairs,
     const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
@@ -1303,6 +1308,7 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
     uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out,
     const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev,
     int32_t* __restrict__ status /* [0] capacity overflows, [1] vertex-budget overflows; may be null */) {
+  constexpr int kHullThreads = NT;
   __shared__ float2 buf[kHullBuf];
   __shared__ float2 lower[kHullChain];
   __shared__ float2 upper[kHullChain];
@@ -1343,7 +1349,7 @@ __global__ void __launch_bounds__(kHullThreads) hull_kernel(
         F.dir[tid] = make_float2(cs, sn);
       }
       __syncthreads();
-      const int kn = filter_round(cu, K, margin, F);
+      const int kn = filter_round<NT>(cu, K, margin, F);
       const bool progress = kn < K - K / 16;
       K = kn;
       if (!progress && it >= 2) break;
@@ -1920,9 +1926,17 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
   PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
                "arguments");
   if (status) PTGS_CUDA_TRY(cudaMemsetAsync(status, 0, 8, (cudaStream_t)stream));
-  hull_kernel<<<(unsigned)n_pairs, kHullThreads, 0, (cudaStream_t)stream>>>(
-      (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-      ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
+  // the number of undecided pairs lives on the device; n_pairs / 8 is a typical share
+  const char* e = getenv("PTGS_HULL_THREADS");
+  const bool narrow = e ? (atoi(e) == 256) : (n_pairs >= 8 * 4 * kNumSMs);
+  if (narrow)
+    hull_kernel<256><<<(unsigned)n_pairs, 256, 0, (cudaStream_t)stream>>>(
+        (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
+        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
+  else
+    hull_kernel<512><<<(unsigned)n_pairs, 512, 0, (cudaStream_t)stream>>>(
+        (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
+        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }
