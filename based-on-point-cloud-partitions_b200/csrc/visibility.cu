@@ -2,21 +2,22 @@
 // Reference: project_points_to_camera (scene/ptgs/shen_partation_densify.py:
 // 410-477), run_graham_scan (:481-539), process_camera_visibility (:890-910).
 //
-// One persistent kernel sweeps (block, point tile) work items.  A tile of 2048
-// points is staged into shared memory with 1-D bulk copies (TMA, mbarrier
-// completion, double buffered so the next tile lands while the current one is
-// being swept), moved once into registers (8 points per thread) and then
-// tested against every camera of the block; camera records are broadcast
-// from shared memory.  Per test: 3 x (mul + 2 fma + add) camera transform in
-// the k-ordered accumulation of the reference's SGEMM, 2 x (mul + fma)
-// intrinsics, a division-free conservative reject, and IEEE divisions only
-// for the survivors.  Counts are reduced with redux.sync per warp and one
-// shared-memory atomic per (warp, camera); shared accumulators are flushed
-// with one global atomic per (work item, camera).
+// One persistent kernel (3 CTAs of 256 threads per SM) pulls (block, point tile) work items from a
+// global counter.  A tile of 1024 points (kSwP = 4 per thread) is staged into shared memory with 1-D
+// bulk copies (cp.async.bulk, mbarrier completion, double buffered so the next tile lands while the
+// current one is being swept) and moved into registers; each warp owns 128 contiguous points.
+// Three box levels come before any per-point work: the CTA culls the block's cameras against the
+// tile box (tiles wholly inside a camera's interior region are counted at once), every warp
+// classifies the surviving cameras against its own run's box, and the (run, camera) pairs that
+// still need points go to a per-CTA queue served by whichever warp is free.  Per point: the camera
+// transform in the k-ordered accumulation of the reference's SGEMM, division-free homogeneous
+// "surely in" / "surely out" tests, and IEEE divisions only for the band in between, compacted
+// into dense 32-lane groups.  Counts are warp uniform (ballot / popc); one global atomic per
+// (pass, camera).
 //
-//   MODE 0  hit counts (+ optional per-point "seen" flag)      -- coverage sweep
-//   MODE 1  hit counts + Graham pivot + 8 directional extremes -- sweep 1
-//   MODE 2  hull candidates                                   -- sweep 2
+//   MODE 0  hit counts (+ optional per-point "seen" flag)           -- coverage sweep
+//   MODE 1  hit counts + Graham pivot + 16 directional extremes     -- sweep 1 (and its sample pass)
+//   MODE 2  hull candidates of the undecided pairs                  -- sweep 2
 #include <cstddef>
 #include <cstdlib>
 
@@ -27,7 +28,7 @@ namespace ptgs {
 constexpr int kSwThreads = 256;
 constexpr int kSwP = 4;                          // points per thread
 constexpr int kSwCtasPerSM = 3;
-constexpr int kSwTile = kSwThreads * kSwP;       // 2048 points per tile
+constexpr int kSwTile = kSwThreads * kSwP;       // 1024 points per tile
 constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
 constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups); MODE 2: half (wider polygon rows)
 constexpr int kDirs = PTGS_EXTREME_DIRS;         // 16 directional extremes per pair
