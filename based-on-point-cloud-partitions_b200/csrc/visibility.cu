@@ -875,8 +875,10 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
             for (int base = 0; base < total; base += 32) {
               if (lane == 0) PTGS_FINE_STAT(7, 1);
               bool hit = false;
+              float u = 0.0f, v = 0.0f;
+              int sl = 0;
               if (base + lane < total) {
-                const int sl = S.slist[wp][base + lane];
+                sl = S.slist[wp][base + lane];
                 const int i = run * (32 * kSwP) + sl;
                 const float qx = S.tile[stage][0][shift0 + i], qy = S.tile[stage][1][shift0 + i],
                             qz = S.tile[stage][2][shift0 + i];
@@ -886,32 +888,61 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
                 p.Z = cam_row(c.r20, c.r21, c.r22, c.tz, qx, qy, qz);
                 p.uh = __fmaf_rn(c.cx, p.Z, __fmul_rn(c.fx, X));
                 p.vh = __fmaf_rn(c.cy, p.Z, __fmul_rn(c.fy, Y));
-                float u, v;
                 if (((front_y ? Y : p.Z) > 0.0f) && project_exact(c, p, u, v)) {
                   hit = true;
                   if (MODE == 0 && a.seen) a.seen[cur.start + i] = 1;
-                  if (MODE == 1) {
-                    u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
-                    v = __fadd_rn(v, 0.0f);
-                    const unsigned long long pk =
-                        ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                    if (pk < S.pvthr[wp] && pk < *reinterpret_cast<volatile unsigned long long*>(gpv))
-                      atomicMin(gpv, pk);
-                    float dv[kDirs];
-                    dir_values(u, v, dv);
-                    const uint32_t idx = base_idx + (uint32_t)sl;
-#pragma unroll
-                    for (int d = 0; d < kDirs; ++d) {
-                      // >=: among equal values the larger point index wins (max of (key, index))
-                      if (dv[d] >= S.thr[wp][d]) {
-                        const unsigned long long val = ((unsigned long long)order_key(dv[d]) << 32) | idx;
-                        if (val > *reinterpret_cast<volatile unsigned long long*>(gex + d)) atomicMax(gex + d, val);
-                      }
-                    }
-                  }
                 }
               }
               cnt += __popc(__ballot_sync(kFullMask, hit));
+              if (MODE == 1) {
+                // Pivot and the 16 directional extremes, warp-convergent: a direction is touched only
+                // when some hit of the group reaches the pair's current value (S.thr, refreshed as the
+                // pass goes); the group's best goes to the global slot with ONE atomic.
+                u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
+                v = __fadd_rn(v, 0.0f);
+                const unsigned long long pk =
+                    ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
+                if (__any_sync(kFullMask, hit && pk < S.pvthr[wp])) {
+                  const uint32_t ph = hit ? (uint32_t)(pk >> 32) : 0xffffffffu, pl = hit ? (uint32_t)pk : 0xffffffffu;
+                  const uint32_t mh = __reduce_min_sync(kFullMask, ph);
+                  const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
+                  if (lane == 0) {
+                    const unsigned long long best = ((unsigned long long)mh << 32) | ml;
+                    if (best < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, best);
+                    if (best < S.pvthr[wp]) S.pvthr[wp] = best;
+                  }
+                }
+                const float u2 = __fadd_rn(u, u), v2 = __fadd_rn(v, v);
+                const uint32_t idx = base_idx + (uint32_t)sl;
+#pragma unroll
+                for (int d = 0; d < kDirs; ++d) {
+                  float dval;
+                  switch (d & 7) {
+                    case 0: dval = u; break;
+                    case 1: dval = __fadd_rn(u2, v); break;
+                    case 2: dval = __fadd_rn(u, v); break;
+                    case 3: dval = __fadd_rn(u, v2); break;
+                    case 4: dval = v; break;
+                    case 5: dval = __fsub_rn(v2, u); break;
+                    case 6: dval = __fsub_rn(v, u); break;
+                    default: dval = __fsub_rn(v, u2); break;
+                  }
+                  if (d >= 8) dval = -dval;
+                  // >=: among equal values the larger point index wins (max of (key, index))
+                  const bool reach = hit && dval >= S.thr[wp][d];
+                  if (__any_sync(kFullMask, reach)) {
+                    const uint32_t key = reach ? order_key(dval) : 0u;
+                    const uint32_t kmax = __reduce_max_sync(kFullMask, key);
+                    const uint32_t imax = __reduce_max_sync(kFullMask, (reach && key == kmax) ? idx : 0u);
+                    if (lane == 0) {
+                      const unsigned long long val = ((unsigned long long)kmax << 32) | imax;
+                      if (val > *reinterpret_cast<volatile unsigned long long*>(gex + d)) atomicMax(gex + d, val);
+                      S.thr[wp][d] = key_to_float(kmax);
+                    }
+                  }
+                }
+                __syncwarp();
+              }
             }
           }
           if (lane == 0 && cnt) atomicAdd(a.n_hit + pair, cnt);
