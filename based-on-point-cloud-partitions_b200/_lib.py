@@ -13,8 +13,8 @@ PTGS_OK = 0
 PTGS_E_CAPACITY = -3
 PTGS_E_RANGE = -4
 CAMERA_FLOATS = 20
-POLY_FLOATS = 52
-EXTREME_DIRS = 16
+EXTREME_DIRS = 8                   # PTGS_EXTREME_DIRS (checked against the library at load)
+POLY_FLOATS = 4 + 3 * EXTREME_DIRS
 PAIR_RECORD_BYTES = 24
 
 _vp, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t
@@ -22,6 +22,7 @@ _vp, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_s
 # name -> (restype, argtypes); mirrors include/ptgs.h one to one
 SIGNATURES = {
     "ptgs_version": (C.c_int, []),
+    "ptgs_extreme_dirs": (C.c_int, []),
     "ptgs_last_error": (C.c_char_p, []),
     "ptgs_launch_count": (_i64, []),
     "ptgs_reset_launch_count": (None, []),
@@ -116,6 +117,9 @@ def load(build_if_missing: bool = True):
         fn = getattr(lib, name)          # AttributeError if the symbol is missing
         fn.restype = res
         fn.argtypes = args
+    global EXTREME_DIRS, POLY_FLOATS
+    EXTREME_DIRS = int(lib.ptgs_extreme_dirs())
+    POLY_FLOATS = 4 + 3 * EXTREME_DIRS
     _lib = lib
     return lib
 

@@ -327,7 +327,8 @@ using namespace ptgs;
 
 extern "C" {
 
-int ptgs_version(void) { return 100; }
+int ptgs_version(void) { return 200; }
+int ptgs_extreme_dirs(void) { return PTGS_EXTREME_DIRS; }
 const char* ptgs_last_error(void) { return g_err; }
 int64_t ptgs_launch_count(void) { return g_launches; }
 void ptgs_reset_launch_count(void) { g_launches = 0; }

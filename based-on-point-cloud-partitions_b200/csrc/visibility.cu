@@ -31,7 +31,9 @@ constexpr int kSwCtasPerSM = 3;
 constexpr int kSwTile = kSwThreads * kSwP;       // 1024 points per tile
 constexpr int kSwStageFloats = kSwTile + 8;      // + alignment slack
 constexpr int kSwCamChunk = 160;                 // cameras staged per chunk (5 lane groups); MODE 2: half (wider polygon rows)
-constexpr int kDirs = PTGS_EXTREME_DIRS;         // 16 directional extremes per pair
+constexpr int kDirs = PTGS_EXTREME_DIRS;         // directional extremes per pair (8 or 16)
+constexpr int kDirStep = 16 / kDirs;             // stride through the table of 16 directions
+static_assert(kDirs == 8 || kDirs == 16, "PTGS_EXTREME_DIRS");
 constexpr int kSwMaxBlocks = 1024;
 constexpr int kCamFloats = PTGS_CAMERA_FLOATS;   // 20
 constexpr int kPolyFloats = PTGS_POLY_FLOATS;    // 28
@@ -142,23 +144,25 @@ __device__ __forceinline__ float key_to_float(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 
-// The 16 directions (a, b) along which a pair's extreme hits are tracked, counter-clockwise from
-// +u: (1,0) (2,1) (1,1) (1,2) (0,1) (-1,2) (-1,1) (-2,1) and their negatives.  value = a*u + b*v with
-// ONE float32 rounding (2u / 2v are exact); the even directions are round 1's eight.
+// The directions (a, b) along which a pair's extreme hits are tracked, counter-clockwise from +u:
+// (1,0) (2,1) (1,1) (1,2) (0,1) (-1,2) (-1,1) (-2,1) and their negatives; kDirs = 8 uses every other one
+// (the axes and diagonals).  value = a*u + b*v with ONE float32 rounding (2u / 2v are exact).
 __constant__ float kDirA[16] = {1, 2, 1, 1, 0, -1, -1, -2, -1, -2, -1, -1, 0, 1, 1, 2};
 __constant__ float kDirB[16] = {0, 1, 1, 2, 1, 2, 1, 1, 0, -1, -1, -2, -1, -2, -1, -1};
-__device__ __forceinline__ void dir_values(float u, float v, float* dv) {
-  const float u2 = __fadd_rn(u, u), v2 = __fadd_rn(v, v);
-  dv[0] = u;
-  dv[1] = __fadd_rn(u2, v);
-  dv[2] = __fadd_rn(u, v);
-  dv[3] = __fadd_rn(u, v2);
-  dv[4] = v;
-  dv[5] = __fsub_rn(v2, u);
-  dv[6] = __fsub_rn(v, u);
-  dv[7] = __fsub_rn(v, u2);
-#pragma unroll
-  for (int d = 0; d < 8; ++d) dv[8 + d] = -dv[d];
+// value of table direction t (0..15); u2 = 2u, v2 = 2v.  t is a compile-time constant at every use.
+__device__ __forceinline__ float dir_value(int t, float u, float v, float u2, float v2) {
+  float r;
+  switch (t & 7) {
+    case 0: r = u; break;
+    case 1: r = __fadd_rn(u2, v); break;
+    case 2: r = __fadd_rn(u, v); break;
+    case 3: r = __fadd_rn(u, v2); break;
+    case 4: r = v; break;
+    case 5: r = __fsub_rn(v2, u); break;
+    case 6: r = __fsub_rn(v, u); break;
+    default: r = __fsub_rn(v, u2); break;
+  }
+  return (t >= 8) ? -r : r;
 }
 
 // ---- conservative tile cull ----------------------------------------------------
@@ -471,8 +475,9 @@ struct SweepSmem {
 // still improve the pair's current global values (thresholds read once per pass).
 template <int MODE>
 __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepArgs a) {
-  constexpr int kChunk = (MODE == 2) ? kSwCamChunk / 2 : kSwCamChunk;          // cameras staged per chunk
-  constexpr int kPolyStride = (MODE == 2) ? 2 * kKrectFloats : kKrectFloats;   // floats per staged polygon row
+  constexpr bool kWidePoly = (MODE == 2) && (kPolyFloats > kKrectFloats);      // 16-edge inner polygons
+  constexpr int kChunk = kWidePoly ? kSwCamChunk / 2 : kSwCamChunk;            // cameras staged per chunk
+  constexpr int kPolyStride = kWidePoly ? 2 * kKrectFloats : kKrectFloats;     // floats per staged polygon row
   static_assert(kPolyFloats <= 2 * kKrectFloats, "inner polygon row");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
@@ -895,53 +900,49 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
               }
               cnt += __popc(__ballot_sync(kFullMask, hit));
               if (MODE == 1) {
-                // Pivot and the 16 directional extremes, warp-convergent: a direction is touched only
-                // when some hit of the group reaches the pair's current value (S.thr, refreshed as the
-                // pass goes); the group's best goes to the global slot with ONE atomic.
+                // Pivot and directional extremes.  Per lane: can this hit reach any of the pair's
+                // current values (S.thr / S.pvthr, refreshed as the pass goes)?  Only then -- rare
+                // once a pair has seen a few tiles -- the group reduces convergently and sends ONE
+                // atomic per improved direction.
                 u = __fadd_rn(u, 0.0f);   // -0.0 -> +0.0 (numerically equal for the reference)
                 v = __fadd_rn(v, 0.0f);
                 const unsigned long long pk =
                     ((unsigned long long)__float_as_uint(v) << 32) | __float_as_uint(u);
-                if (__any_sync(kFullMask, hit && pk < S.pvthr[wp])) {
-                  const uint32_t ph = hit ? (uint32_t)(pk >> 32) : 0xffffffffu, pl = hit ? (uint32_t)pk : 0xffffffffu;
-                  const uint32_t mh = __reduce_min_sync(kFullMask, ph);
-                  const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
-                  if (lane == 0) {
-                    const unsigned long long best = ((unsigned long long)mh << 32) | ml;
-                    if (best < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, best);
-                    if (best < S.pvthr[wp]) S.pvthr[wp] = best;
-                  }
-                }
                 const float u2 = __fadd_rn(u, u), v2 = __fadd_rn(v, v);
-                const uint32_t idx = base_idx + (uint32_t)sl;
+                bool imp = pk < S.pvthr[wp];
 #pragma unroll
-                for (int d = 0; d < kDirs; ++d) {
-                  float dval;
-                  switch (d & 7) {
-                    case 0: dval = u; break;
-                    case 1: dval = __fadd_rn(u2, v); break;
-                    case 2: dval = __fadd_rn(u, v); break;
-                    case 3: dval = __fadd_rn(u, v2); break;
-                    case 4: dval = v; break;
-                    case 5: dval = __fsub_rn(v2, u); break;
-                    case 6: dval = __fsub_rn(v, u); break;
-                    default: dval = __fsub_rn(v, u2); break;
-                  }
-                  if (d >= 8) dval = -dval;
-                  // >=: among equal values the larger point index wins (max of (key, index))
-                  const bool reach = hit && dval >= S.thr[wp][d];
-                  if (__any_sync(kFullMask, reach)) {
-                    const uint32_t key = reach ? order_key(dval) : 0u;
-                    const uint32_t kmax = __reduce_max_sync(kFullMask, key);
-                    const uint32_t imax = __reduce_max_sync(kFullMask, (reach && key == kmax) ? idx : 0u);
+                for (int d = 0; d < kDirs; ++d)
+                  imp = imp || (dir_value(d * kDirStep, u, v, u2, v2) >= S.thr[wp][d]);
+                if (__any_sync(kFullMask, hit && imp)) {
+                  if (__any_sync(kFullMask, hit && pk < S.pvthr[wp])) {
+                    const uint32_t ph = hit ? (uint32_t)(pk >> 32) : 0xffffffffu, pl = hit ? (uint32_t)pk : 0xffffffffu;
+                    const uint32_t mh = __reduce_min_sync(kFullMask, ph);
+                    const uint32_t ml = __reduce_min_sync(kFullMask, ph == mh ? pl : 0xffffffffu);
                     if (lane == 0) {
-                      const unsigned long long val = ((unsigned long long)kmax << 32) | imax;
-                      if (val > *reinterpret_cast<volatile unsigned long long*>(gex + d)) atomicMax(gex + d, val);
-                      S.thr[wp][d] = key_to_float(kmax);
+                      const unsigned long long best = ((unsigned long long)mh << 32) | ml;
+                      if (best < *reinterpret_cast<volatile unsigned long long*>(gpv)) atomicMin(gpv, best);
+                      if (best < S.pvthr[wp]) S.pvthr[wp] = best;
                     }
                   }
+                  const uint32_t idx = base_idx + (uint32_t)sl;
+#pragma unroll
+                  for (int d = 0; d < kDirs; ++d) {
+                    const float dval = dir_value(d * kDirStep, u, v, u2, v2);
+                    // >=: among equal values the larger point index wins (max of (key, index))
+                    const bool reach = hit && dval >= S.thr[wp][d];
+                    if (__any_sync(kFullMask, reach)) {
+                      const uint32_t key = reach ? order_key(dval) : 0u;
+                      const uint32_t kmax = __reduce_max_sync(kFullMask, key);
+                      const uint32_t imax = __reduce_max_sync(kFullMask, (reach && key == kmax) ? idx : 0u);
+                      if (lane == 0) {
+                        const unsigned long long val = ((unsigned long long)kmax << 32) | imax;
+                        if (val > *reinterpret_cast<volatile unsigned long long*>(gex + d)) atomicMax(gex + d, val);
+                        S.thr[wp][d] = key_to_float(kmax);
+                      }
+                    }
+                  }
+                  __syncwarp();
                 }
-                __syncwarp();
               }
             }
           }
@@ -1101,19 +1102,20 @@ __global__ void __launch_bounds__(128) bounds_kernel(
     out[0] = (float)m;
     a_in = shoelace(vx, vy, m);
   }
-  // outer polygon: the 16 supporting half planes a_d*u + b_d*v <= sup_d.  Start from the rectangle of
-  // the four axis directions, clip by the other twelve (each clip adds at most one vertex: <= 16).
+  // outer polygon: the kDirs supporting half planes a_d*u + b_d*v <= sup_d.  Start from the rectangle of
+  // the four axis directions, clip by the others (each clip adds at most one vertex: <= kDirs <= 16).
   double ax[16], ay[16], bx[16], by[16];
-  ax[0] = -sup[8]; ay[0] = -sup[12];
-  ax[1] = sup[0];  ay[1] = -sup[12];
-  ax[2] = sup[0];  ay[2] = sup[4];
-  ax[3] = -sup[8]; ay[3] = sup[4];
+  constexpr int kQ = kDirs / 4;                      // index step between the axis directions
+  ax[0] = -sup[2 * kQ]; ay[0] = -sup[3 * kQ];
+  ax[1] = sup[0];       ay[1] = -sup[3 * kQ];
+  ax[2] = sup[0];       ay[2] = sup[kQ];
+  ax[3] = -sup[2 * kQ]; ay[3] = sup[kQ];
   int n = 4;
   {
     double* sx_ = ax; double* sy_ = ay; double* tx_ = bx; double* ty_ = by;
     for (int d = 1; d < kDirs; ++d) {
-      if ((d & 3) == 0) continue;
-      n = clip_halfplane(sx_, sy_, n, (double)kDirA[d], (double)kDirB[d], sup[d], tx_, ty_);
+      if ((d % kQ) == 0) continue;
+      n = clip_halfplane(sx_, sy_, n, (double)kDirA[d * kDirStep], (double)kDirB[d * kDirStep], sup[d], tx_, ty_);
       double* t = sx_; sx_ = tx_; tx_ = t;
       t = sy_; sy_ = ty_; ty_ = t;
     }
@@ -1605,7 +1607,7 @@ __global__ void __launch_bounds__(128) krect_kernel(
   double vx[8], vy[8];
   int m = 0;
   for (int d = 0; d < 8; ++d) {
-    const uint64_t e = extreme_s[pair * kDirs + 2 * d];      // the eight even (axis / diagonal) directions
+    const uint64_t e = extreme_s[pair * kDirs + d * (kDirs / 8)];      // the eight axis / diagonal directions
     if (!e) continue;
     const int64_t gi = p0 + (int64_t)(e & 0xffffffffull);
     const Proj p = project_pre(c, 0.0f, 0.0f, sx[gi], sy[gi], sz[gi]);

@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import PTGS_F32, PTGS_F64, CAMERA_FLOATS, POLY_FLOATS, EXTREME_DIRS, check
+from ._lib import PTGS_F32, PTGS_F64, CAMERA_FLOATS, check
 
 # constants hard-coded by the reference (file:line in DESIGN.md)
 RADIUS, NB_POINTS = 1.0, 5            # shen_partition_utils.py:28-30
@@ -458,11 +458,11 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
     if P == 0:
         return VisibilityResult(n_hit[:0], area[:0], ratio[:0], keep[:0], flags[:0], cand_count[:0], 0)
     pivot = torch.empty(P, dtype=torch.int64, device=dev)
-    extreme = torch.empty(P * EXTREME_DIRS, dtype=torch.int64, device=dev)
+    extreme = torch.empty(P * _lib.EXTREME_DIRS, dtype=torch.int64, device=dev)
     ratio_lo = torch.empty(P, dtype=torch.float64, device=dev)
     ratio_hi = torch.empty(P, dtype=torch.float64, device=dev)
     need = torch.empty(P, dtype=torch.uint8, device=dev)
-    poly = torch.empty((P, POLY_FLOATS), dtype=torch.float32, device=dev)
+    poly = torch.empty((P, _lib.POLY_FLOATS), dtype=torch.float32, device=dev)
     if cam_split is None:
         cam_split = pick_cam_split(int(ds_x.shape[0]), L)
     ws = _ws(lib.ptgs_visibility_workspace_bytes(L), dev)
@@ -478,7 +478,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         s_off = torch.empty(L + 1, dtype=torch.int64, device=dev)
         n_hit_s = torch.empty(P, dtype=torch.int32, device=dev)
         pivot_s = torch.empty(P, dtype=torch.int64, device=dev)
-        extreme_s = torch.empty(P * EXTREME_DIRS, dtype=torch.int64, device=dev)
+        extreme_s = torch.empty(P * _lib.EXTREME_DIRS, dtype=torch.int64, device=dev)
         krect = torch.empty((P, 32), dtype=torch.float32, device=dev)     # PTGS_KRECT_FLOATS
         check(lib.ptgs_visibility_sample(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                          int(sample_stride), _ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]),
@@ -520,7 +520,9 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                                       _ptr(sub_idx), _ptr(sub_pos), st))
         if caps_in is None:
             # fixed pool (no sync): pairs that do not fit overflow and are re-run
-            total = max(P * 256, 64 << 20) if cand_pool is None else int(cand_pool)
+            # 8 bytes per slot; address space rather than traffic (only emitted candidates are touched)
+            floor = (32 << 20) if int(ds_x.shape[0]) < (20 << 20) else (128 << 20)
+            total = max(P * 256, floor) if cand_pool is None else int(cand_pool)
         else:
             total = int(caps_in[need.bool()].sum().item())
         check(lib.ptgs_visibility_plan(_ptr(n_hit), _ptr(need), _ptr(caps_in), _ptr(poly), _ptr(ratio_lo),

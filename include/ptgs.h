@@ -52,6 +52,8 @@ typedef enum ptgs_status {
 typedef enum ptgs_dtype { PTGS_F32 = 0, PTGS_F64 = 1 } ptgs_dtype;
 
 int ptgs_version(void);
+/* PTGS_EXTREME_DIRS the library was built with (sizes of `extreme` / `poly`). */
+int ptgs_extreme_dirs(void);
 const char* ptgs_last_error(void);
 /* Number of kernel launches issued by this library on the calling thread
  * since the last ptgs_reset_launch_count() (bench.py `gpu_launches`). */
@@ -312,18 +314,19 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  *   pivot[p]   uint64  (bits(v) << 32 | bits(u)) of the Graham pivot: lowest v,
  *                      then lowest u (:509-511); ~0 when n_hit == 0
  *   extreme[p][PTGS_EXTREME_DIRS] uint64  (ordered key << 32 | point position
- *                      inside the block) of the extreme hit along 16 directions
+ *                      inside the block) of the extreme hit along the directions
  *                      (a, b), value a*u + b*v with one float32 rounding,
- *                      counter-clockwise from +u: (1,0) (2,1) (1,1) (1,2) (0,1)
- *                      (-1,2) (-1,1) (-2,1) and their negatives; 0 = none.
+ *                      counter-clockwise from +u: (1,0) (1,1) (0,1) (-1,1) and
+ *                      their negatives (PTGS_EXTREME_DIRS = 8), plus (2,1) (1,2)
+ *                      (-1,2) (-2,1) and their negatives in between (= 16); 0 = none.
  * All three are accumulated with atomics and must be pre-initialised by
  * ptgs_visibility_init (also zeroes cand_count).
  *
  * ptgs_visibility_bounds: per pair
  *   - the inner polygon (the extreme hits that survive the reference's
- *     pivot-row rule, see below) as <= 16 half planes -> `poly`, and its area
+ *     pivot-row rule, see below) as <= PTGS_EXTREME_DIRS half planes -> `poly`, and its area
  *     / (W*H) -> ratio_lo: a lower bound of the reference's ratio;
- *   - the outer polygon (intersection of the 16 supporting half planes of sweep
+ *   - the outer polygon (intersection of the supporting half planes of sweep
  *     1) -> ratio_hi: an upper bound;
  *   - the early decision: n_hit <= min_hits -> dropped (:898); ratio_lo >=
  *     thr + near_eps -> kept; ratio_hi < thr - near_eps -> dropped.  Decided
@@ -401,8 +404,8 @@ int ptgs_visibility_krect(const float* sx, const float* sy, const float* sz,
                           const int32_t* cam_index, const int32_t* n_hit_s,
                           const uint64_t* extreme_s, int64_t n_pairs,
                           double margin_px, float* krect, ptgs_stream_t stream);
-#define PTGS_EXTREME_DIRS 16
-#define PTGS_POLY_FLOATS 52 /* [0]=n_edges [1]=v_pivot [2]=u_pivot [3]=margin, 16 x (a,b,c) */
+#define PTGS_EXTREME_DIRS 8 /* 8 or 16 (compile time); see "extreme" above */
+#define PTGS_POLY_FLOATS (4 + 3 * PTGS_EXTREME_DIRS) /* [0]=n_edges [1]=v_pivot [2]=u_pivot [3]=margin, DIRS x (a,b,c) */
 int ptgs_visibility_bounds(const float* px, const float* py, const float* pz,
                            const int64_t* pt_offsets, int32_t n_blocks,
                            const float* cameras, const int64_t* cam_offsets,
