@@ -185,6 +185,22 @@ def slab_bounds(x, world: int, sample: int = 65536) -> np.ndarray:
     return b
 
 
+def slab_select(x, y, z, lo: float, hi: float):
+    """ptgs_slab_select: the points with lo <= x < hi, compacted in index order.  Returns
+    (planes (3, pitch) of x's dtype, cloud indices int32, device count)."""
+    lib = _lib.load()
+    dev = x.device
+    n = int(x.shape[0])
+    pitch = (max(n, 1) + 3) // 4 * 4
+    sub = torch.empty((3, pitch), dtype=x.dtype, device=dev)
+    sidx = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    m_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+    ws = _ws(lib.ptgs_slab_select_workspace_bytes(n), dev)
+    check(lib.ptgs_slab_select(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, float(lo), float(hi), _ptr(sub[0]),
+                               _ptr(sub[1]), _ptr(sub[2]), _ptr(sidx), _ptr(m_dev), _ptr(ws), ws.numel(), _stream()))
+    return sub, sidx, m_dev
+
+
 def radius_outlier_mask_sharded(x, y, z, rank: int, world: int, group=None, radius=RADIUS, nb_points=NB_POINTS,
                                 bounds=None, reduce=True):
     """A1 over several GPUs: rank r filters the points of its X slab, with the points within one grid
@@ -201,12 +217,7 @@ def radius_outlier_mask_sharded(x, y, z, rank: int, world: int, group=None, radi
     lo, hi = float(bounds[rank]), float(bounds[rank + 1])
     halo = float(radius) * (1.0 + 1.0 / 1024.0)
     keep = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
-    sub = torch.empty((3, max(n, 1)), dtype=x.dtype, device=dev)
-    sidx = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
-    m_dev = torch.zeros(1, dtype=torch.int64, device=dev)
-    ws = _ws(lib.ptgs_slab_select_workspace_bytes(n), dev)
-    check(lib.ptgs_slab_select(_dt(x), _ptr(x), _ptr(y), _ptr(z), n, lo - halo, hi + halo, _ptr(sub[0]),
-                               _ptr(sub[1]), _ptr(sub[2]), _ptr(sidx), _ptr(m_dev), _ptr(ws), ws.numel(), _stream()))
+    sub, sidx, m_dev = slab_select(x, y, z, lo - halo, hi + halo)
     m = int(m_dev.item())
     if m > 0:
         skeep, _ = radius_outlier_mask(sub[0, :m], sub[1, :m], sub[2, :m], radius, nb_points)
@@ -641,6 +652,9 @@ def coverage_sweep(px, py, pz, cameras_d, cam_first=0, cam_count=None, want_seen
 def coverage_sweep_sharded(px, py, pz, cameras_d, rank: int, world: int, group=None, want_seen=False,
                            shard="points", ordered=None):
     """Config c5 over several GPUs.  Every rank holds the whole cloud and all cameras.
+    shard="slabs": rank r orders and sweeps the X slab of the cloud between two quantiles of x
+    (slab_bounds / ptgs_slab_select) against ALL cameras; counts are one int32 sum all-reduce, seen
+    flags one MAX all-reduce.
     shard="points" (default): rank r orders and sweeps only its slice of the cloud
     (multigpu.point_range) against ALL cameras -- the Morton sort and the per-tile camera culls,
     which dominate after the sort, both divide by the number of ranks; per-camera counts are one
@@ -657,6 +671,27 @@ def coverage_sweep_sharded(px, py, pz, cameras_d, rank: int, world: int, group=N
         n_hit = M.gather_camera_counts(n_hit, C, world, group)
         return (n_hit, M.merge_seen(seen, world, group)) if want_seen else n_hit
     n = px.shape[0]
+    if shard == "slabs":
+        # rank r takes the X slab [bounds[r], bounds[r+1]) of the cloud: a spatially compact n / world
+        # points, so tiles and warp runs stay as small as on one GPU (a file-order slice is a random
+        # subset of the whole scene: its tiles cover `world` times the area and are cut by more cameras)
+        import torch.distributed as dist
+        bounds = slab_bounds(px, world)
+        sub, sidx, m_dev = slab_select(px, py, pz, bounds[rank], bounds[rank + 1])
+        m = int(m_dev.item())
+        if m > 0:
+            out = coverage_sweep(sub[0, :m], sub[1, :m], sub[2, :m], cameras_d, want_seen=want_seen)
+            n_hit, seen_l = out if want_seen else (out, None)
+        else:
+            n_hit, seen_l = torch.zeros(C, dtype=torch.int32, device=px.device), None
+        n_hit = M.sum_camera_counts(n_hit.contiguous(), world, group)
+        if not want_seen:
+            return n_hit
+        seen = torch.zeros(max(n, 1), dtype=torch.uint8, device=px.device)
+        if m > 0:
+            seen[sidx[:m].to(torch.int64)] = seen_l
+        dist.all_reduce(seen, op=dist.ReduceOp.MAX, group=group)
+        return n_hit, seen[:n]
     p0, p1 = M.point_range(n, rank, world)
     out = coverage_sweep(px[p0:p1], py[p0:p1], pz[p0:p1], cameras_d, want_seen=want_seen)
     n_hit, seen = out if want_seen else (out, None)

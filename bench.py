@@ -85,7 +85,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -228,15 +228,17 @@ def run_ours(args):
         k_off, k_idx = D.select_cameras(v.keep, res.cam_offsets, res.cam_index, sync=False)
         return v, k_off, k_idx
 
+    # clocks / throttle reasons are sampled (20 ms period) from the warm-up passes to the end of the
+    # timed region: the timed steps alone last a few tens of milliseconds
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(args.warmup, 3)):
         flush.fill_(1)
         vis_step()
     barrier(world)
 
     # ---- timed region: K steps, each bracketed by events, L2 flushed between --
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     lib.ptgs_reset_launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
@@ -436,6 +438,7 @@ def measure_partition(args, out, ctx):
     D, w, dev, world, rank = ctx["D"], ctx["w"], ctx["dev"], ctx["world"], ctx["rank"]
     runs, runs_dev = [], []
     stages = None
+    d2h = 0
     for i in range(4):
         ctx["flush"].fill_(i)
         barrier(world)
@@ -444,14 +447,16 @@ def measure_partition(args, out, ctx):
                                time_stages=True, shard=(rank, world) if world > 1 else None)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
-        host = D.partition_results_to_host(r)
+        # every rank holds the full result; one host copy of it is the job's output (rank 0)
+        host = D.partition_results_to_host(r) if rank == 0 else {}
         torch.cuda.synchronize()
         t2 = time.perf_counter()
         if i > 0:
             runs.append(t2 - t0)
             runs_dev.append(t1 - t0)
             stages = r.timings_ms
-        d2h = sum(a.nbytes for a in host.values() if hasattr(a, "nbytes"))
+        if rank == 0:
+            d2h = sum(a.nbytes for a in host.values() if hasattr(a, "nbytes"))
         del r, host
     best = max_over_ranks(min(runs), world, dev)
     best_dev = max_over_ranks(min(runs_dev), world, dev)
@@ -526,13 +531,15 @@ def measure_c5(args, out, ctx, c5):
 
     def step(timer=None):
         mark = timer.mark if timer is not None else (lambda name: None)
+        if world > 1:
+            # X-slab sharding: every rank selects, orders and sweeps a spatially compact n / N points
+            nh = D.coverage_sweep_sharded(x, y, z, cams_d, rank, world, shard="slabs")
+            mark("c5_sharded_step")
+            return nh
         od = D.spatial_order(xs, ys, zs, xyz_aos=rows)
         mark("c5_order")
         nh = D.coverage_sweep(xs, ys, zs, cams_d, ordered=od)
         mark("c5_sweep")
-        if world > 1:
-            nh = M.sum_camera_counts(nh.contiguous(), world)
-            mark("c5_allreduce")
         return nh
     step()
     barrier(world)
@@ -560,8 +567,8 @@ def measure_c5(args, out, ctx, c5):
            "hits": int(nh64.sum().item()),
            "hits_checksum": int((nh64 * torch.arange(1, C + 1, device=dev)).sum().item()),
            "cameras_with_hits": int((n_hit > 0).sum().item()),
-           "sharding": "points (every rank orders and sweeps n/N points against all cameras; int32 sum all-reduce)"
-           if world > 1 else "single GPU",
+           "sharding": "X slabs (every rank selects the points between two quantiles of x, orders and sweeps them "
+                       "against all cameras; int32 sum all-reduce)" if world > 1 else "single GPU",
            "scene_generation_s": round(c5["gen_s"], 1),
            "hbm": {"algorithmic_bytes_survey_Bc64": float(np.ceil(C / 64.0) * n * 12 + C * 84),
                    "frac_of_peak_at_that_figure": (np.ceil(C / 64.0) * n * 12 + C * 84) / world / (ms * 1e-3) / 1e9 / hbm_peak,
