@@ -254,3 +254,32 @@ def test_slab_sharded_radius_filter_equals_single_gpu(world, f64):
     assert bool((owned == 1).all())
     assert torch.equal(acc, full) and int(acc.sum()) == int(n_full.item())
     assert 0 < int(full.sum()) < full.numel()
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_slab_sharded_coverage_equals_single_gpu(world):
+    """Config-c5 sharding: every rank sweeps the X slab between two quantiles of x; per-camera counts
+    add up to the unsharded sweep's, per-point seen flags scatter back through the slab's index list
+    (the collectives are replaced by sums here; ranks run one after the other on this GPU)."""
+    w = W.make("c3", 0.03)
+    recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
+    recs[::2, 18] = 2.0
+    cams_d = torch.from_numpy(recs).to(DEV)
+    x, y, z = D.aos_to_soa(torch.from_numpy(w.xyz).to(DEV))
+    want, wseen = D.coverage_sweep(x, y, z, cams_d, want_seen=True)
+    bounds = D.slab_bounds(x, world)
+    total = torch.zeros_like(want)
+    seen = torch.zeros_like(wseen)
+    n_sel = 0
+    for r in range(world):
+        sub, sidx, m_dev = D.slab_select(x, y, z, bounds[r], bounds[r + 1])
+        m = int(m_dev.item())
+        n_sel += m
+        idx = sidx[:m].to(torch.int64)
+        assert bool((idx[1:] > idx[:-1]).all())                       # index order kept
+        assert torch.equal(sub[0, :m], x[idx]) and torch.equal(sub[2, :m], z[idx])
+        nh, sl = D.coverage_sweep(sub[0, :m], sub[1, :m], sub[2, :m], cams_d, want_seen=True)
+        total += nh
+        seen[idx] = torch.maximum(seen[idx], sl)
+    assert n_sel == x.shape[0]
+    assert torch.equal(total, want) and torch.equal(seen, wseen) and int(want.sum()) > 1000
