@@ -73,7 +73,8 @@ SIGNATURES = {
     "ptgs_points3d_index": (_i64, [_vp, _i64, _vp, _i64]),
     "ptgs_points3d_decode": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ptgs_pack_records": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
-    "ptgs_unpack_records": (C.c_int, [_vp, _i32, _i64, C.POINTER(_i64), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ptgs_unpack_records": (C.c_int, [_vp, _i32, _i64, C.POINTER(_i64), C.POINTER(_i64), _i64, _vp, _vp, _vp, _vp,
+                                      _vp, _vp]),
     "ptgs_debug_sweep_stats": (C.c_int, [C.POINTER(C.c_uint64), _i32]),
     "ptgs_debug_fma_probe": (C.c_int, [_vp, _i32, _vp]),
     "ptgs_spatial_order_workspace_bytes": (_sz, [_i64]),

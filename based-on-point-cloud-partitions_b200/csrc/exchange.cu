@@ -3,11 +3,12 @@
 // visibility_based_camera_selection, scene/ptgs/shen_partation_densify.py:932-944;
 // the reference is single process, so the exchange has no counterpart there.
 //
-// With range sharding rank r owns the CONTIGUOUS pair range [lo_r, lo_{r+1}).
-// One kernel packs the rank's result vectors into 24-byte records, one
+// With range sharding a rank owns one or a few CONTIGUOUS ranges of the pair
+// list.  One kernel packs the rank's result vectors into 24-byte records, one
 // all-gather (NCCL, issued by the caller on the same stream) delivers every
-// rank's slice, one kernel unpacks the gathered slots straight into the full
-// per-pair vectors.  No zero-filled P x world table, no reduction.
+// rank's slot, one kernel unpacks the gathered slots straight into the full
+// per-pair vectors (range table by value).  No zero-filled P x world table,
+// no reduction.
 #include "common.cuh"
 
 namespace ptgs {
@@ -22,8 +23,11 @@ struct alignas(8) PairRecord {
 };
 static_assert(sizeof(PairRecord) == PTGS_PAIR_RECORD_BYTES, "record layout");
 
-constexpr int kMaxRanks = 64;
-struct RankBounds { int64_t lo[kMaxRanks + 1]; };
+constexpr int kMaxRanges = 128;     // world * chunks
+struct RangeTable {
+  int64_t lo[kMaxRanges + 1];       // range c = pairs [lo[c], lo[c+1])
+  int64_t base[kMaxRanges];         // record position of the range's first pair in the gathered table
+};
 
 __global__ void __launch_bounds__(256) pack_records_kernel(
     const int32_t* __restrict__ n_hit, const double* __restrict__ ratio,
@@ -38,14 +42,17 @@ __global__ void __launch_bounds__(256) pack_records_kernel(
 }
 
 __global__ void __launch_bounds__(256) unpack_records_kernel(
-    const PairRecord* __restrict__ gathered, int world, int64_t slot_pairs, RankBounds rb,
+    const PairRecord* __restrict__ gathered, int n_ranges, RangeTable rt,
     int64_t n_pairs, int32_t* __restrict__ n_hit, double* __restrict__ ratio,
     double* __restrict__ area, uint8_t* __restrict__ keep, uint8_t* __restrict__ flags) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n_pairs) return;
-  int r = 0;                                   // last rank with lo[r] <= p (empty ranks share a bound)
-  for (int k = 1; k < world; ++k) r = (rb.lo[k] <= p) ? k : r;
-  const PairRecord rec = gathered[(int64_t)r * slot_pairs + (p - rb.lo[r])];
+  int lo = 0, hi = n_ranges - 1;               // last range with lo[c] <= p (empty ranges share a bound)
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (rt.lo[mid] <= p) lo = mid; else hi = mid - 1;
+  }
+  const PairRecord rec = gathered[rt.base[lo] + (p - rt.lo[lo])];
   n_hit[p] = rec.n_hit; ratio[p] = rec.ratio; area[p] = rec.area;
   keep[p] = rec.keep; flags[p] = rec.flags;
 }
@@ -69,22 +76,24 @@ int ptgs_pack_records(const int32_t* n_hit, const double* ratio, const double* a
   return PTGS_OK;
 }
 
-int ptgs_unpack_records(const void* gathered, int32_t world, int64_t slot_pairs,
-                        const int64_t* rank_lo_host, int64_t n_pairs, int32_t* n_hit,
-                        double* ratio, double* area, uint8_t* keep, uint8_t* flags,
+int ptgs_unpack_records(const void* gathered, int32_t n_ranges, int64_t table_records,
+                        const int64_t* range_lo_host, const int64_t* range_base_host, int64_t n_pairs,
+                        int32_t* n_hit, double* ratio, double* area, uint8_t* keep, uint8_t* flags,
                         ptgs_stream_t stream) {
-  PTGS_REQUIRE(world >= 1 && world <= kMaxRanks, "world must be in [1,64]");
-  PTGS_REQUIRE(n_pairs >= 0 && slot_pairs >= 0 && rank_lo_host, "arguments");
+  PTGS_REQUIRE(n_ranges >= 1 && n_ranges <= kMaxRanges, "n_ranges must be in [1,128]");
+  PTGS_REQUIRE(n_pairs >= 0 && table_records >= 0 && range_lo_host && range_base_host, "arguments");
   if (n_pairs == 0) return PTGS_OK;
   PTGS_REQUIRE(gathered && n_hit && ratio && area && keep && flags, "arguments");
-  RankBounds rb;
-  for (int r = 0; r <= world; ++r) rb.lo[r] = rank_lo_host[r];
-  PTGS_REQUIRE(rb.lo[0] == 0 && rb.lo[world] == n_pairs, "rank bounds must tile [0, n_pairs)");
-  for (int r = 0; r < world; ++r)
-    PTGS_REQUIRE(rb.lo[r + 1] >= rb.lo[r] && rb.lo[r + 1] - rb.lo[r] <= slot_pairs,
-                 "rank range exceeds the gathered slot");
+  RangeTable rt;
+  for (int c = 0; c <= n_ranges; ++c) rt.lo[c] = range_lo_host[c];
+  for (int c = 0; c < n_ranges; ++c) rt.base[c] = range_base_host[c];
+  PTGS_REQUIRE(rt.lo[0] == 0 && rt.lo[n_ranges] == n_pairs, "ranges must tile [0, n_pairs)");
+  for (int c = 0; c < n_ranges; ++c)
+    PTGS_REQUIRE(rt.lo[c + 1] >= rt.lo[c] && rt.base[c] >= 0 &&
+                     rt.base[c] + (rt.lo[c + 1] - rt.lo[c]) <= table_records,
+                 "range lies outside the gathered table");
   unpack_records_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      (const PairRecord*)gathered, world, slot_pairs, rb, n_pairs, n_hit, ratio, area, keep, flags);
+      (const PairRecord*)gathered, n_ranges, rt, n_pairs, n_hit, ratio, area, keep, flags);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

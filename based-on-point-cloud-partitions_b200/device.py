@@ -994,21 +994,26 @@ def unpack_records_dev(recv: torch.Tensor, plan):
     area = torch.empty(Pa, dtype=torch.float64, device=dev)
     keep = torch.empty(Pa, dtype=torch.uint8, device=dev)
     flags = torch.empty(Pa, dtype=torch.uint8, device=dev)
-    b = np.ascontiguousarray(plan.bounds, dtype=np.int64)
-    check(lib.ptgs_unpack_records(_ptr(recv), plan.world, max(plan.slot, 1), b.ctypes.data_as(C.POINTER(C.c_int64)),
-                                  P, _ptr(n_hit), _ptr(ratio), _ptr(area), _ptr(keep), _ptr(flags), _stream()))
+    lo = np.ascontiguousarray(plan.bounds, dtype=np.int64)
+    base = np.ascontiguousarray(plan.base, dtype=np.int64)
+    i64p = C.POINTER(C.c_int64)
+    check(lib.ptgs_unpack_records(_ptr(recv), len(base), int(recv.shape[0]), lo.ctypes.data_as(i64p),
+                                  base.ctypes.data_as(i64p), P, _ptr(n_hit), _ptr(ratio), _ptr(area), _ptr(keep),
+                                  _ptr(flags), _stream()))
     return n_hit[:P], ratio[:P], area[:P], keep[:P], flags[:P]
 
 
-def range_plan(ds_offsets, cam_offsets, cam_index, rank: int, world: int, cam_off_h=None, block_cost_h=None):
-    """multigpu.RangePlan of a device CSR.  The L-sized host tables are taken from the caller when it
-    has them (partition_device keeps them), otherwise copied from the device once."""
+def range_plan(ds_offsets, cam_offsets, cam_index, rank: int, world: int, cam_off_h=None, block_cost_h=None,
+               chunks: int = 4):
+    """multigpu.RangePlan of a device CSR (world * chunks interleaved ranges).  The L-sized host tables
+    are taken from the caller when it has them (partition_device keeps them), otherwise copied from
+    the device once."""
     from . import multigpu as M
     if cam_off_h is None:
         cam_off_h = cam_offsets.cpu().numpy()
     if block_cost_h is None:
         block_cost_h = (ds_offsets[1:] - ds_offsets[:-1]).cpu().numpy()
-    return M.RangePlan(cam_offsets, cam_index, cam_off_h, block_cost_h, rank, world)
+    return M.RangePlan(cam_offsets, cam_index, cam_off_h, block_cost_h, rank, world, chunks=chunks)
 
 
 def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
@@ -1016,8 +1021,9 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
                        **kw) -> VisibilityResult:
     """A7-A9 with the (block, camera) pairs sharded over the ranks (north star: only the
     visibility pass is partitioned; the per-pair result vectors are all-gathered).
-    shard="ranges": contiguous equal-cost ranges of the pair list (multigpu.RangePlan; pass a
-    `plan` built once per partition result to keep its host arithmetic out of the step), records
+    shard="ranges": contiguous equal-cost ranges of the pair list, a few per rank, interleaved
+    (multigpu.RangePlan; pass a `plan` built once per partition result to keep its host arithmetic
+    out of the step), records
     exchanged as one padded all-gather of the ranks' contiguous slices between a pack and an
     unpack kernel;
     shard="modulo": cameras c % world == rank of every block (multigpu.shard_csr + gather_records).
@@ -1032,7 +1038,7 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
         if timer is not None:
             timer.mark("vis_shard")
         v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, plan.my_off, plan.my_idx, timer=timer, **kw)
-        n = plan.hi - plan.lo
+        n = plan.n_local
         local = (v.n_hit[:n], v.ratio[:n], v.area[:n], v.keep[:n], v.flags[:n])
         n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev, group)
     else:

@@ -123,36 +123,72 @@ def all_range_bounds(cam_off_h, block_cost_h, world: int) -> np.ndarray:
 
 
 class RangePlan:
-    """Static part of the range-sharded visibility pass for one block -> camera CSR: every rank's
-    pair range, this rank's clamped offset table and camera-list view.  Built once per partition
-    result (the tables are L-sized and host resident); the per-step work is then the sweep itself
-    and one exchange."""
+    """Static part of the range-sharded visibility pass for one block -> camera CSR.  The pair list is
+    cut into world * chunks contiguous equal-cost ranges; rank r owns ranges r, r + world, ... (chunks = 1:
+    one contiguous range per rank -- whole blocks plus two partial camera lists, what the entry points
+    that move block DATA per rank use; chunks > 1 interleaves the ranks over the scene, which evens
+    out what the cost model cannot know in advance: which pairs stay undecided and need sweep 2 +
+    the exact hull).  Holds every range's bounds, this rank's offset table / camera list and the
+    position of every range inside the gathered slots.  Built once per partition result (L-sized
+    host arithmetic); the per-step work is then the sweep itself and one exchange."""
 
     def __init__(self, cam_off: torch.Tensor, cam_idx: torch.Tensor, cam_off_h, block_cost_h, rank: int,
-                 world: int):
-        self.rank, self.world = int(rank), int(world)
-        self.bounds = all_range_bounds(cam_off_h, block_cost_h, world)
+                 world: int, chunks: int = 1):
+        self.rank, self.world, self.chunks = int(rank), int(world), max(1, int(chunks))
+        nr = self.world * self.chunks
+        self.bounds = all_range_bounds(cam_off_h, block_cost_h, nr)           # range c = [bounds[c], bounds[c+1])
         self.P = int(self.bounds[-1])
-        self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
-        self.slot = int(np.diff(self.bounds).max()) if world > 0 else self.P
+        length = np.diff(self.bounds)
+        owner = np.arange(nr) % self.world
+        per_rank = np.array([int(length[owner == r].sum()) for r in range(self.world)], dtype=np.int64)
+        self.slot = int(per_rank.max()) if self.world > 0 else self.P
+        # record position of range c inside the gathered (world * slot) table
+        self.base = np.zeros(nr, dtype=np.int64)
+        fill = np.zeros(self.world, dtype=np.int64)
+        for c in range(nr):
+            r = int(owner[c])
+            self.base[c] = r * max(self.slot, 1) + fill[r]
+            fill[r] += length[c]
+        self.mine = [c for c in range(nr) if owner[c] == self.rank]
+        self.n_local = int(per_rank[self.rank])
+        self.lo, self.hi = int(self.bounds[self.mine[0]]), int(self.bounds[self.mine[-1] + 1])   # chunks = 1: the range
         # a host-only plan (cam_off None) carries the bounds and the block span, no device tables
-        self.my_off = (cam_off.clamp(self.lo, self.hi) - self.lo).to(torch.int64).contiguous() \
-            if cam_off is not None else None
-        self.my_idx = cam_idx[self.lo:self.hi] if cam_idx is not None else None
+        if cam_off is not None:
+            off = None
+            for c in self.mine:
+                lo, hi = int(self.bounds[c]), int(self.bounds[c + 1])
+                t = cam_off.clamp(lo, hi) - lo
+                off = t if off is None else off + t
+            self.my_off = off.to(torch.int64).contiguous()
+            parts = [cam_idx[int(self.bounds[c]):int(self.bounds[c + 1])] for c in self.mine]
+            self.my_idx = parts[0] if len(parts) == 1 else torch.cat(parts)
+        else:
+            self.my_off = self.my_idx = None
         co = np.asarray(cam_off_h, dtype=np.int64)
-        if self.hi > self.lo:     # blocks the range touches: [bl0, bl1)
+        self._co = co
+        if self.hi > self.lo:     # blocks the rank's pairs lie in: [bl0, bl1) (chunks = 1: exactly the touched ones)
             self.bl0 = int(np.searchsorted(co, self.lo, side="right")) - 1
             self.bl1 = int(np.searchsorted(co, self.hi, side="left"))
         else:
             self.bl0 = self.bl1 = 0
 
+    def local_counts(self) -> np.ndarray:
+        """Per block: how many of its pairs this rank owns."""
+        cnt = np.zeros(len(self._co) - 1, dtype=np.int64)
+        for c in self.mine:
+            lo, hi = int(self.bounds[c]), int(self.bounds[c + 1])
+            cl = np.clip(self._co, lo, hi)
+            cnt += cl[1:] - cl[:-1]
+        return cnt
+
 
 def exchange_ranges(local, plan: "RangePlan", pack, unpack, group=None):
     """All-gather of the per-pair result vectors of a range-sharded pass.  `local` = this rank's
-    (n_hit, ratio, area, keep, flags) over its range (in range order); pack(local, slot) -> a
-    contiguous (slot, k) send tensor whose first hi - lo rows are the rank's records;
+    (n_hit, ratio, area, keep, flags) over its ranges (in pair order); pack(local, slot) -> a
+    contiguous (slot, k) send tensor whose first n_local rows are the rank's records;
     unpack(recv, plan) -> the full-length vectors from the (world * slot, k) gathered tensor
-    (slot r holds rank r's range).  One collective, no zero fill, no reduction."""
+    (slot r holds rank r's ranges back to back; plan.base[c] = record position of range c).
+    One collective, no zero fill, no reduction."""
     import torch.distributed as dist
     slot = max(plan.slot, 1)
     send = pack(local, slot)
@@ -170,8 +206,8 @@ def pack_slot_torch(local, slot: int) -> torch.Tensor:
 
 
 def unpack_slot_torch(recv: torch.Tensor, plan: "RangePlan"):
-    slot = max(plan.slot, 1)
-    parts = [recv[r * slot: r * slot + int(plan.bounds[r + 1] - plan.bounds[r])] for r in range(plan.world)]
+    parts = [recv[int(plan.base[c]): int(plan.base[c]) + int(plan.bounds[c + 1] - plan.bounds[c])]
+             for c in range(len(plan.base))]
     return unpack_records(torch.cat(parts) if parts else recv[:0])
 
 

@@ -278,8 +278,9 @@ def run_ours(args):
             "leaves": L, "pairs": pairs, "tests_per_step": tests,
             "downsampled_points": int(M_b.sum()), "kept_cameras": n_kept,
             "kept_fraction": n_kept / max(pairs, 1),
-            "parallelism": ("(block, camera) pairs sharded in %d contiguous equal-cost ranges, per-pair records "
-                            "exchanged with one padded all-gather" % world) if world > 1 else "single GPU",
+            "parallelism": ("(block, camera) pairs sharded in %d x %d interleaved contiguous equal-cost ranges, "
+                            "per-pair records exchanged with one padded all-gather" % (world, plan.chunks))
+            if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MB write)",
         },
         "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall,
@@ -288,10 +289,10 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (sweep 1: sweep_kernel<1>), this rank's launch ---------
     k_ms = stage.get("vis_sweep1_count", float("nan"))
     if world > 1:
-        my_pts = float(ds_off_h[plan.bl1] - ds_off_h[plan.bl0])
-        my_pairs = float(plan.hi - plan.lo)
-        my_tests = float(sum(int(M_b[b]) * (min(int(cam_off_h[b + 1]), plan.hi) - max(int(cam_off_h[b]), plan.lo))
-                             for b in range(plan.bl0, plan.bl1)))
+        mine = plan.local_counts()                       # this rank's pairs per block
+        my_pts = float(M_b[mine > 0].sum())
+        my_pairs = float(mine.sum())
+        my_tests = float((mine * M_b).sum())
     else:
         my_pts, my_pairs, my_tests = float(M_b.sum()), float(pairs), float(tests)
     alg_bytes = my_pts * 12 + my_pairs * 80 + my_pairs * 16

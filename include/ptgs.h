@@ -478,27 +478,30 @@ int ptgs_points3d_decode(const uint8_t* file_dev, const int64_t* offsets_dev,
 /* ------------------------------------------------------------------ *
  * Multi-GPU exchange of the per-pair records (the reference is
  * single process -- the loop that is split across GPUs is
- * scene/ptgs/shen_partation_densify.py:932-944).  With range sharding rank r
- * owns the contiguous pair range [rank_lo[r], rank_lo[r+1]).
+ * scene/ptgs/shen_partation_densify.py:932-944).  With range sharding a rank
+ * owns one or a few contiguous ranges of the (block, camera) pair list.
  * ptgs_pack_records: the rank's result vectors -> n_pairs records of
  *   PTGS_PAIR_RECORD_BYTES bytes {f64 ratio, f64 area, i32 n_hit, u8 keep,
  *   u8 flags, u16 0} (8-byte aligned buffer).  The caller all-gathers the
  *   (padded to `slot_pairs` records) buffers of all ranks, e.g. NCCL
  *   all_gather on the same stream.
- * ptgs_unpack_records: gathered = world slots of slot_pairs records in rank
- *   order; rank_lo is a HOST array of world + 1 bounds (rank_lo[0] = 0,
- *   rank_lo[world] = n_pairs); writes the full per-pair vectors.
+ * ptgs_unpack_records: `gathered` = the all-gathered table (table_records
+ *   records); the pair list is tiled by n_ranges (<= 128) contiguous ranges,
+ *   range c = pairs [range_lo[c], range_lo[c+1]) stored from record
+ *   range_base[c] on (HOST arrays of n_ranges + 1 / n_ranges entries;
+ *   range_lo[0] = 0, range_lo[n_ranges] = n_pairs); writes the full per-pair
+ *   vectors.
  * ------------------------------------------------------------------ */
 #define PTGS_PAIR_RECORD_BYTES 24
 int ptgs_pack_records(const int32_t* n_hit, const double* ratio,
                       const double* area, const uint8_t* keep,
                       const uint8_t* flags, int64_t n_pairs, void* records,
                       ptgs_stream_t stream);
-int ptgs_unpack_records(const void* gathered, int32_t world,
-                        int64_t slot_pairs, const int64_t* rank_lo_host,
-                        int64_t n_pairs, int32_t* n_hit, double* ratio,
-                        double* area, uint8_t* keep, uint8_t* flags,
-                        ptgs_stream_t stream);
+int ptgs_unpack_records(const void* gathered, int32_t n_ranges,
+                        int64_t table_records, const int64_t* range_lo_host,
+                        const int64_t* range_base_host, int64_t n_pairs,
+                        int32_t* n_hit, double* ratio, double* area,
+                        uint8_t* keep, uint8_t* flags, ptgs_stream_t stream);
 
 /* ------------------------------------------------------------------ *
  * Coverage sweep (config 5; the camera x all-points pass of the Vast path,

@@ -206,8 +206,8 @@ def test_host_entry_offsets_cover_camera_less_blocks():
         assert np.array_equal(a, b)
 
 
-@pytest.mark.parametrize("world", [2, 3, 8])
-def test_slot_exchange_kernels_equal_single_gpu(world):
+@pytest.mark.parametrize("world,chunks", [(2, 1), (3, 1), (8, 1), (2, 4), (3, 3), (8, 4)])
+def test_slot_exchange_kernels_equal_single_gpu(world, chunks):
     """The product exchange of the range-sharded pass -- ptgs_pack_records per rank, the ranks'
     padded slots laid out as the all-gather delivers them, ptgs_unpack_records -- reproduces the
     unsharded result vectors (ranks run one after the other on this GPU; the collective itself is
@@ -217,9 +217,10 @@ def test_slot_exchange_kernels_equal_single_gpu(world):
     full = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, res.cam_offsets, res.cam_index)
     slots, plan = [], None
     for r in range(world):
-        plan = D.range_plan(res.ds_offsets, res.cam_offsets, res.cam_index, r, world)
+        plan = D.range_plan(res.ds_offsets, res.cam_offsets, res.cam_index, r, world, chunks=chunks)
+        assert int(plan.my_off[-1]) == plan.my_idx.shape[0] == plan.n_local == int(plan.local_counts().sum())
         v = D.visibility(res.ds_x, res.ds_y, res.ds_z, res.ds_offsets, cams_d, plan.my_off, plan.my_idx)
-        n = plan.hi - plan.lo
+        n = plan.n_local
         slots.append(D.pack_records_dev((v.n_hit[:n], v.ratio[:n], v.area[:n], v.keep[:n], v.flags[:n]), plan.slot))
     assert plan.bounds[0] == 0 and plan.bounds[-1] == res.cam_index.shape[0]
     n_hit, ratio, area, keep, flags = D.unpack_records_dev(torch.cat(slots), plan)

@@ -91,6 +91,18 @@ def _worker(rank, world, port, seed, out_dir):
         if plan.hi > plan.lo:   # the block span covers exactly the blocks with a pair in the range
             blk = torch.repeat_interleave(torch.arange(off.shape[0] - 1), off[1:] - off[:-1])[plan.lo:plan.hi]
             assert int(blk.min()) == plan.bl0 and int(blk.max()) == plan.bl1 - 1
+        # several interleaved ranges per rank (the default of the visibility step: evens out the pairs that
+        # stay undecided): rank's pair list = its ranges in pair order, same exchange
+        for chunks in (2, 5):
+            cp = M.RangePlan(off, idx, off.numpy(), cost.numpy(), rank, world, chunks=chunks)
+            assert int(cp.my_off[-1]) == cp.my_idx.shape[0] == cp.n_local
+            pos = torch.cat([torch.arange(int(cp.bounds[c]), int(cp.bounds[c + 1])) for c in cp.mine])
+            assert torch.equal(idx[pos], cp.my_idx)
+            cnt = torch.from_numpy(cp.local_counts())
+            assert torch.equal(cp.my_off[1:] - cp.my_off[:-1], cnt)
+            got5 = M.exchange_ranges(_fake_records(cp.my_off, cp.my_idx), cp, M.pack_slot_torch, M.unpack_slot_torch)
+            for g, w in zip(got5, want):
+                assert torch.equal(g, w), "rank %d: gathered table differs (%d chunks)" % (rank, chunks)
         # coverage sweep exchange (c5): contiguous camera ranges, counts gathered, seen flags merged
         C = 57
         first, cnt = M.camera_range(C, rank, world)
