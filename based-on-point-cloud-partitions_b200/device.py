@@ -893,12 +893,21 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
             tm.mark("A6_voxel")
             loc = np.clip(cam_off_h[b0:b1 + 1], plan.lo, plan.hi) - plan.lo if b1 > b0 else np.zeros(2, np.int64)
             loc_off = torch.from_numpy(np.ascontiguousarray(loc, dtype=np.int64)).to(dev)
-            v = visibility(dx, dy, dz, ds_off, cams_d, loc_off, cam_idx[plan.lo:plan.hi], exact_ratio=exact_ratio)
-            tm.mark("A7_A8_visibility")
             nl = plan.hi - plan.lo
+            v = visibility(dx, dy, dz, ds_off, cams_d, loc_off, cam_idx[plan.lo:plan.hi], exact_ratio=exact_ratio,
+                           defer_check=True)
+            tm.mark("A7_A8_visibility")
             local = (v.n_hit[:nl], v.ratio[:nl], v.area[:nl], v.keep[:nl], v.flags[:nl])
             n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev,
                                                                 group)
+            bad = int((flags & 12).max().item()) if flags.numel() else 0     # same verdict on every rank
+            if bad & 8:
+                raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
+            if bad & 4:       # candidate capacity overflow somewhere: every rank re-runs with the check inside
+                v = visibility(dx, dy, dz, ds_off, cams_d, loc_off, cam_idx[plan.lo:plan.hi], exact_ratio=exact_ratio)
+                local = (v.n_hit[:nl], v.ratio[:nl], v.area[:nl], v.keep[:nl], v.flags[:nl])
+                n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev,
+                                                                    unpack_records_dev, group)
             vis = VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
             vis.n_exact = v.n_exact
             tm.mark("exchange")
@@ -1037,10 +1046,26 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
             plan = range_plan(ds_offsets, cam_offsets, cam_index, rank, world)
         if timer is not None:
             timer.mark("vis_shard")
-        v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, plan.my_off, plan.my_idx, timer=timer, **kw)
+        # the candidate-capacity check of the pass is deferred past the exchange: pack / all-gather /
+        # unpack are queued behind the hull kernel instead of waiting for a host round trip (the GPU
+        # would idle for the host-side launch latency of the collective).  An overflow (rare) re-runs
+        # the pass with the check inside and exchanges again -- on every rank, so that the collectives
+        # stay matched (the overflow flag is part of the exchanged status below).
         n = plan.n_local
+        v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, plan.my_off, plan.my_idx, timer=timer,
+                       defer_check=True, **kw)
         local = (v.n_hit[:n], v.ratio[:n], v.area[:n], v.keep[:n], v.flags[:n])
         n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev, unpack_records_dev, group)
+        # flags bit2 (capacity overflow) / bit3 (vertex budget) travel with the records, so every rank
+        # reaches the same verdict from the exchanged table (this is the step's one host round trip)
+        bad = int((flags & 12).max().item()) if flags.numel() else 0
+        if bad & 8:
+            raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
+        if bad & 4:
+            v = visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, plan.my_off, plan.my_idx, **kw)
+            local = (v.n_hit[:n], v.ratio[:n], v.area[:n], v.keep[:n], v.flags[:n])
+            n_hit, ratio, area, keep, flags = M.exchange_ranges(local, plan, pack_records_dev,
+                                                                unpack_records_dev, group)
     else:
         my_off, my_idx, my_pos = M.shard_csr(cam_offsets, cam_index, rank, world)
         if timer is not None:
