@@ -205,6 +205,12 @@ def run_ours(args):
     recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
     centers = D.camera_centers(w.R, w.T)
 
+    # clocks / throttle reasons are sampled (20 ms period) from here -- the warm-up partition and
+    # visibility passes -- to the end of the timed region: the timed steps alone last a few tens of
+    # milliseconds, less than nvidia-smi needs to start
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     # ---- full partition once (also the warm-up of every kernel) -------------
     res = D.partition_device(xyz, recs, centers, w.threshold, man_trans=w.man_trans)
     torch.cuda.synchronize()
@@ -228,11 +234,6 @@ def run_ours(args):
         k_off, k_idx = D.select_cameras(v.keep, res.cam_offsets, res.cam_index, sync=False)
         return v, k_off, k_idx
 
-    # clocks / throttle reasons are sampled (20 ms period) from the warm-up passes to the end of the
-    # timed region: the timed steps alone last a few tens of milliseconds
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     for _ in range(max(args.warmup, 3)):
         flush.fill_(1)
         vis_step()
@@ -268,6 +269,16 @@ def run_ours(args):
             stage[k] = stage.get(k, 0.0) + t / args.steps
     n_kept = int(k_off[-1].item())
     flags_h = v.flags.cpu().numpy()
+    stage_ranks = None
+    if world > 1:
+        # per-rank stage times (which rank the others wait for at the exchange)
+        import torch.distributed as dist
+        keys = sorted(stage)
+        mine_t = torch.tensor([stage[k] for k in keys], dtype=torch.float64, device=dev)
+        allt = [torch.empty_like(mine_t) for _ in range(world)]
+        dist.all_gather(allt, mine_t)
+        tab = torch.stack(allt).cpu().numpy()
+        stage_ranks = {k: [round(float(x), 4) for x in tab[:, i]] for i, k in enumerate(keys)}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -286,6 +297,8 @@ def run_ours(args):
         "gpu_launches": launches, "clocks": clocks, "wall_s_timed_region": wall,
         "stage_ms": {k: round(t, 4) for k, t in stage.items()},
     }
+    if stage_ranks is not None:
+        out["stage_ms_per_rank"] = stage_ranks
     # ---- roofline of the dominant kernel (sweep 1: sweep_kernel<1>), this rank's launch ---------
     k_ms = stage.get("vis_sweep1_count", float("nan"))
     if world > 1:
