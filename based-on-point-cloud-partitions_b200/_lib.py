@@ -67,8 +67,9 @@ SIGNATURES = {
     "ptgs_visibility_plan": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i64, _vp, _vp]),
     "ptgs_visibility_candidates": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                              _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ptgs_visibility_hull_workspace_bytes": (_sz, [_i64]),
     "ptgs_visibility_hull": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _f64, _f64, _vp,
-                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+                                       _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ptgs_select_cameras": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
     "ptgs_points3d_index": (_i64, [_vp, _i64, _vp, _i64]),
     "ptgs_points3d_decode": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -1188,6 +1188,8 @@ constexpr int kHullMaxParts = 4;    // NT / 128 point partitions of the directio
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
 constexpr int kHullFilterMin = 128; // candidates above which the directional pre-filter runs
+constexpr int kHullTwoLevel = 192;  // sorted points above which the monotone chain runs in two levels
+constexpr int kHullDynSmem = 2 * kHullBuf * 8;   // lower[] + upper[] (dynamic: the static limit is 48 KB)
 
 __device__ __forceinline__ bool lex_less(float2 a, float2 b) {
   return a.x < b.x || (a.x == b.x && a.y < b.y);
@@ -1198,6 +1200,40 @@ __device__ __forceinline__ double cross3(float2 a, float2 b, float2 c) {
   const double abx = __dsub_rn((double)b.x, (double)a.x), aby = __dsub_rn((double)b.y, (double)a.y);
   const double acx = __dsub_rn((double)c.x, (double)a.x), acy = __dsub_rn((double)c.y, (double)a.y);
   return __dsub_rn(__dmul_rn(abx, acy), __dmul_rn(aby, acx));
+}
+
+// One step of the monotone chain: pop while the turn (t2, t1, p) is not strictly convex, then push p.
+// The two topmost stack entries live in registers.  The sign of the float64 cross product is first
+// looked for in float32: |d32 - exact| <= 4 * 2^-24 * (|l| + |r|), the float64 value differs from the
+// exact one by < 2^-50 * (|l| + |r|), so beyond 1e-6 * (|l| + |r|) (and 1e-30: no underflow) both have
+// the sign of d32; the
+// float64 evaluation (the reference's arithmetic) decides the rest, ties included.
+struct ChainTop {
+  float2 t1 = {0.f, 0.f}, t2 = {0.f, 0.f};
+  int ns = 0;
+  bool overflow = false;
+};
+__device__ __forceinline__ bool chain_pops(float2 t2, float2 t1, float2 p, bool lo_chain) {
+  const float abx = t1.x - t2.x, aby = t1.y - t2.y, acx = p.x - t2.x, acy = p.y - t2.y;
+  const float l = abx * acy, r = aby * acx, d = l - r;
+  if (fabsf(d) > fmaxf(1e-6f * (fabsf(l) + fabsf(r)), 1e-30f)) return lo_chain ? d < 0.f : d > 0.f;
+  const double c = cross3(t2, t1, p);
+  return lo_chain ? (c <= 0.0) : (c >= 0.0);
+}
+__device__ __forceinline__ void chain_push(float2* st, ChainTop& c, float2 p, bool lo_chain, int cap) {
+  while (c.ns >= 2 && chain_pops(c.t2, c.t1, p, lo_chain)) {
+    --c.ns;
+    c.t1 = c.t2;
+    if (c.ns >= 2) c.t2 = st[c.ns - 2];
+  }
+  if (c.ns == 1 && c.t1.x == p.x && c.t1.y == p.y) --c.ns;
+  if (c.ns < cap) {
+    st[c.ns++] = p;
+    c.t2 = c.t1;
+    c.t1 = p;
+  } else {
+    c.overflow = true;
+  }
 }
 
 // ---- directional pre-filter of a pair's candidates (in place) ---------------------
@@ -1333,6 +1369,208 @@ __device__ int filter_round(float2* cu, int n, float margin, FilterSmem& F) {
   return F.out;
 }
 
+// ---- multi-CTA pre-filter of the largest candidate lists ---------------------------------------
+// hull_kernel gives a pair ONE CTA; a pair with tens of thousands of candidates then sets the
+// duration of the whole launch (and, sharded, of the step on every rank).  Pairs with more than
+// kPfMinK candidates therefore get one directional filter round up front, spread over as many CTAs
+// as they have 4096-candidate chunks: (1) per chunk the extreme candidates along 64 directions,
+// merged per pair with atomics; (2) per pair the polygon through those extremes; (3) per chunk the
+// candidates that are not strictly inside it (same float32 edge evaluation and margin as
+// filter_round) are appended to a second buffer.  hull_kernel then starts from the survivors
+// (a set, not a sequence: the hull sorts its input, so the append order does not matter).
+constexpr int kPfChunk = 4096;
+constexpr int kPfMinK = 6144;
+constexpr int kPfPolyFloats = 4 + 3 * kFiltDirs;     // [0] = edges, then (a, b, c) per edge
+
+// single CTA: per undecided pair i (position in the sub-list) whether it is pre-filtered
+// (count2[i] = 0, else -1), its slice of the second buffer (off2[i]) and the running number of
+// chunks before it (chunk_prefix[i]; [n_pairs] = total).
+__global__ void __launch_bounds__(1024) pf_plan_kernel(
+    const int64_t* __restrict__ cand_offsets, const int32_t* __restrict__ cand_count,
+    const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev, int64_t n_pairs,
+    int64_t uv2_cap, int64_t* __restrict__ chunk_prefix, int64_t* __restrict__ off2,
+    int32_t* __restrict__ count2) {
+  __shared__ long long sm[33];
+  int64_t n_sub = n_pairs;
+  if (n_sub_dev && *n_sub_dev < n_sub) n_sub = *n_sub_dev;
+  long long carry_sp = 0, carry_ch = 0;
+  for (int64_t s0 = 0; s0 < n_pairs; s0 += 1024) {
+    const int64_t i = s0 + threadIdx.x;
+    long long K = 0;
+    if (i < n_sub) {
+      const int64_t pair = pair_map ? (int64_t)pair_map[i] : i;
+      const long long k = cand_count[pair];
+      const long long cap = cand_offsets[pair + 1] - cand_offsets[pair];
+      if (k > kPfMinK && k <= cap) K = k;
+    }
+    long long tot_sp;
+    const long long sp = carry_sp + block_exclusive_sum<long long, 1024>(K, sm, &tot_sp);
+    carry_sp += tot_sp;
+    const bool big = K > 0 && (sp + K) <= uv2_cap;       // the buffer is granted in list order
+    const long long ch = big ? (K + kPfChunk - 1) / kPfChunk : 0;
+    long long tot_ch;
+    const long long cp = carry_ch + block_exclusive_sum<long long, 1024>(ch, sm, &tot_ch);
+    carry_ch += tot_ch;
+    if (i < n_pairs) {
+      chunk_prefix[i] = cp;
+      off2[i] = sp;
+      count2[i] = big ? 0 : -1;
+    }
+  }
+  if (threadIdx.x == 0) chunk_prefix[n_pairs] = carry_ch;
+}
+
+struct PfItem { int64_t sub; int64_t pair; int chunk; int n; const float2* pts; };
+
+__device__ __forceinline__ bool pf_item(int64_t item, const int64_t* __restrict__ chunk_prefix, int64_t n_pairs,
+                                        const int32_t* __restrict__ pair_map,
+                                        const int64_t* __restrict__ cand_offsets,
+                                        const int32_t* __restrict__ cand_count, const float2* cand_uv,
+                                        PfItem& it) {
+  int64_t lo = 0, hi = n_pairs - 1;            // last sub index with chunk_prefix <= item that owns chunks
+  while (lo < hi) {
+    const int64_t mid = (lo + hi + 1) >> 1;
+    if (chunk_prefix[mid] <= item) lo = mid; else hi = mid - 1;
+  }
+  it.sub = lo;
+  it.pair = pair_map ? (int64_t)pair_map[lo] : lo;
+  it.chunk = (int)(item - chunk_prefix[lo]);
+  const int K = cand_count[it.pair];
+  const int start = it.chunk * kPfChunk;
+  if (start >= K) return false;                // cannot happen for a planned item
+  it.n = (K - start) < kPfChunk ? (K - start) : kPfChunk;
+  it.pts = cand_uv + cand_offsets[it.pair] + start;
+  return true;
+}
+
+// (1) chunk extremes along the 64 directions -> ext[sub][64] = max (ordered key << 32 | index in the pair)
+__global__ void __launch_bounds__(256) pf_extremes_kernel(
+    const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
+    const int32_t* __restrict__ cand_count, const int32_t* __restrict__ pair_map, int64_t n_pairs,
+    const int64_t* __restrict__ chunk_prefix, unsigned long long* __restrict__ ext) {
+  __shared__ float2 s_pts[kPfChunk];
+  __shared__ float s_best[4][kFiltDirs];
+  __shared__ int s_idx[4][kFiltDirs];
+  const int64_t n_items = chunk_prefix[n_pairs];
+  const int d = threadIdx.x & (kFiltDirs - 1), part = threadIdx.x >> 6;
+  float sn, cs;
+  sincospif((float)d * (2.0f / kFiltDirs), &sn, &cs);
+  for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    PfItem it;
+    const bool ok = pf_item(item, chunk_prefix, n_pairs, pair_map, cand_offsets, cand_count, cand_uv, it);
+    if (ok)
+      for (int j = threadIdx.x; j < it.n; j += 256) s_pts[j] = it.pts[j];   // coalesced; the scan below
+    __syncthreads();                                                         // reads broadcast values
+    float best = -__int_as_float(0x7f800000);
+    int bi = 0;
+    if (ok) {
+#pragma unroll 4
+      for (int j = part; j < it.n; j += 4) {
+        const float2 q = s_pts[j];
+        const float dot = fmaf(q.x, cs, q.y * sn);
+        if (dot > best) { best = dot; bi = j; }
+      }
+    }
+    s_best[part][d] = best;
+    s_idx[part][d] = bi;
+    __syncthreads();
+    if (ok && part == 0) {
+#pragma unroll
+      for (int p = 1; p < 4; ++p)
+        if (s_best[p][d] > best) { best = s_best[p][d]; bi = s_idx[p][d]; }
+      if (best > -__int_as_float(0x7f800000)) {
+        const unsigned long long val =
+            ((unsigned long long)order_key(best) << 32) | (unsigned)(it.chunk * kPfChunk + bi);
+        atomicMax(ext + it.sub * kFiltDirs + d, val);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// (2) one thread per pre-filtered pair: polygon through its 64 extremes (distinct consecutive
+// vertices, edges as float half planes a*u + b*v + c -- the construction of filter_round)
+__global__ void __launch_bounds__(128) pf_polygon_kernel(
+    const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
+    const int32_t* __restrict__ pair_map, int64_t n_pairs, const int32_t* __restrict__ count2,
+    const unsigned long long* __restrict__ ext, float* __restrict__ poly) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pairs || count2[i] < 0) return;
+  const int64_t pair = pair_map ? (int64_t)pair_map[i] : i;
+  const float2* cu = cand_uv + cand_offsets[pair];
+  float* out = poly + i * kPfPolyFloats;
+  float2 v[kFiltDirs];
+  int m = 0;
+  for (int k = 0; k < kFiltDirs; ++k) {
+    const unsigned long long e = ext[i * kFiltDirs + k];
+    if (!e) continue;
+    const float2 q = cu[(uint32_t)(e & 0xffffffffull)];
+    if (m && v[m - 1].x == q.x && v[m - 1].y == q.y) continue;
+    v[m++] = q;
+  }
+  while (m > 1 && v[m - 1].x == v[0].x && v[m - 1].y == v[0].y) --m;
+  if (m < 3) { out[0] = 0.0f; return; }
+  for (int k = 0; k < m; ++k) {
+    const int k2 = (k + 1 == m) ? 0 : k + 1;
+    const double a = -((double)v[k2].y - (double)v[k].y), b = (double)v[k2].x - (double)v[k].x;
+    out[4 + 3 * k] = (float)a;
+    out[5 + 3 * k] = (float)b;
+    out[6 + 3 * k] = (float)(-(a * (double)v[k].x + b * (double)v[k].y));
+  }
+  out[0] = (float)m;
+}
+
+// (3) per chunk: candidates that are not strictly inside the pair's polygon -> uv2[off2 + ...]
+__global__ void __launch_bounds__(256) pf_filter_kernel(
+    const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
+    const int32_t* __restrict__ cand_count, const int32_t* __restrict__ pair_map, int64_t n_pairs,
+    const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras,
+    const int64_t* __restrict__ chunk_prefix, const float* __restrict__ poly,
+    const int64_t* __restrict__ off2, int32_t* __restrict__ count2, float2* __restrict__ uv2) {
+  __shared__ float s_e[3 * kFiltDirs];
+  __shared__ int s_m;
+  const int64_t n_items = chunk_prefix[n_pairs];
+  const int lane = threadIdx.x & 31;
+  for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    PfItem it;
+    const bool ok = pf_item(item, chunk_prefix, n_pairs, pair_map, cand_offsets, cand_count, cand_uv, it);
+    __syncthreads();                           // previous item's edges are no longer read
+    if (ok) {
+      const float* pl = poly + it.sub * kPfPolyFloats;
+      if (threadIdx.x == 0) s_m = (int)pl[0];
+      for (int k = threadIdx.x; k < 3 * kFiltDirs; k += 256) s_e[k] = pl[4 + k];
+    }
+    __syncthreads();
+    if (!ok) continue;
+    const int m = s_m;
+    const float* rec = cameras + (int64_t)pair_cam[it.pair] * kCamFloats;
+    const float Dm = fmaxf(rec[16], rec[17]);
+    const float margin = 4e-6f * Dm * Dm;
+    for (int j0 = 0; j0 < it.n; j0 += 256) {
+      const int j = j0 + threadIdx.x;
+      bool keep = false;
+      float2 q = make_float2(0.f, 0.f);
+      if (j < it.n) {
+        q = it.pts[j];
+        bool inside = m >= 3;
+        for (int e = 0; e < m && inside; ++e) {
+          const float f = __fadd_rn(__fadd_rn(__fmul_rn(s_e[3 * e], q.x), __fmul_rn(s_e[3 * e + 1], q.y)),
+                                    s_e[3 * e + 2]);
+          inside = f > margin;
+        }
+        keep = !inside;
+      }
+      const unsigned mk = __ballot_sync(kFullMask, keep);
+      if (mk) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(count2 + it.sub, __popc(mk));
+        base = __shfl_sync(kFullMask, base, 0);
+        if (keep) uv2[off2[it.sub] + base + __popc(mk & lanemask_lt())] = q;
+      }
+    }
+  }
+}
+
 template <int NT>
 __global__ void __launch_bounds__(NT) hull_kernel(
     float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
@@ -1341,11 +1579,16 @@ __global__ void __launch_bounds__(NT) hull_kernel(
     double thr, double near_eps, double* __restrict__ area_out, double* __restrict__ ratio_out,
     uint8_t* __restrict__ keep_out, uint8_t* __restrict__ flags_out,
     const int32_t* __restrict__ pair_map, const int64_t* __restrict__ n_sub_dev,
-    int32_t* __restrict__ status /* [0] capacity overflows, [1] vertex-budget overflows; may be null */) {
+    int32_t* __restrict__ status /* [0] capacity overflows, [1] vertex-budget overflows; may be null */,
+    const int32_t* __restrict__ pf_count2, const int64_t* __restrict__ pf_off2,
+    float2* __restrict__ pf_uv2 /* pre-filtered lists of the largest pairs; may be null */) {
   constexpr int kHullThreads = NT;
   __shared__ float2 buf[kHullBuf];
-  __shared__ float2 lower[kHullChain];
-  __shared__ float2 upper[kHullChain];
+  extern __shared__ __align__(16) unsigned char hull_dyn[];   // kHullDynSmem bytes
+  float2* lower = reinterpret_cast<float2*>(hull_dyn);       // final chains hold <= kHullChain vertices;
+  float2* upper = lower + kHullBuf;                          // the segment chains of the two-level pass
+                                                             // use the whole array
+  __shared__ int s_seg[2][32];
   __shared__ int s_h, s_nl, s_nu, s_flags, s_col;
   if (blockIdx.x >= n_pairs) return;
   if (n_sub_dev && (int64_t)blockIdx.x >= *n_sub_dev) return;
@@ -1368,6 +1611,10 @@ __global__ void __launch_bounds__(NT) hull_kernel(
   __syncthreads();
   const float inf = __int_as_float(0x7f800000);
   float2* cu = cand_uv + off;
+  if (pf_count2 && pf_count2[blockIdx.x] >= 0) {     // the multi-CTA pre-filter already cut this list
+    cu = pf_uv2 + pf_off2[blockIdx.x];
+    K = pf_count2[blockIdx.x];
+  }
   if (K > kHullFilterMin) {
     __shared__ FilterSmem F;
     const float* rec = cameras + (int64_t)pair_cam[pair] * kCamFloats;
@@ -1418,38 +1665,42 @@ __global__ void __launch_bounds__(NT) hull_kernel(
         __syncthreads();
       }
     }
-    // Andrew's monotone chain; pop on cross <= 0 (densify:522).  The lower and
-    // the upper chain are independent: warp 0 / warp 1, one lane each, with the
-    // two topmost stack entries kept in registers.
-    if (tid == 0 || tid == 32) {
-      const bool lo_chain = tid == 0;
+    // Andrew's monotone chain; pop on cross <= 0 (densify:522).  The lower and the upper chain are
+    // independent (warp 0 / warp 1).  A chain is sequential, and with one lane walking up to 2048
+    // sorted points it was what every other warp of the CTA waited for, so above kHullTwoLevel points
+    // it runs in two levels: the 32 lanes of the warp each build the chain of one of 32 consecutive
+    // segments of the sorted array (a hull vertex of the whole set is a hull vertex of its segment),
+    // then lane 0 runs the same chain over the concatenated segment chains, in place.  The chain of
+    // a point set does not depend on which non-vertices were removed first, so the result is the
+    // one-level chain's.
+    if (tid < 64) {
+      const bool lo_chain = tid < 32;
+      const int ln = tid & 31;
       float2* st = lo_chain ? lower : upper;
-      int ns = 0;
-      bool overflow = false;
-      float2 t1 = make_float2(0.f, 0.f), t2 = t1;   // st[ns-1], st[ns-2]
-      for (int i = 0; i < n; ++i) {
-        const float2 p = buf[i];
-        while (ns >= 2) {
-          const double c = cross3(t2, t1, p);
-          if (lo_chain ? (c <= 0.0) : (c >= 0.0)) {
-            --ns;
-            t1 = t2;
-            if (ns >= 2) t2 = st[ns - 2];
-          } else {
-            break;
-          }
-        }
-        if (ns == 1 && t1.x == p.x && t1.y == p.y) --ns;
-        if (ns < kHullChain) {
-          st[ns++] = p;
-          t2 = t1;
-          t1 = p;
-        } else {
-          overflow = true;
-        }
+      int* seg_n = s_seg[lo_chain ? 0 : 1];
+      const bool two = n > kHullTwoLevel;
+      const int seg = two ? (n + 31) >> 5 : n;
+      if (two) {
+        const int i0 = ln * seg, i1 = (i0 + seg < n) ? i0 + seg : n;
+        ChainTop c;
+        for (int i = i0; i < i1; ++i) chain_push(st + i0, c, buf[i], lo_chain, seg);
+        seg_n[ln] = c.ns;
+        __syncwarp();
       }
-      if (overflow) atomicOr(&s_flags, 8);
-      if (lo_chain) s_nl = ns; else s_nu = ns;
+      if (ln == 0) {
+        ChainTop c;
+        if (two) {
+          for (int sgm = 0; sgm < 32; ++sgm) {
+            const int cnt = seg_n[sgm];
+            const float2* src = st + sgm * seg;
+            for (int k = 0; k < cnt; ++k) chain_push(st, c, src[k], lo_chain, kHullChain);
+          }
+        } else {
+          for (int i = 0; i < n; ++i) chain_push(st, c, buf[i], lo_chain, kHullChain);
+        }
+        if (c.overflow) atomicOr(&s_flags, 8);
+        if (lo_chain) s_nl = c.ns; else s_nu = c.ns;
+      }
     }
     __syncthreads();
     pos += m;
@@ -1949,28 +2200,81 @@ int ptgs_visibility_candidates(const float* px, const float* py, const float* pz
   return launch_sweep<2>(a, st);
 }
 
+namespace ptgs {
+struct PfWs {
+  int64_t* chunk_prefix; int64_t* off2; int32_t* count2; unsigned long long* ext; float* poly; float2* uv2;
+  int64_t uv2_cap; size_t bytes;
+};
+static PfWs carve_pf(void* ws, int64_t P) {
+  PfWs w;
+  if (P < 1) P = 1;
+  w.uv2_cap = P * 2048;
+  if (w.uv2_cap < (1ll << 20)) w.uv2_cap = 1ll << 20;
+  if (w.uv2_cap > (16ll << 20)) w.uv2_cap = 16ll << 20;
+  Carver cv(ws);
+  w.chunk_prefix = cv.take<int64_t>(P + 1);
+  w.off2 = cv.take<int64_t>(P);
+  w.count2 = cv.take<int32_t>(P);
+  w.ext = cv.take<unsigned long long>((size_t)P * kFiltDirs);
+  w.poly = cv.take<float>((size_t)P * kPfPolyFloats);
+  w.uv2 = cv.take<float2>((size_t)w.uv2_cap);
+  w.bytes = cv.used() + 256;
+  return w;
+}
+}  // namespace ptgs
+
+size_t ptgs_visibility_hull_workspace_bytes(int64_t n_pairs) { return carve_pf(nullptr, n_pairs).bytes; }
+
 int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* cand_count, const int32_t* n_hit, int64_t n_pairs,
                          const int32_t* pair_cam, const float* cameras, int32_t min_hits,
                          double ratio_threshold, double near_eps, double* area, double* ratio,
                          uint8_t* keep, uint8_t* flags, const int32_t* pair_map,
-                         const int64_t* n_sub_dev, int32_t* status, ptgs_stream_t stream) {
+                         const int64_t* n_sub_dev, int32_t* status, void* workspace,
+                         size_t workspace_bytes, ptgs_stream_t stream) {
   PTGS_REQUIRE(n_pairs >= 0 && n_pairs < (1ll << 31), "n_pairs");
   if (n_pairs == 0) return PTGS_OK;
   PTGS_REQUIRE(cand_offsets && cand_count && n_hit && pair_cam && cameras && area && ratio && keep && flags,
                "arguments");
-  if (status) PTGS_CUDA_TRY(cudaMemsetAsync(status, 0, 8, (cudaStream_t)stream));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (status) PTGS_CUDA_TRY(cudaMemsetAsync(status, 0, 8, st));
+  const int32_t* pf_count2 = nullptr;
+  const int64_t* pf_off2 = nullptr;
+  float2* pf_uv2 = nullptr;
+  if (workspace && workspace_bytes >= ptgs_visibility_hull_workspace_bytes(n_pairs)) {
+    // multi-CTA pre-filter of the pairs with the longest candidate lists (see pf_* above)
+    const PfWs w = carve_pf(workspace, n_pairs);
+    PTGS_CUDA_TRY(cudaMemsetAsync(w.ext, 0, (size_t)n_pairs * kFiltDirs * 8, st));
+    pf_plan_kernel<<<1, 1024, 0, st>>>(cand_offsets, cand_count, pair_map, n_sub_dev, n_pairs, w.uv2_cap,
+                                       w.chunk_prefix, w.off2, w.count2);
+    PTGS_LAUNCH_CHECK();
+    pf_extremes_kernel<<<kNumSMs * 4, 256, 0, st>>>((const float2*)cand_uv, cand_offsets, cand_count, pair_map,
+                                                    n_pairs, w.chunk_prefix, w.ext);
+    PTGS_LAUNCH_CHECK();
+    pf_polygon_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, st>>>(
+        (const float2*)cand_uv, cand_offsets, pair_map, n_pairs, w.count2, w.ext, w.poly);
+    PTGS_LAUNCH_CHECK();
+    pf_filter_kernel<<<kNumSMs * 4, 256, 0, st>>>((const float2*)cand_uv, cand_offsets, cand_count, pair_map,
+                                                  n_pairs, pair_cam, cameras, w.chunk_prefix, w.poly, w.off2,
+                                                  w.count2, w.uv2);
+    PTGS_LAUNCH_CHECK();
+    pf_count2 = w.count2; pf_off2 = w.off2; pf_uv2 = w.uv2;
+  }
   // the number of undecided pairs lives on the device; n_pairs / 8 is a typical share
   const char* e = getenv("PTGS_HULL_THREADS");
   const bool narrow = e ? (atoi(e) == 256) : (n_pairs >= 8 * 4 * kNumSMs);
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(hull_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHullDynSmem));
+  PTGS_CUDA_TRY(cudaFuncSetAttribute(hull_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHullDynSmem));
   if (narrow)
-    hull_kernel<256><<<(unsigned)n_pairs, 256, 0, (cudaStream_t)stream>>>(
+    hull_kernel<256><<<(unsigned)n_pairs, 256, kHullDynSmem, st>>>(
         (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
+        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status, pf_count2, pf_off2,
+        pf_uv2);
   else
-    hull_kernel<512><<<(unsigned)n_pairs, 512, 0, (cudaStream_t)stream>>>(
+    hull_kernel<512><<<(unsigned)n_pairs, 512, kHullDynSmem, st>>>(
         (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status);
+        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status, pf_count2, pf_off2,
+        pf_uv2);
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

@@ -441,7 +441,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                threshold=VISIBLE_RATE, min_hits=MIN_HITS, near_eps=NEAR_EPS,
                cand_capacity=2048, cam_split=None, timer=None, exact_ratio=False,
                cand_pool=None, interior=True, sample_stride=SAMPLE_STRIDE,
-               defer_check=False) -> VisibilityResult:
+               defer_check=False, hull_prefilter=True) -> VisibilityResult:
     """A7-A9 for every (block, camera) pair.
 
     sweep 1 (hit counts, pivot, 8 extremes) -> area bounds + early decision ->
@@ -521,6 +521,7 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
     sub_pos = torch.empty(P, dtype=torch.int32, device=dev)
     cand_off = torch.empty(P + 1, dtype=torch.int64, device=dev)
     hull_status = torch.empty(2, dtype=torch.int32, device=dev)
+    hull_ws = _ws(lib.ptgs_visibility_hull_workspace_bytes(P), dev) if hull_prefilter else None
     caps_in = None
     rounds = 0
     n_exact = None
@@ -550,7 +551,8 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
                                        _ptr(cam_index), _ptr(cameras_d), int(min_hits),
                                        float(threshold), float(near_eps), _ptr(area), _ptr(ratio),
                                        _ptr(keep), _ptr(flags), _ptr(sub_pos), _ptr(sub_off[L:]),
-                                       _ptr(hull_status), st))
+                                       _ptr(hull_status), _ptr(hull_ws), hull_ws.numel() if hull_ws is not None else 0,
+                                       st))
         mark("vis_hull")
         # the one synchronisation: [overflowed pairs, hull budget exceeded, exact pairs]
         stat_d = torch.cat([hull_status.to(torch.int64), sub_off[L:L + 1]])

@@ -436,6 +436,11 @@ int ptgs_visibility_candidates(const float* px, const float* py,
                                float* cand_uv, int32_t* cand_count,
                                void* workspace, size_t workspace_bytes,
                                ptgs_stream_t stream);
+/* workspace (may be NULL): ptgs_visibility_hull_workspace_bytes(n_pairs)
+ * bytes let the call pre-filter the pairs with the longest candidate lists
+ * over several CTAs each (one pair is otherwise one CTA, and the largest pair
+ * sets the duration of the launch); results do not depend on it. */
+size_t ptgs_visibility_hull_workspace_bytes(int64_t n_pairs);
 int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          const int32_t* cand_count, const int32_t* n_hit,
                          int64_t n_pairs, const int32_t* pair_cam,
@@ -443,7 +448,8 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
                          double ratio_threshold, double near_eps, double* area,
                          double* ratio, uint8_t* keep, uint8_t* flags,
                          const int32_t* pair_map, const int64_t* n_sub_dev,
-                         int32_t* status, ptgs_stream_t stream);
+                         int32_t* status, void* workspace,
+                         size_t workspace_bytes, ptgs_stream_t stream);
 /* status (device int32[2], may be NULL; zeroed by the call): [0] pairs whose
  * candidate list overflowed its capacity (flags bit2, re-run them with
  * cand_count slots), [1] pairs whose hull exceeded the vertex budget (bit3). */

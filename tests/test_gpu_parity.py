@@ -311,6 +311,34 @@ def test_visibility_adversarial_hulls():
                 assert bool(vis.keep[j]) == kp, (k, j)
 
 
+def test_visibility_hull_prefilter_large_lists():
+    """Pairs with long candidate lists go through the multi-CTA pre-filter before the hull: the
+    answers equal those of the single-CTA path bit for bit, and the oracle's."""
+    rng = np.random.default_rng(23)
+    n_disc, n_ring = 250000, 150000
+    r = np.concatenate([29.0 * np.sqrt(rng.uniform(0, 1, n_disc)), rng.uniform(29.0, 30.0, n_ring)])
+    t = rng.uniform(0, 2 * np.pi, len(r))
+    pts = np.column_stack([32 + r * np.cos(t), 32 + r * np.sin(t), np.ones(len(r))]).astype(np.float32)
+    recs = [_unit_camera(), _unit_camera(56.0, 60.0), _unit_camera(64.0, 64.0, 2)]
+    x, y, z = D.aos_to_soa(torch.from_numpy(pts).to(DEV))
+    off = torch.tensor([0, len(pts)], dtype=torch.int64, device=DEV)
+    cams = torch.from_numpy(np.stack(recs)).to(DEV)
+    coff = torch.tensor([0, len(recs)], dtype=torch.int64, device=DEV)
+    cidx = torch.arange(len(recs), dtype=torch.int32, device=DEV)
+    out = {}
+    for pf in (True, False):
+        out[pf] = D.visibility(x, y, z, off, cams, coff, cidx, exact_ratio=True, hull_prefilter=pf)
+    a, b = out[True], out[False]
+    assert int(a.cand_count.max()) > 3 * 6144, a.cand_count      # several chunks per pair
+    assert not bool((a.flags & 12).any())
+    for f in ("n_hit", "area", "ratio", "keep", "flags", "cand_count"):
+        assert torch.equal(getattr(a, f), getattr(b, f)), f
+    for j, rec in enumerate(recs):
+        nh, rt, kp = O.camera_visibility(pts, rec)
+        assert int(a.n_hit[j]) == nh
+        assert abs(float(a.ratio[j]) - rt) <= 1e-12 * max(1.0, rt), (j, float(a.ratio[j]), rt)
+
+
 def test_coverage_sweep():
     sc = small_scene(n=70001, c=37, thr=50000, seed=51)
     cams = scene_cameras(sc)

@@ -1,10 +1,10 @@
 #!/bin/bash
-# One GPU-box session (run under gpurun): parity tests, the bench line, an A/B of the sweep's exact
-# path, and the ncu captures the profiles/ summaries are made from.  The .ncu-rep files are
+# One GPU-box session (run under gpurun): parity tests, the bench line, the stage times with
+# and without the hull pre-filter, and the ncu captures the profiles/ summaries are made from.  The .ncu-rep files are
 # summarised ON THE BOX (gpurun_out/ is limited to 64 MiB) and removed.  Outputs under gpurun_out/.
-# usage: bash tools/gpu_session.sh [tag] [steps: tests bench legacy ncu_sweep launches ncu_partition]
+# usage: bash tools/gpu_session.sh [tag] [steps: tests bench stages ncu_sweep launches ncu_partition]
 tag=${1:-s1}; shift
-steps=${@:-tests bench legacy ncu_sweep launches ncu_partition}
+steps=${@:-tests bench stages ncu_sweep launches ncu_partition}
 out=gpurun_out
 mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $out/${tag}_smi.txt 2>&1
@@ -15,9 +15,10 @@ tests)
 bench)
   timeout 900 python bench.py --steps 5 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err
   echo "bench rc=$?" >> $out/${tag}_bench.err ;;
-legacy)
-  PTGS_SWEEP_EXACT=legacy timeout 600 python bench.py --steps 5 --warmup 3 --no-c5 --no-cpu-baseline --secondary '' \
-      > $out/${tag}_bench_legacy_exact.json 2> $out/${tag}_bench_legacy_exact.err ;;
+stages)
+  for m in prefilter noprefilter; do
+    timeout 300 python tools/vis_stages.py c4 5 $m > $out/${tag}_vis_stages_$m.log 2>&1
+  done ;;
 ncu_sweep)
   timeout 300 python tools/vis_once.py c4 2 > $out/${tag}_vis_once.log 2>&1 && \
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel' -s 4 -c 4 -f \
@@ -44,3 +45,4 @@ esac; done
 du -sh $out
 tail -5 $out/${tag}_tests.log 2>/dev/null
 head -c 1200 $out/${tag}_bench.json 2>/dev/null
+tail -n 3 $out/${tag}_vis_stages_*.log 2>/dev/null
