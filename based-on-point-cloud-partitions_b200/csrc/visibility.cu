@@ -1185,6 +1185,7 @@ __global__ void __launch_bounds__(1024) cand_plan_kernel(
 // latency bound: 4 warps per scheduler, one CTA per SM at 128 registers), 256 when there are many
 // (two CTAs per SM overlap one pair's serial phases with the other's parallel ones).
 constexpr int kHullMaxParts = 4;    // NT / 128 point partitions of the directional scan
+constexpr int kHullThreadsMany = 256;   // NT when there are many pairs
 constexpr int kHullBuf = 2048;      // points sorted per round (hull so far + new candidates)
 constexpr int kHullChain = 1024;    // max vertices per monotone chain
 constexpr int kHullFilterMin = 128; // candidates above which the directional pre-filter runs
@@ -1488,36 +1489,53 @@ __global__ void __launch_bounds__(256) pf_extremes_kernel(
   }
 }
 
-// (2) one thread per pre-filtered pair: polygon through its 64 extremes (distinct consecutive
+// (2) one warp per pre-filtered pair: polygon through its 64 extremes (distinct consecutive
 // vertices, edges as float half planes a*u + b*v + c -- the construction of filter_round)
 __global__ void __launch_bounds__(128) pf_polygon_kernel(
     const float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
     const int32_t* __restrict__ pair_map, int64_t n_pairs, const int32_t* __restrict__ count2,
     const unsigned long long* __restrict__ ext, float* __restrict__ poly) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_pairs || count2[i] < 0) return;
+  __shared__ float2 s_v[4][kFiltDirs];
+  __shared__ int s_cnt[4];
+  const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t i = (int64_t)blockIdx.x * 4 + wi;
+  if (i >= n_pairs || count2[i] < 0) return;       // warp uniform
   const int64_t pair = pair_map ? (int64_t)pair_map[i] : i;
   const float2* cu = cand_uv + cand_offsets[pair];
   float* out = poly + i * kPfPolyFloats;
-  float2 v[kFiltDirs];
-  int m = 0;
-  for (int k = 0; k < kFiltDirs; ++k) {
-    const unsigned long long e = ext[i * kFiltDirs + k];
-    if (!e) continue;
-    const float2 q = cu[(uint32_t)(e & 0xffffffffull)];
-    if (m && v[m - 1].x == q.x && v[m - 1].y == q.y) continue;
-    v[m++] = q;
+  // lanes fetch the extremes of directions lane and lane + 32; a direction without one repeats its
+  // predecessor (dropped as a duplicate below); direction 0 always has one (every planned pair has candidates)
+  const float nanv = __int_as_float(0x7fc00000);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const unsigned long long e = ext[i * kFiltDirs + lane + 32 * h];
+    s_v[wi][lane + 32 * h] = e ? cu[(uint32_t)(e & 0xffffffffull)] : make_float2(nanv, nanv);
   }
-  while (m > 1 && v[m - 1].x == v[0].x && v[m - 1].y == v[0].y) --m;
-  if (m < 3) { out[0] = 0.0f; return; }
-  for (int k = 0; k < m; ++k) {
+  __syncwarp();
+  if (lane == 0) {
+    float2* v = s_v[wi];
+    int m = 0;
+    for (int k = 0; k < kFiltDirs; ++k) {
+      const float2 q = v[k];
+      if (q.x != q.x) continue;                                          // no extreme along k
+      if (m && v[m - 1].x == q.x && v[m - 1].y == q.y) continue;
+      v[m++] = q;                                                         // m <= k: in place
+    }
+    while (m > 1 && v[m - 1].x == v[0].x && v[m - 1].y == v[0].y) --m;
+    s_cnt[wi] = m;
+  }
+  __syncwarp();
+  const int m = s_cnt[wi];
+  if (m < 3) { if (lane == 0) out[0] = 0.0f; return; }
+  for (int k = lane; k < m; k += 32) {
     const int k2 = (k + 1 == m) ? 0 : k + 1;
-    const double a = -((double)v[k2].y - (double)v[k].y), b = (double)v[k2].x - (double)v[k].x;
+    const float2 p = s_v[wi][k], q = s_v[wi][k2];
+    const double a = -((double)q.y - (double)p.y), b = (double)q.x - (double)p.x;
     out[4 + 3 * k] = (float)a;
     out[5 + 3 * k] = (float)b;
-    out[6 + 3 * k] = (float)(-(a * (double)v[k].x + b * (double)v[k].y));
+    out[6 + 3 * k] = (float)(-(a * (double)p.x + b * (double)p.y));
   }
-  out[0] = (float)m;
+  if (lane == 0) out[0] = (float)m;
 }
 
 // (3) per chunk: candidates that are not strictly inside the pair's polygon -> uv2[off2 + ...]
@@ -2251,7 +2269,7 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
     pf_extremes_kernel<<<kNumSMs * 4, 256, 0, st>>>((const float2*)cand_uv, cand_offsets, cand_count, pair_map,
                                                     n_pairs, w.chunk_prefix, w.ext);
     PTGS_LAUNCH_CHECK();
-    pf_polygon_kernel<<<(unsigned)((n_pairs + 127) / 128), 128, 0, st>>>(
+    pf_polygon_kernel<<<(unsigned)((n_pairs + 3) / 4), 128, 0, st>>>(
         (const float2*)cand_uv, cand_offsets, pair_map, n_pairs, w.count2, w.ext, w.poly);
     PTGS_LAUNCH_CHECK();
     pf_filter_kernel<<<kNumSMs * 4, 256, 0, st>>>((const float2*)cand_uv, cand_offsets, cand_count, pair_map,
@@ -2262,19 +2280,20 @@ int ptgs_visibility_hull(float* cand_uv, const int64_t* cand_offsets,
   }
   // the number of undecided pairs lives on the device; n_pairs / 8 is a typical share
   const char* e = getenv("PTGS_HULL_THREADS");
-  const bool narrow = e ? (atoi(e) == 256) : (n_pairs >= 8 * 4 * kNumSMs);
-  PTGS_CUDA_TRY(cudaFuncSetAttribute(hull_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHullDynSmem));
-  PTGS_CUDA_TRY(cudaFuncSetAttribute(hull_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHullDynSmem));
-  if (narrow)
-    hull_kernel<256><<<(unsigned)n_pairs, 256, kHullDynSmem, st>>>(
-        (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status, pf_count2, pf_off2,
-        pf_uv2);
-  else
-    hull_kernel<512><<<(unsigned)n_pairs, 512, kHullDynSmem, st>>>(
-        (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,
-        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status, pf_count2, pf_off2,
-        pf_uv2);
+  const int nt = e ? atoi(e) : (n_pairs >= 8 * 4 * kNumSMs ? kHullThreadsMany : 512);
+#define PTGS_HULL_LAUNCH(NT)                                                                                  \
+  do {                                                                                                        \
+    PTGS_CUDA_TRY(cudaFuncSetAttribute(hull_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,          \
+                                       kHullDynSmem));                                                        \
+    hull_kernel<NT><<<(unsigned)n_pairs, NT, kHullDynSmem, st>>>(                                             \
+        (float2*)cand_uv, cand_offsets, cand_count, n_hit, n_pairs, pair_cam, cameras, min_hits,              \
+        ratio_threshold, near_eps, area, ratio, keep, flags, pair_map, n_sub_dev, status, pf_count2, pf_off2, \
+        pf_uv2);                                                                                              \
+  } while (0)
+  if (nt == 128) PTGS_HULL_LAUNCH(128);
+  else if (nt == 256) PTGS_HULL_LAUNCH(256);
+  else PTGS_HULL_LAUNCH(512);
+#undef PTGS_HULL_LAUNCH
   PTGS_LAUNCH_CHECK();
   return PTGS_OK;
 }

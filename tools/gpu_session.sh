@@ -16,12 +16,12 @@ bench)
   timeout 900 python bench.py --steps 5 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err
   echo "bench rc=$?" >> $out/${tag}_bench.err ;;
 stages)
-  for m in prefilter noprefilter; do
-    timeout 300 python tools/vis_stages.py c4 5 $m > $out/${tag}_vis_stages_$m.log 2>&1
-  done ;;
+  for m in prefilter noprefilter; do for nt in ${HULL_NT:-256}; do
+    PTGS_HULL_THREADS=$nt timeout 300 python tools/vis_stages.py c4 5 $m > $out/${tag}_vis_stages_${m}_$nt.log 2>&1
+  done; done ;;
 ncu_sweep)
   timeout 300 python tools/vis_once.py c4 2 > $out/${tag}_vis_once.log 2>&1 && \
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel' -s 4 -c 4 -f \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel|pf_' -s 8 -c 8 -f \
       -o /tmp/${tag}_sweep python tools/vis_once.py c4 2 > $out/${tag}_ncu_sweep.log 2>&1
   if [ -f /tmp/${tag}_sweep.ncu-rep ]; then
     tests=$(python -c "import json;print(json.load(open('$out/${tag}_vis_once.log'))['tests'])" 2>/dev/null || echo 0)
