@@ -380,9 +380,10 @@ def assign_cameras(centers: np.ndarray, boxes: np.ndarray, device, want_host=Fal
 def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None, sync=True, xyz_aos=None):
     """A6 over every block at once.  Voxels of a block come out in ascending
     key order; ds_first gives the reference's first-occurrence order.  xyz_aos: the cloud as (N,3)
-    rows of the planes' dtype (optional; makes the entry gather of an index-list call cheaper)."""
+    rows of the planes' dtype (optional; makes the entry gather of an index-list call cheaper).
+    With xyz_aos the planes may be None (the rows are then the only source)."""
     lib = _lib.load()
-    dev = x.device
+    dev = offsets.device
     L = offsets.shape[0] - 1
     ne = indices.shape[0] if indices is not None else int(n_entries)
     pitch = (ne + 8 + 3) // 4 * 4
@@ -392,8 +393,9 @@ def voxel_downsample(x, y, z, offsets, indices, voxel=VOXEL_SIZE, n_entries=None
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     ws = _ws(lib.ptgs_voxel_downsample_workspace_bytes(ne, L), dev)
     if xyz_aos is not None:
-        assert xyz_aos.dtype == x.dtype and xyz_aos.is_contiguous() and xyz_aos.shape[0] == x.shape[0]
-    check(lib.ptgs_voxel_downsample(_dt(x), _ptr(x), _ptr(y), _ptr(z), _ptr(xyz_aos), _ptr(offsets), _ptr(indices),
+        assert xyz_aos.is_cuda and xyz_aos.is_contiguous() and xyz_aos.shape[1] == 3
+        assert x is None or (xyz_aos.dtype == x.dtype and xyz_aos.shape[0] == x.shape[0])
+    check(lib.ptgs_voxel_downsample(_dt(x if x is not None else xyz_aos), _ptr(x), _ptr(y), _ptr(z), _ptr(xyz_aos), _ptr(offsets), _ptr(indices),
                                     ne, L, float(voxel), _ptr(buf[0]), _ptr(buf[1]), _ptr(buf[2]),
                                     _ptr(ds_first), _ptr(ds_off), _ptr(status), _ptr(ws), ws.numel(),
                                     _stream()))
@@ -1084,7 +1086,7 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
 def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
                            cam_records: torch.Tensor, cam_offsets: np.ndarray,
                            cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
-                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2, exchange=None):
+                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2, exchange=None, streams=2):
     """visibility_based_camera_selection (shen_partation_densify.py:911-954)
     for HOST inputs: the expanded blocks' points back to back
     (`block_points` (sum N_b, 3) float32/float64, ideally pinned), the camera
@@ -1147,16 +1149,30 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
             ev_full = torch.cuda.Event()
             ev_full.record(copy)
     parts, n_ds = [], 0
-    for (pts_d, off_d, coff_d, cidx_d, ev, n_e, nb) in staged:
-        main.wait_event(ev)
-        for t in (pts_d, off_d, coff_d, cidx_d, cams_d):
-            t.record_stream(main)
-        x, y, z = aos_to_soa(pts_d)
-        # no host synchronisation inside a group: the host queues group g+1 while group g runs
-        ds_off, dx, dy, dz, _ = voxel_downsample(x, y, z, off_d, None, voxel, n_entries=n_e, sync=False)
-        args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d)
-        vis = visibility(*args, threshold=threshold, defer_check=True)
+    # groups alternate between the current stream and side streams: the latency-bound tail of one
+    # group's visibility pass (sample pass, hull, small kernels) overlaps the next group's A6
+    lanes = [main] + [_side_stream(device, i) for i in range(max(0, min(int(streams), len(staged)) - 1))]
+    for ln in lanes[1:]:
+        ln.wait_stream(main)
+    for g, (pts_d, off_d, coff_d, cidx_d, ev, n_e, nb) in enumerate(staged):
+        ln = lanes[g % len(lanes)]
+        with torch.cuda.stream(ln):
+            ln.wait_event(ev)
+            for t in (pts_d, off_d, coff_d, cidx_d, cams_d):
+                t.record_stream(ln)
+            # the uploaded rows are read as they are (no plane layout pass); no host synchronisation
+            # inside a group: the host queues group g+1 while group g runs
+            ds_off, dx, dy, dz, _ = voxel_downsample(None, None, None, off_d, None, voxel, n_entries=n_e,
+                                                     sync=False, xyz_aos=pts_d)
+            args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d)
+            vis = visibility(*args, threshold=threshold, defer_check=True)
         parts.append([vis, ds_off, nb, args, coff_d, cidx_d])
+    for ln in lanes[1:]:
+        main.wait_stream(ln)
+    for part in parts:                        # results are consumed on the current stream from here on
+        v = part[0]
+        for t in (v.n_hit, v.area, v.ratio, v.keep, v.flags, part[1]) + ((v.pending,) if getattr(v, "pending", None) is not None else ()):
+            t.record_stream(main)
     for part in parts:          # deferred candidate-capacity checks (rare: re-run that group)
         pend = getattr(part[0], "pending", None)
         if pend is not None:
@@ -1210,6 +1226,15 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
 
 
 _COPY_STREAMS = {}
+_SIDE_STREAMS = {}
+
+
+def _side_stream(device, i):
+    d = torch.device(device)
+    key = (d.index if d.index is not None else torch.cuda.current_device(), i)
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(device=device)
+    return _SIDE_STREAMS[key]
 
 
 def _copy_stream(device):

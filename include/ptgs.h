@@ -257,11 +257,15 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
  *   count (:588-591), cast to float32 (:605).
  *   Inputs: planar coordinates, block CSR (offsets[L+1], indices; indices may
  *   be NULL = identity, i.e. the blocks' points are stored back to back).
- *   xyz_aos (may be NULL; only read when `indices` is given): the same cloud
- *   as (N,3) rows of the same dtype.  With an index list the call first packs
- *   the entries' coordinates into one 16 / 32-byte record each (workspace) so
- *   that the three passes that need them read whole sectors; reading the rows
- *   instead of three planes makes that one gather 2-3x cheaper.
+ *   xyz_aos (may be NULL): the same cloud as (N,3) rows of the same dtype;
+ *   when it is given it is the source that is read and x / y / z may be NULL.
+ *   With an index list the call first packs the entries' coordinates into one
+ *   16 / 32-byte record each (workspace) so that the three passes that need
+ *   them read whole sectors; reading the rows instead of three planes makes
+ *   that one gather 2-3x cheaper.  Without one (blocks uploaded back to back
+ *   as rows) no plane layout pass is needed at all.
+ *   The sort moves (key | entry position) as ONE 64-bit word when both fit
+ *   (keys-only radix sort), else (key, position) pairs; same results.
  *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
  *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
  *   index list of the first point of the voxel.  Voxels of a block are
