@@ -225,8 +225,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) vox_key_kernel(
     PointSrc<T> src, const int64_t* __restrict__ offsets,
     int64_t n_entries, int L, const T* __restrict__ bmin, double voxel,
-    const VoxLayout* __restrict__ lay, int idx_bits, uint64_t* __restrict__ keys,
-    uint32_t* __restrict__ vals) {
+    const VoxLayout* __restrict__ lay, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   __shared__ int64_t s_off[kVoxMaxBlocks + 1];
   for (int i = threadIdx.x; i <= L; i += blockDim.x) s_off[i] = offsets[i];
   __syncthreads();
@@ -269,14 +268,8 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
       if (i < ly) k = (k << 1) | ((vy >> i) & 1ull);
       if (i < lz) k = (k << 1) | ((vz >> i) & 1ull);
     }
-    // idx_bits > 0: the entry position rides in the low bits of the key (below the sorted bit
-    // range), the sort moves 8 bytes per entry instead of 12 and there is no value array
-    if (idx_bits) {
-      keys[e] = (k << idx_bits) | (uint64_t)e;
-    } else {
-      keys[e] = k;
-      vals[e] = (uint32_t)e;
-    }
+    keys[e] = k;
+    vals[e] = (uint32_t)e;
   }
 }
 
@@ -284,14 +277,14 @@ constexpr int kHeadTile = 2048;
 
 // head flag = key differs from the predecessor; per tile head counts.
 __global__ void __launch_bounds__(256) vox_head_count_kernel(
-    const uint64_t* __restrict__ keys, int64_t n, int idx_bits, int32_t* __restrict__ tile_count) {
+    const uint64_t* __restrict__ keys, int64_t n, int32_t* __restrict__ tile_count) {
   __shared__ int s[33];
   const int64_t base = (int64_t)blockIdx.x * kHeadTile;
   int c = 0;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const int64_t i = base + k * 256 + threadIdx.x;
-    if (i < n) c += (i == 0 || (keys[i] >> idx_bits) != (keys[i - 1] >> idx_bits)) ? 1 : 0;
+    if (i < n) c += (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
   }
   int tot;
   block_exclusive_sum<int, 256>(c, s, &tot);
@@ -319,30 +312,25 @@ template <typename T>
 __global__ void __launch_bounds__(256) vox_mean_kernel(
     PointSrc<T> src, const int64_t* __restrict__ offsets,
     const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
-    int L, const VoxLayout* __restrict__ lay, int idx_bits, const int64_t* __restrict__ tile_base,
+    int L, const VoxLayout* __restrict__ lay, const int64_t* __restrict__ tile_base,
     float* __restrict__ ds_x, float* __restrict__ ds_y, float* __restrict__ ds_z,
     int32_t* __restrict__ ds_first, int64_t* __restrict__ ds_offsets) {
   __shared__ int s[33];
   const VoxLayout l = *lay;
   const int shift_b = l.total_bits - l.bits_b;
-  const uint64_t idx_mask = (1ull << idx_bits) - 1ull;
-  auto entry_of = [&](int64_t j, uint64_t raw) -> int64_t {
-    return idx_bits ? (int64_t)(raw & idx_mask) : (int64_t)vals[j];
-  };
   const int64_t base = (int64_t)blockIdx.x * kHeadTile;
   int64_t out = tile_base[blockIdx.x];
 #pragma unroll 1
   for (int k = 0; k < 8; ++k) {
     const int64_t i = base + k * 256 + threadIdx.x;
-    uint64_t key = 0, raw = 0;
+    uint64_t key = 0;
     int f = 0;
     bool first_of_block = false;
     if (i < n) {
-      raw = keys[i];
-      key = raw >> idx_bits;
+      key = keys[i];
       if (i == 0) { f = 1; first_of_block = true; }
       else {
-        const uint64_t prev = keys[i - 1] >> idx_bits;
+        const uint64_t prev = keys[i - 1];
         f = key != prev;
         first_of_block = (shift_b >= 64 ? 0 : (key >> shift_b)) != (shift_b >= 64 ? 0 : (prev >> shift_b));
       }
@@ -352,22 +340,20 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
     if (f) {
       const int64_t rank = out + ex;
       const int b = shift_b >= 64 ? 0 : (int)(key >> shift_b);
-      const int64_t e0 = entry_of(i, raw);
+      const uint32_t e0 = vals[i];
       // np.add.reduce over axis 0 starts from the identity +0.0, so a voxel
       // whose members are all -0.0 averages to +0.0
       T sx, sy, sz;
       {
         T px, py, pz;
-        src.load(e0, px, py, pz);
+        src.load((int64_t)e0, px, py, pz);
         sx = T(0) + px; sy = T(0) + py; sz = T(0) + pz;
       }
       int64_t j = i + 1;
       long long cnt = 1;
-      for (; j < n; ++j) {
-        const uint64_t rj = keys[j];
-        if ((rj >> idx_bits) != key) break;
+      for (; j < n && keys[j] == key; ++j) {
         T px, py, pz;
-        src.load(entry_of(j, rj), px, py, pz);
+        src.load((int64_t)vals[j], px, py, pz);
         sx = sx + px; sy = sy + py; sz = sz + pz;   // sequential, entry order
         ++cnt;
       }
@@ -375,7 +361,7 @@ __global__ void __launch_bounds__(256) vox_mean_kernel(
       ds_x[rank] = (float)(sx / c);
       ds_y[rank] = (float)(sy / c);
       ds_z[rank] = (float)(sz / c);
-      ds_first[rank] = (int32_t)(e0 - offsets[b]);
+      ds_first[rank] = (int32_t)((int64_t)e0 - offsets[b]);
       if (first_of_block) ds_offsets[b] = rank;   // provisional: non-empty blocks only
     }
     out += tot;
@@ -397,11 +383,10 @@ __global__ void vox_fix_offsets_kernel(const int64_t* __restrict__ offsets, int 
 }
 
 static size_t vox_sort_temp_bytes(int64_t n) {
-  size_t pairs = 0, keys = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, pairs, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
                                   (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0, 64);
-  cub::DeviceRadixSort::SortKeys(nullptr, keys, (const uint64_t*)nullptr, (uint64_t*)nullptr, (int64_t)n, 0, 64);
-  return pairs > keys ? pairs : keys;
+  return bytes;
 }
 
 struct VoxWs {
@@ -464,27 +449,17 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const void
               lay.bits_b, lay.bits_x, lay.bits_y, lay.bits_z);
     return PTGS_E_RANGE;
   }
-  // entry position inside the key when both fit 64 bits (keys-only sort: 16 instead of 24 bytes
-  // moved per entry and pass); the stable sort leaves equal voxels in entry order either way
-  int idx_bits = 1;
-  while (idx_bits < 32 && ((int64_t)(n - 1) >> idx_bits)) ++idx_bits;
-  if (idx_bits + lay.total_bits > 64 || getenv("PTGS_VOXEL_SORT_PAIRS")) idx_bits = 0;
-  vox_key_kernel<T><<<grid, 256, 0, st>>>(src, offsets, n, L, bmin, voxel, w.lay, idx_bits, w.keys_a, w.vals_a);
+  vox_key_kernel<T><<<grid, 256, 0, st>>>(src, offsets, n, L, bmin, voxel, w.lay, w.keys_a, w.vals_a);
   PTGS_LAUNCH_CHECK();
-  if (idx_bits) {
-    PTGS_CUDA_TRY(cub::DeviceRadixSort::SortKeys(w.sort_tmp, w.sort_bytes, w.keys_a, w.keys_b, (int64_t)n,
-                                                 idx_bits, idx_bits + lay.total_bits, st));
-  } else {
-    PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_bytes, w.keys_a, w.keys_b,
-                                                  w.vals_a, w.vals_b, (int64_t)n, 0, lay.total_bits, st));
-  }
+  PTGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_bytes, w.keys_a, w.keys_b,
+                                                w.vals_a, w.vals_b, (int64_t)n, 0, lay.total_bits, st));
   count_launch(2 + (lay.total_bits + 7) / 8);
-  vox_head_count_kernel<<<(unsigned)w.n_tiles, 256, 0, st>>>(w.keys_b, n, idx_bits, w.tile_count);
+  vox_head_count_kernel<<<(unsigned)w.n_tiles, 256, 0, st>>>(w.keys_b, n, w.tile_count);
   PTGS_LAUNCH_CHECK();
   vox_scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_count, w.n_tiles, w.tile_base, w.total);
   PTGS_LAUNCH_CHECK();
   vox_mean_kernel<T><<<(unsigned)w.n_tiles, 256, 0, st>>>(src, offsets, w.keys_b, w.vals_b,
-                                                         n, L, w.lay, idx_bits, w.tile_base, ds_x, ds_y, ds_z,
+                                                         n, L, w.lay, w.tile_base, ds_x, ds_y, ds_z,
                                                          ds_first, ds_offsets);
   PTGS_LAUNCH_CHECK();
   vox_fix_offsets_kernel<<<1, 32, 0, st>>>(offsets, L, w.total, ds_offsets);

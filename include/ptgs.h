@@ -264,8 +264,6 @@ int ptgs_assign_cameras(const double* centers, int32_t n_cameras,
  *   them read whole sectors; reading the rows instead of three planes makes
  *   that one gather 2-3x cheaper.  Without one (blocks uploaded back to back
  *   as rows) no plane layout pass is needed at all.
- *   The sort moves (key | entry position) as ONE 64-bit word when both fit
- *   (keys-only radix sort), else (key, position) pairs; same results.
  *   Outputs: ds_x/ds_y/ds_z (float32, capacity = offsets[L]), ds_offsets[L+1]
  *   (int64), ds_first (int32, capacity as ds_x): position inside the block's
  *   index list of the first point of the voxel.  Voxels of a block are

@@ -2,8 +2,6 @@
 ptgs_b200.device) against the CPU oracle on the same seeded inputs.
 Bit-exact for masks, split lines, index sets, voxel means, hit counts and keep
 decisions; hull areas to 1e-12 relative (float64 summation order only)."""
-import os
-
 import numpy as np
 import pytest
 import torch
@@ -164,14 +162,6 @@ def test_voxel_downsample():
         assert np.array_equal(f[order], wfirst)
         assert np.array_equal(g[order].view(np.uint32), want.view(np.uint32))
     assert any(len(l) > 0 and ds_off[b + 1] - ds_off[b] < len(l) for b, l in enumerate(lists))
-    # the (key, entry) pair sort that clouds too large for an in-key entry index fall back to
-    os.environ["PTGS_VOXEL_SORT_PAIRS"] = "1"
-    try:
-        alt = D.voxel_downsample(x, y, z, off, idx)
-    finally:
-        del os.environ["PTGS_VOXEL_SORT_PAIRS"]
-    for a, b in zip(alt, (torch.from_numpy(ds_off).to(DEV), dx, dy, dz, dfirst)):
-        assert torch.equal(a, b)
     # rows as the only source (what the host-buffer entry uploads): blocks stored back to back
     rows = _dev_xyz(sc)[idx.to(torch.int64)].contiguous()
     got_rows = D.voxel_downsample(None, None, None, off, None, n_entries=idx.shape[0], xyz_aos=rows)
