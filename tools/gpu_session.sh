@@ -2,7 +2,7 @@
 # One GPU-box session (run under gpurun): parity tests, the bench line, the stage times with
 # and without the hull pre-filter, and the ncu captures the profiles/ summaries are made from.  The .ncu-rep files are
 # summarised ON THE BOX (gpurun_out/ is limited to 64 MiB) and removed.  Outputs under gpurun_out/.
-# usage: bash tools/gpu_session.sh [tag] [steps: tests bench stages ncu_sweep launches ncu_partition]
+# usage: bash tools/gpu_session.sh [tag] [steps: tests bench stages ncu_sweep launches launches_bench ncu_partition]
 tag=${1:-s1}; shift
 steps=${@:-tests bench stages ncu_sweep launches ncu_partition}
 out=gpurun_out
@@ -36,6 +36,13 @@ launches)
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
       --log-file $out/${tag}_launches_partition_c4.csv python tools/partition_once.py c4 > $out/${tag}_ncu_launches.log 2>&1
   python tools/launch_summary.py $out/${tag}_launches_partition_c4.csv > $out/${tag}_launches_partition_c4_summary.txt 2>&1 ;;
+launches_bench)
+  # the launch list of the bench command itself (the timed steps are the "step" ranges of the summary)
+  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --csv \
+      --log-file $out/${tag}_launches_bench.csv python bench.py --steps 2 --warmup 3 --no-c5 --no-cpu-baseline --secondary '' \
+      > $out/${tag}_launches_bench.log 2>&1
+  python tools/launch_summary.py $out/${tag}_launches_bench.csv > $out/${tag}_launches_bench_summary.txt 2>&1
+  gzip -f $out/${tag}_launches_bench.csv ;;
 ncu_partition)
   timeout 900 ncu --set full --clock-control none --profile-from-start off \
       -k regex:'vox_|radius_count|gather_sorted|hist_kernel|partition_kernel|expand_|aos_|cand_plan|keep_' -c 80 -f \
