@@ -174,12 +174,27 @@ __global__ void __launch_bounds__(256) vox_minmax_kernel(
   flush();
 }
 
+// The host needs the key layout (number of sorted bits) before it can queue the sort.  It is read
+// through pinned host memory that the layout kernel writes directly: a cudaMemcpyAsync would queue
+// behind whatever large device -> host copy another stream has in flight (partition_device's early
+// copy of the index list), and the stage would wait for all of it.
+struct VoxHostSlot { VoxLayout lay; int32_t status; };
+static VoxHostSlot* vox_host_slot() {
+  thread_local VoxHostSlot* slot = nullptr;
+  if (!slot) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, sizeof(VoxHostSlot), cudaHostAllocDefault) == cudaSuccess) slot = (VoxHostSlot*)p;
+    else (void)cudaGetLastError();
+  }
+  return slot;
+}
+
 // single CTA: decode per block min, global max voxel index per axis, layout.
 template <typename T>
 __global__ void __launch_bounds__(1024) vox_layout_kernel(
     const typename KeyOf<T>::type* __restrict__ mm, const int64_t* __restrict__ offsets, int L,
     double voxel, T* __restrict__ bmin /* [L][3] */, VoxLayout* __restrict__ lay,
-    int32_t* __restrict__ status) {
+    int32_t* __restrict__ status, VoxHostSlot* host_slot /* pinned host memory, may be null */) {
   __shared__ long long smax[3];
   if (threadIdx.x < 3) smax[threadIdx.x] = 0;
   __syncthreads();
@@ -218,6 +233,11 @@ __global__ void __launch_bounds__(1024) vox_layout_kernel(
     l.max_vz = (int32_t)min(smax[2], 0x7fffffffll);
     *lay = l;
     *status = ok ? PTGS_OK : PTGS_E_RANGE;
+    if (host_slot) {
+      host_slot->lay = l;
+      host_slot->status = ok ? PTGS_OK : PTGS_E_RANGE;
+      __threadfence_system();
+    }
   }
 }
 
@@ -437,13 +457,20 @@ static int voxel_impl(const void* vx, const void* vy, const void* vz, const void
   vox_minmax_kernel<T><<<grid, 256, 0, st>>>(src, indices ? (V4*)w.ent : nullptr, offsets, n, L, mm);
   if (indices) src.ent = (const V4*)w.ent;
   PTGS_LAUNCH_CHECK();
-  vox_layout_kernel<T><<<1, 1024, 0, st>>>(mm, offsets, L, voxel, bmin, w.lay, status_dev);
+  VoxHostSlot* hs = vox_host_slot();
+  vox_layout_kernel<T><<<1, 1024, 0, st>>>(mm, offsets, L, voxel, bmin, w.lay, status_dev, hs);
   PTGS_LAUNCH_CHECK();
   VoxLayout lay;
   int32_t status;
-  PTGS_CUDA_TRY(cudaMemcpyAsync(&lay, w.lay, sizeof(lay), cudaMemcpyDeviceToHost, st));
-  PTGS_CUDA_TRY(cudaMemcpyAsync(&status, status_dev, sizeof(status), cudaMemcpyDeviceToHost, st));
-  PTGS_CUDA_TRY(cudaStreamSynchronize(st));
+  if (hs) {
+    PTGS_CUDA_TRY(cudaStreamSynchronize(st));
+    lay = hs->lay;
+    status = hs->status;
+  } else {
+    PTGS_CUDA_TRY(cudaMemcpyAsync(&lay, w.lay, sizeof(lay), cudaMemcpyDeviceToHost, st));
+    PTGS_CUDA_TRY(cudaMemcpyAsync(&status, status_dev, sizeof(status), cudaMemcpyDeviceToHost, st));
+    PTGS_CUDA_TRY(cudaStreamSynchronize(st));
+  }
   if (status != PTGS_OK) {
     set_error("voxel_downsample: voxel grid does not fit the 64-bit key (bits b/x/y/z = %d/%d/%d/%d)",
               lay.bits_b, lay.bits_x, lay.bits_y, lay.bits_z);

@@ -85,6 +85,7 @@ class PartitionDeviceResult:
     pt_counts_h: np.ndarray = None     # host copies of the L-sized tables (no extra synchronisation)
     cam_offsets_h: np.ndarray = None
     ds_block0: int = 0                 # first block of ds_* (range-sharded runs keep only their own blocks)
+    pt_index_host: tuple = None        # (pinned int32 tensor, event): early device -> host copy of pt_index
 
 
 def leaf_id(path: int, depth: int) -> str:
@@ -815,7 +816,7 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
                      threshold: int, man_trans: np.ndarray | None = None, radius_filter: bool = True,
                      do_visibility: bool = True, time_stages: bool = False,
                      shard: tuple | None = None, split_xyz: torch.Tensor | None = None,
-                     exact_ratio: bool = False) -> PartitionDeviceResult:
+                     exact_ratio: bool = False, host_results: bool = False) -> PartitionDeviceResult:
     """run_DataPartition (shen_partition_utils.py:57-93) on the device.
 
     xyz         (N,3) float32 CUDA tensor: the scene cloud as fetchPly returns it.
@@ -836,6 +837,9 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
                 result and kept-camera CSR; ds_* hold the rank's own blocks (ds_block0 = first).
     exact_ratio every pair's exact hull ratio (default: pairs decided by the
                 area bounds skip the exact hull, see visibility()).
+    host_results the caller will ask for partition_results_to_host(): the expanded index list (the
+                large output, 4 bytes per expanded point) starts its device -> pinned host copy on the
+                copy stream as soon as A4 has produced it, underneath A6-A9.
     """
     assert xyz.is_cuda
     dev = xyz.device
@@ -879,6 +883,16 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
         leaf_ids=[leaf_id(p, d) for p, d in zip(lp.tolist(), ld.tolist())], boxes=boxes,
         pt_offsets=pt_off, pt_index=pt_idx, cam_offsets=cam_off, cam_index=cam_idx)
     res.pt_counts_h, res.cam_offsets_h = pt_cnt_h, cam_off_h
+    if host_results:
+        main, copy = torch.cuda.current_stream(dev), _copy_stream(dev)
+        copy.wait_stream(main)                                   # pt_idx is complete on the main stream
+        with torch.cuda.stream(copy):
+            idx_h = torch.empty(int(pt_idx.shape[0]), dtype=torch.int32, pin_memory=True)
+            idx_h.copy_(pt_idx, non_blocking=True)
+            pt_idx.record_stream(copy)
+            done = torch.cuda.Event()
+            done.record(copy)
+        res.pt_index_host = (idx_h, done)
     if do_visibility:
         cams_d = torch.from_numpy(np.ascontiguousarray(cam_records, dtype=np.float32)).to(dev)
         # the input rows double as the gather source of A6 when the planes carry the same values
@@ -937,9 +951,13 @@ def partition_results_to_host(res: PartitionDeviceResult) -> dict:
     (4 bytes per expanded point); it lands in pinned memory so the copy runs at PCIe speed."""
     out = {"leaf_bounds": res.leaf_bounds, "leaf_ids": res.leaf_ids, "leaf_count": res.leaf_count,
            "boxes": res.boxes}
-    n = int(res.pt_index.shape[0])
-    idx_h = torch.empty(n, dtype=torch.int32, pin_memory=True)
-    idx_h.copy_(res.pt_index, non_blocking=True)
+    staged = getattr(res, "pt_index_host", None)
+    if staged is not None:                    # partition_device(host_results=True) started the copy after A4
+        idx_h, done = staged
+        done.synchronize()
+    else:
+        idx_h = torch.empty(int(res.pt_index.shape[0]), dtype=torch.int32, pin_memory=True)
+        idx_h.copy_(res.pt_index, non_blocking=True)
     out["pt_index"] = idx_h.numpy()
     small = {"pt_offsets": res.pt_offsets, "cam_offsets": res.cam_offsets, "cam_index": res.cam_index}
     if res.vis is not None:

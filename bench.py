@@ -458,7 +458,8 @@ def measure_partition(args, out, ctx):
         barrier(world)
         t0 = time.perf_counter()
         r = D.partition_device(ctx["xyz"], ctx["recs"], ctx["centers"], w.threshold, man_trans=w.man_trans,
-                               time_stages=True, shard=(rank, world) if world > 1 else None)
+                               time_stages=True, shard=(rank, world) if world > 1 else None,
+                               host_results=(rank == 0))
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         # every rank holds the full result; one host copy of it is the job's output (rank 0)

@@ -368,6 +368,20 @@ def test_coverage_sweep():
     assert all(torch.equal(a, b) for a, b in zip(od, od2))
 
 
+def test_partition_results_to_host_early_copy():
+    """partition_device(host_results=True) starts the index list's device -> host copy under A6-A9;
+    the host result set equals the one copied afterwards."""
+    sc = small_scene(n=90000, c=40, thr=12000, seed=71)
+    cams = scene_cameras(sc)
+    recs = D.camera_records(cams.R, cams.T, cams.FoVx, cams.FoVy, cams.width, cams.height)
+    centers = D.camera_centers(cams.R, cams.T)
+    a = D.partition_results_to_host(D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, host_results=True))
+    b = D.partition_results_to_host(D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold))
+    assert set(a) == set(b) and len(a["pt_index"]) > len(sc.xyz) // 2
+    for k in a:
+        assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), k
+
+
 def test_spatial_order_is_a_permutation_and_local():
     rng = np.random.default_rng(7)
     n = 300001
