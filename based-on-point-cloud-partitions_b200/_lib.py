@@ -16,6 +16,7 @@ CAMERA_FLOATS = 20
 EXTREME_DIRS = 8                   # PTGS_EXTREME_DIRS (checked against the library at load)
 POLY_FLOATS = 4 + 3 * EXTREME_DIRS
 PAIR_RECORD_BYTES = 24
+COMPACT_XY_STATIC_MAX_POINTS = 1 << 26    # PTGS_COMPACT_XY_STATIC_MAX_POINTS
 
 _vp, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t
 
@@ -38,6 +39,7 @@ SIGNATURES = {
     "ptgs_slab_keep": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _f64, _f64, _vp, _vp]),
     "ptgs_compact_xy_workspace_bytes": (_sz, [_i64]),
     "ptgs_compact_xy": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ptgs_compact_xy_static": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "ptgs_bounds_xy": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _vp]),
     "ptgs_balanced_split_workspace_bytes": (_sz, [C.c_int, _i64, _f64, C.c_int]),
     "ptgs_balanced_split": (C.c_int, [C.c_int, _vp, _vp, _vp, _i64, _vp, _f64, C.c_int, _f64,

@@ -3,6 +3,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace ptgs {
@@ -321,6 +323,39 @@ static int bounds_impl(const void* x, const void* y, const int64_t* n_dev,
   return PTGS_OK;
 }
 
+// ---- allocation-free stream compaction (ptgs_compact_xy_static) ------------------------------
+// The per-tile counts and bases of compact_count / scan_tiles / compact_scatter live in a
+// file-scope device array instead of a caller workspace.  Every GPU that loads the library holds
+// the array (384 KB) until exit.  In host code the NAME below is a host-side stand-in, not a device
+// address: the address a kernel can use comes from cudaGetSymbolAddress, looked up once per device
+// with that device current.
+constexpr int64_t kStaticCompactMaxPoints = PTGS_COMPACT_XY_STATIC_MAX_POINTS;
+constexpr int64_t kStaticCompactMaxTiles = kStaticCompactMaxPoints / kCompactTile;
+constexpr size_t kStaticCountBytes = (size_t)kStaticCompactMaxTiles * sizeof(int32_t);   // 128 KB, multiple of 256
+constexpr size_t kStaticCompactBytes = kStaticCountBytes + (size_t)kStaticCompactMaxTiles * sizeof(int64_t);
+static_assert(kStaticCompactMaxPoints % kCompactTile == 0 && kStaticCountBytes % 256 == 0, "scratch layout");
+static __device__ __align__(256) unsigned char g_compact_static_scratch[kStaticCompactBytes];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_mu;
+static void* g_static_addr[kMaxDevices] = {};
+
+// device address of the scratch array on the CURRENT device (set-up: first call per device)
+static int compact_static_address(unsigned char** out) {
+  int dev = -1;
+  PTGS_CUDA_TRY(cudaGetDevice(&dev));
+  PTGS_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal above 63");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev]) {
+    void* ptr = nullptr;
+    PTGS_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_compact_static_scratch));
+    PTGS_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_static_addr[dev] = ptr;
+  }
+  *out = static_cast<unsigned char*>(g_static_addr[dev]);
+  return PTGS_OK;
+}
+
 }  // namespace ptgs
 
 using namespace ptgs;
@@ -461,6 +496,44 @@ int ptgs_compact_xy(int dtype, const void* x, const void* y,
   Carver cv(workspace);
   int32_t* tile_count = cv.take<int32_t>(tiles);
   int64_t* tile_base = cv.take<int64_t>(tiles);
+  compact_count_kernel<<<(int)tiles, 256, 0, st>>>(keep, n, tile_count);
+  PTGS_LAUNCH_CHECK();
+  scan_tiles_kernel<<<1, 1024, 0, st>>>(tile_count, tiles, tile_base, n_out);
+  PTGS_LAUNCH_CHECK();
+  if (dtype == PTGS_F32)
+    compact_scatter_kernel<float><<<(int)tiles, 256, 0, st>>>(
+        (const float*)x, (const float*)y, keep, n, tile_base, (float*)out_x, (float*)out_y);
+  else
+    compact_scatter_kernel<double><<<(int)tiles, 256, 0, st>>>(
+        (const double*)x, (const double*)y, keep, n, tile_base, (double*)out_x, (double*)out_y);
+  PTGS_LAUNCH_CHECK();
+  return PTGS_OK;
+}
+
+int ptgs_compact_xy_static(int dtype, const void* x, const void* y, const uint8_t* keep, int64_t n,
+                           void* out_x, void* out_y, int64_t* n_out, ptgs_stream_t stream) {
+  PTGS_REQUIRE(n >= 0 && n_out, "arguments");
+  PTGS_REQUIRE(dtype == PTGS_F32 || dtype == PTGS_F64, "dtype");
+  if (n > kStaticCompactMaxPoints) {
+    set_error("compact_xy_static: n = %lld exceeds the built-in scratch (PTGS_COMPACT_XY_STATIC_MAX_POINTS = %lld); "
+              "use ptgs_compact_xy with a caller workspace",
+              (long long)n, (long long)kStaticCompactMaxPoints);
+    return PTGS_E_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t tiles = (n + kCompactTile - 1) / kCompactTile;
+  if (tiles == 0) {
+    PTGS_CUDA_TRY(cudaMemsetAsync(n_out, 0, 8, st));
+    return PTGS_OK;
+  }
+  PTGS_REQUIRE(x && y && keep && out_x && out_y, "arguments");
+  unsigned char* scratch = nullptr;
+  const int rc = compact_static_address(&scratch);
+  if (rc != PTGS_OK) return rc;
+  // entries [0, tiles) of both tables are written by the first two kernels before anything reads
+  // them, so nothing has to start at zero and the previous call's contents do not matter
+  int32_t* tile_count = reinterpret_cast<int32_t*>(scratch);
+  int64_t* tile_base = reinterpret_cast<int64_t*>(scratch + kStaticCountBytes);
   compact_count_kernel<<<(int)tiles, 256, 0, st>>>(keep, n, tile_count);
   PTGS_LAUNCH_CHECK();
   scan_tiles_kernel<<<1, 1024, 0, st>>>(tile_count, tiles, tile_base, n_out);

@@ -143,6 +143,28 @@ int ptgs_compact_xy(int dtype, const void* x, const void* y,
                     int64_t* n_out, void* workspace, size_t workspace_bytes,
                     ptgs_stream_t stream);
 
+/* Allocation-free variant of ptgs_compact_xy.  It has NO counterpart in the
+ * reference: it was added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, outputs and results as
+ * ptgs_compact_xy, but the per-tile scratch lives in a file-scope
+ * `static __device__` array of the library (384 KB, held by every GPU that
+ * loads the library until exit) instead of a caller workspace; the call
+ * performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *   Limit: n <= PTGS_COMPACT_XY_STATIC_MAX_POINTS; a larger n is rejected
+ *   with PTGS_E_WORKSPACE (ptgs_last_error names the limit) before anything
+ *   is launched -- use ptgs_compact_xy with a caller workspace then.
+ *   The array is SHARED by every call on the device and keeps the last
+ *   call's contents (nothing in it has to start at zero: each call rewrites
+ *   the entries it reads).  Calls that can overlap on the GPU -- different
+ *   streams, or host threads on different streams -- race on it: serialise
+ *   them (one stream, or events).  The first call on each device looks up the
+ *   array's device address (cudaGetSymbolAddress, with that device current). */
+#define PTGS_COMPACT_XY_STATIC_MAX_POINTS (1ll << 26)
+int ptgs_compact_xy_static(int dtype, const void* x, const void* y,
+                           const uint8_t* keep, int64_t n, void* out_x,
+                           void* out_y, int64_t* n_out, ptgs_stream_t stream);
+
 /* ------------------------------------------------------------------ *
  * A2 -- XY bounds, scene/ptgs/shen_partition_utils.py:66-70.
  *   n is a DEVICE count (so it can be chained after ptgs_compact_xy).
