@@ -1,13 +1,23 @@
 """Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list per kernel.
-usage: python tools/launch_summary.py launches.csv [skip_first_n_launches]"""
-import collections, csv, sys
-rows = list(csv.reader(open(sys.argv[1])))
+usage: python tools/launch_summary.py launches.csv[.gz] [skip_first_n_launches] [--only REGEX]
+       --only: aggregate only the kernels whose name matches (e.g. the kernels of the visibility step,
+       so that a kernel's share of the STEP can be read off a launch list of the whole bench command)"""
+import collections, csv, gzip, io, re, sys
+only = None
+if "--only" in sys.argv:
+    i = sys.argv.index("--only")
+    only = re.compile(sys.argv[i + 1])
+    del sys.argv[i:i + 2]
+raw = gzip.open(sys.argv[1], "rt").read() if sys.argv[1].endswith(".gz") else open(sys.argv[1]).read()
+rows = list(csv.reader(io.StringIO(raw)))
 skip = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
 h = rows[hi]; idx = {k: i for i, k in enumerate(h)}
 agg = collections.OrderedDict(); total = 0.0; n = 0
 for r in rows[hi + 1:]:
     if len(r) < len(h) or r[idx["Metric Name"]] != "gpu__time_duration.sum":
+        continue
+    if only is not None and not only.search(r[idx["Kernel Name"]]):
         continue
     n += 1
     if n <= skip:
