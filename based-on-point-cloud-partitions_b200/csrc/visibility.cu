@@ -343,6 +343,35 @@ __device__ __forceinline__ bool inner_all_in(const Cam& c, const float* pl, cons
   return in;
 }
 
+// inner_all_in evaluated by a whole warp for ONE camera: lane e owns polygon edge e (same forms,
+// same margins; all lanes must call it).
+__device__ __forceinline__ bool inner_all_in_warp(const Cam& c, const float* pl, const float* b, int lane) {
+  const int ne = (int)pl[0];
+  if (ne < 3) return false;
+  const float S = fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + b[3] + b[4] + b[5] +
+                  fmaxf(fabsf(c.tx), fmaxf(fabsf(c.ty), fabsf(c.tz)));
+  const float mF = S * (1.0f / 65536.0f);
+  const Form Y = form(c.r10, c.r11, c.r12, c.ty, b);
+  const Form Z = form(c.r20, c.r21, c.r22, c.tz, b);
+  const Form F = (c.front_axis == 1.0f) ? Y : Z;
+  if (!(F.mid - F.rad > mF) || !(Z.mid - Z.rad > mF)) return false;     // warp uniform
+  bool ok = true;
+  if (lane < ne) {
+    const float a0 = fmaf(c.fx, c.r00, c.cx * c.r20), a1 = fmaf(c.fx, c.r01, c.cx * c.r21),
+                a2 = fmaf(c.fx, c.r02, c.cx * c.r22), ad = fmaf(c.fx, c.tx, c.cx * c.tz);
+    const float c0 = fmaf(c.fy, c.r10, c.cy * c.r20), c1 = fmaf(c.fy, c.r11, c.cy * c.r21),
+                c2 = fmaf(c.fy, c.r12, c.cy * c.r22), cd = fmaf(c.fy, c.ty, c.cy * c.tz);
+    const float margin = pl[3];
+    const float ea = pl[4 + 3 * lane], eb = pl[5 + 3 * lane];
+    const float ec = pl[6 + 3 * lane] - 2.0f * margin;
+    const float mPe = mF * (fabsf(ea) * (c.fx + fabsf(c.cx)) + fabsf(eb) * (c.fy + fabsf(c.cy)) + fabsf(ec));
+    const Form G = form(fmaf(ea, a0, fmaf(eb, c0, ec * c.r20)), fmaf(ea, a1, fmaf(eb, c1, ec * c.r21)),
+                        fmaf(ea, a2, fmaf(eb, c2, ec * c.r22)), fmaf(ea, ad, fmaf(eb, cd, ec * c.tz)), b);
+    ok = G.mid - G.rad > mPe;
+  }
+  return __all_sync(kFullMask, ok);
+}
+
 // ---- work item schedule -----------------------------------------------------
 // item_prefix[b] = number of work items of the blocks before b; a block has
 // tiles_b * split_b items, split_b = min(cam_split, C_b).
@@ -1000,6 +1029,169 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
     }
     item = S.next_item;            // published by the barriers of the camera loop
     if (item < n_items) cur = decode_item(a, S.prefix, item);
+  }
+}
+
+// ---- hull candidates of the undecided pairs, one warp per 128-point run ---------------------
+// sweep_kernel<2> stages every 1024-point tile of every block that owns an undecided pair and
+// pays the item machinery (tile staging, CTA barriers, queue) for a handful of cameras per
+// block: 1.17 ms at c4 for 13 % of the pairs, half of its issue slots idle at barriers.  The
+// candidate pass needs none of it: a warp loads one run of 128 consecutive points of a block
+// straight from global memory (4 per lane, coalesced), builds the run's box, lets lane j test
+// undecided camera j of the block against the box (outside the image -> skipped, wholly inside
+// the pair's inner polygon -> nothing to emit) and evaluates its points for the survivors with
+// the arithmetic of the sweep.  The emitted SET per pair is defined per point (hit, not on the
+// excluded pivot row, not strictly inside the inner polygon), so it does not depend on how the
+// points are grouped; the box tests are the conservative ones of the sweep.
+constexpr int kCrRun = 128;
+constexpr int kCrWarps = 8;
+
+__global__ void __launch_bounds__(1024) cand_schedule_kernel(
+    const int64_t* __restrict__ pt_offsets, const int64_t* __restrict__ cam_offsets, int L,
+    int64_t* __restrict__ run_prefix) {
+  __shared__ long long sm[33];
+  long long carry = 0;
+  for (int s = 0; s < L; s += 1024) {
+    const int b = s + threadIdx.x;
+    long long v = 0;
+    if (b < L && cam_offsets[b + 1] > cam_offsets[b])
+      v = (pt_offsets[b + 1] - pt_offsets[b] + kCrRun - 1) / kCrRun;
+    long long tot;
+    const long long ex = block_exclusive_sum<long long, 1024>(v, sm, &tot);
+    if (b < L) run_prefix[b] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) run_prefix[L] = carry;
+}
+
+__global__ void __launch_bounds__(kCrWarps * 32) cand_runs_kernel(
+    const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz,
+    const int64_t* __restrict__ pt_offsets, int L, const float* __restrict__ cameras,
+    const int64_t* __restrict__ cam_offsets, const int32_t* __restrict__ cam_index,
+    const int32_t* __restrict__ pair_map, const float* __restrict__ poly,
+    const int64_t* __restrict__ cand_offsets, float2* __restrict__ cand_uv,
+    int32_t* __restrict__ cand_count, const int64_t* __restrict__ run_prefix) {
+  __shared__ int64_t s_prefix[kSwMaxBlocks + 1];
+  __shared__ __align__(16) float s_cam[kCrWarps][kCamFloats];
+  __shared__ __align__(16) float s_poly[kCrWarps][kPolyFloats];
+  for (int i = threadIdx.x; i <= L; i += blockDim.x) s_prefix[i] = run_prefix[i];
+  __syncthreads();
+  const int64_t n_runs = s_prefix[L];
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const float qnan = __int_as_float(0x7fc00000);
+  const float inf = __int_as_float(0x7f800000);
+  for (int64_t run = (int64_t)blockIdx.x * kCrWarps + wp; run < n_runs; run += (int64_t)gridDim.x * kCrWarps) {
+    int lo = 0, hi = L - 1;                 // last block with prefix <= run: the one that owns it
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_prefix[mid] <= run) lo = mid; else hi = mid - 1;
+    }
+    const int b = lo;
+    const int64_t p0 = pt_offsets[b] + (run - s_prefix[b]) * kCrRun;
+    const int64_t rem = pt_offsets[b + 1] - p0;
+    const int cnt = (int)(rem < kCrRun ? rem : kCrRun);
+    float x[4], y[4], z[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = k * 32 + lane;
+      const bool ok = i < cnt;
+      x[k] = ok ? __ldg(px + p0 + i) : qnan;    // NaN never hits
+      y[k] = ok ? __ldg(py + p0 + i) : qnan;
+      z[k] = ok ? __ldg(pz + p0 + i) : qnan;
+    }
+    float wb[6];                             // centre xyz, half extent xyz (padded like the sweep's boxes)
+    {
+      float bl[3] = {inf, inf, inf}, bh[3] = {-inf, -inf, -inf};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        bl[0] = fminf(bl[0], x[k]); bh[0] = fmaxf(bh[0], x[k]);
+        bl[1] = fminf(bl[1], y[k]); bh[1] = fmaxf(bh[1], y[k]);
+        bl[2] = fminf(bl[2], z[k]); bh[2] = fmaxf(bh[2], z[k]);
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          bl[a] = fminf(bl[a], __shfl_xor_sync(kFullMask, bl[a], d));
+          bh[a] = fmaxf(bh[a], __shfl_xor_sync(kFullMask, bh[a], d));
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const float pad = (fabsf(bl[a]) + fabsf(bh[a])) * (1.0f / 1048576.0f);
+        wb[a] = 0.5f * bl[a] + 0.5f * bh[a];
+        wb[3 + a] = (0.5f * bh[a] - 0.5f * bl[a]) + pad;
+      }
+    }
+    const int64_t cam_base = cam_offsets[b];
+    const int nc = (int)(cam_offsets[b + 1] - cam_base);
+    for (int g0 = 0; g0 < nc; g0 += 32) {
+      bool live = false;
+      if (g0 + lane < nc) {
+        const int64_t slot = cam_base + g0 + lane;
+        float rec[kCamFloats];
+#pragma unroll
+        for (int q = 0; q < kCamFloats / 4; ++q)
+          reinterpret_cast<float4*>(rec)[q] =
+              __ldg(reinterpret_cast<const float4*>(cameras + (int64_t)cam_index[slot] * kCamFloats) + q);
+        const Cam cj = load_cam(rec);
+        live = tile_may_hit(cj, wb);
+      }
+      unsigned pm = __ballot_sync(kFullMask, live);
+      while (pm) {
+        const int j = __ffs(pm) - 1;
+        pm &= pm - 1;
+        const int64_t slot = cam_base + g0 + j;
+        const int64_t pair = pair_map ? (int64_t)pair_map[slot] : slot;
+        __syncwarp();                        // the previous camera's staged records are no longer read
+        if (lane < kCamFloats / 4)
+          reinterpret_cast<float4*>(s_cam[wp])[lane] =
+              __ldg(reinterpret_cast<const float4*>(cameras + (int64_t)cam_index[slot] * kCamFloats) + lane);
+        else if (lane - 8 >= 0 && lane - 8 < kPolyFloats / 4)
+          reinterpret_cast<float4*>(s_poly[wp])[lane - 8] =
+              __ldg(reinterpret_cast<const float4*>(poly + pair * kPolyFloats) + (lane - 8));
+        __syncwarp();
+        const Cam c = load_cam(s_cam[wp]);
+        const float* pl = s_poly[wp];
+        // the whole run projects strictly inside the pair's inner polygon: nothing to emit
+        // (lane e tests edge e; few cameras get here, so one lane per camera would idle the warp)
+        if (inner_all_in_warp(c, pl, wb, lane)) continue;
+        const float w1 = __fadd_rn(c.w, 1.0f), h1 = __fadd_rn(c.h, 1.0f);
+        const int ne = (int)pl[0];
+        const float margin = pl[3];
+        const int64_t o0 = cand_offsets[pair];
+        const int cap = (int)(cand_offsets[pair + 1] - o0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          bool emit = false;
+          float u = 0.0f, v = 0.0f;
+          const Proj p = project_pre(c, w1, h1, x[k], y[k], z[k]);
+          if (p.maybe && project_exact(c, p, u, v)) {
+            u = __fadd_rn(u, 0.0f);
+            v = __fadd_rn(v, 0.0f);
+            // the pivot's row: only the pivot itself takes part (see ptgs.h)
+            const bool excluded = (v == pl[1]) && (u != pl[2]);
+            if (!excluded) {
+              bool inside = ne > 0;
+              for (int e = 0; e < ne; ++e) {
+                const float f = __fadd_rn(
+                    __fadd_rn(__fmul_rn(pl[4 + 3 * e], u), __fmul_rn(pl[5 + 3 * e], v)), pl[6 + 3 * e]);
+                inside = inside && (f > margin);
+              }
+              emit = !inside;
+            }
+          }
+          const unsigned em = __ballot_sync(kFullMask, emit);
+          if (em) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(cand_count + pair, __popc(em));
+            base = __shfl_sync(kFullMask, base, 0);
+            const int slot_c = base + __popc(em & lanemask_lt());
+            if (emit && slot_c < cap) cand_uv[o0 + slot_c] = make_float2(u, v);
+          }
+        }
+      }
+    }
   }
 }
 
@@ -2208,6 +2400,18 @@ int ptgs_visibility_candidates(const float* px, const float* py, const float* pz
   }
   cudaStream_t st = (cudaStream_t)stream;
   int64_t* item_prefix = (int64_t*)workspace;
+  const char* mode = getenv("PTGS_SWEEP2");
+  if (!(mode && strcmp(mode, "tiles") == 0)) {
+    // one warp per 128-point run of the blocks that own an undecided pair (cand_runs_kernel)
+    cand_schedule_kernel<<<1, 1024, 0, st>>>(pt_offsets, cam_offsets, n_blocks, item_prefix);
+    PTGS_LAUNCH_CHECK();
+    cand_runs_kernel<<<kNumSMs * 16, kCrWarps * 32, 0, st>>>(px, py, pz, pt_offsets, n_blocks, cameras, cam_offsets,
+                                                            cam_index, pair_map, poly, cand_offsets,
+                                                            (float2*)cand_uv, cand_count, item_prefix);
+    PTGS_LAUNCH_CHECK();
+    return PTGS_OK;
+  }
+  // PTGS_SWEEP2=tiles: the tile-staged sweep (A/B runs; same candidate sets)
   int rc = schedule(pt_offsets, cam_offsets, n_blocks, cam_split, item_prefix, st);
   if (rc) return rc;
   SweepArgs a = {};

@@ -316,6 +316,35 @@ def test_visibility_adversarial_hulls():
                 assert bool(vis.keep[j]) == kp, (k, j)
 
 
+def test_candidate_pass_variants_agree():
+    """The warp-per-run candidate pass (default) and the tile-staged sweep (PTGS_SWEEP2=tiles) emit
+    the same candidate sets: identical counts per pair and identical hull results."""
+    import os
+    sc = small_scene(n=140000, c=70, thr=20000, seed=43, oblique_fraction=0.4)
+    cams = scene_cameras(sc)
+    recs = D.camera_records(cams.R, cams.T, cams.FoVx, cams.FoVy, cams.width, cams.height)
+    centers = D.camera_centers(cams.R, cams.T)
+    res = D.partition_device(_dev_xyz(sc), recs, centers, sc.threshold, do_visibility=False)
+    ds_off, dx, dy, dz, _ = D.voxel_downsample(*D.aos_to_soa(_dev_xyz(sc)), res.pt_offsets, res.pt_index)
+    cams_d = torch.from_numpy(recs).to(DEV)
+    out = {}
+    for mode in ("runs", "tiles"):
+        for exact in (True, False):
+            if mode == "tiles":
+                os.environ["PTGS_SWEEP2"] = "tiles"
+            try:
+                out[mode, exact] = D.visibility(dx, dy, dz, ds_off, cams_d, res.cam_offsets, res.cam_index,
+                                                exact_ratio=exact)
+            finally:
+                os.environ.pop("PTGS_SWEEP2", None)
+    for exact in (True, False):
+        a, b = out["runs", exact], out["tiles", exact]
+        if exact:
+            assert int(a.cand_count.sum()) > 1000 and a.n_exact == len(a.keep)
+        for f in ("n_hit", "area", "ratio", "keep", "flags", "cand_count"):
+            assert torch.equal(getattr(a, f), getattr(b, f)), (f, exact)
+
+
 def test_visibility_hull_prefilter_large_lists():
     """Pairs with long candidate lists go through the multi-CTA pre-filter before the hull: the
     answers equal those of the single-CTA path bit for bit, and the oracle's."""

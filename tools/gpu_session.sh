@@ -21,7 +21,7 @@ stages)
   done; done ;;
 ncu_sweep)
   timeout 300 python tools/vis_once.py c4 2 > $out/${tag}_vis_once.log 2>&1 && \
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel|pf_' -s 8 -c 8 -f \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel|pf_|cand_runs' -s 8 -c 8 -f \
       -o /tmp/${tag}_sweep python tools/vis_once.py c4 2 > $out/${tag}_ncu_sweep.log 2>&1
   if [ -f /tmp/${tag}_sweep.ncu-rep ]; then
     tests=$(python -c "import json;print(json.load(open('$out/${tag}_vis_once.log'))['tests'])" 2>/dev/null || echo 0)
@@ -29,6 +29,7 @@ ncu_sweep)
     python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep sweep_kernel '<(int)1' > $out/${tag}_ncu_sweep1_lines.txt 2>&1
     python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep sweep_kernel '<(int)2' > $out/${tag}_ncu_sweep2_lines.txt 2>&1
     python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep hull_kernel > $out/${tag}_ncu_hull_lines.txt 2>&1
+    python tools/ncu_lines.py /tmp/${tag}_sweep.ncu-rep cand_runs_kernel > $out/${tag}_ncu_cand_runs_lines.txt 2>&1
     python tools/ncu_json.py /tmp/${tag}_sweep.ncu-rep 'sweep_kernel<1' $tests c4 $out/${tag}_sweep1_ncu.json > /dev/null 2>> $out/${tag}_ncu_sweep.log
   fi ;;
 launches)
