@@ -906,8 +906,12 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
             pt_off_h = np.concatenate([[0], np.cumsum(pt_cnt_h)]).astype(np.int64)
             e0, e1 = int(pt_off_h[b0]), int(pt_off_h[b1])
             sub_off = torch.from_numpy(pt_off_h[b0:b1 + 1] - e0).to(dev)
-            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, sub_off, pt_idx[e0:e1], xyz_aos=aos) if b1 > b0 else \
-                voxel_downsample(x, y, z, torch.zeros(2, dtype=torch.int64, device=dev), pt_idx[:0])
+            # sync=False: no host read-back of the voxel count here -- a small device -> host copy would
+            # queue behind the index list's copy (host_results) on the copy engine; the planes keep their
+            # full capacity until the exchange's own synchronisation below
+            ds_off, dx, dy, dz, dfirst = voxel_downsample(x, y, z, sub_off, pt_idx[e0:e1], xyz_aos=aos, sync=False) \
+                if b1 > b0 else \
+                voxel_downsample(x, y, z, torch.zeros(2, dtype=torch.int64, device=dev), pt_idx[:0], sync=False)
             tm.mark("A6_voxel")
             loc = np.clip(cam_off_h[b0:b1 + 1], plan.lo, plan.hi) - plan.lo if b1 > b0 else np.zeros(2, np.int64)
             loc_off = torch.from_numpy(np.ascontiguousarray(loc, dtype=np.int64)).to(dev)
@@ -928,6 +932,8 @@ def partition_device(xyz: torch.Tensor, cam_records: np.ndarray, cam_centers: np
                                                                     unpack_records_dev, group)
             vis = VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
             vis.n_exact = v.n_exact
+            m_ds = int(ds_off[-1].item())
+            dx, dy, dz, dfirst = dx[:m_ds], dy[:m_ds], dz[:m_ds], dfirst[:m_ds]
             tm.mark("exchange")
             res.ds_block0 = b0
         else:
