@@ -1110,7 +1110,8 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
 def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
                            cam_records: torch.Tensor, cam_offsets: np.ndarray,
                            cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
-                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2, exchange=None, streams=2):
+                           threshold=VISIBLE_RATE, rank=0, world=1, group=None, groups=2, exchange=None, streams=2,
+                           trace=None):
     """visibility_based_camera_selection (shen_partation_densify.py:911-954)
     for HOST inputs: the expanded blocks' points back to back
     (`block_points` (sum N_b, 3) float32/float64, ideally pinned), the camera
@@ -1143,17 +1144,34 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
         bl0 = bl1 = 0
     loc_off = np.clip(cam_offsets, lo, hi) - lo            # this rank's block -> camera CSR (global blocks)
     n_local = int(block_offsets[bl1] - block_offsets[bl0])
-    # group boundaries: consecutive local blocks, ~equal point counts
-    G = max(1, min(int(groups), max(bl1 - bl0, 1)))
+    # group boundaries: consecutive local blocks; `groups` = a count (~equal point counts) or the
+    # groups' shares of the points (a small first group starts the kernels early, a small last one
+    # shortens what is left to do once the last byte has landed)
+    if isinstance(groups, (list, tuple)):
+        shares = np.cumsum(np.asarray(groups, dtype=np.float64))
+        shares = shares / shares[-1]
+    else:
+        G = max(1, int(groups))
+        shares = np.arange(1, G + 1, dtype=np.float64) / G
+    shares = shares[: max(bl1 - bl0, 1)]
+    G = len(shares)
     cuts = [bl0]
-    for g in range(1, G):
-        b = int(np.searchsorted(block_offsets, block_offsets[bl0] + n_local * g / G, side="left"))
+    for g in range(G - 1):
+        b = int(np.searchsorted(block_offsets, block_offsets[bl0] + n_local * shares[g], side="left"))
         cuts.append(min(max(b, cuts[-1]), bl1))
     cuts.append(bl1)
     spans = [(cuts[i], cuts[i + 1]) for i in range(G) if cuts[i + 1] > cuts[i]]
     main = torch.cuda.current_stream(device)
     copy = _copy_stream(device)
     copy.wait_stream(main)
+    # trace (diagnostics): a list that receives (label, ms since the call started on the device)
+    tev = []
+    def _tmark(label, stream):
+        if trace is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            tev.append((label, e))
+    _tmark("start", main)
     staged = []
     with torch.cuda.stream(copy):
         cams_d = cam_records.to(device, non_blocking=True)
@@ -1166,12 +1184,13 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
             cidx_d = torch.from_numpy(cam_index[lo + c0:lo + c1]).to(device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy)
+            _tmark("upload%d" % len(staged), copy)
             staged.append((pts_d, off_d, coff_d, cidx_d, ev, p1 - p0, b1 - b0))
-        if world > 1:
-            full_off_d = torch.from_numpy(cam_offsets).to(device, non_blocking=True)
-            full_idx_d = torch.from_numpy(cam_index).to(device, non_blocking=True)
-            ev_full = torch.cuda.Event()
-            ev_full.record(copy)
+        # the whole block -> camera CSR: the final selection is ONE call on the concatenated results
+        full_off_d = torch.from_numpy(cam_offsets).to(device, non_blocking=True)
+        full_idx_d = torch.from_numpy(cam_index).to(device, non_blocking=True)
+        ev_full = torch.cuda.Event()
+        ev_full.record(copy)
     parts, n_ds = [], 0
     # groups alternate between the current stream and side streams: the latency-bound tail of one
     # group's visibility pass (sample pass, hull, small kernels) overlaps the next group's A6
@@ -1186,10 +1205,13 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
                 t.record_stream(ln)
             # the uploaded rows are read as they are (no plane layout pass); no host synchronisation
             # inside a group: the host queues group g+1 while group g runs
+            _tmark("g%d_begin" % g, ln)
             ds_off, dx, dy, dz, _ = voxel_downsample(None, None, None, off_d, None, voxel, n_entries=n_e,
                                                      sync=False, xyz_aos=pts_d)
+            _tmark("g%d_A6" % g, ln)
             args = (dx, dy, dz, ds_off, cams_d, coff_d, cidx_d)
             vis = visibility(*args, threshold=threshold, defer_check=True)
+            _tmark("g%d_vis" % g, ln)
         parts.append([vis, ds_off, nb, args, coff_d, cidx_d])
     for ln in lanes[1:]:
         main.wait_stream(ln)
@@ -1197,33 +1219,36 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
         v = part[0]
         for t in (v.n_hit, v.area, v.ratio, v.keep, v.flags, part[1]) + ((v.pending,) if getattr(v, "pending", None) is not None else ()):
             t.record_stream(main)
-    for part in parts:          # deferred candidate-capacity checks (rare: re-run that group)
-        pend = getattr(part[0], "pending", None)
-        if pend is not None:
-            st_h = pend.cpu()
+    # deferred candidate-capacity checks, ONE read-back for all groups (rare: re-run that group)
+    pends = [getattr(part[0], "pending", None) for part in parts]
+    if any(pd is not None for pd in pends):
+        st_all = torch.stack([pd if pd is not None else torch.zeros(3, dtype=torch.int64, device=device)
+                              for pd in pends]).cpu()
+        for part, st_h in zip(parts, st_all):
             if int(st_h[1]):
                 raise RuntimeError("visibility: convex hull exceeds the kernel's vertex budget")
             if int(st_h[0]):
                 part[0] = visibility(*part[3], threshold=threshold)
     if world <= 1:
-        # kept-camera lists per group, one round of D2H at the end
-        # kept_offsets has L + 1 entries whatever blocks were skipped: blocks before bl0 / after bl1
-        # have no cameras (searchsorted above) and repeat the running total
-        k_offs, k_idxs, nh, rt, kp, fl = [np.zeros(1 + bl0, np.int64)], [], [], [], [], []
-        sel = [select_cameras(p[0].keep, p[4], p[5], sync=False) for p in parts]
-        base = 0
-        for (vis, ds_off, nb, _a, _c, _i), (k_off, k_idx) in zip(parts, sel):
-            ko = k_off.cpu().numpy()
-            k_offs.append(ko[1:] + base)
-            k_idxs.append(k_idx[: int(ko[nb])].cpu().numpy())
-            base += int(ko[nb])
-            nh.append(vis.n_hit.cpu().numpy()); rt.append(vis.ratio.cpu().numpy())
-            kp.append(vis.keep.cpu().numpy()); fl.append(vis.flags.cpu().numpy())
-            n_ds += int(ds_off[nb].item())
-        k_offs.append(np.full(L - bl1, base, np.int64))
-        cat = lambda xs, dt: np.concatenate(xs) if xs else np.zeros(0, dt)
-        out = (np.concatenate(k_offs), cat(k_idxs, np.int32), cat(nh, np.int32), cat(rt, np.float64),
-               cat(kp, np.uint8), cat(fl, np.uint8))
+        # one selection over the concatenated keep flags and ONE round of device -> host copies
+        # (per-group copies are synchronous round trips: 6 per group)
+        main.wait_event(ev_full)
+        full_off_d.record_stream(main); full_idx_d.record_stream(main)
+        live = [p[0] for p in parts]
+        cat = lambda f, dt: (torch.cat([getattr(v, f) for v in live]) if live
+                             else torch.zeros(0, dtype=dt, device=device))
+        n_hit, ratio, keep, flags = (cat("n_hit", torch.int32), cat("ratio", torch.float64),
+                                     cat("keep", torch.uint8), cat("flags", torch.uint8))
+        k_off, k_idx = select_cameras(keep, full_off_d, full_idx_d, sync=False)
+        n_ds_d = torch.stack([p[1][p[2]] for p in parts]).sum() if parts else torch.zeros((), dtype=torch.int64, device=device)
+        small = torch.cat([k_off, n_ds_d.reshape(1)]).cpu().numpy()          # synchronises
+        ko, n_ds = small[:L + 1], int(small[L + 1])
+        out = (ko, k_idx[: int(ko[L])].cpu().numpy(), n_hit.cpu().numpy(), ratio.cpu().numpy(),
+               keep.cpu().numpy(), flags.cpu().numpy())
+        if trace is not None:
+            _tmark("end", main)
+            torch.cuda.synchronize()
+            trace.extend((lb, round(tev[0][1].elapsed_time(e), 3)) for lb, e in tev)
         return out, n_ds
     # world > 1: the groups' records are this rank's pairs lo..hi-1 in order; ONE exchange
     live = [p[0] for p in parts if p[0].n_hit.shape[0] > 0 and p[5].shape[0] > 0]

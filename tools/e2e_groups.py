@@ -14,7 +14,6 @@ import ptgs_b200  # noqa: F401
 from ptgs_b200 import device as D, workload as W
 
 name = sys.argv[1] if len(sys.argv) > 1 else "c4"
-group_counts = [int(a) for a in sys.argv[2:]] or [2, 4, 6, 8, 12]
 dev = torch.device("cuda", 0)
 w = W.make(name, 1.0)
 recs = D.camera_records(w.R, w.T, w.FoVx, w.FoVy, w.width, w.height)
@@ -49,18 +48,22 @@ h2d_ms = (time.perf_counter() - t0) / 3 * 1e3
 print(json.dumps({"workload": name, "h2d_bytes": nbytes, "bare_h2d_ms": round(h2d_ms, 3),
                   "h2d_GBps": round(nbytes / h2d_ms / 1e6, 2)}))
 del dst
-for streams in (1, 2, 3):
-    for g in group_counts:
-        one = lambda: D.visibility_select_host(host, blk_off, recs_pinned, cam_off, cam_idx, dev, groups=g,
-                                               streams=streams)
-        for _ in range(2):
-            ref = one()
-        ts = []
-        for _ in range(4):
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            outp = one()
-            torch.cuda.synchronize()
-            ts.append((time.perf_counter() - t0) * 1e3)
-        print(json.dumps({"groups": g, "streams": streams, "ms_best": round(min(ts), 3),
-                          "ms_mean": round(float(np.mean(ts)), 3), "kept": int(outp[0][4].sum())}))
+configs = [(4, 2), ([0.35, 0.3, 0.2, 0.1, 0.05], 2), ([0.4, 0.3, 0.2, 0.1], 2), ([0.3, 0.3, 0.2, 0.12, 0.08], 2),
+           ([0.45, 0.3, 0.15, 0.1], 2), ([0.3, 0.25, 0.2, 0.15, 0.1], 2), ([0.35, 0.3, 0.2, 0.1, 0.05], 3),
+           ([0.5, 0.3, 0.2], 2), ([0.3, 0.25, 0.2, 0.15, 0.1], 3)]
+for g, streams in configs:
+    one = lambda: D.visibility_select_host(host, blk_off, recs_pinned, cam_off, cam_idx, dev, groups=g, streams=streams)
+    for _ in range(2):
+        ref = one()
+    ts = []
+    for _ in range(5):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        outp = one()
+        torch.cuda.synchronize()
+        ts.append((time.perf_counter() - t0) * 1e3)
+    print(json.dumps({"groups": g, "streams": streams, "ms_best": round(min(ts), 3),
+                      "ms_mean": round(float(np.mean(ts)), 3), "kept": int(outp[0][4].sum())}), flush=True)
+tr = []
+D.visibility_select_host(host, blk_off, recs_pinned, cam_off, cam_idx, dev, groups=[0.35, 0.3, 0.2, 0.1, 0.05], streams=2, trace=tr)
+print(json.dumps({"trace_decreasing_streams2": tr}))
