@@ -82,6 +82,25 @@ struct PointSrc {
   }
 };
 
+// bit i of x -> bit 2i (32 source bits) / bit 3i (10 source bits)
+__device__ __forceinline__ uint64_t spread2(uint64_t x) {
+  x &= 0xffffffffull;
+  x = (x | (x << 16)) & 0x0000ffff0000ffffull;
+  x = (x | (x << 8)) & 0x00ff00ff00ff00ffull;
+  x = (x | (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | (x << 2)) & 0x3333333333333333ull;
+  x = (x | (x << 1)) & 0x5555555555555555ull;
+  return x;
+}
+__device__ __forceinline__ uint32_t spread3(uint32_t x) {
+  x &= 0x3ffu;
+  x = (x | (x << 16)) & 0xff0000ffu;
+  x = (x | (x << 8)) & 0x0300f00fu;
+  x = (x | (x << 4)) & 0x030c30c3u;
+  x = (x | (x << 2)) & 0x09249249u;
+  return x;
+}
+
 __device__ __forceinline__ int find_block(const int64_t* s_off, int L, int64_t e) {
   int lo = 0, hi = L - 1;  // last b with off[b] <= e
   while (lo < hi) {
@@ -252,8 +271,16 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
   const VoxLayout l = *lay;
   const T vs = (T)voxel;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += stride) {
-    const int b = find_block(s_off, L, e);
+  // 32 consecutive entries almost always lie in one block: one search per warp (lane 0's entry),
+  // the lanes behind a block boundary search for themselves
+  const int64_t n_pad = (n_entries + 31) & ~(int64_t)31;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_pad; e += stride) {
+    const int64_t e_first = e - (threadIdx.x & 31);
+    int b = 0;
+    if ((threadIdx.x & 31) == 0) b = find_block(s_off, L, e_first < n_entries ? e_first : n_entries - 1);
+    b = __shfl_sync(kFullMask, b, 0);
+    if (e >= n_entries) continue;
+    if (e >= s_off[b + 1]) b = find_block(s_off, L, e);
     T px, py, pz;
     src.load(e, px, py, pz);
     const uint64_t vx = (uint64_t)VoxArith<T>::vid(px, bmin[3 * b], vs);
@@ -272,9 +299,7 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
     const uint64_t cx = vx >> lx, cy = vy >> ly;
     uint64_t cell;
     if (l.morton) {
-      cell = 0;
-      for (int i = 0; i < l.bits_m / 2; ++i)
-        cell |= (((cx >> i) & 1ull) << (2 * i + 1)) | (((cy >> i) & 1ull) << (2 * i));
+      cell = (spread2(cx) << 1) | spread2(cy);      // bit i of cx -> 2i + 1, of cy -> 2i
     } else {
       cell = (cx << (l.bits_y - ly)) | cy;
     }
@@ -283,10 +308,17 @@ __global__ void __launch_bounds__(256) vox_key_kernel(
     k = (k << l.bits_m) | cell;
     // fine bits: 3-D Morton, so that 256 / 32 consecutive voxels (a warp's share
     // of a sweep tile / one register slot of a warp) are compact cubes
-    for (int i = kVoxCoarseShift - 1; i >= 0; --i) {
-      if (i < lx) k = (k << 1) | ((vx >> i) & 1ull);
-      if (i < ly) k = (k << 1) | ((vy >> i) & 1ull);
-      if (i < lz) k = (k << 1) | ((vz >> i) & 1ull);
+    if (lx == kVoxCoarseShift && ly == kVoxCoarseShift && lz == kVoxCoarseShift) {
+      // all three axes have their 6 fine bits: x5 y5 z5 ... x0 y0 z0 by bit spreading
+      const uint32_t m = (1u << kVoxCoarseShift) - 1u;
+      k = (k << (3 * kVoxCoarseShift)) |
+          (uint64_t)((spread3((uint32_t)vx & m) << 2) | (spread3((uint32_t)vy & m) << 1) | spread3((uint32_t)vz & m));
+    } else {
+      for (int i = kVoxCoarseShift - 1; i >= 0; --i) {
+        if (i < lx) k = (k << 1) | ((vx >> i) & 1ull);
+        if (i < ly) k = (k << 1) | ((vy >> i) & 1ull);
+        if (i < lz) k = (k << 1) | ((vz >> i) & 1ull);
+      }
     }
     keys[e] = k;
     vals[e] = (uint32_t)e;
