@@ -469,15 +469,18 @@ __device__ unsigned long long g_sweep_stats[8];
 #endif
 
 // ---- the sweep ---------------------------------------------------------------
-struct SweepSmem {
+// Members a mode does not use shrink to one element: the coverage sweep (MODE 0) has no polygons
+// (20 KB), which is what lets 3 CTAs fit one SM next to the 8 KB prefix table of its 1024 super-tiles.
+template <int MODE>
+struct SweepSmemT {
   alignas(128) float tile[2][3][kSwStageFloats];
   alignas(16) float cam[kSwCamChunk][kCamFloats];
   // MODE 1: kSwCamChunk krect records (kKrectFloats each); MODE 2: kSwCamChunk / 2 inner polygons
   // (rows of 2 * kKrectFloats >= kPolyFloats floats) -- the same bytes
-  alignas(16) float poly[kSwCamChunk * kKrectFloats];
-  long long cand_off[kSwCamChunk];                        // MODE 2
-  int cand_cap[kSwCamChunk];                              // MODE 2
-  int pair_of[kSwCamChunk];                               // MODE 2
+  alignas(16) float poly[MODE == 0 ? 4 : kSwCamChunk * kKrectFloats];
+  long long cand_off[MODE == 2 ? kSwCamChunk : 1];        // MODE 2
+  int cand_cap[MODE == 2 ? kSwCamChunk : 1];              // MODE 2
+  int pair_of[MODE == 2 ? kSwCamChunk : 1];               // MODE 2
   int act[kSwThreads];                                    // cameras of the round that survive the tile cull
   long long pair[kSwCamChunk];                            // output slot (pair id / camera) of the staged cameras
   int nact;
@@ -509,6 +512,7 @@ __global__ void __launch_bounds__(kSwThreads, kSwCtasPerSM) sweep_kernel(SweepAr
   constexpr int kPolyStride = kWidePoly ? 2 * kKrectFloats : kKrectFloats;     // floats per staged polygon row
   static_assert(kPolyFloats <= 2 * kKrectFloats, "inner polygon row");
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  using SweepSmem = SweepSmemT<MODE>;
   SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
 
@@ -2240,6 +2244,7 @@ static CovPlan coverage_plan(int64_t n, int32_t cam_count) {
 // ---- host side -----------------------------------------------------------------
 template <int MODE>
 static int launch_sweep(const SweepArgs& a, cudaStream_t st) {
+  using SweepSmem = SweepSmemT<MODE>;
   static_assert(sizeof(SweepSmem) < 112 * 1024, "two CTAs per SM");
   PTGS_CUDA_TRY(cudaFuncSetAttribute(sweep_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(SweepSmem)));

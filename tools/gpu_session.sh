@@ -44,6 +44,13 @@ launches_bench)
       > $out/${tag}_launches_bench.log 2>&1
   python tools/launch_summary.py $out/${tag}_launches_bench.csv > $out/${tag}_launches_bench_summary.txt 2>&1
   gzip -f $out/${tag}_launches_bench.csv ;;
+ncu_c5)
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|cov_cull|order_' -c 12 -f \
+      -o /tmp/${tag}_c5 python tools/configs_report.py c5 > $out/${tag}_ncu_c5.log 2>&1
+  if [ -f /tmp/${tag}_c5.ncu-rep ]; then
+    python tools/ncu_summary.py /tmp/${tag}_c5.ncu-rep > $out/${tag}_ncu_c5_summary.txt 2>&1
+    python tools/ncu_lines.py /tmp/${tag}_c5.ncu-rep sweep_kernel '<(int)0' > $out/${tag}_ncu_c5_sweep0_lines.txt 2>&1
+  fi ;;
 ncu_partition)
   timeout 900 ncu --set full --clock-control none --profile-from-start off \
       -k regex:'vox_|radius_count|gather_sorted|hist_kernel|partition_kernel|expand_|aos_|cand_plan|keep_' -c 80 -f \
