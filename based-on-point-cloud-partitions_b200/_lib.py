@@ -61,6 +61,7 @@ SIGNATURES = {
     "ptgs_visibility_count": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp,
                                         _vp, _vp, _vp, _sz, _vp]),
     "ptgs_visibility_sample": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i64, _vp]),
+    "ptgs_visibility_sample_count": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "ptgs_visibility_krect": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _f64,
                                         _vp, _vp]),
     "ptgs_visibility_bounds": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp,

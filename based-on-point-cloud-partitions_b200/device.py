@@ -10,6 +10,8 @@ from __future__ import annotations
 import ctypes as C
 from dataclasses import dataclass, field
 
+import os as _os
+
 import numpy as np
 import torch
 
@@ -497,11 +499,16 @@ def visibility(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam_index,
         check(lib.ptgs_visibility_sample(_ptr(ds_x), _ptr(ds_y), _ptr(ds_z), _ptr(ds_offsets), L,
                                          int(sample_stride), _ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]),
                                          _ptr(s_off), cap, st))
-        check(lib.ptgs_visibility_init(P, _ptr(n_hit_s), _ptr(pivot_s), _ptr(extreme_s), None, st))
-        check(lib.ptgs_visibility_count(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
-                                        _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
-                                        pick_cam_split(cap, L), _ptr(n_hit_s), _ptr(pivot_s),
-                                        _ptr(extreme_s), None, _ptr(ws), ws.numel(), st))
+        if _os.environ.get("PTGS_SAMPLE_PASS") == "sweep":      # A/B: the tile sweep on the sample
+            check(lib.ptgs_visibility_init(P, _ptr(n_hit_s), _ptr(pivot_s), _ptr(extreme_s), None, st))
+            check(lib.ptgs_visibility_count(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
+                                            _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
+                                            pick_cam_split(cap, L), _ptr(n_hit_s), _ptr(pivot_s),
+                                            _ptr(extreme_s), None, _ptr(ws), ws.numel(), st))
+        else:                                                    # one warp per pair, no atomics
+            check(lib.ptgs_visibility_sample_count(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
+                                                   _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index), P,
+                                                   _ptr(n_hit_s), _ptr(pivot_s), _ptr(extreme_s), st))
         check(lib.ptgs_visibility_krect(_ptr(smp[0]), _ptr(smp[1]), _ptr(smp[2]), _ptr(s_off), L,
                                         _ptr(cameras_d), _ptr(cam_offsets), _ptr(cam_index),
                                         _ptr(n_hit_s), _ptr(extreme_s), P, float(KRECT_MARGIN_PX),

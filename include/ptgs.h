@@ -422,6 +422,18 @@ int ptgs_visibility_sample(const float* px, const float* py, const float* pz,
                            int32_t stride, float* sx, float* sy, float* sz,
                            int64_t* s_offsets, int64_t capacity,
                            ptgs_stream_t stream);
+/* The sample pass itself, pair-centric: what ptgs_visibility_init +
+ * ptgs_visibility_count (krect = NULL) produce on the sample, with one warp per
+ * pair and no atomics (n_hit_s / pivot_s / extreme_s are written for every
+ * pair; pivot_s may be NULL).  The extremes are hits of the sample; among equal
+ * values the largest sample index wins, as in the sweep. */
+int ptgs_visibility_sample_count(const float* sx, const float* sy,
+                                 const float* sz, const int64_t* s_offsets,
+                                 int32_t n_blocks, const float* cameras,
+                                 const int64_t* cam_offsets,
+                                 const int32_t* cam_index, int64_t n_pairs,
+                                 int32_t* n_hit_s, uint64_t* pivot_s,
+                                 uint64_t* extreme_s, ptgs_stream_t stream);
 int ptgs_visibility_krect(const float* sx, const float* sy, const float* sz,
                           const int64_t* s_offsets, int32_t n_blocks,
                           const float* cameras, const int64_t* cam_offsets,

@@ -337,6 +337,15 @@ def test_candidate_pass_variants_agree():
                                                 exact_ratio=exact)
             finally:
                 os.environ.pop("PTGS_SWEEP2", None)
+    # the sample pass as a tile sweep instead of one warp per pair: a different (equally valid) interior
+    # polygon at most, identical results
+    os.environ["PTGS_SAMPLE_PASS"] = "sweep"
+    try:
+        alt = D.visibility(dx, dy, dz, ds_off, cams_d, res.cam_offsets, res.cam_index, exact_ratio=True)
+    finally:
+        os.environ.pop("PTGS_SAMPLE_PASS", None)
+    for f in ("n_hit", "area", "ratio", "keep", "flags"):
+        assert torch.equal(getattr(alt, f), getattr(out["runs", True], f)), f
     for exact in (True, False):
         a, b = out["runs", exact], out["tiles", exact]
         if exact:
