@@ -21,7 +21,7 @@ stages)
   done; done ;;
 ncu_sweep)
   timeout 300 python tools/vis_once.py c4 2 > $out/${tag}_vis_once.log 2>&1 && \
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel|pf_|cand_runs' -s 8 -c 8 -f \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'sweep_kernel|hull_kernel|pf_|cand_runs|sample_pairs' -s 8 -c 8 -f \
       -o /tmp/${tag}_sweep python tools/vis_once.py c4 2 > $out/${tag}_ncu_sweep.log 2>&1
   if [ -f /tmp/${tag}_sweep.ncu-rep ]; then
     tests=$(python -c "import json;print(json.load(open('$out/${tag}_vis_once.log'))['tests'])" 2>/dev/null || echo 0)
