@@ -1786,7 +1786,7 @@ __global__ void __launch_bounds__(256) pf_filter_kernel(
 }
 
 template <int NT>
-__global__ void __launch_bounds__(NT) hull_kernel(
+__global__ void __launch_bounds__(NT, NT == 256 ? 3 : 1) hull_kernel(
     float2* __restrict__ cand_uv, const int64_t* __restrict__ cand_offsets,
     const int32_t* __restrict__ cand_count, const int32_t* __restrict__ n_hit, int64_t n_pairs,
     const int32_t* __restrict__ pair_cam, const float* __restrict__ cameras, int min_hits,
