@@ -1068,7 +1068,7 @@ __global__ void __launch_bounds__(1024) cand_schedule_kernel(
   if (threadIdx.x == 0) run_prefix[L] = carry;
 }
 
-__global__ void __launch_bounds__(kCrWarps * 32) cand_runs_kernel(
+__global__ void __launch_bounds__(kCrWarps * 32, 4) cand_runs_kernel(
     const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz,
     const int64_t* __restrict__ pt_offsets, int L, const float* __restrict__ cameras,
     const int64_t* __restrict__ cam_offsets, const int32_t* __restrict__ cam_index,
