@@ -399,7 +399,10 @@ def measure_e2e(args, out, ctx):
     cam_off = res.cam_offsets.cpu().numpy()
     cam_idx = res.cam_index.cpu().numpy()
     steps = max(2, min(args.steps, 6))
-    groups = 4 if blocks.numel() * blocks.element_size() > (256 << 20) else 2
+    # upload groups per rank: each group costs ~0.9 ms of fixed work (A6's layout read-back, sample pass, hull
+    # tail), so a rank that uploads little uses fewer (about one group per 96 MB of its own blocks, 1..4)
+    local_bytes = blocks.numel() * blocks.element_size() / max(world, 1)
+    groups = int(min(4, max(1, round(local_bytes / (96 << 20)))))
 
     def one():
         return D.visibility_select_host(blocks, blk_off, recs_pinned, cam_off, cam_idx, dev,
