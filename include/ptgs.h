@@ -375,6 +375,11 @@ int ptgs_voxel_downsample(int dtype, const void* x, const void* y,
  * always indexed by p.  cand_uv[cand_offsets[p] + k] (float2, k < capacity of the pair);
  * cand_count[p] receives the number of candidates even when it exceeds the
  * pair's capacity (the caller then re-runs the pair with a larger capacity).
+ * The candidate SET of a pair is defined per point, the order inside the list
+ * is not (the hull sorts).  Implementation: one warp per run of 128 consecutive
+ * points of the blocks that own a listed pair (box tests per run, per-point
+ * evaluation for the cameras the box cannot decide); `cam_split` only matters
+ * to the tile-staged variant kept for A/B runs (environment PTGS_SWEEP2=tiles).
  *
  * ptgs_visibility_hull (cand_uv is compacted in place by a directional
  * pre-filter that drops candidates strictly inside the hull): exact convex hull (float64 orientation tests with the
