@@ -1114,6 +1114,28 @@ def visibility_sharded(ds_x, ds_y, ds_z, ds_offsets, cameras_d, cam_offsets, cam
     return VisibilityResult(n_hit, area, ratio, keep, flags, None, v.rounds)
 
 
+def upload_group_cuts(block_offsets: np.ndarray, bl0: int, bl1: int, groups) -> list:
+    """Block boundaries of the upload groups of visibility_select_host: consecutive blocks of
+    [bl0, bl1); `groups` = a count (~equal point counts) or the groups' shares of the points (a small
+    first group starts the kernels early, a small last one shortens what is left to do once the last
+    byte has landed).  Returns cuts with cuts[0] = bl0, cuts[-1] = bl1, non-decreasing (a group may
+    be empty when a block is larger than a share)."""
+    n_local = int(block_offsets[bl1] - block_offsets[bl0])
+    if isinstance(groups, (list, tuple, np.ndarray)):
+        shares = np.cumsum(np.asarray(groups, dtype=np.float64))
+        shares = shares / shares[-1]
+    else:
+        G = max(1, int(groups))
+        shares = np.arange(1, G + 1, dtype=np.float64) / G
+    shares = shares[: max(bl1 - bl0, 1)]
+    cuts = [bl0]
+    for g in range(len(shares) - 1):
+        b = int(np.searchsorted(block_offsets, block_offsets[bl0] + n_local * shares[g], side="left"))
+        cuts.append(min(max(b, cuts[-1]), bl1))
+    cuts.append(bl1)
+    return cuts
+
+
 def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray,
                            cam_records: torch.Tensor, cam_offsets: np.ndarray,
                            cam_index: np.ndarray, device, voxel=VOXEL_SIZE,
@@ -1151,22 +1173,8 @@ def visibility_select_host(block_points: torch.Tensor, block_offsets: np.ndarray
         bl0 = bl1 = 0
     loc_off = np.clip(cam_offsets, lo, hi) - lo            # this rank's block -> camera CSR (global blocks)
     n_local = int(block_offsets[bl1] - block_offsets[bl0])
-    # group boundaries: consecutive local blocks; `groups` = a count (~equal point counts) or the
-    # groups' shares of the points (a small first group starts the kernels early, a small last one
-    # shortens what is left to do once the last byte has landed)
-    if isinstance(groups, (list, tuple)):
-        shares = np.cumsum(np.asarray(groups, dtype=np.float64))
-        shares = shares / shares[-1]
-    else:
-        G = max(1, int(groups))
-        shares = np.arange(1, G + 1, dtype=np.float64) / G
-    shares = shares[: max(bl1 - bl0, 1)]
-    G = len(shares)
-    cuts = [bl0]
-    for g in range(G - 1):
-        b = int(np.searchsorted(block_offsets, block_offsets[bl0] + n_local * shares[g], side="left"))
-        cuts.append(min(max(b, cuts[-1]), bl1))
-    cuts.append(bl1)
+    cuts = upload_group_cuts(block_offsets, bl0, bl1, groups)
+    G = len(cuts) - 1
     spans = [(cuts[i], cuts[i + 1]) for i in range(G) if cuts[i + 1] > cuts[i]]
     main = torch.cuda.current_stream(device)
     copy = _copy_stream(device)
